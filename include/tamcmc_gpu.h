@@ -1,0 +1,157 @@
+/*
+ * tamcmc_gpu.h -- C-ABI of the B200-native TAMCMC hot path (libtamcmc_gpu.so).
+ *
+ * Plain pointers and sizes only; no torch / Eigen types.  Every entry point returns an int
+ * status (0 = ok, <0 = fatal, see TG_E_*) and never calls exit(); the message of the last
+ * failure on the calling thread is available from tg_last_error().  The reference has no
+ * FFI: its operator API for this path is the Model_def registry, so each entry point cites
+ * the reference interface (file:line under /root/reference/tamcmc) it stands in for.
+ * INTEGRATION.md shows the binding a maintainer would add on the reference side.
+ *
+ * Threading contract (reference: one OpenMP thread per chain on shared Model_def objects,
+ * sources/MALA.cpp:632-655): one host thread per handle, one handle per GPU, all work of a
+ * handle on one CUDA stream; calls on the same handle are not re-entrant, different handles
+ * are independent.
+ */
+#ifndef TAMCMC_GPU_H
+#define TAMCMC_GPU_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TG_OK              0
+#define TG_E_BADARG       -1   /* bad sizes / null pointers / bad case id (reference: exit(), model_def.cpp:266-285) */
+#define TG_E_CUDA         -2   /* CUDA runtime error */
+#define TG_E_UNSUPPORTED  -3   /* model case the reference itself kills with exit() (cases 4, 5) */
+#define TG_E_NODEVICE     -4   /* no CUDA device: there is NO CPU fallback */
+
+/* per-chain status bits (reference behaviour in brackets) */
+#define TG_ST_EMPTY_WINDOW  1  /* imax-imin<=0 [exit(EXIT_FAILURE), build_lorentzian.cpp:428-443] -> logL=NaN, rejected */
+#define TG_ST_NAN_WINDOW    2  /* Gamma or f_s NaN: window undefined [uninitialised pmin/pmax, Q1]  -> logL=NaN, rejected */
+#define TG_ST_NAN_LOGL      4  /* logL is NaN [warning + reject, MALA.cpp:507-509] */
+#define TG_ST_BAD_PRIOR     8  /* prior kind the reference exits on (multivariate Gaussian / unknown switch) */
+#define TG_ST_CHOL_FAIL    16  /* (Sigma+eps2 I)*sigma not positive definite [Eigen llt yields NaN silently] */
+#define TG_ST_MODE_OVERFLOW 32 /* more Lorentzian components than the device table holds */
+
+typedef struct tg_handle tg_handle;
+
+/* Everything Config::setup (sources/config.cpp:80-189) leaves behind for MALA / Model_def. */
+typedef struct tg_problem {
+    /* ---- Data{x,y,sigma_y,Nx}, headers/data.h:24-35 (after the freq_range crop) ---- */
+    long          Nx;             /* bins held by THIS handle (a shard when bin-sharded)                */
+    const double *x, *y;          /* [Nx]                                                                */
+    const double *sigma_y;        /* [Nx] or NULL (only the chi_square likelihood reads it)              */
+    /* bin-sharded variant: the window arithmetic needs the GLOBAL grid.       */
+    long          Nx_global;      /* 0 => not sharded (== Nx)                                            */
+    long          shard_lo;       /* global index of this shard's first bin                              */
+    double        x_first, x_second, x_last; /* global x[0], x[1], x[Nx_global-1]; ignored if Nx_global==0 */
+    /* ---- Modeling: registry switches, Config/default/{models,likelihoods,priors}_ctrl.list ---- */
+    int           model_case;     /* model_fct_name_switch   0..14, model_def.cpp:215-265                */
+    int           likelihood_case;/* likelihood_fct_name_switch 0 chi(2,2p) | 1 chi_square, :298-307      */
+    int           prior_case;     /* prior_fct_name_switch   0..3, model_def.cpp:329-341                 */
+    double        likelihood_params; /* p of chi(2,2p), truncated to long like model_def.cpp:300-301     */
+    int           plength[11];    /* Input_Data.plength, io_ms_global.cpp:996-1001                       */
+    int           Np;             /* == sum(plength)                                                      */
+    const double *params0;        /* [Np]  Input_Data.inputs                                              */
+    const int    *relax;          /* [Np]  Input_Data.relax (1 = free variable)                           */
+    const double *priors;         /* [4*Np] Input_Data.priors, 4 x Np column-major: priors[4*i+r]         */
+    const int    *priors_switch;  /* [Np]  Input_Data.priors_names_switch (primepriors_ctrl.list)         */
+    double        extra_priors[4];/* Input_Data.extra_priors                                              */
+    /* ---- MALA: Config/default/config_default.cfg !MALA section, MALA.cpp:53-112 ---- */
+    int           Nchains;        /* total chains C held by this handle                                   */
+    int           chains_per_ensemble; /* tempering swaps stay inside an ensemble; 0 => Nchains           */
+    const double *Tcoefs;         /* [Nchains] temperatures (lambda^m, MALA.cpp:103)                      */
+    double        c0, epsilon1, epsilon2, A1, target_acceptance;
+    int           n_learn;        /* number of learning zones = periods_learn.size()                      */
+    const long   *Nt_learn;       /* [n_learn+1]                                                          */
+    const long   *periods_learn;  /* [n_learn]                                                            */
+    long          dN_mixing;      /* swap attempt every dN_mixing steps (i != 0)                          */
+    const double *init_err;       /* [Nv] initial std-dev per free variable (A*x+B, MALA.cpp:253-258); NULL => 1 */
+    unsigned long long seed;      /* Philox key (reference: time(NULL), MALA.cpp:62)                      */
+    int           device;         /* CUDA device ordinal                                                  */
+    int           flags;          /* TG_F_* */
+} tg_problem;
+
+#define TG_F_FIX_SWAP_BOOKKEEPING 1 /* fix quirk Q8 (stale logPosterior[B] after a swap, MALA.cpp:417-428); default replicates */
+
+/* Per-step records the reference hands to Outputs (MALA.cpp:696-707), for nsteps steps.
+ * Any pointer may be NULL (that record is skipped).  All are HOST buffers. */
+typedef struct tg_records {
+    double *vars;        /* [nsteps][C][Nv]  Outputs::update_buffer_params                  */
+    double *logL;        /* [nsteps][C]      tempered logLikelihood  (update_buffer_stat_criteria) */
+    double *logPrior;    /* [nsteps][C]                                                    */
+    double *logPost;     /* [nsteps][C]                                                    */
+    double *Pmove;       /* [nsteps][C]      update_buffer_proposals                        */
+    unsigned char *moved;/* [nsteps][C]                                                    */
+    int    *swap_attempt;/* [nsteps][E]      tempted_mixing  (update_buffer_ptempering), E = ensembles */
+    int    *swap_chain0; /* [nsteps][E]      chain_A (ensemble-local index) or -1           */
+    double *swap_Pswap;  /* [nsteps][E]                                                    */
+    int    *swap_done;   /* [nsteps][E]      swaped                                        */
+    int    *status;      /* [nsteps][C]      TG_ST_* bits of the PROPOSED point             */
+} tg_records;
+
+const char *tg_last_error(void);
+int tg_version(void);
+
+/* Uploads the problem, allocates all device state, initialises the proposal like
+ * MALA::MALA + init_proposal (MALA.cpp:53-112, :246-289) and evaluates every chain once at
+ * params0 like the Model_def constructor (model_def.cpp:139-143). */
+int tg_create(const tg_problem *p, tg_handle **out);
+int tg_destroy(tg_handle *h);
+
+/* Batched Model_def::generate_model (model_def.cpp:358-367 = call_model :210-289 +
+ * call_likelihood :291-320 + call_prior :322-356) for B parameter vectors.
+ * params [B][Np] and T [B] are HOST buffers copied in, results are copied out:
+ * logL (already divided by T), logPrior, logPost [B]; status [B] (TG_ST_*), may be NULL;
+ * model [B][Nx] may be NULL (parity / getmodel path, tools/getmodel.cpp:111). */
+int tg_eval(tg_handle *h, const double *params, int B, const double *T,
+            double *logL, double *logPrior, double *logPost, int *status, double *model);
+
+/* Same evaluation with the parameter vectors already resident in HBM (uploaded once by
+ * tg_eval_upload); nothing crosses PCIe.  Results stay on the device until tg_eval_fetch. */
+int tg_eval_upload(tg_handle *h, const double *params, int B, const double *T);
+int tg_eval_resident(tg_handle *h, int B);
+int tg_eval_fetch(tg_handle *h, int B, double *logL, double *logPrior, double *logPost, int *status);
+
+/* Algorithmic work of the last evaluation: L[b] = sum over modes (2l+1)*(imax-imin)
+ * (SURVEY 8(d)); K = number of active Harvey terms of chain 0. */
+int tg_last_work(tg_handle *h, int B, double *L, int *K);
+
+/* Sampler state <-> host: restore files (outputs.cpp:863-1025, MALA::restore_proposal
+ * MALA.cpp:191-244, model_def.cpp:104-128).  vars [C][Nv], mu [C][Nv], sigma [C],
+ * covarmat [C][Nv][Nv] (row-major per chain).  NULL pointers are skipped.
+ * tg_set_state re-evaluates every chain at the new vars. */
+int tg_get_state(tg_handle *h, double *vars, double *mu, double *sigma, double *covarmat,
+                 double *logL, double *logPrior, double *logPost);
+int tg_set_state(tg_handle *h, const double *vars, const double *mu, const double *sigma, const double *covarmat);
+
+/* MALA::execute (MALA.cpp:608-737) for iterations i0 .. i0+nsteps-1, entirely on the device:
+ * proposal (new_prop_values :335-353), generate_model, MH accept (update_position_MH :447-538),
+ * Robbins-Monro update (update_proposal :292-315), tempering swap (parallel_tempering :381-445).
+ * No per-step host transfer; the per-step records are drained into rec (may be NULL) at the end. */
+int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec);
+
+/* Sizes implied by the problem. */
+int tg_sizes(tg_handle *h, int *Nv, int *Np, int *C, int *E, long *Nx);
+
+/* Bin-sharded variant: per-chain partial sums (sum y/m, sum ln m) of the proposed points live in
+ * a device buffer of 2*C doubles; the caller all-reduces it (ncclAllReduce sum, fp64) between
+ * tg_step_begin and tg_step_end.  tg_run == loop { tg_step_begin; tg_step_end }. */
+int tg_step_begin(tg_handle *h, long i);
+int tg_step_end(tg_handle *h, long i);
+int tg_partials_device_ptr(tg_handle *h, void **ptr, int *count);
+int tg_sync(tg_handle *h);
+
+/* Kernel timing of the dominant kernel (CUDA events on the handle's stream), accumulated since
+ * the last reset: number of launches and total milliseconds. */
+int tg_kernel_time(tg_handle *h, int reset, long *launches, double *ms_eval, long *total_launches);
+int tg_set_tuning(tg_handle *h, int chains_per_block, int bins_per_thread, int use_graph);
+
+/* FP64 roofline denominator: DFMA-saturating microkernel, returns measured TFLOP/s (2 flop per DFMA). */
+int tg_measure_fp64_peak(int device, double *tflops, double *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

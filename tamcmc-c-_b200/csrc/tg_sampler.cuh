@@ -1,0 +1,360 @@
+// tg_sampler.cuh -- device-resident adaptive Metropolis-Hastings + parallel tempering.
+//
+// Reference (under /root/reference/tamcmc/sources/MALA.cpp):
+//   new_prop_values :335-353   x' = x + chol((Sigma+eps2 I)*sigma) z
+//   update_position_MH :447-538, update_proposal :292-315, p1/p2/p3 :135-176,
+//   parallel_tempering :381-445, execute :608-737 (gamma=c0/(1+i), learning zones, swap cadence)
+// RNG: counter-based Philox4x32-10 keyed by (seed, purpose), counter (iteration, chain, index) --
+// replaces rand()/Box-Muller with racy static state (random_JB.cpp, quirk Q10); trajectories are
+// therefore only statistically comparable with the reference.
+#pragma once
+#include "tg_internal.cuh"
+#include "tg_prologue.cuh"
+#include "tg_eval.cuh"
+
+#define TG_TAG_PROP 0x50524f50u
+#define TG_TAG_MH   0x4d485f55u
+#define TG_TAG_PT   0x50545f55u
+#define TG_MAX_LEARN 16
+
+struct TgMala {
+    double c0, eps1, eps2, A1, target;
+    int    n_learn;
+    long   Nt_learn[TG_MAX_LEARN + 1];
+    long   periods[TG_MAX_LEARN];
+    long   dN_mixing;
+    unsigned long long seed;
+    int    flags;
+};
+
+struct TgCtrl {            // lives in device memory so that a captured CUDA graph can be replayed
+    long i;                // current iteration
+    long i0;               // first iteration of the current record chunk
+    unsigned int ticket;   // CTA completion counter of the finish kernel
+    int pad;
+};
+
+struct TgState {
+    int C, E, Ce, Nv, Np;
+    double *vars_cur, *vars_prop;          // [C][Nv]
+    double *params_cur, *params_prop;      // [C][Np]
+    double *logL_cur, *logPrior_cur, *logPost_cur, *Pmove;   // [C]
+    int    *moved;                         // [C]
+    double *mu, *sigma, *cov, *chol;       // [C][Nv], [C], [C][Nv][Nv] x2 (row-major)
+    int    *chol_valid;                    // [C]
+    int    *sticky_status;                 // [C]
+    const int    *index_to_relax;          // [Nv]
+    const double *Tcoefs;                  // [C]
+    TgCtrl *ctrl;
+};
+
+struct TgRecDev {          // device ring of per-step records (drained once per chunk)
+    long    cap;           // steps the ring holds
+    double *vars, *logL, *logPrior, *logPost, *Pmove;
+    unsigned char *moved;
+    int    *swap_attempt, *swap_chain0, *swap_done, *status;
+    double *swap_Pswap;
+};
+
+// two standard normals from one Philox block
+__device__ __forceinline__ void tg_normal_pair(uint4 r, double *z0, double *z1)
+{
+    const double u1 = tg_u01(r.x, r.y), u2 = tg_u01(r.z, r.w);
+    const double rad = sqrt(-2.0 * log(u1));
+    double s, c;
+    sincospi(2.0 * u2, &s, &c);
+    *z0 = rad * c; *z1 = rad * s;
+}
+
+// In-CTA Cholesky (lower, right-looking) of the n x n matrix S (leading dimension ld), in place.
+// Returns (to every thread) 0 on success, 1 if a pivot was not positive.
+__device__ int tg_cholesky_inplace(double *S, int n, int ld)
+{
+    __shared__ int fail;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    if (tid == 0) fail = 0;
+    __syncthreads();
+    for (int j = 0; j < n; j++) {
+        const double djj = S[j * ld + j];
+        __syncthreads();                           // everyone has read the pivot before it is overwritten
+        const double dj = sqrt(djj);
+        if (tid == 0) { if (!(djj > 0.0)) fail = 1; S[j * ld + j] = dj; }
+        for (int i = j + 1 + tid; i < n; i += nt) S[i * ld + j] = S[i * ld + j] / dj;
+        __syncthreads();
+        const int r = n - j - 1;                   // trailing block is r x r, lower part only
+        for (int e = tid; e < r * r; e += nt) {
+            const int ii = e / r, kk = e - ii * r;
+            if (kk <= ii) {
+                const int i = j + 1 + ii, k = j + 1 + kk;
+                S[i * ld + k] = fma(-S[i * ld + j], S[k * ld + j], S[i * ld + k]);
+            }
+        }
+        __syncthreads();
+    }
+    return fail;
+}
+
+struct TgProposeArgs {
+    TgState   s;
+    TgMala    m;
+    TgProArgs pro;          // pro.params == s.params_prop
+    int       smem_matrix;  // 1: the Nv x Nv factor is staged in shared memory
+};
+
+// K1: one CTA per chain.  (Re)factorise Sigma+eps2*I when the covariance changed, draw z, form
+// x' = x + sqrt(sigma)*L z (== chol((Sigma+eps2 I)*sigma) z up to rounding), scatter into params,
+// then run the model prologue + log-prior on the proposed parameter vector.
+__global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
+{
+    extern __shared__ double tg_dyn_smem[];
+    __shared__ double s_z[512];
+    const TgState &s = a.s;
+    const int c = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    const int Nv = s.Nv, Np = s.Np;
+    const long it = s.ctrl->i;
+    double *Lg = s.chol + (size_t)c * Nv * Nv;
+    const int ld = a.smem_matrix ? (Nv | 1) : Nv;
+    double *L = a.smem_matrix ? tg_dyn_smem : Lg;
+
+    if (!s.chol_valid[c]) {
+        const double *cv = s.cov + (size_t)c * Nv * Nv;
+        for (int e = tid; e < Nv * Nv; e += nt) {
+            const int i = e / Nv, k = e - i * Nv;
+            L[i * ld + k] = cv[e] + ((i == k) ? a.m.eps2 : 0.0);
+        }
+        __syncthreads();
+        const int fail = tg_cholesky_inplace(L, Nv, ld);
+        if (a.smem_matrix) for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; Lg[e] = (k <= i) ? L[i * ld + k] : 0.0; }
+        if (tid == 0) { s.chol_valid[c] = 1; if (fail) s.sticky_status[c] |= TG_ST_CHOL_FAIL; else s.sticky_status[c] &= ~TG_ST_CHOL_FAIL; }
+    } else if (a.smem_matrix) {
+        for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; L[i * ld + k] = Lg[e]; }
+    }
+    // standard normals, Nv <= 512 per pass
+    const double sq = sqrt(s.sigma[c]);
+    const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PROP, (uint32_t)(a.m.seed >> 32));
+    for (int v0 = 0; v0 < Nv; v0 += 512) {
+        __syncthreads();
+        for (int v = v0 + tid; v < Nv && v < v0 + 512; v += nt) {
+            double z0, z1;
+            tg_normal_pair(tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)c, (uint32_t)(v >> 1)), key), &z0, &z1);
+            s_z[v - v0] = (v & 1) ? z1 : z0;
+        }
+        __syncthreads();
+        // partial products of rows with this block of z (lower triangle => k <= i)
+        for (int i = tid; i < Nv; i += nt) {
+            double acc = 0.0;
+            const int kend = min(i, v0 + 511);
+            for (int k = v0; k <= kend; k++) acc = fma(L[i * ld + k], s_z[k - v0], acc);
+            if (i >= v0) {
+                const double prev = (v0 == 0) ? s.vars_cur[(size_t)c * Nv + i] : s.vars_prop[(size_t)c * Nv + i];
+                s.vars_prop[(size_t)c * Nv + i] = prev + sq * acc;
+            }
+        }
+    }
+    // params_prop = params_cur with the free variables replaced (Model_def::update_params_with_vars)
+    for (int i = tid; i < Np; i += nt) s.params_prop[(size_t)c * Np + i] = s.params_cur[(size_t)c * Np + i];
+    __syncthreads();
+    for (int v = tid; v < Nv; v += nt) s.params_prop[(size_t)c * Np + s.index_to_relax[v]] = s.vars_prop[(size_t)c * Nv + v];
+    __syncthreads();
+    tg_prologue_body(a.pro, c, tg_dyn_smem);
+}
+
+struct TgFinishArgs {
+    TgDesc    d;
+    TgState   s;
+    TgMala    m;
+    TgTables  t;            // tables of the PROPOSED points (status, logprior)
+    const double2 *partials; int ntiles;
+    double2  *sums;         // [C]
+    int       presummed;    // 1: sums already hold the (all-reduced) totals
+    TgRecDev  rec;
+    int       record;
+};
+
+__device__ __forceinline__ void tg_write_record(const TgFinishArgs &a, long slot, int c, int st, int tid, int nt)
+{
+    const TgState &s = a.s;
+    if (slot < 0 || slot >= a.rec.cap) return;
+    const size_t rc = (size_t)slot * s.C + c;
+    if (a.rec.vars) for (int v = tid; v < s.Nv; v += nt) a.rec.vars[rc * s.Nv + v] = s.vars_cur[(size_t)c * s.Nv + v];
+    if (tid == 0) {
+        a.rec.logL[rc] = s.logL_cur[c]; a.rec.logPrior[rc] = s.logPrior_cur[c]; a.rec.logPost[rc] = s.logPost_cur[c];
+        a.rec.Pmove[rc] = s.Pmove[c]; a.rec.moved[rc] = (unsigned char)s.moved[c];
+        if (st >= 0) a.rec.status[rc] = st;
+    }
+}
+
+// K3: one CTA per chain: likelihood reduction -> MH accept -> Robbins-Monro update -> record;
+// the last CTA to finish performs the tempering swaps of every ensemble and advances the
+// iteration counter.
+__global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
+{
+    __shared__ double r1[256], r2[256];
+    __shared__ int s_accept, s_last, s_learn;
+    __shared__ double s_r, s_scale;
+    const TgState &s = a.s;
+    const int c = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    const int Nv = s.Nv, Np = s.Np;
+    const long it = s.ctrl->i;
+    const long slot = it - s.ctrl->i0;
+
+    // 1. logL of the proposed point
+    double2 sum;
+    if (!a.presummed) {
+        double a1 = 0, a2 = 0;
+        for (int t = tid; t < a.ntiles; t += nt) { const double2 v = a.partials[(size_t)c * a.ntiles + t]; a1 += v.x; a2 += v.y; }
+        r1[tid] = a1; r2[tid] = a2;
+        __syncthreads();
+        for (int h = 128; h > 0; h >>= 1) { if (tid < h) { r1[tid] += r1[tid + h]; r2[tid] += r2[tid + h]; } __syncthreads(); }
+        sum = make_double2(r1[0], r2[0]);
+    } else {
+        sum = a.sums[c];
+    }
+    // 2. Metropolis-Hastings decision (MALA.cpp:475-535)
+    if (tid == 0) {
+        int st = a.t.status[c] | s.sticky_status[c];
+        const double T = s.Tcoefs[c];
+        const double logL = tg_logl_from_sums(a.d, sum, T, st);
+        const double logPr = a.t.logprior[c];
+        const double logPo = logL + logPr;
+        double r;
+        if (logL != logL) { r = 0.0; st |= TG_ST_NAN_LOGL; }
+        else if (logPo == -CUDART_INF) r = 0.0;
+        else { r = exp(logPo - s.logPost_cur[c]); r = (r < 1.0) ? r : 1.0; if (r != r) r = 0.0; }   // NaN ratio: reference is fatal (:504-506); reject here
+        const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_MH, (uint32_t)(a.m.seed >> 32));
+        const uint4 rn = tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)c, 0u), key);
+        const double u = tg_u01(rn.x, rn.y);
+        const int acc = (u <= r);
+        if (acc) { s.logL_cur[c] = logL; s.logPrior_cur[c] = logPr; s.logPost_cur[c] = logPo; }
+        s.moved[c] = acc; s.Pmove[c] = r;
+        s_accept = acc; s_r = r;
+        if (a.record && slot >= 0 && slot < a.rec.cap) a.rec.status[(size_t)slot * s.C + c] = st;
+        // learning zone? (MALA.cpp:641-652)
+        int learn = 0, which = 0;
+        for (int l = 0; l < a.m.n_learn; l++) if (it >= a.m.Nt_learn[l] && it < a.m.Nt_learn[l + 1]) { learn = 1; which = l; }
+        if (learn && (it % a.m.periods[which]) != 0) learn = 0;
+        s_learn = learn;
+    }
+    __syncthreads();
+    if (s_accept) {
+        for (int v = tid; v < Nv; v += nt) s.vars_cur[(size_t)c * Nv + v] = s.vars_prop[(size_t)c * Nv + v];
+        for (int i = tid; i < Np; i += nt) s.params_cur[(size_t)c * Np + i] = s.params_prop[(size_t)c * Np + i];
+    }
+    __syncthreads();
+    // 3. Robbins-Monro update of (mu, Sigma, sigma) with the p3/p2/p1 truncations (MALA.cpp:292-315)
+    if (s_learn) {
+        const double gamma = a.m.c0 / (1.0 + (double)it);
+        double *mu = s.mu + (size_t)c * Nv, *cov = s.cov + (size_t)c * Nv * Nv;
+        const double *xv = s.vars_cur + (size_t)c * Nv;
+        double part = 0;
+        for (int v = tid; v < Nv; v += nt) { const double m = mu[v] + gamma * (xv[v] - mu[v]); mu[v] = m; part += m * m; }
+        r1[tid] = part; __syncthreads();
+        for (int h = 128; h > 0; h >>= 1) { if (tid < h) r1[tid] += r1[tid + h]; __syncthreads(); }
+        if (tid == 0) { const double nrm = sqrt(r1[0]); s_scale = (nrm <= a.m.A1) ? 1.0 : a.m.A1 / nrm; }
+        __syncthreads();
+        if (s_scale != 1.0) for (int v = tid; v < Nv; v += nt) mu[v] = mu[v] * s_scale;
+        __syncthreads();
+        part = 0;
+        for (int e = tid; e < Nv * Nv; e += nt) {
+            const int i = e / Nv, k = e - i * Nv;
+            const double mat = (xv[i] - mu[i]) * (xv[k] - mu[k]);
+            const double cn = cov[e] + gamma * (mat - cov[e]);
+            cov[e] = cn; part += cn * cn;
+        }
+        r1[tid] = part; __syncthreads();
+        for (int h = 128; h > 0; h >>= 1) { if (tid < h) r1[tid] += r1[tid + h]; __syncthreads(); }
+        if (tid == 0) { const double nrm = sqrt(r1[0]); s_scale = (nrm <= a.m.A1) ? 1.0 : a.m.A1 / nrm; }
+        __syncthreads();
+        if (s_scale != 1.0) for (int e = tid; e < Nv * Nv; e += nt) cov[e] = cov[e] * s_scale;
+        if (tid == 0) {
+            double sg = s.sigma[c] + gamma * (s_r - a.m.target);
+            if (sg < a.m.eps1) sg = a.m.eps1;
+            if (sg > a.m.A1) sg = a.m.A1;
+            s.sigma[c] = sg;
+            s.chol_valid[c] = 0;
+        }
+    }
+    if (a.record) tg_write_record(a, slot, c, -1, tid, nt);
+
+    // 4. last CTA: tempering swaps (MALA.cpp:381-445, :676-692), then advance the iteration
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) { const unsigned t = atomicAdd(&s.ctrl->ticket, 1u); s_last = (t == (unsigned)(s.C - 1)); }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int attempt = (a.m.dN_mixing > 0) && (it % a.m.dN_mixing == 0) && (it != 0) && (s.Ce >= 2);
+    for (int e0 = 0; e0 < s.E; e0 += nt) {        // decisions, one thread per ensemble
+        const int e = e0 + tid;
+        int doswap = 0, A = -1;
+        double rT = 0.0;
+        if (e < s.E && attempt) {
+            const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PT, (uint32_t)(a.m.seed >> 32));
+            const uint4 rn = tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)e, 0u), key);
+            A = (int)(rn.z % (uint32_t)(s.Ce - 1));
+            const int gA = e * s.Ce + A, gB = gA + 1;
+            const double TA = s.Tcoefs[gA], TB = s.Tcoefs[gB];
+            const double LA = __ldcg(s.logL_cur + gA), LB = __ldcg(s.logL_cur + gB);   // written by other CTAs: read through L2
+            const double LA_TB = LA * TA / TB, LB_TA = LB * TB / TA;
+            rT = exp(LA_TB + LB_TA - LA - LB); rT = (rT < 1.0) ? rT : 1.0;
+            const double u = tg_u01(rn.x, rn.y);
+            doswap = (u <= rT);
+            if (doswap) {
+                const double prA = __ldcg(s.logPrior_cur + gA), prB = __ldcg(s.logPrior_cur + gB);
+                s.logL_cur[gA] = LB_TA; s.logPrior_cur[gA] = prB; s.logPost_cur[gA] = LB_TA + prB;
+                s.logL_cur[gB] = LA_TB; s.logPrior_cur[gB] = prA;
+                // Q8: the reference adds logPrior[ind_A] AFTER it was overwritten with B's prior (MALA.cpp:417,:428)
+                s.logPost_cur[gB] = LA_TB + ((a.m.flags & TG_F_FIX_SWAP_BOOKKEEPING) ? prA : prB);
+                const int mv = __ldcg(s.moved + gA); s.moved[gA] = __ldcg(s.moved + gB); s.moved[gB] = mv;
+                const double pm = __ldcg(s.Pmove + gA); s.Pmove[gA] = __ldcg(s.Pmove + gB); s.Pmove[gB] = pm;
+            }
+        }
+        if (e < s.E) {
+            // stash the decision in the (now dead) sums buffer of the ensemble's first chain
+            a.sums[e * s.Ce].x = doswap ? (double)(A + 1) : 0.0;
+            if (a.record && slot >= 0 && slot < a.rec.cap) {
+                const size_t re = (size_t)slot * s.E + e;
+                a.rec.swap_attempt[re] = attempt; a.rec.swap_chain0[re] = attempt ? A : -1;
+                a.rec.swap_Pswap[re] = doswap ? rT : 0.0; a.rec.swap_done[re] = doswap;
+            }
+        }
+    }
+    __syncthreads();
+    if (attempt) {
+        for (int e = 0; e < s.E; e++) {           // row exchanges, whole CTA per ensemble
+            const int A1 = (int)a.sums[e * s.Ce].x;
+            if (A1 == 0) continue;
+            const int gA = e * s.Ce + A1 - 1, gB = gA + 1;
+            for (int v = tid; v < Nv; v += nt) { const double t = __ldcg(s.vars_cur + (size_t)gA * Nv + v); s.vars_cur[(size_t)gA * Nv + v] = __ldcg(s.vars_cur + (size_t)gB * Nv + v); s.vars_cur[(size_t)gB * Nv + v] = t; }
+            for (int i = tid; i < Np; i += nt) { const double t = __ldcg(s.params_cur + (size_t)gA * Np + i); s.params_cur[(size_t)gA * Np + i] = __ldcg(s.params_cur + (size_t)gB * Np + i); s.params_cur[(size_t)gB * Np + i] = t; }
+            __syncthreads();
+            if (a.record) { tg_write_record(a, slot, gA, -1, tid, nt); tg_write_record(a, slot, gB, -1, tid, nt); }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) { s.ctrl->ticket = 0u; s.ctrl->i = it + 1; }
+}
+
+// Installs the evaluation of params_cur as the current state (Model_def ctor, model_def.cpp:139-143)
+__global__ void tg_k_install_current(TgDesc d, TgState s, TgTables t, const double2 *sums)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= s.C) return;
+    const double L = tg_logl_from_sums(d, sums[c], s.Tcoefs[c], t.status[c]);
+    s.logL_cur[c] = L; s.logPrior_cur[c] = t.logprior[c]; s.logPost_cur[c] = L + t.logprior[c];
+    s.Pmove[c] = 0.0; s.moved[c] = 0;
+}
+
+// FP64 roofline denominator: 8 independent DFMA chains per thread, no memory traffic.
+__global__ void __launch_bounds__(256) tg_k_dfma_peak(double *out, int iters, double a, double b)
+{
+    double v0 = threadIdx.x, v1 = v0 + 1, v2 = v0 + 2, v3 = v0 + 3, v4 = v0 + 4, v5 = v0 + 5, v6 = v0 + 6, v7 = v0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            v0 = fma(v0, a, b); v1 = fma(v1, a, b); v2 = fma(v2, a, b); v3 = fma(v3, a, b);
+            v4 = fma(v4, a, b); v5 = fma(v5, a, b); v6 = fma(v6, a, b); v7 = fma(v7, a, b);
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = v0 + v1 + v2 + v3 + v4 + v5 + v6 + v7;
+}

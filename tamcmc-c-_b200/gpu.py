@@ -1,0 +1,329 @@
+"""ctypes binding of include/tamcmc_gpu.h and the host-side mirror of the reference interface.
+
+``GpuModelDef`` mirrors ``Model_def`` (tamcmc/headers/model_def.h:58-83): public per-chain members
+``params, vars, logLikelihood, logPrior, logPosterior, Pmove, moved`` and the methods
+``generate_model / call_model / update_params_with_vars``; ``GpuMALA`` mirrors ``MALA``
+(tamcmc/headers/MALA.h) with ``execute``.  All numerical work happens in libtamcmc_gpu.so.
+"""
+import ctypes as C
+import os
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import numpy as np
+
+from .build import LIB_PATH, build_library
+
+ST_EMPTY_WINDOW, ST_NAN_WINDOW, ST_NAN_LOGL, ST_BAD_PRIOR, ST_CHOL_FAIL, ST_MODE_OVERFLOW = 1, 2, 4, 8, 16, 32
+F_FIX_SWAP_BOOKKEEPING = 1
+
+EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", "tg_eval_upload", "tg_eval_resident",
+           "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
+           "tg_step_end", "tg_partials_device_ptr", "tg_sync", "tg_kernel_time", "tg_set_tuning",
+           "tg_measure_fp64_peak"]
+
+
+class TgError(RuntimeError):
+    pass
+
+
+class _Problem(C.Structure):
+    _fields_ = [
+        ("Nx", C.c_long), ("x", C.c_void_p), ("y", C.c_void_p), ("sigma_y", C.c_void_p),
+        ("Nx_global", C.c_long), ("shard_lo", C.c_long),
+        ("x_first", C.c_double), ("x_second", C.c_double), ("x_last", C.c_double),
+        ("model_case", C.c_int), ("likelihood_case", C.c_int), ("prior_case", C.c_int),
+        ("likelihood_params", C.c_double), ("plength", C.c_int * 11), ("Np", C.c_int),
+        ("params0", C.c_void_p), ("relax", C.c_void_p), ("priors", C.c_void_p), ("priors_switch", C.c_void_p),
+        ("extra_priors", C.c_double * 4),
+        ("Nchains", C.c_int), ("chains_per_ensemble", C.c_int), ("Tcoefs", C.c_void_p),
+        ("c0", C.c_double), ("epsilon1", C.c_double), ("epsilon2", C.c_double), ("A1", C.c_double),
+        ("target_acceptance", C.c_double),
+        ("n_learn", C.c_int), ("Nt_learn", C.c_void_p), ("periods_learn", C.c_void_p), ("dN_mixing", C.c_long),
+        ("init_err", C.c_void_p), ("seed", C.c_ulonglong), ("device", C.c_int), ("flags", C.c_int),
+    ]
+
+
+class _Records(C.Structure):
+    _fields_ = [("vars", C.c_void_p), ("logL", C.c_void_p), ("logPrior", C.c_void_p), ("logPost", C.c_void_p),
+                ("Pmove", C.c_void_p), ("moved", C.c_void_p), ("swap_attempt", C.c_void_p),
+                ("swap_chain0", C.c_void_p), ("swap_Pswap", C.c_void_p), ("swap_done", C.c_void_p),
+                ("status", C.c_void_p)]
+
+
+class GpuLibrary:
+    """Loaded libtamcmc_gpu.so.  Raises if the library cannot be loaded: there is no fallback."""
+
+    def __init__(self, path=None):
+        path = path or LIB_PATH
+        if not os.path.exists(path):
+            raise TgError("libtamcmc_gpu.so not built (%s); run tamcmc_b200.build_library()" % path)
+        L = self.lib = C.CDLL(path)
+        self.path = path
+        L.tg_last_error.restype = C.c_char_p
+        for name in EXPORTS[1:]:
+            getattr(L, name).restype = C.c_int
+        L.tg_create.argtypes = [C.POINTER(_Problem), C.POINTER(C.c_void_p)]
+        L.tg_destroy.argtypes = [C.c_void_p]
+        L.tg_eval.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p] + [C.c_void_p] * 5
+        L.tg_eval_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.tg_eval_resident.argtypes = [C.c_void_p, C.c_int]
+        L.tg_eval_fetch.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
+        L.tg_last_work.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_int)]
+        L.tg_get_state.argtypes = [C.c_void_p] + [C.c_void_p] * 7
+        L.tg_set_state.argtypes = [C.c_void_p] + [C.c_void_p] * 4
+        L.tg_run.argtypes = [C.c_void_p, C.c_long, C.c_long, C.POINTER(_Records)]
+        L.tg_sizes.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 4 + [C.POINTER(C.c_long)]
+        L.tg_step_begin.argtypes = [C.c_void_p, C.c_long]
+        L.tg_step_end.argtypes = [C.c_void_p, C.c_long]
+        L.tg_partials_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int)]
+        L.tg_sync.argtypes = [C.c_void_p]
+        L.tg_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_double), C.POINTER(C.c_long)]
+        L.tg_set_tuning.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.tg_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+
+    def check(self, rc):
+        if rc != 0:
+            raise TgError("libtamcmc_gpu error %d: %s" % (rc, self.lib.tg_last_error().decode()))
+
+    def measure_fp64_peak(self, device=0):
+        t, ms = C.c_double(0), C.c_double(0)
+        self.check(self.lib.tg_measure_fp64_peak(device, C.byref(t), C.byref(ms)))
+        return t.value, ms.value
+
+
+_LIB = None
+
+
+def load_library(build=True):
+    global _LIB
+    if _LIB is None:
+        if build:
+            build_library()
+        _LIB = GpuLibrary()
+    return _LIB
+
+
+@dataclass
+class MalaConfig:
+    """!MALA section of Config/default/config_default.cfg (defaults as shipped)."""
+    Nchains: int = 10
+    lambda_temp: float = 1.7
+    chains_per_ensemble: int = 0
+    Tcoefs: Optional[np.ndarray] = None
+    c0: float = 10.0
+    epsilon1: float = 1e-12
+    epsilon2: float = 1e-12
+    A1: float = 1e14
+    target_acceptance: float = 0.234
+    Nt_learn: List[int] = field(default_factory=lambda: [500, 1500, 100000])
+    periods_learn: List[int] = field(default_factory=lambda: [1, 1])
+    dN_mixing: int = 1
+    seed: int = 12345
+    flags: int = 0
+
+    def tcoefs(self):
+        if self.Tcoefs is not None:
+            return np.ascontiguousarray(self.Tcoefs, dtype=np.float64)
+        ce = self.chains_per_ensemble or self.Nchains
+        return np.power(self.lambda_temp, (np.arange(self.Nchains) % ce).astype(np.float64))   # MALA.cpp:103
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data
+
+
+class GpuModelDef:
+    """Model_def-shaped adapter: owns one tg_handle (one GPU, one stream)."""
+
+    def __init__(self, prob, mala: Optional[MalaConfig] = None, device=0, shard=None, lib=None):
+        self.lib = lib or load_library()
+        self.prob = prob
+        self.mala = mala or MalaConfig()
+        self._keep = []
+        P = _Problem()
+        f64 = lambda a: self._hold(np.ascontiguousarray(a, dtype=np.float64))
+        i32 = lambda a: self._hold(np.ascontiguousarray(a, dtype=np.int32))
+        i64 = lambda a: self._hold(np.ascontiguousarray(a, dtype=np.int64))
+        x, y = f64(prob.x), f64(prob.y)
+        P.Nx, P.x, P.y = x.size, _p(x), _p(y)
+        P.sigma_y = _p(f64(prob.sigma_y)) if prob.sigma_y is not None else None
+        if shard is not None:   # dict(Nx_global, shard_lo, x_first, x_second, x_last)
+            P.Nx_global, P.shard_lo = shard["Nx_global"], shard["shard_lo"]
+            P.x_first, P.x_second, P.x_last = shard["x_first"], shard["x_second"], shard["x_last"]
+        P.model_case, P.likelihood_case, P.prior_case = prob.model_case, prob.like_case, prob.prior_case
+        P.likelihood_params = float(prob.likelihood_params)
+        P.plength = (C.c_int * 11)(*[int(v) for v in prob.plength])
+        P.Np = prob.Np
+        P.params0, P.relax = _p(f64(prob.params)), _p(i32(prob.relax))
+        P.priors, P.priors_switch = _p(f64(prob.priors)), _p(i32(prob.priors_switch))
+        P.extra_priors = (C.c_double * 4)(*[float(v) for v in prob.extra_priors])
+        m = self.mala
+        T = f64(m.tcoefs())
+        P.Nchains, P.chains_per_ensemble, P.Tcoefs = m.Nchains, m.chains_per_ensemble, _p(T)
+        P.c0, P.epsilon1, P.epsilon2, P.A1, P.target_acceptance = m.c0, m.epsilon1, m.epsilon2, m.A1, m.target_acceptance
+        P.n_learn = len(m.periods_learn)
+        P.Nt_learn, P.periods_learn = _p(i64(m.Nt_learn)), _p(i64(m.periods_learn))
+        P.dN_mixing = m.dN_mixing
+        P.init_err = _p(f64(prob.init_errors())) if prob.err_frac is not None else None
+        P.seed, P.device, P.flags = m.seed, device, m.flags
+        self.Tcoefs = T
+        h = C.c_void_p()
+        self.lib.check(self.lib.lib.tg_create(C.byref(P), C.byref(h)))
+        self.h = h
+        nv, np_, c, e, nx = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_long()
+        self.lib.check(self.lib.lib.tg_sizes(h, C.byref(nv), C.byref(np_), C.byref(c), C.byref(e), C.byref(nx)))
+        self.Nvars, self.Nparams, self.Nmodels, self.Nensembles, self.Nx = nv.value, np_.value, c.value, e.value, nx.value
+        self.index_to_relax = prob.index_to_relax
+        # Model_def public members (model_def.h:58-69)
+        self.params = np.tile(np.asarray(prob.params, dtype=np.float64), (self.Nmodels, 1))
+        self.vars = self.params[:, self.index_to_relax].copy()
+        self.logLikelihood = np.zeros(self.Nmodels)
+        self.logPrior = np.zeros(self.Nmodels)
+        self.logPosterior = np.zeros(self.Nmodels)
+        self.Pmove = np.zeros(self.Nmodels)
+        self.moved = np.zeros(self.Nmodels, dtype=bool)
+        self.status = np.zeros(self.Nmodels, dtype=np.int32)
+        self.refresh_from_device()
+
+    def _hold(self, a):
+        self._keep.append(a)
+        return a
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lib.tg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- Model_def interface -------------------------------------------------------------
+    def update_params_with_vars(self, m=None):
+        """model_def.cpp:370-378"""
+        if m is None:
+            self.params[:, self.index_to_relax] = self.vars
+        else:
+            self.params[m, self.index_to_relax] = self.vars[m]
+
+    def evaluate(self, params, T=None, want_model=False):
+        """Batched generate_model for arbitrary parameter vectors [B, Np] (tg_eval)."""
+        params = np.ascontiguousarray(np.atleast_2d(params), dtype=np.float64)
+        B = params.shape[0]
+        assert params.shape[1] == self.Nparams
+        T = np.ones(B) if T is None else np.ascontiguousarray(T, dtype=np.float64)
+        logL, logPr, logPo = np.empty(B), np.empty(B), np.empty(B)
+        st = np.zeros(B, dtype=np.int32)
+        model = np.empty((B, self.Nx)) if want_model else None
+        self.lib.check(self.lib.lib.tg_eval(self.h, _p(params), B, _p(T), _p(logL), _p(logPr), _p(logPo), _p(st), _p(model)))
+        return dict(logL=logL, logPrior=logPr, logPost=logPo, status=st, model=model)
+
+    def generate_model(self, m=None, Tcoefs=None):
+        """model_def.cpp:358-367 for chain m (or all chains): fills logLikelihood/logPrior/logPosterior."""
+        T = self.Tcoefs if Tcoefs is None else np.asarray(Tcoefs, dtype=np.float64)
+        rows = np.arange(self.Nmodels) if m is None else np.atleast_1d(m)
+        r = self.evaluate(self.params[rows], T[rows])
+        self.logLikelihood[rows], self.logPrior[rows], self.logPosterior[rows] = r["logL"], r["logPrior"], r["logPost"]
+        self.status[rows] = r["status"]
+        return self.logPosterior[rows] if m is None else float(self.logPosterior[rows][0])
+
+    def call_model(self, m=0):
+        """model_def.cpp:210-289: the model spectrum of chain m (parity / getmodel path)."""
+        return self.evaluate(self.params[m:m + 1], want_model=True)["model"][0]
+
+    def call_model_explicit(self, params):
+        """model_def.cpp:199-208"""
+        return self.evaluate(params, want_model=True)["model"][0]
+
+    def last_work(self, B):
+        L = np.zeros(B)
+        K = C.c_int(0)
+        self.lib.check(self.lib.lib.tg_last_work(self.h, B, _p(L), C.byref(K)))
+        return L, K.value
+
+    # -- resident evaluation (no PCIe traffic inside the timed region) -----------------------
+    def eval_upload(self, params, T):
+        params = np.ascontiguousarray(params, dtype=np.float64)
+        T = np.ascontiguousarray(T, dtype=np.float64)
+        self.lib.check(self.lib.lib.tg_eval_upload(self.h, _p(params), params.shape[0], _p(T)))
+        self.sync()
+
+    def eval_resident(self, B):
+        self.lib.check(self.lib.lib.tg_eval_resident(self.h, B))
+
+    def eval_fetch(self, B):
+        logL, logPr, logPo = np.empty(B), np.empty(B), np.empty(B)
+        st = np.zeros(B, dtype=np.int32)
+        self.lib.check(self.lib.lib.tg_eval_fetch(self.h, B, _p(logL), _p(logPr), _p(logPo), _p(st)))
+        return dict(logL=logL, logPrior=logPr, logPost=logPo, status=st)
+
+    # -- device state ------------------------------------------------------------------------
+    def refresh_from_device(self):
+        self.lib.check(self.lib.lib.tg_get_state(self.h, _p(self.vars), None, None, None, _p(self.logLikelihood),
+                                                 _p(self.logPrior), _p(self.logPosterior)))
+        self.update_params_with_vars()
+
+    def get_proposal(self):
+        Cn, Nv = self.Nmodels, self.Nvars
+        mu, sigma, cov = np.empty((Cn, Nv)), np.empty(Cn), np.empty((Cn, Nv, Nv))
+        self.lib.check(self.lib.lib.tg_get_state(self.h, None, _p(mu), _p(sigma), _p(cov), None, None, None))
+        return mu, sigma, cov
+
+    def set_state(self, vars_=None, mu=None, sigma=None, covarmat=None):
+        f = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+        v, m_, s, c = f(vars_), f(mu), f(sigma), f(covarmat)
+        self.lib.check(self.lib.lib.tg_set_state(self.h, _p(v), _p(m_), _p(s), _p(c)))
+        self.refresh_from_device()
+
+    def sync(self):
+        self.lib.check(self.lib.lib.tg_sync(self.h))
+
+    def set_tuning(self, chains_per_block=0, bins_per_thread=0, use_graph=-1):
+        self.lib.check(self.lib.lib.tg_set_tuning(self.h, chains_per_block, bins_per_thread, use_graph))
+
+    def kernel_time(self, reset=0):
+        n, ms, tot = C.c_long(0), C.c_double(0), C.c_long(0)
+        self.lib.check(self.lib.lib.tg_kernel_time(self.h, reset, C.byref(n), C.byref(ms), C.byref(tot)))
+        return n.value, ms.value, tot.value
+
+
+class GpuMALA:
+    """MALA-shaped driver: ``execute`` runs the sampling loop on the device (MALA.cpp:540-739)."""
+
+    def __init__(self, model_current: GpuModelDef):
+        self.model = model_current
+        self.Nchains = model_current.Nmodels
+        self.Tcoefs = model_current.Tcoefs
+
+    def execute(self, i0, nsteps, record=True, record_vars=True):
+        md = self.model
+        Cn, Nv, E = md.Nmodels, md.Nvars, md.Nensembles
+        out = None
+        rec = None
+        if record:
+            out = dict(
+                vars=np.empty((nsteps, Cn, Nv)) if record_vars else None,
+                logL=np.empty((nsteps, Cn)), logPrior=np.empty((nsteps, Cn)), logPost=np.empty((nsteps, Cn)),
+                Pmove=np.empty((nsteps, Cn)), moved=np.empty((nsteps, Cn), dtype=np.uint8),
+                swap_attempt=np.empty((nsteps, E), dtype=np.int32), swap_chain0=np.empty((nsteps, E), dtype=np.int32),
+                swap_Pswap=np.empty((nsteps, E)), swap_done=np.empty((nsteps, E), dtype=np.int32),
+                status=np.empty((nsteps, Cn), dtype=np.int32))
+            rec = _Records(*[_p(out[k]) for k in ("vars", "logL", "logPrior", "logPost", "Pmove", "moved",
+                                                   "swap_attempt", "swap_chain0", "swap_Pswap", "swap_done", "status")])
+        md.lib.check(md.lib.lib.tg_run(md.h, i0, nsteps, C.byref(rec) if rec is not None else None))
+        md.refresh_from_device()
+        return out
+
+    def step_begin(self, i):
+        self.model.lib.check(self.model.lib.lib.tg_step_begin(self.model.h, i))
+
+    def step_end(self, i):
+        self.model.lib.check(self.model.lib.lib.tg_step_end(self.model.h, i))
+
+    def partials_ptr(self):
+        p, n = C.c_void_p(), C.c_int()
+        self.model.lib.check(self.model.lib.lib.tg_partials_device_ptr(self.model.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
