@@ -148,6 +148,10 @@ int tg_sync(tg_handle *h);
 int tg_kernel_time(tg_handle *h, int reset, long *launches, double *ms_eval, long *total_launches);
 int tg_set_tuning(tg_handle *h, int chains_per_block, int bins_per_thread, int use_graph);
 
+/* Device-side stopwatch on the handle's stream (CUDA events): which = 0 start, 1 stop. */
+int tg_event_record(tg_handle *h, int which);
+int tg_event_elapsed_ms(tg_handle *h, double *ms);
+
 /* FP64 roofline denominator: DFMA-saturating microkernel, returns measured TFLOP/s (2 flop per DFMA). */
 int tg_measure_fp64_peak(int device, double *tflops, double *ms);
 

@@ -15,6 +15,7 @@ computes a model, a likelihood or a prior on the CPU; if the CUDA library is mis
 present the calls raise.
 """
 from . import workloads  # noqa: F401
+from . import sharding  # noqa: F401
 from .build import build_library, LIB_PATH  # noqa: F401
 from .gpu import (GpuLibrary, GpuModelDef, GpuMALA, MalaConfig, TgError, load_library,  # noqa: F401
                   ST_EMPTY_WINDOW, ST_NAN_WINDOW, ST_NAN_LOGL, ST_BAD_PRIOR, ST_CHOL_FAIL, ST_MODE_OVERFLOW)

@@ -44,6 +44,7 @@ struct tg_handle {
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
     long       n_eval_launch = 0, n_launch_total = 0; double ms_eval = 0;
     std::vector<void *> allocs;
+    cudaEvent_t watch[2] = {nullptr, nullptr};
 };
 
 template <typename T> static int dalloc(tg_handle *h, T **p, size_t n)
@@ -302,6 +303,7 @@ extern "C" int tg_destroy(tg_handle *h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->graph) cudaGraphExecDestroy(h->graph);
     for (auto e : h->ev_pool) cudaEventDestroy(e);
+    for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
     for (void *q : h->allocs) cudaFree(q);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -578,5 +580,23 @@ extern "C" int tg_measure_fp64_peak(int device, double *tflops, double *ms_out)
     const double flops = (double)blocks * 256.0 * iters * 64.0 * 2.0;
     if (tflops) *tflops = flops / (best * 1e-3) / 1e12;
     if (ms_out) *ms_out = best;
+    return TG_OK;
+}
+
+extern "C" int tg_event_record(tg_handle *h, int which)
+{
+    if (!h || which < 0 || which > 1) return fail(TG_E_BADARG, "tg_event_record: bad argument");
+    CK(cudaSetDevice(h->device));
+    if (!h->watch[which]) CK(cudaEventCreate(&h->watch[which]));
+    CK(cudaEventRecord(h->watch[which], h->stream));
+    return TG_OK;
+}
+extern "C" int tg_event_elapsed_ms(tg_handle *h, double *ms)
+{
+    if (!h || !ms || !h->watch[0] || !h->watch[1]) return fail(TG_E_BADARG, "tg_event_elapsed_ms: record both events first");
+    CK(cudaSetDevice(h->device));
+    CK(cudaEventSynchronize(h->watch[1]));
+    float f = 0; CK(cudaEventElapsedTime(&f, h->watch[0], h->watch[1]));
+    *ms = f;
     return TG_OK;
 }

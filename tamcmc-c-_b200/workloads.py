@@ -110,7 +110,7 @@ def s_local(Nx=10000, seed=12345, make_y=None):
     return _local_problem("S-local", x, modes, a1=1.0, inc=45.0, N0=1.0, trunc_c=20.0, seed=seed, make_y=make_y)
 
 
-def _local_problem(name, x, modes, a1, inc, N0, trunc_c, seed, make_y, y=None):
+def _local_problem(name, x, modes, a1, inc, N0, trunc_c, seed, make_y, y=None, asym=0.0, do_amp=0):
     nfl = [sum(1 for m in modes if m[0] == l) for l in range(4)]
     b = _Builder()
     for l in range(4):
@@ -127,7 +127,7 @@ def _local_problem(name, x, modes, a1, inc, N0, trunc_c, seed, make_y, y=None):
     b.add("Splitting_a3", 0.0, 0)
     b.add("sqrt(splitting_a1).cosi", ci, 1, PRIOR_UNIFORM, (0.0, 2.5), _ERR["a1cos"])
     b.add("sqrt(splitting_a1).sini", si, 1, PRIOR_UNIFORM, (0.0, 2.5), _ERR["a1cos"])
-    b.add("Lorentzian_asymetry", 0.0, 0)
+    b.add("Lorentzian_asymetry", asym, 1 if asym != 0 else 0, PRIOR_JEFFREYS_ABS, (5.0, 200.0), _ERR["asym"])
     for l in range(4):
         for m in modes:
             if m[0] == l:
@@ -135,7 +135,7 @@ def _local_problem(name, x, modes, a1, inc, N0, trunc_c, seed, make_y, y=None):
     b.add("White_Noise_N0", N0, 1, PRIOR_GAUSSIAN, (N0, 0.1 * N0), _ERR["n0"])
     b.add("Inclination", 0.0, 0)
     b.add("Truncation parameter", trunc_c, 0)
-    b.add("Switch for fit of Amplitudes or Heights", 0.0, 0)
+    b.add("Switch for fit of Amplitudes or Heights", float(do_amp), 0)
     v, relax, pri, sw, names, ea, eb = b.arrays()
     nf = sum(nfl)
     plength = np.array([nf, 0, nfl[0], nfl[1], nfl[2], nfl[3], 6, nf, 1, 1, 2], dtype=np.int32)
@@ -238,3 +238,164 @@ def perturbed_params(prob, C, scale=0.3, seed=7):
     P[:, idx] += scale * err[None, :] * g.standard_normal((C, idx.size))
     P[0] = prob.params
     return P
+
+
+# ---------------------------------------------------------------------------------------------
+# Small problems covering every live model case of Config/default/models_ctrl.list (parity tests)
+# ---------------------------------------------------------------------------------------------
+def small_global(model_case, Nx=6000, step=0.05, norders=4, lmax=3, asym=0.0, do_amp=0, trunc_c=20.0,
+                 a3=0.0, x0=900.0, seed=3):
+    """A reduced global fit (few orders) for model cases 2,3,6,7,8,9,10,12,13."""
+    assert model_case in (2, 3, 6, 7, 8, 9, 10, 12, 13)
+    g = np.random.Generator(np.random.Philox(key=seed + model_case))
+    x = x0 + np.arange(Nx) * step
+    dnu = 55.0
+    f0 = x0 + 40.0 + dnu * np.arange(norders) + g.normal(0, 0.3, norders)
+    f = [f0, f0 + dnu / 2 - 2.0 + g.normal(0, 0.2, norders), f0 - 5.0 + g.normal(0, 0.2, norders),
+         f0 + dnu / 2 - 9.0 + g.normal(0, 0.2, norders)]
+    W = np.linspace(0.6, 2.4, norders)            # straddles the Gamma=1 branch of the window logic
+    H = 20.0 * np.exp(-0.5 * ((f0 - f0.mean()) / 80.0) ** 2)
+    V = (1.5, 0.53, 0.08)
+    a1, inc, eta = 1.3, 52.0, 3e-4
+    b = _Builder()
+    for k in range(norders):
+        b.add("Height_l", H[k], 1, PRIOR_JEFFREYS, (1.0, 1000.0), _ERR["height"])
+    for l in range(1, lmax + 1):
+        b.add("Visibility_l%d" % l, V[l - 1], 1, PRIOR_GAUSSIAN, (V[l - 1], 0.1), _ERR["v%d" % l])
+    for l in range(lmax + 1):
+        for k in range(norders):
+            b.add("Frequency_l", f[l][k], 1, PRIOR_GUG, (f[l][k] - 2.0, f[l][k] + 2.0, 0.3, 0.4), _ERR["freq"])
+    # Snlm block: a1, eta, a3, sqrt(a1)cos i, sqrt(a1) sin i, asym [, extra a1 terms]
+    direct = model_case in (3, 6, 7, 8, 12, 13)
+    b.add("Splitting_a1", a1 if direct else 0.0, 1 if direct and model_case not in (7, 8) else 0, PRIOR_UNIFORM, (0.0, 5.0), _ERR["a1"])
+    b.add("Asphericity_eta", eta, 1, PRIOR_UNIFORM_ABS, (0.0, 1e-2), _ERR["eta"])
+    b.add("Splitting_a3", a3, 1 if a3 != 0 else 0, PRIOR_UNIFORM, (-0.2, 0.2), _ERR["a3"])
+    if direct:
+        b.add("Empty", 0.0, 0)
+        b.add("Empty", 0.0, 0)
+    else:
+        b.add("sqrt(splitting_a1).cosi", np.sqrt(a1) * np.cos(np.deg2rad(inc)), 1, PRIOR_UNIFORM, (0.0, 2.5), _ERR["a1cos"])
+        b.add("sqrt(splitting_a1).sini", np.sqrt(a1) * np.sin(np.deg2rad(inc)), 1, PRIOR_UNIFORM, (0.0, 2.5), _ERR["a1cos"])
+    b.add("Lorentzian_asymetry", asym, 1 if asym != 0 else 0, PRIOR_JEFFREYS_ABS, (5.0, 200.0), _ERR["asym"])
+    nsplit = 6
+    if model_case == 6:
+        b.add("Splitting_a1(l=2)", 0.8, 1, PRIOR_UNIFORM, (0.0, 5.0), _ERR["a1"]); nsplit = 7
+    if model_case == 7:
+        for k in range(norders):
+            b.add("Splitting_a1(n)", 0.7 + 0.2 * k, 1, PRIOR_UNIFORM, (0.0, 5.0), _ERR["a1"])
+        nsplit = 6 + norders
+    if model_case == 8:
+        for k in range(2 * norders):
+            b.add("Splitting_a1(n,l)", 0.6 + 0.15 * k, 1, PRIOR_UNIFORM, (0.0, 5.0), _ERR["a1"])
+        nsplit = 6 + 2 * norders
+    if model_case == 9:      # numax_dip?, alpha, Gamma_alpha, Wdip, DeltaGamma_dip  (models.cpp:1408-1411)
+        for nm, v in zip(("nudip", "alfa", "GammaAlfa", "Wdip", "DeltaGammadip"), (f0.mean() - 10.0, 3.0, 1.5, 400.0, 2.0)):
+            b.add("Width:" + nm, v, 1, PRIOR_UNIFORM, (0.2 * v, 3.0 * v), _ERR["width"])
+        nwidth = 5
+    elif model_case == 10:   # numax, nudip, alpha, Gamma_alpha, Wdip, DeltaGamma_dip (models.cpp:1590-1594)
+        for nm, v in zip(("numax", "nudip", "alfa", "GammaAlfa", "Wdip", "DeltaGammadip"),
+                         (f0.mean(), f0.mean() - 10.0, 3.0, 1.5, 400.0, 2.0)):
+            b.add("Width:" + nm, v, 1, PRIOR_UNIFORM, (0.2 * v, 3.0 * v), _ERR["width"])
+        nwidth = 6
+    else:
+        for k in range(norders):
+            b.add("Width_l", W[k], 1, PRIOR_JEFFREYS, (step, dnu / 3.0), _ERR["width"])
+        nwidth = norders
+    noise = [(0.0, 0.0, 1.0), (30.0, 9.0, 3.7), (8.0, 2.2, 2.0)]
+    for (h, tc, p) in noise:
+        free = 1 if tc != 0 else 0
+        b.add("Harvey-Noise_H", h, free, PRIOR_GAUSSIAN, (h, 0.1 * max(h, 1)), _ERR["hH"])
+        b.add("Harvey-Noise_tc", tc, free, PRIOR_GAUSSIAN, (tc, 0.1 * max(tc, 1)), _ERR["htc"])
+        b.add("Harvey-Noise_p", p, free, PRIOR_UG, (1.0, 4.5, 0.2), _ERR["hp"])
+    b.add("White_Noise_N0", 0.6, 1, PRIOR_GAUSSIAN, (0.6, 0.05), _ERR["n0"])
+    if model_case == 12:     # 9 free height ratios: l=1 (m0, m1), l=2 (m0, m1, m2), l=3 (m0..m3)
+        r = [0.4, 0.3, 0.3, 0.2, 0.15, 0.3, 0.15, 0.1, 0.1]
+        for v in r:
+            b.add("Hlm_ratio", v, 1, PRIOR_UNIFORM, (0.0, 1.0), (0.0, 0.05))
+        ninc = 9
+    elif model_case == 13:   # 2*Nfl1 + 3*Nfl2 + 4*Nfl3 heights
+        ninc = (2 + 3 + 4) * norders
+        for k in range(ninc):
+            b.add("Hlm", 3.0 + 0.37 * (k % 11), 1, PRIOR_JEFFREYS, (1.0, 1000.0), _ERR["height"])
+    else:
+        b.add("Inclination", inc if direct else 0.0, 1 if direct else 0, PRIOR_UNIFORM, (0.0, 90.0), _ERR["inc"])
+        ninc = 1
+    b.add("Truncation parameter", trunc_c, 0)
+    b.add("Switch for fit of Amplitudes or Heights", float(do_amp), 0)
+    v, relax, pri, sw, names, ea, eb = b.arrays()
+    plength = np.array([norders, lmax] + [norders if l <= lmax else 0 for l in range(4)] + [nsplit, nwidth, 10, ninc, 2],
+                       dtype=np.int32)
+    assert plength.sum() == v.size, (plength.sum(), v.size)
+    extra = np.array([1.0, 2.0, 0.2, 1.0 if model_case == 12 else 0.0])
+    return Problem(name="small-global-%d" % model_case, model_case=model_case, like_case=0, prior_case=2,
+                   plength=plength, params=v, relax=relax, priors=pri, priors_switch=sw, extra_priors=extra,
+                   x=x, y=np.ones_like(x), names=names, err_frac=ea, err_off=eb)
+
+
+def small_local(model_case=11, Nx=1500, step=0.02, asym=0.0, do_amp=0, trunc_c=20.0, x0=95.0):
+    """A local fit with l=0,1,2,3 modes for model cases 11 (basic) and 14 (Hnlm)."""
+    x = x0 + np.arange(Nx) * step
+    span = Nx * step
+    modes = [(0, x0 + 0.30 * span, 900.0, 0.31), (0, x0 + 0.75 * span, 500.0, 1.2), (1, x0 + 0.52 * span, 700.0, 0.45),
+             (2, x0 + 0.22 * span, 400.0, 0.33), (3, x0 + 0.62 * span, 90.0, 0.38)]
+    if model_case == 11:
+        return _local_problem("small-local-11", x, modes, a1=0.45, inc=63.0, N0=110.0, trunc_c=trunc_c, seed=5,
+                              make_y=None, asym=asym, do_amp=do_amp)
+    nfl = [sum(1 for m in modes if m[0] == l) for l in range(4)]
+    b = _Builder()
+    for l in range(4):
+        for m in modes:
+            if m[0] == l:
+                for k in range(l + 1):
+                    b.add("Height_lm", m[2] / (1.0 + k), 1, PRIOR_JEFFREYS, (1.0, 10000.0), _ERR["height"])
+    for l in range(4):
+        for m in modes:
+            if m[0] == l:
+                b.add("Frequency_l", m[1], 1, PRIOR_UNIFORM, (m[1] - 3.0, m[1] + 3.0), _ERR["freq"])
+    b.add("Splitting_a1", 0.45, 1, PRIOR_UNIFORM, (0.0, 1.5), _ERR["a1"])
+    b.add("Asphericity_eta", 0.0, 0)
+    b.add("Splitting_a3", 0.01, 1, PRIOR_UNIFORM, (-0.05, 0.05), _ERR["a3"])
+    b.add("Empty", 0.0, 0); b.add("Empty", 0.0, 0)
+    b.add("Lorentzian_asymetry", asym, 1 if asym != 0 else 0, PRIOR_JEFFREYS_ABS, (5.0, 200.0), _ERR["asym"])
+    for l in range(4):
+        for m in modes:
+            if m[0] == l:
+                b.add("Width_l", m[3], 1, PRIOR_JEFFREYS, (step, 20.0), _ERR["width"])
+    b.add("White_Noise_N0", 110.0, 1, PRIOR_GAUSSIAN, (110.0, 11.0), _ERR["n0"])
+    b.add("Inclination", 0.0, 0)
+    b.add("Truncation parameter", trunc_c, 0)
+    b.add("Switch for fit of Amplitudes or Heights", float(do_amp), 0)
+    v, relax, pri, sw, names, ea, eb = b.arrays()
+    nh = nfl[0] + 2 * nfl[1] + 3 * nfl[2] + 4 * nfl[3]
+    nf = sum(nfl)
+    plength = np.array([nh, 0, nfl[0], nfl[1], nfl[2], nfl[3], 6, nf, 1, 1, 2], dtype=np.int32)
+    assert plength.sum() == v.size
+    return Problem(name="small-local-14", model_case=14, like_case=0, prior_case=3, plength=plength, params=v,
+                   relax=relax, priors=pri, priors_switch=sw, extra_priors=np.array([0.0, 2.0, 0.2, 2.0]),
+                   x=x, y=np.ones_like(x), names=names, err_frac=ea, err_off=eb)
+
+
+def gauss_problem(model_case=0, Nx=800, like_case=1, seed=11):
+    """model_Test_Gaussian (case 0) / model_Harvey_Gaussian (case 1)."""
+    g = np.random.Generator(np.random.Philox(key=seed))
+    x = np.linspace(50.0, 450.0, Nx)
+    b = _Builder()
+    b.add("Hmax", 8.0, 1, PRIOR_UNIFORM, (0.0, 50.0), (0.1, 0.0))
+    b.add("Gsigma", 30.0, 1, PRIOR_UNIFORM, (1.0, 200.0), (0.01, 1.0))
+    b.add("Numax", 240.0, 1, PRIOR_UNIFORM, (100.0, 400.0), (0.01, 2.0))
+    if model_case == 0:
+        b.add("White_Noise_N0", 1.5, 1, PRIOR_UNIFORM, (0.0, 10.0), (0.015, 0.002))
+        plength = np.array([4] + [0] * 10, dtype=np.int32)
+    else:
+        b.add("Harvey-Noise_H", 12.0, 1, PRIOR_UNIFORM, (0.0, 100.0), _ERR["hH"])
+        b.add("Harvey-Noise_tc", 9.0, 1, PRIOR_UNIFORM, (0.0, 100.0), _ERR["htc"])
+        b.add("Harvey-Noise_p", 2.3, 1, PRIOR_UNIFORM, (1.0, 5.0), _ERR["hp"])
+        b.add("White_Noise_N0", 1.5, 1, PRIOR_UNIFORM, (0.0, 10.0), _ERR["n0"])
+        plength = np.array([7] + [0] * 10, dtype=np.int32)
+    v, relax, pri, sw, names, ea, eb = b.arrays()
+    m = v[0] * np.exp(-0.5 * (x - v[2]) ** 2 / v[1] ** 2) + (v[3] if model_case == 0 else 1.5 + 12.0 / (1 + (1e-3 * 9.0 * x) ** 2.3))
+    sig = 0.25 * np.ones(Nx)
+    y = m + sig * g.standard_normal(Nx) if like_case == 1 else m * g.exponential(1.0, Nx)
+    return Problem(name="gauss-%d" % model_case, model_case=model_case, like_case=like_case, prior_case=model_case,
+                   plength=plength, params=v, relax=relax, priors=pri, priors_switch=sw,
+                   extra_priors=np.zeros(4), x=x, y=y, sigma_y=sig, names=names, err_frac=ea, err_off=eb)

@@ -1,0 +1,176 @@
+"""GPU tests of the device-resident sampler (MALA::execute replacement): bookkeeping invariants,
+reproducibility / resume, and posterior agreement with (a) the Fisher-matrix prediction and (b) a
+CPU sampler that follows MALA.cpp with the oracle as its model -- within Monte-Carlo error, the
+only parity that is meaningful for the sampler (reference RNG is rand()+time(NULL), quirk Q10)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _gauss(W):
+    return W.gauss_problem(0, like_case=1, Nx=400)
+
+
+def test_records_and_invariants(tb, W):
+    prob = _gauss(W)
+    cfg = tb.MalaConfig(Nchains=6, Nt_learn=[50, 400], periods_learn=[1], c0=5.0, dN_mixing=2, seed=99,
+                        flags=tb.gpu.F_FIX_SWAP_BOOKKEEPING)
+    md = tb.GpuModelDef(prob, cfg)
+    out = tb.GpuMALA(md).execute(0, 600)
+    assert np.all(out["status"] == 0)
+    assert np.allclose(out["logPost"], out["logL"] + out["logPrior"], rtol=0, atol=1e-9)
+    assert np.all((out["Pmove"] >= 0) & (out["Pmove"] <= 1))
+    # swap cadence: every dN_mixing steps, never at i == 0 (MALA.cpp:676)
+    att = out["swap_attempt"][:, 0]
+    assert att[0] == 0 and np.array_equal(att[1:], (np.arange(1, 600) % 2 == 0).astype(np.int32))
+    assert np.all(out["swap_chain0"][att == 1] >= 0) and np.all(out["swap_chain0"][att == 1] < 5)
+    assert np.all(out["swap_chain0"][att == 0] == -1) and np.all(out["swap_done"][att == 0] == 0)
+    assert 0.05 < out["swap_done"][att == 1].mean() <= 1.0
+    # a chain that did not move and was not swapped keeps its variables
+    v = out["vars"]
+    for i in range(1, 600):
+        sw = set()
+        if out["swap_done"][i, 0]:
+            a = out["swap_chain0"][i, 0]; sw = {a, a + 1}
+        for c in range(6):
+            if not out["moved"][i, c] and c not in sw:
+                assert np.array_equal(v[i, c], v[i - 1, c])
+    # host mirror == last record
+    assert np.array_equal(md.vars, v[-1]) and np.array_equal(md.logLikelihood, out["logL"][-1])
+    mu, sigma, cov = md.get_proposal()
+    assert np.all(sigma > 0) and np.all(np.linalg.eigvalsh(cov[0]) > -1e-12)
+    md.close()
+
+
+def test_reproducible_and_resumable(tb, W):
+    prob = _gauss(W)
+    mk = lambda seed: tb.MalaConfig(Nchains=4, Nt_learn=[20, 10000], periods_learn=[1], c0=5.0, seed=seed,
+                                    flags=tb.gpu.F_FIX_SWAP_BOOKKEEPING)
+    a = tb.GpuModelDef(prob, mk(5)); ra = tb.GpuMALA(a).execute(0, 150)
+    b = tb.GpuModelDef(prob, mk(5)); rb1 = tb.GpuMALA(b).execute(0, 100)
+    for k in ("vars", "logL", "moved", "swap_done"):
+        assert np.array_equal(ra[k][:100], rb1[k])
+    # restore into a fresh handle (restore files: vars, mu, sigma, covarmat) and continue at i0=100
+    mu, sigma, cov = b.get_proposal()
+    c = tb.GpuModelDef(prob, mk(5))
+    c.set_state(vars_=b.vars, mu=mu, sigma=sigma, covarmat=cov)
+    rc = tb.GpuMALA(c).execute(100, 50)
+    for k in ("vars", "logL", "logPost", "moved", "swap_done", "Pmove"):
+        assert np.array_equal(ra[k][100:], rc[k]), k
+    d = tb.GpuModelDef(prob, mk(6)); rd = tb.GpuMALA(d).execute(0, 100)
+    assert not np.array_equal(rd["vars"], rb1["vars"])
+    for m in (a, b, c, d):
+        m.close()
+
+
+def test_graph_and_direct_launch_agree(tb, W):
+    prob = _gauss(W)
+    cfg = tb.MalaConfig(Nchains=4, Nt_learn=[10, 10000], periods_learn=[2], c0=5.0, seed=3)
+    a = tb.GpuModelDef(prob, cfg); a.set_tuning(0, 0, 1); ra = tb.GpuMALA(a).execute(0, 100)
+    b = tb.GpuModelDef(prob, cfg); b.set_tuning(0, 0, 0); rb = tb.GpuMALA(b).execute(0, 100)
+    for k in ra:
+        assert np.array_equal(ra[k], rb[k]), k
+    a.close(); b.close()
+
+
+def _cpu_sampler(oracle, prob, cfg, nsteps, rng):
+    """MALA.cpp:608-692 with numpy RNG and the oracle as generate_model."""
+    C = cfg.Nchains
+    T = cfg.tcoefs()
+    idx = prob.index_to_relax
+    Nv = idx.size
+    params = np.tile(prob.params, (C, 1))
+    x = params[:, idx].copy()
+    cur = oracle.generate_models(prob, params, T)
+    logL, logPr, logPo = cur["logL"].copy(), cur["logPrior"].copy(), cur["logPost"].copy()
+    err = prob.init_errors()
+    cov = np.tile(np.diag(err**2), (C, 1, 1))
+    sigma = 2.38**2 * T**0.2 / Nv
+    mu = x.copy()
+    keep = np.empty((nsteps, Nv))
+    for i in range(nsteps):
+        gamma = cfg.c0 / (1.0 + i)
+        prop = params.copy()
+        xn = np.empty_like(x)
+        for m in range(C):
+            L = np.linalg.cholesky((cov[m] + cfg.epsilon2 * np.eye(Nv)) * sigma[m])
+            xn[m] = x[m] + L @ rng.standard_normal(Nv)
+        prop[:, idx] = xn
+        new = oracle.generate_models(prob, prop, T)
+        for m in range(C):
+            if np.isnan(new["logL"][m]) or new["logPost"][m] == -np.inf:
+                r = 0.0
+            else:
+                r = min(1.0, np.exp(new["logPost"][m] - logPo[m]))
+            if rng.random() <= r:
+                x[m], params[m] = xn[m], prop[m]
+                logL[m], logPr[m], logPo[m] = new["logL"][m], new["logPrior"][m], new["logPost"][m]
+            learn = any(cfg.Nt_learn[l] <= i < cfg.Nt_learn[l + 1] and i % cfg.periods_learn[l] == 0 for l in range(len(cfg.periods_learn)))
+            if learn:
+                mu[m] = mu[m] + gamma * (x[m] - mu[m])
+                d = x[m] - mu[m]
+                cov[m] = cov[m] + gamma * (np.outer(d, d) - cov[m])
+                sigma[m] = min(max(sigma[m] + gamma * (r - cfg.target_acceptance), cfg.epsilon1), cfg.A1)
+        if i % cfg.dN_mixing == 0 and i != 0:
+            A = rng.integers(0, C - 1); B = A + 1
+            LA_TB, LB_TA = logL[A] * T[A] / T[B], logL[B] * T[B] / T[A]
+            rT = min(1.0, np.exp(LA_TB + LB_TA - logL[A] - logL[B]))
+            if rng.random() <= rT:
+                x[[A, B]] = x[[B, A]]; params[[A, B]] = params[[B, A]]
+                prA, prB = logPr[A], logPr[B]
+                logL[A], logPr[A], logPo[A] = LB_TA, prB, LB_TA + prB
+                logL[B], logPr[B], logPo[B] = LA_TB, prA, LA_TB + prA
+        keep[i] = x[0]
+    return keep
+
+
+def test_posterior_matches_fisher_and_cpu_sampler(tb, W, oracle):
+    prob = _gauss(W)
+    cfg = tb.MalaConfig(Nchains=4, Nt_learn=[100, 4000], periods_learn=[1], c0=5.0, dN_mixing=1, seed=2024,
+                        flags=tb.gpu.F_FIX_SWAP_BOOKKEEPING)
+    # Fisher prediction around the maximum: cov = (J^T J / sigma^2)^-1 (chi-square likelihood, flat priors)
+    p0 = prob.params.copy()
+    J = np.empty((prob.x.size, 4))
+    for k in range(4):
+        h = 1e-5 * max(1.0, abs(p0[k]))
+        a, b = p0.copy(), p0.copy(); a[k] += h; b[k] -= h
+        J[:, k] = (oracle.model(0, a, prob.plength, prob.x)[1] - oracle.model(0, b, prob.plength, prob.x)[1]) / (2 * h)
+    # likelihood_chi_square is -sum((y-m)^2/sigma^2) (no 1/2): posterior covariance = (2 J^T J / sigma^2)^-1
+    fisher_cov = np.linalg.inv(2.0 * (J.T / prob.sigma_y**2) @ J)
+    md = tb.GpuModelDef(prob, cfg)
+    mala = tb.GpuMALA(md)
+    mala.execute(0, 4000, record=False)
+    out = mala.execute(4000, 30000)
+    s = out["vars"][:, 0, :]
+    acc = out["moved"][:, 0].mean()
+    assert 0.1 < acc < 0.45, acc                       # adapted towards target_acceptance = 0.234
+    gpu_mean, gpu_std = s.mean(axis=0), s.std(axis=0)
+    fstd = np.sqrt(np.diag(fisher_cov))
+    assert np.all(np.abs(gpu_std / fstd - 1.0) < 0.2), (gpu_std, fstd)
+    # CPU sampler (same algorithm, oracle model)
+    cpu = _cpu_sampler(oracle, prob, cfg, 14000, np.random.default_rng(7))[4000:]
+    cpu_mean, cpu_std = cpu.mean(axis=0), cpu.std(axis=0)
+    assert np.all(np.abs(gpu_mean - cpu_mean) < 0.35 * fstd), (gpu_mean, cpu_mean, fstd)
+    assert np.all(np.abs(gpu_std / cpu_std - 1.0) < 0.3), (gpu_std, cpu_std)
+    # hotter chains are broader
+    hot = out["vars"][:, 3, :].std(axis=0)
+    assert np.all(hot > gpu_std)
+    md.close()
+
+
+def test_global_fit_runs_and_learns(tb, W, oracle):
+    """A reduced global MS fit: the sampler runs, adapts and keeps the chains at high posterior."""
+    prob = W.small_global(3, Nx=4000, step=0.08)
+    st, m, _ = oracle.model(prob.model_case, prob.params, prob.plength, prob.x)
+    prob.y = m * (-np.log(W.philox_uniform(m.size, 8)))
+    cfg = tb.MalaConfig(Nchains=10, Nt_learn=[100, 100000], periods_learn=[1], c0=2.0, seed=1)
+    md = tb.GpuModelDef(prob, cfg)
+    l0 = md.logLikelihood[0]
+    out = tb.GpuMALA(md).execute(0, 3000)
+    assert np.all((out["status"] & ~tb.ST_NAN_LOGL & ~tb.ST_EMPTY_WINDOW) == 0)
+    late = out["moved"][2000:, 0].mean()
+    assert 0.03 < late < 0.6, late
+    assert out["logL"][-500:, 0].mean() > l0 - 5 * prob.Nv     # stays near the mode of the posterior
+    assert np.all(np.diff(out["logL"][-500:].mean(axis=0) * cfg.tcoefs()) < 0)   # hotter chains sit at lower untempered logL
+    md.close()
