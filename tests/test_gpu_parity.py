@@ -155,11 +155,11 @@ def test_prior_hard_limits(tb, W, oracle):
     P[1, pl[0]] = -0.1                                        # negative visibility => -inf (priors_calc.cpp:53-57)
     iS = pl[0] + pl[1] + pl[2:6].sum()
     P[2, iS + 2] = 0.5 * P[2, iS]                             # |a3/a1| >= 0.2 => -inf (:137-139)
-    P[3, pl[0] + pl[1]] += 100.0                              # frequency far outside its GUG core: finite penalty
+    P[3, pl[0] + pl[1]] += 3.5                                # frequency outside its GUG core (+-2): finite Gaussian penalty
     P[4, 0] = 2000.0                                          # height beyond the Jeffreys range => -inf
     r, ref = _check(md, oracle, prob, P, np.ones(5), want_model=False)
     assert r["logPrior"][1] == -np.inf and r["logPrior"][2] == -np.inf and r["logPrior"][4] == -np.inf
-    assert np.isfinite(r["logPrior"][3]) and r["logPrior"][3] < r["logPrior"][0] - 1000
+    assert np.isfinite(r["logPrior"][3]) and r["logPrior"][3] < r["logPrior"][0] - 5
     md.close()
 
 
