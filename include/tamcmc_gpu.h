@@ -73,6 +73,7 @@ typedef struct tg_problem {
     int           flags;          /* TG_F_* */
 } tg_problem;
 
+#define TG_F_NO_TILE_ORDER        2 /* launch the bin tiles in index order instead of heaviest-first (scheduling only; results identical) */
 #define TG_F_FIX_SWAP_BOOKKEEPING 1 /* fix quirk Q8 (stale logPosterior[B] after a swap, MALA.cpp:417-428); default replicates */
 
 /* Per-step records the reference hands to Outputs (MALA.cpp:696-707), for nsteps steps.
@@ -147,6 +148,8 @@ int tg_sync(tg_handle *h);
  * the last reset: number of launches and total milliseconds. */
 int tg_kernel_time(tg_handle *h, int reset, long *launches, double *ms_eval, long *total_launches);
 int tg_set_tuning(tg_handle *h, int chains_per_block, int bins_per_thread, int use_graph);
+/* A CTA of the fused kernel covers nsub sub-tiles of 256*bins_per_thread bins per chain (default 1). */
+int tg_set_subtiles(tg_handle *h, int nsub);
 
 /* Device-side stopwatch on the handle's stream (CUDA events): which = 0 start, 1 stop. */
 int tg_event_record(tg_handle *h, int which);

@@ -37,7 +37,12 @@ struct tg_handle {
     EvalBuf    ev;               // tg_eval batches
     EvalBuf    sp;               // sampler's proposed points (cap == C)
     int        ntiles = 0, bpt = 4, chains_per_block = 0, use_graph = 1, steps_per_graph = 16;
-    int        smem_matrix = 0; size_t propose_smem = 0;
+    int        smem_matrix = 0; size_t propose_smem = 0, spec_smem = 0;
+    cudaStream_t side = nullptr;           // speculative proposal-adaptation kernel runs here, next to the fused kernel
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    double    *stage_mu = nullptr, *stage_cov = nullptr;   // tg_get_state staging ([C][Nv], [C][Nv][Nv])
+    int        list_cap = 4, max_cpb = 1, nsub = 1;
+    int       *tile_order = nullptr;       // launch order -> tile, heaviest first (NULL: identity)
     cudaGraphExec_t graph = nullptr;
     // eval-kernel timing
     bool       timing = false;
@@ -111,16 +116,17 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
         tg_k_prologue<<<B, TG_PRO_THREADS, TG_PRO_SMEM(h->d.Np), h->stream>>>(pa);
         h->n_launch_total++;
     }
-    TgEvalArgs ea{h->d, b.t, h->x, h->y, h->lnx, h->sig, b.partials, model, B, h->ntiles, h->chains_per_block};
+    TgEvalArgs ea{h->d, b.t, h->x, h->y, h->lnx, h->sig, b.partials, model, h->tile_order, B, h->ntiles, h->chains_per_block, h->nsub, h->list_cap};
+    const size_t esm = TG_EVAL_SMEM(h->chains_per_block, h->list_cap);
     dim3 grid(h->ntiles, (B + h->chains_per_block - 1) / h->chains_per_block);
     if (h->timing) {
         if (h->ev_used >= 8192) { int r = harvest_events(h); if (r) return r; }
         cudaEventRecord(next_event(h), h->stream);
     }
     switch (h->bpt) {
-    case 1: tg_k_eval<1><<<grid, TG_THREADS, 0, h->stream>>>(ea); break;
-    case 2: tg_k_eval<2><<<grid, TG_THREADS, 0, h->stream>>>(ea); break;
-    default: tg_k_eval<4><<<grid, TG_THREADS, 0, h->stream>>>(ea); break;
+    case 1: tg_k_eval<1><<<grid, TG_THREADS, esm, h->stream>>>(ea); break;
+    case 2: tg_k_eval<2><<<grid, TG_THREADS, esm, h->stream>>>(ea); break;
+    default: tg_k_eval<4><<<grid, TG_THREADS, esm, h->stream>>>(ea); break;
     }
     if (h->timing) cudaEventRecord(next_event(h), h->stream);
     h->n_eval_launch++; h->n_launch_total++;
@@ -129,18 +135,58 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
     return TG_OK;
 }
 
+// Launch order of the bin tiles: heaviest first (tiles crossed by many truncation windows cost
+// several times more than noise-only tiles; dispatching them first lets the light tiles fill the
+// tail of the grid).  Estimated once from the windows of chain 0 at the initial point -- the order
+// only affects scheduling, never results.
+static int build_tile_order(tg_handle *h)
+{
+    const int nt = h->ntiles, tile = TG_THREADS * h->bpt * h->nsub, nc = h->d.ncomp_max;
+    if (!h->tile_order) { int r = dalloc(h, &h->tile_order, (size_t)(h->d.Nx + TG_THREADS - 1) / TG_THREADS); if (r) return r; }
+    std::vector<int> lo(std::max(nc, 1)), hi(std::max(nc, 1)), order(nt);
+    int ncomp = 0;
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(&ncomp, h->sp.t.ncomp, sizeof(int), cudaMemcpyDeviceToHost));
+    if (nc > 0) {
+        CK(cudaMemcpy(lo.data(), h->sp.t.lo, (size_t)nc * 4, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(hi.data(), h->sp.t.hi, (size_t)nc * 4, cudaMemcpyDeviceToHost));
+    }
+    std::vector<int> diff(nt + 1, 0);
+    for (int k = 0; k < ncomp && k < nc; k++) {
+        if (hi[k] <= lo[k]) continue;
+        const int t0 = std::max(0, lo[k] / tile), t1 = std::min(nt - 1, (hi[k] - 1) / tile);
+        if (t1 >= t0) { diff[t0]++; diff[t1 + 1]--; }
+    }
+    std::vector<int> w(nt);
+    for (int t = 0, c = 0; t < nt; t++) { c += diff[t]; w[t] = c; order[t] = t; }
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return w[a] > w[b]; });
+    CK(cudaMemcpy(h->tile_order, order.data(), (size_t)nt * 4, cudaMemcpyHostToDevice));
+    return TG_OK;
+}
+
 extern "C" int tg_set_tuning(tg_handle *h, int chains_per_block, int bins_per_thread, int use_graph)
 {
     if (!h) return fail(TG_E_BADARG, "null handle");
     if (bins_per_thread == 1 || bins_per_thread == 2 || bins_per_thread == 4) {
         if (bins_per_thread != h->bpt) {
-            // partials buffers were sized for the finest tiling at create time, so any bpt fits
+            // partials buffers were sized for the finest tiling at create time, so any tiling fits
             h->bpt = bins_per_thread;
-            h->ntiles = (h->d.Nx + TG_THREADS * h->bpt - 1) / (TG_THREADS * h->bpt);
+            h->ntiles = (h->d.Nx + TG_THREADS * h->bpt * h->nsub - 1) / (TG_THREADS * h->bpt * h->nsub);
+            if (h->tile_order) { int r = build_tile_order(h); if (r) return r; }
         }
     }
-    if (chains_per_block > 0) h->chains_per_block = chains_per_block;
+    if (chains_per_block > 0) h->chains_per_block = std::min(chains_per_block, h->max_cpb);
     if (use_graph >= 0) h->use_graph = use_graph;
+    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+    return TG_OK;
+}
+
+extern "C" int tg_set_subtiles(tg_handle *h, int nsub)
+{
+    if (!h || nsub < 1 || nsub > 64) return fail(TG_E_BADARG, "tg_set_subtiles: bad argument");
+    h->nsub = nsub;
+    h->ntiles = (h->d.Nx + TG_THREADS * h->bpt * h->nsub - 1) / (TG_THREADS * h->bpt * h->nsub);
+    if (h->tile_order) { int r = build_tile_order(h); if (r) return r; }
     if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
     return TG_OK;
 }
@@ -228,7 +274,22 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     { int r = alloc_evalbuf(h, h->ev, C); if (r) return r; }
     h->bpt = 4;
     h->ntiles = (d.Nx + TG_THREADS * h->bpt - 1) / (TG_THREADS * h->bpt);
-    h->chains_per_block = std::min(C, 8);
+    // shared-memory lists of the fused kernel: one list of <= ncomp_max components per chain of a group
+    {
+        h->list_cap = std::max(4, (d.ncomp_max + 3) & ~3);
+        int maxdyn = 0; CK(cudaDeviceGetAttribute(&maxdyn, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+        const size_t budget = std::min<size_t>((size_t)maxdyn - 2048, 100 * 1024);       // <= 100 KB: two CTAs per SM stay resident
+        int m = TG_MAXG;
+        while (m > 1 && TG_EVAL_SMEM(m, h->list_cap) > budget) m--;
+        if (TG_EVAL_SMEM(m, h->list_cap) > (size_t)maxdyn - 2048) return fail(TG_E_BADARG, "too many Lorentzian components for the shared-memory list of the fused kernel");
+        h->max_cpb = m;
+        const size_t need = TG_EVAL_SMEM(m, h->list_cap);
+        CK(cudaFuncSetAttribute(tg_k_eval<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+        CK(cudaFuncSetAttribute(tg_k_eval<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+        CK(cudaFuncSetAttribute(tg_k_eval<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+        const int groups = (C + m - 1) / m;                                               // balanced chain groups of <= max_cpb
+        h->chains_per_block = (C + groups - 1) / groups;
+    }
 
     // ---- MALA configuration ----
     TgMala &m = h->m;
@@ -245,7 +306,8 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     DA(s.vars_cur, C * Nv); DA(s.vars_prop, C * Nv); DA(s.params_cur, C * Np);
     s.params_prop = h->sp.params;
     DA(s.logL_cur, C); DA(s.logPrior_cur, C); DA(s.logPost_cur, C); DA(s.Pmove, C); DA(s.moved, C);
-    DA(s.mu, C * Nv); DA(s.sigma, C); DA(s.cov, C * Nv * Nv); DA(s.chol, C * Nv * Nv); DA(s.chol_valid, C); DA(s.sticky_status, C);
+    DA(s.mu, 3 * C * Nv); DA(s.sigma, C); DA(s.cov, 3 * C * Nv * Nv); DA(s.chol, 3 * C * Nv * Nv); DA(s.live, C); DA(s.chol_fail, 3 * C); DA(s.sticky_status, C);
+    DA(h->stage_mu, C * Nv); DA(h->stage_cov, C * Nv * Nv);
     DA(s.ctrl, 1);
     s.index_to_relax = h->index_to_relax; s.Tcoefs = h->Tcoefs;
     {
@@ -261,21 +323,31 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         CK(cudaMemcpyAsync(s.params_cur, params.data(), params.size() * 8, cudaMemcpyHostToDevice, h->stream));
         CK(cudaMemcpyAsync(s.sigma, sigma.data(), sigma.size() * 8, cudaMemcpyHostToDevice, h->stream));
         CK(cudaMemcpyAsync(s.cov, cov.data(), cov.size() * 8, cudaMemcpyHostToDevice, h->stream));
-        CK(cudaMemsetAsync(s.chol_valid, 0, C * 4, h->stream));
+        CK(cudaMemsetAsync(s.live, 0, C * 4, h->stream));
+        CK(cudaMemsetAsync(s.chol_fail, 0, 3 * C * 4, h->stream));
         CK(cudaMemsetAsync(s.sticky_status, 0, C * 4, h->stream));
         CK(cudaMemsetAsync(s.ctrl, 0, sizeof(TgCtrl), h->stream));
         CK(cudaStreamSynchronize(h->stream));
     }
-    // propose kernel shared memory: Cholesky factor staged in smem when it fits
+    // shared memory: the speculative kernel stages the Nv x Nv matrix when it fits; the propose kernel only
+    // needs the prologue scratch
     {
         const size_t ld = (size_t)(d.Nv | 1);
-        const size_t need_mat = (size_t)d.Nv * ld * 8, need_pro = TG_PRO_SMEM(d.Np);
+        const size_t need_mat = ((size_t)d.Nv * ld + 4 * (size_t)d.Nv) * 8, need_pro = TG_PRO_SMEM(d.Np);
         int maxdyn = 0; CK(cudaDeviceGetAttribute(&maxdyn, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
-        const size_t budget = (size_t)maxdyn > 12 * 1024 ? (size_t)maxdyn - 12 * 1024 : 0;   // static smem of the kernel
+        const size_t budget = (size_t)maxdyn > 12 * 1024 ? (size_t)maxdyn - 12 * 1024 : 0;   // static smem of the kernels
         h->smem_matrix = (need_mat <= budget) ? 1 : 0;
-        h->propose_smem = std::max(h->smem_matrix ? need_mat : 0, need_pro);
-        CK(cudaFuncSetAttribute(tg_k_propose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->propose_smem));
-        if (need_pro > 48 * 1024) CK(cudaFuncSetAttribute(tg_k_prologue, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_pro));
+        h->spec_smem = h->smem_matrix ? need_mat : 4 * (size_t)d.Nv * 8;
+        h->propose_smem = need_pro;
+        CK(cudaFuncSetAttribute(tg_k_spec, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spec_smem));
+        if (need_pro > 48 * 1024) {
+            CK(cudaFuncSetAttribute(tg_k_propose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_pro));
+            CK(cudaFuncSetAttribute(tg_k_prologue, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_pro));
+        }
+        int lo = 0, hi = 0; CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CK(cudaStreamCreateWithPriority(&h->side, cudaStreamNonBlocking, hi));
+        CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     }
     // record ring
     {
@@ -290,9 +362,12 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     {
         int r = launch_eval_kernels(h, h->sp, s.params_cur, C, nullptr, true, true); if (r) return r;
         tg_k_install_current<<<(C + 127) / 128, 128, 0, h->stream>>>(h->d, h->s, h->sp.t, h->sp.sums);
+        TgSpecArgs sa{h->s, h->m, h->smem_matrix, 1};
+        tg_k_spec<<<dim3(C, 1), 256, h->spec_smem, h->stream>>>(sa);      // chol(Sigma + eps2 I) of the live slot
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(h->stream));
     }
+    if (!(p->flags & TG_F_NO_TILE_ORDER)) { int r = build_tile_order(h); if (r) return r; }
     return TG_OK;
 }
 
@@ -304,6 +379,9 @@ extern "C" int tg_destroy(tg_handle *h)
     if (h->graph) cudaGraphExecDestroy(h->graph);
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
+    if (h->side) { cudaStreamSynchronize(h->side); cudaStreamDestroy(h->side); }
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     for (void *q : h->allocs) cudaFree(q);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -384,7 +462,7 @@ extern "C" int tg_last_work(tg_handle *h, int B, double *L, int *K)
         std::vector<double> nz(TG_NOISE_STRIDE);
         CK(cudaMemcpy(nz.data(), h->ev.t.noise, TG_NOISE_STRIDE * 8, cudaMemcpyDeviceToHost));
         int k = 0;
-        for (int j = 0; j < (int)nz[TG_N_NH]; j++) if (nz[4 * j + 1] != 0.0) k++;
+        for (int j = 0; j < (int)nz[TG_N_NH]; j++) if (nz[TG_HS * j + TG_H_A] != 0.0) k++;
         *K = k;
     }
     return TG_OK;
@@ -401,9 +479,14 @@ extern "C" int tg_get_state(tg_handle *h, double *vars, double *mu, double *sigm
     CK(cudaStreamSynchronize(h->stream));
     const size_t C = h->s.C, Nv = h->s.Nv;
     if (vars) CK(cudaMemcpy(vars, h->s.vars_cur, C * Nv * 8, cudaMemcpyDeviceToHost));
-    if (mu) CK(cudaMemcpy(mu, h->s.mu, C * Nv * 8, cudaMemcpyDeviceToHost));
+    if (mu || covarmat) {
+        tg_k_gather_live<<<(unsigned)C, 256, 0, h->stream>>>(h->s, mu ? h->stage_mu : nullptr, covarmat ? h->stage_cov : nullptr);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    if (mu) CK(cudaMemcpy(mu, h->stage_mu, C * Nv * 8, cudaMemcpyDeviceToHost));
     if (sigma) CK(cudaMemcpy(sigma, h->s.sigma, C * 8, cudaMemcpyDeviceToHost));
-    if (covarmat) CK(cudaMemcpy(covarmat, h->s.cov, C * Nv * Nv * 8, cudaMemcpyDeviceToHost));
+    if (covarmat) CK(cudaMemcpy(covarmat, h->stage_cov, C * Nv * Nv * 8, cudaMemcpyDeviceToHost));
     if (logL) CK(cudaMemcpy(logL, h->s.logL_cur, C * 8, cudaMemcpyDeviceToHost));
     if (logPrior) CK(cudaMemcpy(logPrior, h->s.logPrior_cur, C * 8, cudaMemcpyDeviceToHost));
     if (logPost) CK(cudaMemcpy(logPost, h->s.logPost_cur, C * 8, cudaMemcpyDeviceToHost));
@@ -421,12 +504,19 @@ extern "C" int tg_set_state(tg_handle *h, const double *vars, const double *mu, 
     if (!h) return fail(TG_E_BADARG, "null handle");
     CK(cudaSetDevice(h->device));
     const size_t C = h->s.C, Nv = h->s.Nv;
-    if (mu) CK(cudaMemcpyAsync(h->s.mu, mu, C * Nv * 8, cudaMemcpyHostToDevice, h->stream));
-    if (sigma) CK(cudaMemcpyAsync(h->s.sigma, sigma, C * 8, cudaMemcpyHostToDevice, h->stream));
-    if (covarmat) {
-        CK(cudaMemcpyAsync(h->s.cov, covarmat, C * Nv * Nv * 8, cudaMemcpyHostToDevice, h->stream));
-        CK(cudaMemsetAsync(h->s.chol_valid, 0, C * 4, h->stream));
+    if (mu || covarmat) {
+        // bring the live (mu, Sigma) of every chain into slot 0 (contiguous [C][..] block), overwrite what was given
+        tg_k_gather_live<<<(unsigned)C, 256, 0, h->stream>>>(h->s, h->stage_mu, h->stage_cov);
+        CK(cudaMemcpyAsync(h->s.mu, h->stage_mu, C * Nv * 8, cudaMemcpyDeviceToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->s.cov, h->stage_cov, C * Nv * Nv * 8, cudaMemcpyDeviceToDevice, h->stream));
+        CK(cudaMemsetAsync(h->s.live, 0, C * 4, h->stream));
+        if (mu) CK(cudaMemcpyAsync(h->s.mu, mu, C * Nv * 8, cudaMemcpyHostToDevice, h->stream));
+        if (covarmat) CK(cudaMemcpyAsync(h->s.cov, covarmat, C * Nv * Nv * 8, cudaMemcpyHostToDevice, h->stream));
+        TgSpecArgs sa{h->s, h->m, h->smem_matrix, 1};
+        tg_k_spec<<<dim3((unsigned)C, 1), 256, h->spec_smem, h->stream>>>(sa);
+        CK(cudaGetLastError());
     }
+    if (sigma) CK(cudaMemcpyAsync(h->s.sigma, sigma, C * 8, cudaMemcpyHostToDevice, h->stream));
     if (vars) {
         CK(cudaMemcpyAsync(h->s.vars_cur, vars, C * Nv * 8, cudaMemcpyHostToDevice, h->stream));
         tg_k_scatter_vars<<<(unsigned)C, 128, 0, h->stream>>>(h->s);
@@ -445,12 +535,23 @@ static int launch_step(tg_handle *h, bool begin, bool end, int presummed)
 {
     const int C = h->s.C;
     if (begin) {
-        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}, h->smem_matrix};
+        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}};
         tg_k_propose<<<C, 256, h->propose_smem, h->stream>>>(pa);
         h->n_launch_total++;
+        if (h->m.n_learn > 0) {
+            // fork: both outcomes of the proposal adaptation (Robbins-Monro update + Cholesky) are prepared
+            // on the high-priority side stream while the fused model+likelihood kernel runs
+            CK(cudaEventRecord(h->ev_fork, h->stream));
+            CK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+            TgSpecArgs sa{h->s, h->m, h->smem_matrix, 0};
+            tg_k_spec<<<dim3(C, 2), 256, h->spec_smem, h->side>>>(sa);
+            CK(cudaEventRecord(h->ev_join, h->side));
+            h->n_launch_total++;
+        }
         int r = launch_eval_kernels(h, h->sp, h->sp.params, C, nullptr, false, presummed != 0); if (r) return r;
     }
     if (end) {
+        if (h->m.n_learn > 0) CK(cudaStreamWaitEvent(h->stream, h->ev_join, 0));
         TgFinishArgs fa{h->d, h->s, h->m, h->sp.t, h->sp.partials, h->ntiles, h->sp.sums, presummed, h->rec, 1};
         tg_k_finish<<<C, 256, 0, h->stream>>>(fa);
         h->n_launch_total++;
@@ -505,7 +606,7 @@ extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
                 cudaGraphDestroy(g);
             }
             if (h->graph) {
-                for (; k + G <= n; k += G) { CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += 3L * G; h->n_eval_launch += G; }
+                for (; k + G <= n; k += G) { CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += (h->m.n_learn > 0 ? 4L : 3L) * G; h->n_eval_launch += G; }
             }
         }
         for (; k < n; k++) { int r = launch_step(h, true, true, 0); if (r) return r; }

@@ -33,19 +33,26 @@ struct TgTables {
     double *ifc, *t2sq;        // [B][ncomp_max]  asymmetry extras: 1/fc, (0.5*Gamma*asym/fc)^2
     int    *lo, *hi;           // [B][ncomp_max]  window [lo,hi) in LOCAL bin indices
     int    *ncomp;             // [B]
-    double *noise;             // [B][TG_NOISE_STRIDE] : per Harvey (H, a=1e-3*tc, p, ln a), then N0, asym, gaussA, gaussNu, gaussS2, flags
+    double *noise;             // [B][TG_NOISE_STRIDE] : per ACTIVE Harvey term (H, a=1e-3*tc, p, ln a, a^p clamped, exponent class), then N0, asym, gaussA, gaussNu, gaussS2, flags
     int    *status;            // [B]  TG_ST_* bits
     double *work;              // [B]  L = sum (2l+1)*(hi-lo)
     double *logprior;          // [B]
 };
-#define TG_NOISE_STRIDE (4 * TG_MAXH + 8)
-#define TG_N_N0     (4 * TG_MAXH + 0)
-#define TG_N_ASYM   (4 * TG_MAXH + 1)
-#define TG_N_GA     (4 * TG_MAXH + 2)
-#define TG_N_GNU    (4 * TG_MAXH + 3)
-#define TG_N_GS2    (4 * TG_MAXH + 4)
-#define TG_N_NH     (4 * TG_MAXH + 5)   // number of Harvey slots (as double)
-#define TG_N_GAUSS  (4 * TG_MAXH + 6)   // 0 none, 1 gaussian term present
+#define TG_HS       6                    // doubles per Harvey term
+#define TG_H_H      0
+#define TG_H_A      1
+#define TG_H_P      2
+#define TG_H_LNA    3
+#define TG_H_AP     4                    // a^p for the integer classes (clamped), else a
+#define TG_H_CLS    5                    // exponent class: 0..4 exact small integer, -1 general
+#define TG_NOISE_STRIDE (TG_HS * TG_MAXH + 8)
+#define TG_N_N0     (TG_HS * TG_MAXH + 0)
+#define TG_N_ASYM   (TG_HS * TG_MAXH + 1)
+#define TG_N_GA     (TG_HS * TG_MAXH + 2)
+#define TG_N_GNU    (TG_HS * TG_MAXH + 3)
+#define TG_N_GS2    (TG_HS * TG_MAXH + 4)
+#define TG_N_NH     (TG_HS * TG_MAXH + 5)   // number of ACTIVE Harvey terms (as double)
+#define TG_N_GAUSS  (TG_HS * TG_MAXH + 6)   // 0 none, 1 gaussian term present
 
 // ---------------------------------------------------------------------------------------
 // device helpers
@@ -64,6 +71,46 @@ __device__ __forceinline__ double tg_rcp(double t)
     double r2 = fma(r1, e, r1);
     // inf*0 = NaN in the residual when t is 0/inf/denormal-flushed: keep the seed there
     return (r2 == r2) ? r2 : ((t == t) ? r : t);
+}
+
+// Fast reciprocal for arguments known to be finite, normal and >= ~1e-290 in magnitude (products
+// of 1+profile terms, products of positive model values): MUFU.RCP64H seed r (relative error
+// e <= ~2^-20) and ONE cubic correction r(1+e+e^2) -> truncation error e^3 <= 2^-60, i.e. <= 1 ulp
+// after rounding.  3 DFMA instead of the 4 of two Newton steps; no special-value handling
+// (inf/0 give NaN, which the likelihood turns into a rejected proposal).
+__device__ __forceinline__ double tg_rcp_fast(double t)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(t));
+    const double e = fma(-t, r, 1.0);
+    const double p = fma(e, e, e);
+    return fma(r, p, r);
+}
+
+// Harvey exponent class: 0..4 for exact small integers (plain products), -1 otherwise
+__device__ __forceinline__ int tg_pclass(double p)
+{
+    return (p == 0.0) ? 0 : (p == 1.0) ? 1 : (p == 2.0) ? 2 : (p == 3.0) ? 3 : (p == 4.0) ? 4 : -1;
+}
+// a^ip, clamped so that a^ip * xmax^ip <= 1e140 (keeps products of two Harvey denominators finite;
+// a clamped term contributes < 1e-140 H, the reference's own value there is smaller still)
+__device__ __forceinline__ double tg_apow(double a, int ip, double xmax)
+{
+    if (ip < 1) return a;
+    const double a2 = a * a, x2 = xmax * xmax;
+    const double ap = (ip == 1) ? a : (ip == 2) ? a2 : (ip == 3) ? a2 * a : a2 * a2;
+    const double xp = (ip == 1) ? xmax : (ip == 2) ? x2 : (ip == 3) ? x2 * xmax : x2 * x2;
+    const double lim = 1e140 / fabs(xp);
+    return (ap > lim) ? lim : ap;
+}
+
+// one active Harvey term of the noise table: y += H/(1+(a x)^p), a = 1e-3*tc (noise_models.cpp:32)
+__device__ __forceinline__ void tg_set_harvey(double *nz, int slot, double H, double a, double p, double xmax)
+{
+    double *q = nz + TG_HS * slot;
+    const int cls = tg_pclass(p);
+    q[TG_H_H] = H; q[TG_H_A] = a; q[TG_H_P] = p; q[TG_H_LNA] = log(a);
+    q[TG_H_AP] = tg_apow(a, cls, xmax); q[TG_H_CLS] = (double)cls;
 }
 
 // Philox4x32-10 (Salmon et al. 2011), counter-based: no shared RNG state between chains

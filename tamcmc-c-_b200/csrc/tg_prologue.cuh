@@ -237,7 +237,12 @@ __device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff
         atomicOr(&S.status, st);
     }
     const double g2 = W * W;                 // pow(gamma_l,2)
-    const double q = 4.0 / g2;               // 4*profile/g2 -> profile*(4/g2): <= 1 ulp from the reference
+    double q = 4.0 / g2;                     // 4*profile/g2 -> profile*(4/g2): <= 1 ulp from the reference
+    {   // keep 1+q*d^2 <= ~1e70 so that the product of four such terms stays finite (Gamma < ~1e-31 only)
+        const double range = d.x_last - d.x_first;
+        const double qmax = 1e70 / (range * range);
+        if (q > qmax) q = qmax;
+    }
     const double ifc = 1.0 / fc;
     const double t2 = 0.5 * W * S.asym / fc;
     const size_t base = (size_t)b * d.ncomp_max + coff;
@@ -294,8 +299,10 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                 nz[TG_N_NH] = 0; nz[TG_N_GAUSS] = 1;
             } else {                 // model_Harvey_Gaussian, :1968-1992 : noise = |params[3..6]|, Nharvey=1
                 nz[TG_N_GA] = fabs(p[0]); nz[TG_N_GNU] = p[2]; nz[TG_N_GS2] = fabs(p[1]) * fabs(p[1]);
-                nz[0] = fabs(p[3]); nz[1] = 1e-3 * fabs(p[4]); nz[2] = fabs(p[5]); nz[3] = log(nz[1]); nz[TG_N_N0] = fabs(p[6]);
-                nz[TG_N_NH] = 1; nz[TG_N_GAUSS] = 1;
+                nz[TG_N_N0] = fabs(p[6]); nz[TG_N_NH] = 0; nz[TG_N_GAUSS] = 1;
+                if (fabs(p[4]) != 0.0) {   // harvey_like skips a term iff tc == 0 (noise_models.cpp:31, Q5)
+                    tg_set_harvey(nz, 0, fabs(p[3]), 1e-3 * fabs(p[4]), fabs(p[5]), d.x_last); nz[TG_N_NH] = 1;
+                }
             }
         } else {
             S.trunc_c = p[iI + Ninc];
@@ -329,14 +336,14 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
             // noise: |noise_params| ; Nharvey=(Nnoise-1)/3 (global) or 0 (local)
             const int nH = (fam == 1) ? (Nnoise - 1) / 3 : 0;
             if (nH > TG_MAXH) S.status |= TG_ST_MODE_OVERFLOW;
+            int na = 0;                    // only the ACTIVE terms (tc != 0, noise_models.cpp:31) are listed, in order
             for (int k = 0; k < nH && k < TG_MAXH; k++) {
-                nz[4 * k + 0] = fabs(p[iN + 3 * k]);
-                nz[4 * k + 1] = 1e-3 * fabs(p[iN + 3 * k + 1]);
-                nz[4 * k + 2] = fabs(p[iN + 3 * k + 2]);
-                nz[4 * k + 3] = log(nz[4 * k + 1]);
+                if (fabs(p[iN + 3 * k + 1]) == 0.0) continue;
+                tg_set_harvey(nz, na, fabs(p[iN + 3 * k]), 1e-3 * fabs(p[iN + 3 * k + 1]), fabs(p[iN + 3 * k + 2]), d.x_last);
+                na++;
             }
             nz[TG_N_N0] = fabs(p[iN + Nnoise - 1]);
-            nz[TG_N_NH] = nH < TG_MAXH ? nH : TG_MAXH;
+            nz[TG_N_NH] = na;
             nz[TG_N_ASYM] = S.asym;
             nz[TG_N_GAUSS] = 0;
             if (fam == 2) {

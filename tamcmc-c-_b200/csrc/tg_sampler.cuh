@@ -40,8 +40,14 @@ struct TgState {
     double *params_cur, *params_prop;      // [C][Np]
     double *logL_cur, *logPrior_cur, *logPost_cur, *Pmove;   // [C]
     int    *moved;                         // [C]
-    double *mu, *sigma, *cov, *chol;       // [C][Nv], [C], [C][Nv][Nv] x2 (row-major)
-    int    *chol_valid;                    // [C]
+    // Adaptive proposal.  (mu, Sigma, chol(Sigma+eps2 I)) live in THREE slots per chain: the live one
+    // and the two candidates of the running step ("proposal rejected" / "proposal accepted"), which the
+    // speculative kernel fills while the fused model+likelihood kernel runs; the finish kernel only
+    // switches live[c].  Slot-major: mu [3][C][Nv], cov / chol [3][C][Nv][Nv] (row-major, lower part of chol).
+    double *mu, *cov, *chol;
+    double *sigma;                         // [C]
+    int    *live;                          // [C]  live slot 0..2
+    int    *chol_fail;                     // [3][C]
     int    *sticky_status;                 // [C]
     const int    *index_to_relax;          // [Nv]
     const double *Tcoefs;                  // [C]
@@ -66,44 +72,151 @@ __device__ __forceinline__ void tg_normal_pair(uint4 r, double *z0, double *z1)
     *z0 = rad * c; *z1 = rad * s;
 }
 
-// In-CTA Cholesky (lower, right-looking) of the n x n matrix S (leading dimension ld), in place.
-// Returns (to every thread) 0 on success, 1 if a pivot was not positive.
-__device__ int tg_cholesky_inplace(double *S, int n, int ld)
+__device__ __forceinline__ size_t tg_slot_vec(const TgState &s, int slot, int c) { return ((size_t)slot * s.C + c) * s.Nv; }
+__device__ __forceinline__ size_t tg_slot_mat(const TgState &s, int slot, int c) { return ((size_t)slot * s.C + c) * s.Nv * s.Nv; }
+
+// learning zone of iteration it?  (MALA.cpp:641-652)
+__device__ __forceinline__ int tg_learning(const TgMala &m, long it)
 {
-    __shared__ int fail;
-    const int tid = threadIdx.x, nt = blockDim.x;
-    if (tid == 0) fail = 0;
+    int learn = 0, which = 0;
+    for (int l = 0; l < m.n_learn; l++) if (it >= m.Nt_learn[l] && it < m.Nt_learn[l + 1]) { learn = 1; which = l; }
+    if (learn && (it % m.periods[which]) != 0) learn = 0;
+    return learn;
+}
+
+// In-CTA Cholesky (lower, right-looking) of the n x n matrix S (leading dimension ld; shared or global
+// memory), 256 threads as a 16x16 grid, ONE barrier per column: while the rank-1 update of column j runs,
+// every thread recomputes the next pivot from the double-buffered diagonal, so the freshly updated
+// entries of column j+1 are scaled in the same pass.  On exit the strictly lower part and the diagonal of
+// S hold L.  work: 4*n doubles (two column buffers, two diagonal buffers).  Returns 1 if a pivot was <= 0 / NaN.
+__device__ int tg_cholesky_inplace(double *S, int n, int ld, double *work)
+{
+    __shared__ int s_fail;
+    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+    double *col0 = work, *dg0 = work + 2 * n;     // column buffers col0 + (j&1)*n, diagonal buffers dg0 + (j&1)*n
+    if (tid == 0) s_fail = 0;
+    for (int i = tid; i < n; i += blockDim.x) dg0[i] = S[i * ld + i];
     __syncthreads();
-    for (int j = 0; j < n; j++) {
-        const double djj = S[j * ld + j];
-        __syncthreads();                           // everyone has read the pivot before it is overwritten
-        const double dj = sqrt(djj);
-        if (tid == 0) { if (!(djj > 0.0)) fail = 1; S[j * ld + j] = dj; }
-        for (int i = j + 1 + tid; i < n; i += nt) S[i * ld + j] = S[i * ld + j] / dj;
-        __syncthreads();
-        const int r = n - j - 1;                   // trailing block is r x r, lower part only
-        for (int e = tid; e < r * r; e += nt) {
-            const int ii = e / r, kk = e - ii * r;
-            if (kk <= ii) {
-                const int i = j + 1 + ii, k = j + 1 + kk;
-                S[i * ld + k] = fma(-S[i * ld + j], S[k * ld + j], S[i * ld + k]);
+    {   // column 0
+        const double pv = dg0[0];
+        const double inv = rsqrt(pv);
+        if (tid == 0) { if (!(pv > 0.0)) s_fail = 1; S[0] = pv * inv; }
+        for (int i = 1 + tid; i < n; i += blockDim.x) { const double v = S[i * ld] * inv; S[i * ld] = v; col0[i] = v; }
+    }
+    __syncthreads();
+    for (int j = 0; j + 1 < n; j++) {
+        const double *cj = col0 + (j & 1) * n; double *cn = col0 + ((j + 1) & 1) * n;
+        const double *dj = dg0 + (j & 1) * n;  double *dn = dg0 + ((j + 1) & 1) * n;
+        // next pivot, recomputed by every thread with the same arithmetic as the diagonal update below
+        const double cnext = cj[j + 1];
+        const double pv = fma(-cnext, cnext, dj[j + 1]);
+        const double inv = rsqrt(pv);
+        if (tid == 0) { if (!(pv > 0.0)) s_fail = 1; S[(j + 1) * ld + (j + 1)] = pv * inv; }
+        for (int t = j + 1 + tid; t < n; t += blockDim.x) { const double c = cj[t]; dn[t] = fma(-c, c, dj[t]); }
+        // strictly-lower trailing update; column j+1 is scaled on the fly
+        const int r = n - j - 1;
+        for (int ii = ty; ii < r; ii += 16) {
+            const int i = j + 1 + ii;
+            const double ci = cj[i];
+            double *row = S + (size_t)i * ld + (j + 1);
+            for (int kk = tx; kk < ii; kk += 16) {
+                double v = fma(-ci, cj[j + 1 + kk], row[kk]);
+                if (kk == 0) { v *= inv; cn[i] = v; }
+                row[kk] = v;
             }
         }
         __syncthreads();
     }
-    return fail;
+    return s_fail;
+}
+
+// One Cholesky job: L = chol(cov + eps2*I) of (slot, chain) -> chol[slot][c]; staged in shared memory
+// when it fits (dyn = shared-memory buffer of Nv*ld + 4*Nv doubles, or NULL: factorise in place in HBM).
+__device__ void tg_factor_slot(const TgState &s, double eps2, int slot, int c, double *dyn, double *work)
+{
+    const int Nv = s.Nv, tid = threadIdx.x, nt = blockDim.x;
+    const double *cv = s.cov + tg_slot_mat(s, slot, c);
+    double *Lg = s.chol + tg_slot_mat(s, slot, c);
+    const int ld = dyn ? (Nv | 1) : Nv;
+    double *L = dyn ? dyn : Lg;
+    for (int e = tid; e < Nv * Nv; e += nt) {
+        const int i = e / Nv, k = e - i * Nv;
+        if (k <= i) L[i * ld + k] = cv[e] + ((i == k) ? eps2 : 0.0);
+    }
+    __syncthreads();
+    const int fail = tg_cholesky_inplace(L, Nv, ld, work);
+    if (dyn) for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; if (k <= i) Lg[e] = L[i * ld + k]; }
+    if (tid == 0) s.chol_fail[slot * s.C + c] = fail;
+}
+
+struct TgSpecArgs {
+    TgState s;
+    TgMala  m;
+    int     smem_matrix;    // 1: the Nv x Nv matrix is staged in shared memory
+    int     init;           // 1: factorise the LIVE slot of every chain (create / restore); 0: speculative step
+};
+
+// K_spec: grid (C, 2).  blockIdx.y = 0: "proposal rejected" candidate (x = vars_cur), 1: "accepted"
+// (x = vars_prop).  Robbins-Monro update of (mu, Sigma) with the p3/p2 truncations (MALA.cpp:292-315,
+// :135-176) from the live slot into candidate slot (live+1+cand)%3, then its Cholesky factor.  Runs on a
+// second stream next to the fused model+likelihood kernel of the same step; the finish kernel selects
+// the candidate that matches the Metropolis decision.  The acceptance only enters sigma (a scalar,
+// applied as sqrt(sigma) at proposal time), so both candidates are exact.
+__global__ void __launch_bounds__(256) tg_k_spec(TgSpecArgs a)
+{
+    extern __shared__ double tg_dyn_smem[];
+    __shared__ double r1[256];
+    __shared__ double s_scale;
+    const TgState &s = a.s;
+    const int c = blockIdx.x, cand = blockIdx.y, tid = threadIdx.x, nt = blockDim.x;
+    const int Nv = s.Nv;
+    double *dyn = a.smem_matrix ? tg_dyn_smem : nullptr;
+    double *work = a.smem_matrix ? tg_dyn_smem + (size_t)Nv * (Nv | 1) : tg_dyn_smem;
+    const int live = s.live[c];
+    if (a.init) { if (cand == 0) tg_factor_slot(s, a.m.eps2, live, c, dyn, work); return; }
+    const long it = s.ctrl->i;
+    if (!tg_learning(a.m, it)) return;
+    const int slot = (live + 1 + cand) % 3;
+    const double gamma = a.m.c0 / (1.0 + (double)it);
+    const double *xv = (cand ? s.vars_prop : s.vars_cur) + (size_t)c * Nv;
+    const double *mu0 = s.mu + tg_slot_vec(s, live, c), *cov0 = s.cov + tg_slot_mat(s, live, c);
+    double *mu = s.mu + tg_slot_vec(s, slot, c), *cov = s.cov + tg_slot_mat(s, slot, c);
+    // mu <- p3(mu + gamma (x - mu))
+    double part = 0;
+    for (int v = tid; v < Nv; v += nt) { const double m = mu0[v] + gamma * (xv[v] - mu0[v]); mu[v] = m; part += m * m; }
+    r1[tid] = part; __syncthreads();
+    for (int h = 128; h > 0; h >>= 1) { if (tid < h) r1[tid] += r1[tid + h]; __syncthreads(); }
+    if (tid == 0) { const double nrm = sqrt(r1[0]); s_scale = (nrm <= a.m.A1) ? 1.0 : a.m.A1 / nrm; }
+    __syncthreads();
+    if (s_scale != 1.0) for (int v = tid; v < Nv; v += nt) mu[v] = mu[v] * s_scale;
+    __syncthreads();
+    // Sigma <- p2(Sigma + gamma ((x-mu)(x-mu)^T - Sigma))
+    part = 0;
+    for (int e = tid; e < Nv * Nv; e += nt) {
+        const int i = e / Nv, k = e - i * Nv;
+        const double mat = (xv[i] - mu[i]) * (xv[k] - mu[k]);
+        const double cn = cov0[e] + gamma * (mat - cov0[e]);
+        cov[e] = cn; part += cn * cn;
+    }
+    __syncthreads();
+    r1[tid] = part; __syncthreads();
+    for (int h = 128; h > 0; h >>= 1) { if (tid < h) r1[tid] += r1[tid + h]; __syncthreads(); }
+    if (tid == 0) { const double nrm = sqrt(r1[0]); s_scale = (nrm <= a.m.A1) ? 1.0 : a.m.A1 / nrm; }
+    __syncthreads();
+    if (s_scale != 1.0) for (int e = tid; e < Nv * Nv; e += nt) cov[e] = cov[e] * s_scale;
+    __syncthreads();
+    tg_factor_slot(s, a.m.eps2, slot, c, dyn, work);
 }
 
 struct TgProposeArgs {
     TgState   s;
     TgMala    m;
     TgProArgs pro;          // pro.params == s.params_prop
-    int       smem_matrix;  // 1: the Nv x Nv factor is staged in shared memory
 };
 
-// K1: one CTA per chain.  (Re)factorise Sigma+eps2*I when the covariance changed, draw z, form
-// x' = x + sqrt(sigma)*L z (== chol((Sigma+eps2 I)*sigma) z up to rounding), scatter into params,
-// then run the model prologue + log-prior on the proposed parameter vector.
+// K1: one CTA per chain.  Draw z, form x' = x + sqrt(sigma)*L z with L = chol(Sigma+eps2 I) of the live
+// slot (== chol((Sigma+eps2 I)*sigma) z, MALA.cpp:335-353, up to rounding), scatter into params, then run
+// the model prologue + log-prior on the proposed parameter vector.
 __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
 {
     extern __shared__ double tg_dyn_smem[];
@@ -112,23 +225,7 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
     const int c = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
     const long it = s.ctrl->i;
-    double *Lg = s.chol + (size_t)c * Nv * Nv;
-    const int ld = a.smem_matrix ? (Nv | 1) : Nv;
-    double *L = a.smem_matrix ? tg_dyn_smem : Lg;
-
-    if (!s.chol_valid[c]) {
-        const double *cv = s.cov + (size_t)c * Nv * Nv;
-        for (int e = tid; e < Nv * Nv; e += nt) {
-            const int i = e / Nv, k = e - i * Nv;
-            L[i * ld + k] = cv[e] + ((i == k) ? a.m.eps2 : 0.0);
-        }
-        __syncthreads();
-        const int fail = tg_cholesky_inplace(L, Nv, ld);
-        if (a.smem_matrix) for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; Lg[e] = (k <= i) ? L[i * ld + k] : 0.0; }
-        if (tid == 0) { s.chol_valid[c] = 1; if (fail) s.sticky_status[c] |= TG_ST_CHOL_FAIL; else s.sticky_status[c] &= ~TG_ST_CHOL_FAIL; }
-    } else if (a.smem_matrix) {
-        for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; L[i * ld + k] = Lg[e]; }
-    }
+    const double *L = s.chol + tg_slot_mat(s, s.live[c], c);
     // standard normals, Nv <= 512 per pass
     const double sq = sqrt(s.sigma[c]);
     const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PROP, (uint32_t)(a.m.seed >> 32));
@@ -140,12 +237,14 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
             s_z[v - v0] = (v & 1) ? z1 : z0;
         }
         __syncthreads();
-        // partial products of rows with this block of z (lower triangle => k <= i)
-        for (int i = tid; i < Nv; i += nt) {
+        // partial products of rows with this block of z (lower triangle => k <= i): one warp per row,
+        // lanes stride the row (coalesced), fixed shuffle tree
+        for (int i = (tid >> 5); i < Nv; i += (nt >> 5)) {
             double acc = 0.0;
             const int kend = min(i, v0 + 511);
-            for (int k = v0; k <= kend; k++) acc = fma(L[i * ld + k], s_z[k - v0], acc);
-            if (i >= v0) {
+            for (int k = v0 + (tid & 31); k <= kend; k += 32) acc = fma(L[(size_t)i * Nv + k], s_z[k - v0], acc);
+            acc = tg_warp_sum(acc);
+            if ((tid & 31) == 0 && i >= v0) {
                 const double prev = (v0 == 0) ? s.vars_cur[(size_t)c * Nv + i] : s.vars_prop[(size_t)c * Nv + i];
                 s.vars_prop[(size_t)c * Nv + i] = prev + sq * acc;
             }
@@ -191,7 +290,7 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
 {
     __shared__ double r1[256], r2[256];
     __shared__ int s_accept, s_last, s_learn;
-    __shared__ double s_r, s_scale;
+    __shared__ double s_r;
     const TgState &s = a.s;
     const int c = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
@@ -229,11 +328,7 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
         s.moved[c] = acc; s.Pmove[c] = r;
         s_accept = acc; s_r = r;
         if (a.record && slot >= 0 && slot < a.rec.cap) a.rec.status[(size_t)slot * s.C + c] = st;
-        // learning zone? (MALA.cpp:641-652)
-        int learn = 0, which = 0;
-        for (int l = 0; l < a.m.n_learn; l++) if (it >= a.m.Nt_learn[l] && it < a.m.Nt_learn[l + 1]) { learn = 1; which = l; }
-        if (learn && (it % a.m.periods[which]) != 0) learn = 0;
-        s_learn = learn;
+        s_learn = tg_learning(a.m, it);
     }
     __syncthreads();
     if (s_accept) {
@@ -241,38 +336,17 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
         for (int i = tid; i < Np; i += nt) s.params_cur[(size_t)c * Np + i] = s.params_prop[(size_t)c * Np + i];
     }
     __syncthreads();
-    // 3. Robbins-Monro update of (mu, Sigma, sigma) with the p3/p2/p1 truncations (MALA.cpp:292-315)
-    if (s_learn) {
+    // 3. Robbins-Monro update (MALA.cpp:292-315): (mu, Sigma, chol) were prepared for both outcomes by
+    //    tg_k_spec; select the candidate slot of this outcome and update sigma with the p1 truncation.
+    if (s_learn && tid == 0) {
         const double gamma = a.m.c0 / (1.0 + (double)it);
-        double *mu = s.mu + (size_t)c * Nv, *cov = s.cov + (size_t)c * Nv * Nv;
-        const double *xv = s.vars_cur + (size_t)c * Nv;
-        double part = 0;
-        for (int v = tid; v < Nv; v += nt) { const double m = mu[v] + gamma * (xv[v] - mu[v]); mu[v] = m; part += m * m; }
-        r1[tid] = part; __syncthreads();
-        for (int h = 128; h > 0; h >>= 1) { if (tid < h) r1[tid] += r1[tid + h]; __syncthreads(); }
-        if (tid == 0) { const double nrm = sqrt(r1[0]); s_scale = (nrm <= a.m.A1) ? 1.0 : a.m.A1 / nrm; }
-        __syncthreads();
-        if (s_scale != 1.0) for (int v = tid; v < Nv; v += nt) mu[v] = mu[v] * s_scale;
-        __syncthreads();
-        part = 0;
-        for (int e = tid; e < Nv * Nv; e += nt) {
-            const int i = e / Nv, k = e - i * Nv;
-            const double mat = (xv[i] - mu[i]) * (xv[k] - mu[k]);
-            const double cn = cov[e] + gamma * (mat - cov[e]);
-            cov[e] = cn; part += cn * cn;
-        }
-        r1[tid] = part; __syncthreads();
-        for (int h = 128; h > 0; h >>= 1) { if (tid < h) r1[tid] += r1[tid + h]; __syncthreads(); }
-        if (tid == 0) { const double nrm = sqrt(r1[0]); s_scale = (nrm <= a.m.A1) ? 1.0 : a.m.A1 / nrm; }
-        __syncthreads();
-        if (s_scale != 1.0) for (int e = tid; e < Nv * Nv; e += nt) cov[e] = cov[e] * s_scale;
-        if (tid == 0) {
-            double sg = s.sigma[c] + gamma * (s_r - a.m.target);
-            if (sg < a.m.eps1) sg = a.m.eps1;
-            if (sg > a.m.A1) sg = a.m.A1;
-            s.sigma[c] = sg;
-            s.chol_valid[c] = 0;
-        }
+        const int nl = (s.live[c] + 1 + s_accept) % 3;
+        s.live[c] = nl;
+        if (s.chol_fail[nl * s.C + c]) s.sticky_status[c] |= TG_ST_CHOL_FAIL; else s.sticky_status[c] &= ~TG_ST_CHOL_FAIL;
+        double sg = s.sigma[c] + gamma * (s_r - a.m.target);
+        if (sg < a.m.eps1) sg = a.m.eps1;
+        if (sg > a.m.A1) sg = a.m.A1;
+        s.sigma[c] = sg;
     }
     if (a.record) tg_write_record(a, slot, c, -1, tid, nt);
 
@@ -333,6 +407,15 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     }
     __syncthreads();
     if (tid == 0) { s.ctrl->ticket = 0u; s.ctrl->i = it + 1; }
+}
+
+// Live (mu, Sigma) of every chain -> contiguous [C][Nv], [C][Nv][Nv] (restore files / tg_get_state)
+__global__ void tg_k_gather_live(TgState s, double *mu_out, double *cov_out)
+{
+    const int c = blockIdx.x, live = s.live[c];
+    const size_t nv = s.Nv, nn = nv * nv;
+    if (mu_out) for (size_t e = threadIdx.x; e < nv; e += blockDim.x) mu_out[c * nv + e] = s.mu[tg_slot_vec(s, live, c) + e];
+    if (cov_out) for (size_t e = threadIdx.x; e < nn; e += blockDim.x) cov_out[c * nn + e] = s.cov[tg_slot_mat(s, live, c) + e];
 }
 
 // Installs the evaluation of params_cur as the current state (Model_def ctor, model_def.cpp:139-143)
