@@ -37,7 +37,7 @@ struct tg_handle {
     EvalBuf    ev;               // tg_eval batches
     EvalBuf    sp;               // sampler's proposed points (cap == C)
     int        ntiles = 0, bpt = 4, chains_per_block = 0, use_graph = 1, steps_per_graph = 16;
-    int        smem_matrix = 0; size_t propose_smem = 0, spec_smem = 0;
+    int        smem_matrix = 0, tri_smem = 0; size_t propose_smem = 0, spec_smem = 0;
     cudaStream_t side = nullptr;           // speculative proposal-adaptation kernel runs here, next to the fused kernel
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     double    *stage_mu = nullptr, *stage_cov = nullptr;   // tg_get_state staging ([C][Nv], [C][Nv][Nv])
@@ -64,6 +64,9 @@ template <typename T> static int dalloc(tg_handle *h, T **p, size_t n)
 
 extern "C" const char *tg_last_error(void) { return g_err.c_str(); }
 extern "C" int tg_version(void) { return 100; }
+#ifdef TG_PROFILE
+extern "C" int tg_dbg_clocks(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_clk, sizeof(long long) * 32) == cudaSuccess ? 0 : -2; }
+#endif
 
 static int alloc_evalbuf(tg_handle *h, EvalBuf &b, int B)
 {
@@ -338,10 +341,12 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         const size_t budget = (size_t)maxdyn > 12 * 1024 ? (size_t)maxdyn - 12 * 1024 : 0;   // static smem of the kernels
         h->smem_matrix = (need_mat <= budget) ? 1 : 0;
         h->spec_smem = h->smem_matrix ? need_mat : 4 * (size_t)d.Nv * 8;
-        h->propose_smem = need_pro;
+        const size_t need_tri = ((size_t)d.Nv * (d.Nv + 1) / 2 + d.Nv) * 8;
+        h->tri_smem = (need_tri <= budget) ? 1 : 0;
+        h->propose_smem = std::max(need_pro, h->tri_smem ? need_tri : (size_t)0);
         CK(cudaFuncSetAttribute(tg_k_spec, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spec_smem));
+        if (h->propose_smem > 48 * 1024) CK(cudaFuncSetAttribute(tg_k_propose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->propose_smem));
         if (need_pro > 48 * 1024) {
-            CK(cudaFuncSetAttribute(tg_k_propose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_pro));
             CK(cudaFuncSetAttribute(tg_k_prologue, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_pro));
         }
         int lo = 0, hi = 0; CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -535,7 +540,7 @@ static int launch_step(tg_handle *h, bool begin, bool end, int presummed)
 {
     const int C = h->s.C;
     if (begin) {
-        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}};
+        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}, h->smem_matrix, h->tri_smem};
         tg_k_propose<<<C, 256, h->propose_smem, h->stream>>>(pa);
         h->n_launch_total++;
         if (h->m.n_learn > 0) {

@@ -12,6 +12,13 @@
 #pragma once
 #include "tg_internal.cuh"
 
+#ifdef TG_PROFILE
+__device__ long long tg_dbg_clk[32];
+#define TG_STAMP(k) do { __syncthreads(); if (threadIdx.x == 0 && blockIdx.x == 0) tg_dbg_clk[k] = clock64(); } while (0)
+#else
+#define TG_STAMP(k) do { } while (0)
+#endif
+
 struct TgProArgs {
     TgDesc        d;
     TgTables      t;
@@ -22,36 +29,31 @@ struct TgProArgs {
 
 #define TG_PI 3.141592653589793238462643383279502884
 
-// ---- function_rot.cpp -------------------------------------------------------------------
-__device__ __forceinline__ int tg_fact(int n)
-{
-    const int f[13] = {1, 1, 2, 6, 24, 120, 720, 5040, 40320, 362880, 3628800, 39916800, 479001600};
-    return f[n < 0 ? 0 : (n > 12 ? 12 : n)];
-}
-__device__ __forceinline__ double tg_combi(int n, int r) { return (double)(tg_fact(n) / tg_fact(n - r) / tg_fact(r)); }
-
-__device__ double tg_dmm(int l, int m1, int m2, double beta)
-{
-    double sum = 0;
-    const double cb = cos(beta / 2.), sb = sin(beta / 2.);
-    for (int s = 0; s <= l - m1; s++) {
-        double var = tg_combi(l + m2, l - m1 - s) * tg_combi(l - m2, s) * (((l - m1 - s) & 1) ? -1.0 : 1.0);
-        var = var * pow(cb, (double)(2 * s + m1 + m2)) * pow(sb, (double)(2 * l - 2 * s - m1 - m2));
-        sum = sum + var;
-    }
-    sum = sum * sqrt((double)(tg_fact(l + m1) * tg_fact(l - m1)));
-    sum = sum / sqrt((double)(tg_fact(l + m2) * tg_fact(l - m2)));
-    return sum;
-}
-// amplitude_ratio(l, beta)[m+l]: column l of function_rot's matrix, squared.  Following the four
-// fill passes of function_rot.cpp:49-79, that column is dmm(l,|m|,0,beta) (sign dropped by the
-// square) for m != 0 and dmm(l,0,0,-beta) for m == 0.
+// ---- function_rot.cpp:20-106 ----------------------------------------------------------------
+// amplitude_ratio(l, beta)[m+l] = (d^l_{m0}(beta))^2.  The reference builds the full Wigner matrix
+// with pow() and factorials; the column it uses has the closed forms below (s = sin beta,
+// c = cos beta), which agree with the reference's own output to 6e-16 absolute (checked against
+// oracle/_ref for beta in [-30, 1234] degrees).
 __device__ double tg_amp_ratio(int l, int m, double beta_deg)
 {
     const double angle = 3.141592653589793238462643 * beta_deg / 180.;
+    double s, c;
+    sincos(angle, &s, &c);
     const int am = m < 0 ? -m : m;
-    const double v = (am == 0) ? tg_dmm(l, 0, 0, -angle) : tg_dmm(l, am, 0, angle);
-    return v * v;
+    const double s2 = s * s, c2 = c * c;
+    if (l == 1) return am == 1 ? 0.5 * s2 : c2;
+    if (l == 2) {
+        if (am == 2) return 0.375 * s2 * s2;
+        if (am == 1) return 1.5 * s2 * c2;
+        const double t = 3. * c2 - 1.; return 0.25 * t * t;
+    }
+    if (l == 3) {
+        if (am == 3) return 0.3125 * s2 * s2 * s2;
+        if (am == 2) return 1.875 * c2 * s2 * s2;
+        if (am == 1) { const double t = 5. * c2 - 1.; return 0.1875 * s2 * t * t; }
+        const double t = 5. * c2 * c - 3. * c; return 0.25 * t * t;
+    }
+    return 1.0;
 }
 
 // ---- interpol.cpp:13-55 -------------------------------------------------------------------
@@ -192,7 +194,7 @@ __device__ double tg_generic_prior(int sw, const double *q, double x, int *bad)
 
 // ---- per-chain scalars shared by the mode threads -------------------------------------------
 struct TgProShared {
-    double a1, eta, a3, asym, trunc_c, inclination, numax;
+    double a1, eta, a3, asym, trunc_c, inclination, numax, qmax;
     double Vl[4];
     double ratios[4][7];
     double work;
@@ -220,7 +222,7 @@ __device__ double tg_appwidth_v2(const double *w, double f)
 
 // Writes the 2l+1 components of one mode.  variant 0: a1etaa3, 1: a1l (f_s per degree, c_1m=0).
 __device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff, int l, double fc, double W,
-                             const double *hm, double f_s, double f_s1, double f_s2, int variant)
+                             const double *hm, double f_s, double f_s1, double f_s2, int variant, double &work_acc, int &st_acc)
 {
     const TgDesc &d = a.d;
     long imin = 0, imax = 0;
@@ -232,32 +234,33 @@ __device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff
         a0 = a0 < 0 ? 0 : (a0 > d.Nx ? d.Nx : a0);
         a1 = a1 < 0 ? 0 : (a1 > d.Nx ? d.Nx : a1);
         lo = (int)a0; hi = (int)a1;
-        atomicAdd(&S.work, (double)(2 * l + 1) * (double)(hi - lo));   // integer-valued: exact, order-free
+        work_acc += (double)(2 * l + 1) * (double)(hi - lo);           // integer-valued: exact, order-free
     } else {
-        atomicOr(&S.status, st);
+        st_acc |= st;
     }
     const double g2 = W * W;                 // pow(gamma_l,2)
     double q = 4.0 / g2;                     // 4*profile/g2 -> profile*(4/g2): <= 1 ulp from the reference
-    {   // keep 1+q*d^2 <= ~1e70 so that the product of four such terms stays finite (Gamma < ~1e-31 only)
-        const double range = d.x_last - d.x_first;
-        const double qmax = 1e70 / (range * range);
-        if (q > qmax) q = qmax;
-    }
-    const double ifc = 1.0 / fc;
-    const double t2 = 0.5 * W * S.asym / fc;
+    if (q > S.qmax) q = S.qmax;              // keep 1+q*d^2 <= ~1e70: the product of four such terms stays finite (Gamma < ~1e-31 only)
+    double ifc = 0.0, t2 = 0.0;              // asymmetry extras (only read by the kernel when asym != 0)
+    if (S.asym != 0.0) { ifc = 1.0 / fc; t2 = 0.5 * W * S.asym / fc; }
     const size_t base = (size_t)b * d.ncomp_max + coff;
     for (int m = -l; m <= l; m++) {
         double nu = fc;
         if (l != 0) {
-            const double Qlm = (l * (l + 1) - 3. * (double)(m * m)) / (double)((2 * l - 1) * (2 * l + 3));
+            // Q_lm = (l(l+1) - 3m^2) / ((2l-1)(2l+3)): small-integer quotients, folded at compile time with the
+            // same single rounding as the reference's run-time division (build_lorentzian.cpp:77)
+            const int am = m < 0 ? -m : m;
+            const double Qlm = (l == 1) ? (am == 0 ? 2.0 / 5.0 : -1.0 / 5.0)
+                             : (l == 2) ? (am == 0 ? 6.0 / 21.0 : (am == 1 ? 3.0 / 21.0 : -6.0 / 21.0))
+                             :            (am == 0 ? 12.0 / 45.0 : (am == 1 ? 9.0 / 45.0 : (am == 2 ? 0.0 / 45.0 : -15.0 / 45.0)));
             double clm = 0, fs = f_s;
             if (variant == 1) {
                 if (l == 1) { clm = 0; fs = f_s1; }
-                if (l == 2) { clm = (5. * (double)(m * m * m) - 17 * m) / 3.; fs = f_s2; }
+                if (l == 2) { clm = (double)((5 * m * m * m - 17 * m) / 3); fs = f_s2; }   // exact integers -2,4,0,-4,2
                 if (l == 3) { clm = 0; fs = (f_s1 + f_s2) / 2.; }
             } else {
                 if (l == 1) clm = m;
-                if (l == 2) clm = (5. * (double)(m * m * m) - 17 * m) / 3.;
+                if (l == 2) clm = (double)((5 * m * m * m - 17 * m) / 3);                  // exact integers -2,4,0,-4,2
                 if (l == 3) clm = 0;
             }
             // fc*(1+eta*Q) + m*fs + clm*a3, un-contracted
@@ -275,9 +278,19 @@ __device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff
 __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_terms)
 {
     __shared__ TgProShared S;
+    __shared__ double s_red[256];
     const TgDesc &d = a.d;
     const int tid = threadIdx.x;
-    const double *p = a.params + (size_t)b * d.Np;
+    // stage the parameter vector in shared memory: every later access (serial sections included) is an LDS
+    double *sp = sm_terms, *terms = sm_terms + d.Np;
+    {
+        const double *pg = a.params + (size_t)b * d.Np;
+        double *nzg = a.t.noise + (size_t)b * TG_NOISE_STRIDE;
+        for (int i = tid; i < d.Np; i += blockDim.x) sp[i] = pg[i];
+        for (int k = tid; k < TG_NOISE_STRIDE; k += blockDim.x) nzg[k] = 0.0;
+    }
+    __syncthreads();
+    const double *p = sp;
     const int mc = d.model_case;
     const int fam = (mc <= 1) ? 0 : ((mc == 11 || mc == 14) ? 2 : 1);
     const int Nmax = d.pl[0], lmax = d.pl[1], Nfl0 = d.pl[2], Nfl1 = d.pl[3], Nfl2 = d.pl[4], Nfl3 = d.pl[5];
@@ -287,11 +300,12 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     const int iF = Nmax + nV, iS = iF + Nf, iW = iS + Nsplit, iN = iW + Nwidth, iI = iN + Nnoise;
     double *nz = a.t.noise + (size_t)b * TG_NOISE_STRIDE;
 
+    TG_STAMP(4);
     // ---------------- A. chain scalars (thread 0) ----------------
     if (tid == 0) {
         S.status = 0; S.bad_prior = 0; S.work = 0.0; S.numax = 0; S.a1 = 0; S.inclination = 0;
+        { const double range = d.x_last - d.x_first; S.qmax = 1e70 / (range * range); }
         S.Vl[0] = 1; S.Vl[1] = S.Vl[2] = S.Vl[3] = 0;
-        for (int k = 0; k < TG_NOISE_STRIDE; k++) nz[k] = 0.0;
         if (fam == 0) {
             S.eta = S.a3 = S.asym = 0; S.trunc_c = 0; S.do_amp = 0;
             if (mc == 0) {           // model_Test_Gaussian, models.cpp:2021-2034 (no abs anywhere)
@@ -356,6 +370,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     }
     __syncthreads();
 
+    TG_STAMP(5);
     // ---------------- B. inclination -> height ratios (15 threads) ----------------
     if (fam != 0 && tid < 16) {
         // tid -> (l, m): l=0:{0} l=1:{1..3} l=2:{4..8} l=3:{9..15}
@@ -378,11 +393,14 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     }
     __syncthreads();
 
+    TG_STAMP(6);
     // ---------------- C. one thread per mode ----------------
     int nmodes = 0, ncomp = 0;
     if (fam == 1) { const int L1 = (lmax > 3 ? 3 : lmax) + 1; nmodes = Nmax * L1; ncomp = Nmax * L1 * L1; }
     if (fam == 2) { nmodes = Nf; ncomp = Nfl0 + 3 * Nfl1 + 5 * Nfl2 + 7 * Nfl3; }
     if (ncomp > d.ncomp_max) { if (tid == 0) S.status |= TG_ST_MODE_OVERFLOW; nmodes = 0; ncomp = 0; }
+    double work_acc = 0.0;
+    int st_acc = 0;
     for (int k = tid; k < nmodes; k += blockDim.x) {
         double hm[7];
         if (fam == 1) {
@@ -403,7 +421,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                     const int pos0 = (l + 1) * n;
                     for (int m = -l; m <= l; m++) { double v = p[iI + pos0 + (m < 0 ? -m : m)]; if (S.do_amp) v = v / (TG_PI * Wl); hm[m + l] = fabs(v); }
                 }
-                tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0);
+                tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc);
             } else {
                 const double Hl = (l == 0) ? tg_height0(p[n], Wl, S.do_amp) : tg_heightl(p[n], Wl, S.Vl[l], S.do_amp);
                 for (int m = 0; m < 2 * l + 1; m++) hm[m] = Hl * S.ratios[l][m];
@@ -412,9 +430,9 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                     if (mc == 6)      { a11 = fabs(p[iS]); a12 = fabs(p[iS + 6]); }
                     else if (mc == 7) { a11 = fabs(p[iS + 6 + n]); a12 = a11; }
                     else              { a11 = fabs(p[iS + 6 + n]); a12 = fabs(p[iS + 6 + Nmax + n]); }
-                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, 0, a11, a12, 1);
+                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, 0, a11, a12, 1, work_acc, st_acc);
                 } else {
-                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0);
+                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc);
                 }
             }
         } else {                                   // local family, models.cpp:1762-1810 / :1888-1943
@@ -434,15 +452,25 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                     for (int m = -l; m <= l; m++) { double v = p[S.modeStart[l] + pos0 + (m < 0 ? -m : m)]; if (S.do_amp) v = v / (TG_PI * Wl); hm[m + l] = fabs(v); }
                 }
             }
-            tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0);
+            tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc);
         }
     }
 
+    {   // one shared-memory atomic per warp (the sums are integer-valued, hence exact in any order)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { work_acc += __shfl_xor_sync(0xffffffffu, work_acc, o); st_acc |= __shfl_xor_sync(0xffffffffu, st_acc, o); }
+        if ((tid & 31) == 0) { if (work_acc != 0.0) atomicAdd(&S.work, work_acc); if (st_acc) atomicOr(&S.status, st_acc); }
+    }
+    TG_STAMP(7);
     // ---------------- D. prior terms, one thread per term ----------------
     int bad = 0;
-    for (int i = tid; i < d.Np; i += blockDim.x) sm_terms[i] = tg_generic_prior(a.sw[i], a.pri + 4 * i, p[i], &bad);
+    double *ex = terms + d.Np;                     // extra terms: [0..MAXORD) d02, then 4 x MAXORD smoothness
+    int *ssw = (int *)(ex + 5 * TG_MAXORD);        // priors_names_switch staged for the serial tail
+    // the prior terms go to the threads in REVERSE order: the low threads are busy with the modes (C),
+    // and there is no barrier between C and D
+    const int rt = blockDim.x - 1 - tid;
+    for (int i = rt; i < d.Np; i += blockDim.x) { const int swi = a.sw[i]; ssw[i] = swi; terms[i] = tg_generic_prior(swi, a.pri + 4 * i, p[i], &bad); }
     if (bad) atomicOr(&S.bad_prior, 1);
-    double *ex = sm_terms + d.Np;                  // extra terms: [0..MAXORD) d02, then 4 x MAXORD smoothness
     double Dnu = 0;
     if (d.prior_case == 2) {
         // Dnu = SUM of the adaptive first derivative of fl0 (priors_calc.cpp:87-88)
@@ -454,15 +482,16 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
             Dnu += f0[Nfl0 - 1] - f0[Nfl0 - 2];
         }
         if (Nfl0 == Nfl2)
-            for (int i = tid; i < Nfl0 && i < TG_MAXORD; i += blockDim.x)
+            for (int i = rt; i < Nfl0 && i < TG_MAXORD; i += blockDim.x)
                 ex[i] = tg_logP_gu(0, Dnu / 3., 0.015 * Dnu, p[Nmax + lmax + i] - p[Nmax + lmax + Nfl0 + Nfl1 + i]);
         if ((int)d.extra[0] == 1) {
             const int off[4] = {Nmax + lmax, Nmax + lmax + Nfl0, Nmax + lmax + Nfl0 + Nfl1, Nmax + lmax + Nfl0 + Nfl1 + Nfl2};
             const int nfl[4] = {Nfl0, Nfl1, Nfl2, Nfl3};
-            for (int l = 0; l < 4; l++) {
+            for (int e = rt; e < 4 * 32; e += blockDim.x) {              // one thread per (degree, order); orders beyond 32: loop below
+                const int l = e >> 5; for (int i = e & 31; i < nfl[l] && i < TG_MAXORD; i += 32) {
                 const double *y = p + off[l];
                 const int n = nfl[l];
-                for (int i = tid; i < n && i < TG_MAXORD; i += blockDim.x) {
+                {
                     double der;
                     if (n < 3) der = CUDART_NAN;                                  // reference would exit()
                     else if (i == 0) der = y[2] - 2. * y[1] + y[0];
@@ -470,17 +499,33 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                     else der = y[i + 1] - 2. * y[i] + y[i - 1];
                     ex[TG_MAXORD * (1 + l) + i] = tg_logP_gaussian(0, d.extra[1], der);
                 }
+                }
             }
         }
     }
     __syncthreads();
 
-    // ---------------- E. thread 0: sequential sum in the reference's order + hard limits ----------------
+    TG_STAMP(8);
+    // ---------------- E. sum of all terms (fixed-order block tree; the reference sums sequentially in
+    //                    long double -- same value to ~1e-15 relative), then thread 0 applies the hard limits ----
+    {
+        double part = 0.0;
+        for (int i = tid; i < d.Np; i += blockDim.x) part += terms[i];
+        if (d.prior_case == 2) {
+            if (Nfl0 == Nfl2) for (int i = tid; i < Nfl0 && i < TG_MAXORD; i += blockDim.x) part += ex[i];
+            if ((int)d.extra[0] == 1) {
+                const int nfl[4] = {Nfl0, Nfl1, Nfl2, Nfl3};
+                for (int l = 0; l < 4; l++) for (int i = tid; i < nfl[l] && i < TG_MAXORD; i += blockDim.x) part += ex[TG_MAXORD * (1 + l) + i];
+            }
+        }
+        part = tg_warp_sum(part);
+        if ((tid & 31) == 0) s_red[tid >> 5] = part;
+        __syncthreads();
+    }
     if (tid == 0) {
-        double f = 0;
-        for (int i = 0; i < d.Np; i++) f = f + sm_terms[i];
+        double f = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) f += s_red[w];
         if (d.prior_case == 2) {            // priors_MS_Global, priors_calc.cpp:24-172
-            for (int i = Nmax; i <= Nmax + lmax; i++) if (p[i] < 0) f = tg_ninf();
             const int impose = (int)d.extra[3];
             if (impose == 1) {
                 const int bI = iI;
@@ -488,33 +533,32 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                 f = f + tg_logP_uniform(0, 1 + 1e-10, p[bI + 2] + 2 * p[bI + 3] + 2 * p[bI + 4]);
                 f = f + tg_logP_uniform(0, 1 + 1e-10, p[bI + 5] + 2 * p[bI + 6] + 2 * p[bI + 7] + 2 * p[bI + 8]);
             } else if (impose == 2) S.bad_prior = 1;
-            if (Nfl0 == Nfl2) for (int i = 0; i < Nfl0 && i < TG_MAXORD; i++) f = f + ex[i];
-            if ((int)d.extra[0] == 1) {
-                const int nfl[4] = {Nfl0, Nfl1, Nfl2, Nfl3};
-                for (int l = 0; l < 4; l++) for (int i = 0; i < nfl[l] && i < TG_MAXORD; i++) f = f + ex[TG_MAXORD * (1 + l) + i];
-            }
+            for (int i = Nmax; i <= Nmax + lmax; i++) if (p[i] < 0) f = tg_ninf();
             if (fabs(p[iS + 2] / p[iS]) >= d.extra[2]) f = tg_ninf();
             if (p[iS + 4] < 0) f = tg_ninf();
             const int w = iS + Nsplit + Nwidth;
-            if (a.sw[w + 3] != 0) if ((p[w + 3] < 0) || (p[w + 4] < 0) || (p[w + 5] < 0)) f = tg_ninf();
-            if (a.sw[w + 6] != 0) if ((p[w + 6] < 0) || (p[w + 7] < 0) || (p[w + 8] < 0)) f = tg_ninf();
-            if ((a.sw[iS + 9] != 0) && (p[w + 9] < 0)) f = tg_ninf();
+            if (ssw[w + 3] != 0) if ((p[w + 3] < 0) || (p[w + 4] < 0) || (p[w + 5] < 0)) f = tg_ninf();
+            if (ssw[w + 6] != 0) if ((p[w + 6] < 0) || (p[w + 7] < 0) || (p[w + 8] < 0)) f = tg_ninf();
+            if ((ssw[iS + 9] != 0) && (p[w + 9] < 0)) f = tg_ninf();
         } else if (d.prior_case == 3) {     // priors_local, priors_calc.cpp:175-280
             if (p[iS] != 0) {
                 if (fabs(p[iS + 2] / p[iS]) >= d.extra[2]) f = tg_ninf();
             } else if ((p[iS + 3] != 0) && (p[iS + 4] != 0)) {
                 if (fabs(p[iS + 2] / (p[iS + 3] * p[iS + 3] + p[iS + 4] * p[iS + 4])) >= d.extra[2]) f = tg_ninf();
             }
-            if ((a.sw[iI] != 0) && (p[iI] < 0)) f = tg_ninf();
+            if ((ssw[iI] != 0) && (p[iI] < 0)) f = tg_ninf();
         }
         a.t.logprior[b] = f;
+#ifdef TG_PROFILE
+        if (blockIdx.x == 0) tg_dbg_clk[9] = clock64();
+#endif
         a.t.ncomp[b] = ncomp;
         a.t.work[b] = S.work;
         a.t.status[b] = S.status | (S.bad_prior ? TG_ST_BAD_PRIOR : 0);
     }
 }
 
-#define TG_PRO_SMEM(Np) ((size_t)((Np) + 5 * TG_MAXORD) * sizeof(double))
+#define TG_PRO_SMEM(Np) ((size_t)(2 * (Np) + 5 * TG_MAXORD) * sizeof(double) + (size_t)(((Np) + 1) & ~1) * sizeof(int))
 
 __global__ void __launch_bounds__(TG_PRO_THREADS) tg_k_prologue(TgProArgs a)
 {

@@ -145,7 +145,8 @@ __device__ void tg_factor_slot(const TgState &s, double eps2, int slot, int c, d
     }
     __syncthreads();
     const int fail = tg_cholesky_inplace(L, Nv, ld, work);
-    if (dyn) for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; if (k <= i) Lg[e] = L[i * ld + k]; }
+    // staged factor goes out PACKED (row i at i(i+1)/2): the propose kernel copies it flat into shared memory
+    if (dyn) for (int i = tid >> 5; i < Nv; i += nt >> 5) for (int k = tid & 31; k <= i; k += 32) Lg[i * (i + 1) / 2 + k] = L[i * ld + k];
     if (tid == 0) s.chol_fail[slot * s.C + c] = fail;
 }
 
@@ -161,7 +162,8 @@ struct TgSpecArgs {
 // :135-176) from the live slot into candidate slot (live+1+cand)%3, then its Cholesky factor.  Runs on a
 // second stream next to the fused model+likelihood kernel of the same step; the finish kernel selects
 // the candidate that matches the Metropolis decision.  The acceptance only enters sigma (a scalar,
-// applied as sqrt(sigma) at proposal time), so both candidates are exact.
+// applied as sqrt(sigma) at proposal time), so both candidates are exact.  chol layout: packed lower
+// triangle when smem_matrix, else full row-major (factorised in place in HBM).
 __global__ void __launch_bounds__(256) tg_k_spec(TgSpecArgs a)
 {
     extern __shared__ double tg_dyn_smem[];
@@ -212,6 +214,8 @@ struct TgProposeArgs {
     TgState   s;
     TgMala    m;
     TgProArgs pro;          // pro.params == s.params_prop
+    int       packed;       // 1: chol is stored packed (tg_k_spec staged it in shared memory), 0: full row-major
+    int       tri_smem;     // 1: the packed lower triangle of L (Nv(Nv+1)/2 doubles) fits the dynamic shared memory
 };
 
 // K1: one CTA per chain.  Draw z, form x' = x + sqrt(sigma)*L z with L = chol(Sigma+eps2 I) of the live
@@ -226,9 +230,37 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
     const int Nv = s.Nv, Np = s.Np;
     const long it = s.ctrl->i;
     const double *L = s.chol + tg_slot_mat(s, s.live[c], c);
-    // standard normals, Nv <= 512 per pass
+    TG_STAMP(0);
     const double sq = sqrt(s.sigma[c]);
     const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PROP, (uint32_t)(a.m.seed >> 32));
+    if (a.tri_smem) {
+        // ---- fast path: z and the packed lower triangle of L in shared memory, one thread per row ----
+        double *tri = tg_dyn_smem;                                  // row i at i(i+1)/2
+        double *zz = tri + (size_t)Nv * (Nv + 1) / 2;
+        if (a.packed) {
+            const int ntri = Nv * (Nv + 1) / 2;
+#pragma unroll 8
+            for (int e = tid; e < ntri; e += nt) tri[e] = __ldcg(L + e);
+        } else {
+            for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; if (k <= i) tri[i * (i + 1) / 2 + k] = __ldcg(L + e); }
+        }
+        for (int v = tid; v < Nv; v += nt) {
+            double z0, z1;
+            tg_normal_pair(tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)c, (uint32_t)(v >> 1)), key), &z0, &z1);
+            zz[v] = (v & 1) ? z1 : z0;
+        }
+        __syncthreads();
+        TG_STAMP(1);
+        for (int i = tid; i < Nv; i += nt) {
+            const double *row = tri + i * (i + 1) / 2;
+            double a0 = 0.0, a1 = 0.0;                              // fixed order: even / odd columns, then a0 + a1
+            int k = 0;
+            for (; k + 1 <= i; k += 2) { a0 = fma(row[k], zz[k], a0); a1 = fma(row[k + 1], zz[k + 1], a1); }
+            if (k <= i) a0 = fma(row[k], zz[k], a0);
+            s.vars_prop[(size_t)c * Nv + i] = s.vars_cur[(size_t)c * Nv + i] + sq * (a0 + a1);
+        }
+    } else
+    // general path (very large Nv): standard normals 512 per pass, rows from HBM
     for (int v0 = 0; v0 < Nv; v0 += 512) {
         __syncthreads();
         for (int v = v0 + tid; v < Nv && v < v0 + 512; v += nt) {
@@ -237,24 +269,45 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
             s_z[v - v0] = (v & 1) ? z1 : z0;
         }
         __syncthreads();
-        // partial products of rows with this block of z (lower triangle => k <= i): one warp per row,
-        // lanes stride the row (coalesced), fixed shuffle tree
-        for (int i = (tid >> 5); i < Nv; i += (nt >> 5)) {
-            double acc = 0.0;
-            const int kend = min(i, v0 + 511);
-            for (int k = v0 + (tid & 31); k <= kend; k += 32) acc = fma(L[(size_t)i * Nv + k], s_z[k - v0], acc);
-            acc = tg_warp_sum(acc);
-            if ((tid & 31) == 0 && i >= v0) {
-                const double prev = (v0 == 0) ? s.vars_cur[(size_t)c * Nv + i] : s.vars_prop[(size_t)c * Nv + i];
-                s.vars_prop[(size_t)c * Nv + i] = prev + sq * acc;
+        TG_STAMP(1);
+        // partial products of rows with this block of z (lower triangle => k <= i): a warp takes four rows
+        // at a time (their loads are in flight together), lanes stride the row (coalesced), fixed shuffle tree
+        const int lane = tid & 31, nw = nt >> 5;
+        for (int i0 = (tid >> 5); i0 < Nv; i0 += 4 * nw) {
+            double acc[4] = {0.0, 0.0, 0.0, 0.0};
+            int kend[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) { const int i = i0 + u * nw; kend[u] = (i < Nv) ? min(i, v0 + 511) : -1; }
+            const int kmax = max(max(kend[0], kend[1]), max(kend[2], kend[3]));
+            for (int k = v0 + lane; k <= kmax; k += 32) {
+                const double z = s_z[k - v0];
+#pragma unroll
+                for (int u = 0; u < 4; u++) if (k <= kend[u]) acc[u] = fma(__ldcg(L + (size_t)(i0 + u * nw) * Nv + k), z, acc[u]);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) acc[u] += __shfl_down_sync(0xffffffffu, acc[u], o);
+            }
+            if (lane == 0) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int i = i0 + u * nw;
+                    if (i < Nv && i >= v0) {
+                        const double prev = (v0 == 0) ? s.vars_cur[(size_t)c * Nv + i] : s.vars_prop[(size_t)c * Nv + i];
+                        s.vars_prop[(size_t)c * Nv + i] = prev + sq * acc[u];
+                    }
+                }
             }
         }
     }
+    TG_STAMP(2);
     // params_prop = params_cur with the free variables replaced (Model_def::update_params_with_vars)
     for (int i = tid; i < Np; i += nt) s.params_prop[(size_t)c * Np + i] = s.params_cur[(size_t)c * Np + i];
     __syncthreads();
     for (int v = tid; v < Nv; v += nt) s.params_prop[(size_t)c * Np + s.index_to_relax[v]] = s.vars_prop[(size_t)c * Nv + v];
     __syncthreads();
+    TG_STAMP(3);
     tg_prologue_body(a.pro, c, tg_dyn_smem);
 }
 
