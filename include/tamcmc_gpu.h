@@ -73,7 +73,7 @@ typedef struct tg_problem {
     int           flags;          /* TG_F_* */
 } tg_problem;
 
-#define TG_F_NO_TILE_ORDER        2 /* launch the bin tiles in index order instead of heaviest-first (scheduling only; results identical) */
+#define TG_F_NO_TILE_ORDER        2 /* one work item per 1024-bin sub-tile in index order instead of heaviest-first + long noise-only items (scheduling only; results identical) */
 #define TG_F_FIX_SWAP_BOOKKEEPING 1 /* fix quirk Q8 (stale logPosterior[B] after a swap, MALA.cpp:417-428); default replicates */
 
 /* Per-step records the reference hands to Outputs (MALA.cpp:696-707), for nsteps steps.
@@ -147,9 +147,10 @@ int tg_sync(tg_handle *h);
 /* Kernel timing of the dominant kernel (CUDA events on the handle's stream), accumulated since
  * the last reset: number of launches and total milliseconds. */
 int tg_kernel_time(tg_handle *h, int reset, long *launches, double *ms_eval, long *total_launches);
-int tg_set_tuning(tg_handle *h, int chains_per_block, int bins_per_thread, int use_graph);
-/* A CTA of the fused kernel covers nsub sub-tiles of 256*bins_per_thread bins per chain (default 1). */
-int tg_set_subtiles(tg_handle *h, int nsub);
+/* Tuning of the fused kernel (never changes results; 0 / -1 = keep): chains per work unit at most, chains per
+ * unit where truncation windows are expected, sub-tiles of 1024 bins per unit in the noise-only parts of the
+ * spectrum, CUDA-graph replay of tg_run. */
+int tg_set_tuning(tg_handle *h, int chains_per_block, int heavy_group, int light_subtiles, int use_graph);
 
 /* Device-side stopwatch on the handle's stream (CUDA events): which = 0 start, 1 stop. */
 int tg_event_record(tg_handle *h, int which);

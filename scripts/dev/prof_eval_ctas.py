@@ -1,0 +1,45 @@
+"""Developer check: per-CTA timeline of the fused kernel (TG_PROFILE build)."""
+import sys, os, ctypes as C, numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import tamcmc_b200_loader
+tb = tamcmc_b200_loader.load()
+W = tb.workloads
+here = os.path.dirname(os.path.abspath(__file__))
+lib = tb.gpu.GpuLibrary(os.path.join(here, "libtamcmc_gpu_prof.so"))
+prob = W.s_global(Nx=1000000)
+prob.y = np.abs(np.random.default_rng(1).standard_normal(prob.x.size)) + 0.1
+Cn = 10
+P, T = W.perturbed_params(prob, Cn), W.tcoefs(Cn)
+md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=Cn), lib=lib)
+md.eval_upload(P, T)
+for _ in range(5): md.eval_resident(Cn)
+md.sync()
+buf = (C.c_longlong * (8192 * 6))()
+lib.lib.tg_dbg_ctas.argtypes = [C.POINTER(C.c_longlong)]
+lib.lib.tg_dbg_ctas(buf)
+a = np.array(buf, dtype=np.int64).reshape(8192, 6); a = a[a[:, 5] > 0]; a = a[a[:, 4] >= a[:, 4].max() - 150000]   # last launch only
+t0, t1, t2 = a[:, 0], a[:, 1], a[:, 2]
+sm = a[:, 3] >> 32; tile = a[:, 3] & 0xffffffff
+g0, g1 = a[:, 4], a[:, 5]
+dur = (g1 - g0) / 1e3
+print("kernel span %.1f us (globaltimer)" % ((g1.max() - g0.min()) / 1e3))
+print("CTA duration us: min %.2f median %.2f mean %.2f p90 %.2f max %.2f" % (dur.min(), np.median(dur), dur.mean(), np.percentile(dur, 90), dur.max()))
+ph1 = (t1 - t0) / 1965.0
+print("phase-1 us: median %.2f mean %.2f max %.2f" % (np.median(ph1), ph1.mean(), ph1.max()))
+order = np.argsort(-dur)
+ph2 = (t2 - t1) / 1965.0
+nsubs = np.round(ph2 / np.median(ph2[dur < np.median(dur) * 1.5]) ).astype(int)
+for lo_, hi_ in ((0, 350000), (350000, 10**9)):
+    sel = (tile >= lo_) & (tile < hi_)
+    print("items with first bin in [%d,%d): n=%d, dur median %.2f mean %.2f" % (lo_, hi_, sel.sum(), np.median(dur[sel]), dur[sel].mean()))
+print("top CTAs (dur, tile, sm, start):", [(round(float(dur[k]), 1), int(tile[k]), int(sm[k]), round(float((g0[k] - g0.min()) / 1e3), 1)) for k in order[:8]])
+busy = np.zeros(148)
+for k in range(len(a)): busy[sm[k]] += dur[k]
+print("per-SM sum of CTA durations us: min %.1f mean %.1f max %.1f (2 resident -> /2)" % (busy.min(), busy.mean(), busy.max()))
+last = np.array([(g1[sm == s].max() - g0.min()) / 1e3 for s in range(148) if np.any(sm == s)])
+print("per-SM finish time us: min %.1f mean %.1f max %.1f" % (last.min(), last.mean(), last.max()))
+heavy = dur > 3 * np.median(dur)
+print("heavy CTAs: %d, mean dur %.1f us; light: %d, mean dur %.2f us" % (heavy.sum(), dur[heavy].mean(), (~heavy).sum(), dur[~heavy].mean()))
+# histogram
+h, e = np.histogram(dur, bins=[0, 1, 2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 1000])
+print("hist", list(zip(e[:-1].tolist(), h.tolist())))

@@ -18,3 +18,10 @@ names = ["start", "rng done", "matvec done", "scatter done", "stage params", "A 
 for k in range(1, 10):
     print("%-14s +%7d cycles (%.2f us)" % (names[k], v[k] - v[k - 1], (v[k] - v[k - 1]) / 1965.0))
 print("total %.2f us" % ((v[9] - v[0]) / 1965.0))
+
+out2 = (C.c_longlong * 16)()
+lib.lib.tg_dbg_specs.argtypes = [C.POINTER(C.c_longlong)]
+lib.lib.tg_dbg_specs(out2)
+w = np.array(out2[:6], dtype=np.int64)
+for k, nm in enumerate(["mu update", "cov update", "stage matrix", "cholesky", "write factor"]):
+    print("spec %-14s +%7d cycles (%.2f us)" % (nm, w[k + 1] - w[k], (w[k + 1] - w[k]) / 1965.0))

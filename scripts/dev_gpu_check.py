@@ -37,14 +37,13 @@ for mk in (lambda: W.s_local(), lambda: W.s_global(Nx=200000), lambda: W.s_globa
     md.sync(); dt = (time.time() - t) / 20
     n, ms, tot = md.kernel_time(reset=2)
     print("  resident eval: %.1f us/batch wall; eval kernel %.1f us avg over %d launches" % (dt * 1e6, ms / n * 1e3, n))
-    for bpt in (2, 4):
-        for nsub in (1, 2, 4):
-            for cpb in (1, 2, 5, 8):
-                md.set_tuning(cpb, bpt, -1, nsub); md.kernel_time(reset=1)
-                for _ in range(10): md.eval_resident(C)
-                n, ms, tot = md.kernel_time(reset=2)
-                print("    bpt=%d nsub=%d cpb=%d: eval kernel %.1f us" % (bpt, nsub, cpb, ms / n * 1e3))
-    md.set_tuning(5, 4, -1, 1)
+    for ls in (2, 4, 8):
+        for hg in (1, 2, 3, 5):
+            md.set_tuning(5, ls, -1, hg); md.kernel_time(reset=1)
+            for _ in range(10): md.eval_resident(C)
+            n, ms, tot = md.kernel_time(reset=2)
+            print("    light_sub=%d heavy_group=%d: eval kernel %.1f us" % (ls, hg, ms / n * 1e3))
+    md.set_tuning(5, 4, -1, 3)
     # sampler
     mala = tb.GpuMALA(md)
     t = time.time(); out = mala.execute(0, 64); dt = time.time() - t

@@ -36,13 +36,14 @@ struct tg_handle {
     int       *index_to_relax = nullptr; double *Tcoefs = nullptr;
     EvalBuf    ev;               // tg_eval batches
     EvalBuf    sp;               // sampler's proposed points (cap == C)
-    int        ntiles = 0, bpt = 4, chains_per_block = 0, use_graph = 1, steps_per_graph = 16;
-    int        smem_matrix = 0, tri_smem = 0; size_t propose_smem = 0, spec_smem = 0;
-    cudaStream_t side = nullptr;           // speculative proposal-adaptation kernel runs here, next to the fused kernel
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int        nitems = 0, max_items = 0, light_sub = 8, chains_per_block = 0, heavy_group = 2, use_graph = 1, steps_per_graph = 16;
+    int        smem_matrix = 0, tri_smem = 0; size_t propose_smem = 0, spec_smem = 0; int fused_spec = 0;
     double    *stage_mu = nullptr, *stage_cov = nullptr;   // tg_get_state staging ([C][Nv], [C][Nv][Nv])
-    int        list_cap = 4, max_cpb = 1, nsub = 1;
-    int       *tile_order = nullptr;       // launch order -> tile, heaviest first (NULL: identity)
+    int        list_cap = 4, max_cpb = 1;
+    struct UnitTable { int4 *dev = nullptr; int n = 0, B = -1, cap = 0; };
+    UnitTable  u_sp, u_ev;                 // work units of the fused kernel in launch order: sampler (B = C), tg_eval batches
+    std::vector<int4> items_host;          // bin partition: (first bin, sub-tiles, weight = windows crossing, heavy?)
+    bool       no_order = false;
     cudaGraphExec_t graph = nullptr;
     // eval-kernel timing
     bool       timing = false;
@@ -65,6 +66,8 @@ template <typename T> static int dalloc(tg_handle *h, T **p, size_t n)
 extern "C" const char *tg_last_error(void) { return g_err.c_str(); }
 extern "C" int tg_version(void) { return 100; }
 #ifdef TG_PROFILE
+extern "C" int tg_dbg_ctas(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_cta, sizeof(long long) * TG_DBG_CTAS * 6) == cudaSuccess ? 0 : -2; }
+extern "C" int tg_dbg_specs(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_spec, sizeof(long long) * 16) == cudaSuccess ? 0 : -2; }
 extern "C" int tg_dbg_clocks(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_clk, sizeof(long long) * 32) == cudaSuccess ? 0 : -2; }
 #endif
 
@@ -74,9 +77,9 @@ static int alloc_evalbuf(tg_handle *h, EvalBuf &b, int B)
     const size_t nc = (size_t)B * h->d.ncomp_max;
     b.cap = B;
     DA(b.t.nu, nc); DA(b.t.h, nc); DA(b.t.q, nc); DA(b.t.ifc, nc); DA(b.t.t2sq, nc); DA(b.t.lo, nc); DA(b.t.hi, nc);
-    DA(b.t.ncomp, B); DA(b.t.noise, (size_t)B * TG_NOISE_STRIDE); DA(b.t.status, B); DA(b.t.work, B); DA(b.t.logprior, B);
+    DA(b.t.ncomp, B); DA(b.t.wlo, B); DA(b.t.whi, B); DA(b.t.noise, (size_t)B * TG_NOISE_STRIDE); DA(b.t.status, B); DA(b.t.work, B); DA(b.t.logprior, B);
     DA(b.params, (size_t)B * h->d.Np); DA(b.T, B);
-    DA(b.partials, (size_t)B * h->ntiles); DA(b.sums, B);
+    DA(b.partials, (size_t)B * h->max_items); DA(b.sums, B);
     DA(b.logL, B); DA(b.logPrior, B); DA(b.logPost, B); DA(b.status, B);
     return TG_OK;
 }
@@ -111,6 +114,8 @@ static int harvest_events(tg_handle *h)
     return TG_OK;
 }
 
+static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B);
+
 // prologue (optional) + fused kernel + per-chain reduction for B points
 static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_dev, int B, double *model, bool do_prologue, bool do_reduce)
 {
@@ -119,78 +124,119 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
         tg_k_prologue<<<B, TG_PRO_THREADS, TG_PRO_SMEM(h->d.Np), h->stream>>>(pa);
         h->n_launch_total++;
     }
-    TgEvalArgs ea{h->d, b.t, h->x, h->y, h->lnx, h->sig, b.partials, model, h->tile_order, B, h->ntiles, h->chains_per_block, h->nsub, h->list_cap};
+    tg_handle::UnitTable &u = (&b == &h->sp) ? h->u_sp : h->u_ev;
+    if (B != u.B) { int r = build_units(h, u, B); if (r) return r; }     // never inside a graph capture: tg_run builds u_sp first
     const size_t esm = TG_EVAL_SMEM(h->chains_per_block, h->list_cap);
-    dim3 grid(h->ntiles, (B + h->chains_per_block - 1) / h->chains_per_block);
+    TgEvalArgs ea{h->d, b.t, h->x, h->y, h->lnx, h->sig, b.partials, model, u.dev, B, h->nitems, h->chains_per_block, h->list_cap};
+    dim3 grid(u.n);
     if (h->timing) {
         if (h->ev_used >= 8192) { int r = harvest_events(h); if (r) return r; }
         cudaEventRecord(next_event(h), h->stream);
     }
-    switch (h->bpt) {
-    case 1: tg_k_eval<1><<<grid, TG_THREADS, esm, h->stream>>>(ea); break;
-    case 2: tg_k_eval<2><<<grid, TG_THREADS, esm, h->stream>>>(ea); break;
-    default: tg_k_eval<4><<<grid, TG_THREADS, esm, h->stream>>>(ea); break;
-    }
+    tg_k_eval<<<grid, TG_THREADS, esm, h->stream>>>(ea);
     if (h->timing) cudaEventRecord(next_event(h), h->stream);
     h->n_eval_launch++; h->n_launch_total++;
-    if (do_reduce) { tg_k_reduce<<<B, 256, 0, h->stream>>>(b.partials, h->ntiles, b.sums); h->n_launch_total++; }
+    if (do_reduce) { tg_k_reduce<<<B, 256, 0, h->stream>>>(b.partials, h->nitems, b.sums); h->n_launch_total++; }
     CK(cudaGetLastError());
     return TG_OK;
 }
 
-// Launch order of the bin tiles: heaviest first (tiles crossed by many truncation windows cost
-// several times more than noise-only tiles; dispatching them first lets the light tiles fill the
-// tail of the grid).  Estimated once from the windows of chain 0 at the initial point -- the order
-// only affects scheduling, never results.
-static int build_tile_order(tg_handle *h)
+// Work items of the fused kernel (scheduling only -- the kernel classifies every sub-tile again from
+// the window unions of the launch, so results never depend on this table): single sub-tiles of 1024
+// bins where truncation windows are expected, heaviest first (they cost several times more than
+// noise-only bins, and dispatching them first lets the light items fill the tail of the grid), then
+// runs of light_sub sub-tiles over the noise-only parts.  Estimated from the B chains held in `b`.
+static int build_items(tg_handle *h, EvalBuf &b, int B)
 {
-    const int nt = h->ntiles, tile = TG_THREADS * h->bpt * h->nsub, nc = h->d.ncomp_max;
-    if (!h->tile_order) { int r = dalloc(h, &h->tile_order, (size_t)(h->d.Nx + TG_THREADS - 1) / TG_THREADS); if (r) return r; }
-    std::vector<int> lo(std::max(nc, 1)), hi(std::max(nc, 1)), order(nt);
-    int ncomp = 0;
-    CK(cudaStreamSynchronize(h->stream));
-    CK(cudaMemcpy(&ncomp, h->sp.t.ncomp, sizeof(int), cudaMemcpyDeviceToHost));
-    if (nc > 0) {
-        CK(cudaMemcpy(lo.data(), h->sp.t.lo, (size_t)nc * 4, cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(hi.data(), h->sp.t.hi, (size_t)nc * 4, cudaMemcpyDeviceToHost));
+    const int SUB = TG_THREADS * 4, nt = (h->d.Nx + SUB - 1) / SUB, nc = h->d.ncomp_max;
+    std::vector<int4> items;
+    if (h->no_order) {
+        for (int t = 0; t < nt; t++) items.push_back(make_int4(t * SUB, 1, 0, 1));
+    } else {
+        std::vector<int> wlo(B), whi(B), lo(std::max(nc, 1)), hi(std::max(nc, 1));
+        int ncomp = 0;
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaMemcpy(wlo.data(), b.t.wlo, (size_t)B * 4, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(whi.data(), b.t.whi, (size_t)B * 4, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(&ncomp, b.t.ncomp, sizeof(int), cudaMemcpyDeviceToHost));
+        if (nc > 0) {
+            CK(cudaMemcpy(lo.data(), b.t.lo, (size_t)nc * 4, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(hi.data(), b.t.hi, (size_t)nc * 4, cudaMemcpyDeviceToHost));
+        }
+        int ulo = h->d.Nx, uhi = 0;
+        for (int c = 0; c < B; c++) if (whi[c] > wlo[c]) { ulo = std::min(ulo, wlo[c]); uhi = std::max(uhi, whi[c]); }
+        int t0 = nt, t1 = nt;                       // heavy tiles [t0, t1), one tile of margin for drifting windows
+        if (uhi > ulo) { t0 = std::max(0, ulo / SUB - 1); t1 = std::min(nt, (uhi + SUB - 1) / SUB + 1); }
+        std::vector<int> diff(nt + 1, 0), w(nt, 0);
+        for (int k = 0; k < ncomp && k < nc; k++) {
+            if (hi[k] <= lo[k]) continue;
+            const int a0 = std::max(0, lo[k] / SUB), a1 = std::min(nt - 1, (hi[k] - 1) / SUB);
+            if (a1 >= a0) { diff[a0]++; diff[a1 + 1]--; }
+        }
+        for (int t = 0, c = 0; t < nt; t++) { c += diff[t]; w[t] = c; }
+        const int L = std::max(1, h->light_sub);
+        for (int t = 0; t < t0; t += L) items.push_back(make_int4(t * SUB, std::min(L, t0 - t), 0, 0));
+        for (int t = t0; t < t1; t++) items.push_back(make_int4(t * SUB, 1, w[t], 1));
+        for (int t = t1; t < nt; t += L) items.push_back(make_int4(t * SUB, std::min(L, nt - t), 0, 0));
     }
-    std::vector<int> diff(nt + 1, 0);
-    for (int k = 0; k < ncomp && k < nc; k++) {
-        if (hi[k] <= lo[k]) continue;
-        const int t0 = std::max(0, lo[k] / tile), t1 = std::min(nt - 1, (hi[k] - 1) / tile);
-        if (t1 >= t0) { diff[t0]++; diff[t1 + 1]--; }
-    }
-    std::vector<int> w(nt);
-    for (int t = 0, c = 0; t < nt; t++) { c += diff[t]; w[t] = c; order[t] = t; }
-    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return w[a] > w[b]; });
-    CK(cudaMemcpy(h->tile_order, order.data(), (size_t)nt * 4, cudaMemcpyHostToDevice));
+    bool same = items.size() == h->items_host.size();
+    for (size_t k = 0; same && k < items.size(); k++) same = items[k].x == h->items_host[k].x && items[k].y == h->items_host[k].y && items[k].z == h->items_host[k].z;
+    if (same) return TG_OK;
+    h->items_host = items;
+    h->nitems = (int)items.size();
+    h->u_sp.B = h->u_ev.B = -1;                     // units are rebuilt at the next launch
+    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }     // grid size changed
     return TG_OK;
 }
 
-extern "C" int tg_set_tuning(tg_handle *h, int chains_per_block, int bins_per_thread, int use_graph)
+// Units = items x chain groups: few chains per unit where windows are expected (an item there costs
+// 5-10x a noise-only sub-tile), up to chains_per_block elsewhere; costliest first (LPT scheduling).
+static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B)
 {
-    if (!h) return fail(TG_E_BADARG, "null handle");
-    if (bins_per_thread == 1 || bins_per_thread == 2 || bins_per_thread == 4) {
-        if (bins_per_thread != h->bpt) {
-            // partials buffers were sized for the finest tiling at create time, so any tiling fits
-            h->bpt = bins_per_thread;
-            h->ntiles = (h->d.Nx + TG_THREADS * h->bpt * h->nsub - 1) / (TG_THREADS * h->bpt * h->nsub);
-            if (h->tile_order) { int r = build_tile_order(h); if (r) return r; }
+    std::vector<int4> units;
+    std::vector<double> cost;
+    const int gl = std::max(1, h->chains_per_block), gh = std::max(1, std::min(h->heavy_group, gl));
+    for (size_t k = 0; k < h->items_host.size(); k++) {
+        const int4 it = h->items_host[k];
+        const int gmax = (it.w && !h->no_order) ? gh : gl;
+        const int groups = (B + gmax - 1) / gmax, g = (B + groups - 1) / groups;      // balanced
+        for (int c0 = 0; c0 < B; c0 += g) {
+            const int G = std::min(g, B - c0);
+            units.push_back(make_int4(it.x, it.y | (G << 16), c0, (int)k));
+            cost.push_back((double)G * it.y * (20.0 + 6.25 * it.z) + 15.0);
         }
     }
-    if (chains_per_block > 0) h->chains_per_block = std::min(chains_per_block, h->max_cpb);
-    if (use_graph >= 0) h->use_graph = use_graph;
-    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+    if (!h->no_order) {
+        std::vector<int> idx(units.size());
+        for (size_t k = 0; k < idx.size(); k++) idx[k] = (int)k;
+        std::stable_sort(idx.begin(), idx.end(), [&](int a, int b2) { return cost[a] > cost[b2]; });
+        std::vector<int4> u2(units.size());
+        for (size_t k = 0; k < idx.size(); k++) u2[k] = units[idx[k]];
+        units.swap(u2);
+    }
+    if ((int)units.size() > u.cap) {
+        void *q = nullptr;
+        CK(cudaMalloc(&q, units.size() * sizeof(int4)));
+        h->allocs.push_back(q);                     // the old (smaller) table is released with the handle
+        u.dev = (int4 *)q; u.cap = (int)units.size();
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(u.dev, units.data(), units.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    u.n = (int)units.size(); u.B = B;
     return TG_OK;
 }
 
-extern "C" int tg_set_subtiles(tg_handle *h, int nsub)
+extern "C" int tg_set_tuning(tg_handle *h, int chains_per_block, int heavy_group, int light_subtiles, int use_graph)
 {
-    if (!h || nsub < 1 || nsub > 64) return fail(TG_E_BADARG, "tg_set_subtiles: bad argument");
-    h->nsub = nsub;
-    h->ntiles = (h->d.Nx + TG_THREADS * h->bpt * h->nsub - 1) / (TG_THREADS * h->bpt * h->nsub);
-    if (h->tile_order) { int r = build_tile_order(h); if (r) return r; }
+    if (!h) return fail(TG_E_BADARG, "null handle");
+    if (chains_per_block > 0) { h->chains_per_block = std::min(chains_per_block, h->max_cpb); h->u_sp.B = h->u_ev.B = -1; }
+    if (heavy_group > 0) { h->heavy_group = heavy_group; h->u_sp.B = h->u_ev.B = -1; }
+    if (use_graph >= 0) h->use_graph = use_graph;
     if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+    if (light_subtiles > 0 && light_subtiles != h->light_sub) {
+        h->light_sub = std::min(light_subtiles, 4096);
+        int r = build_items(h, h->sp, h->s.C); if (r) return r;
+    }
     return TG_OK;
 }
 
@@ -269,14 +315,14 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     CK(cudaMemcpyAsync(h->index_to_relax, idx.data(), (size_t)d.Nv * 4, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->Tcoefs, p->Tcoefs, (size_t)p->Nchains * 8, cudaMemcpyHostToDevice, h->stream));
 
-    // ---- tiling / tuning defaults ----
-    h->bpt = 1;      // size the partial buffers for the finest tiling, then pick the default
-    h->ntiles = (d.Nx + TG_THREADS - 1) / TG_THREADS;
+    // ---- tiling: partial sums are sized for one item per 1024-bin sub-tile (the finest partition) ----
+    h->max_items = (d.Nx + TG_THREADS * 4 - 1) / (TG_THREADS * 4);
+    h->no_order = (p->flags & TG_F_NO_TILE_ORDER) != 0;
+    for (int t = 0; t < h->max_items; t++) h->items_host.push_back(make_int4(t * TG_THREADS * 4, 1, 0, 1));   // until chain tables exist
+    h->nitems = h->max_items;
     const int C = p->Nchains;
     { int r = alloc_evalbuf(h, h->sp, C); if (r) return r; }
     { int r = alloc_evalbuf(h, h->ev, C); if (r) return r; }
-    h->bpt = 4;
-    h->ntiles = (d.Nx + TG_THREADS * h->bpt - 1) / (TG_THREADS * h->bpt);
     // shared-memory lists of the fused kernel: one list of <= ncomp_max components per chain of a group
     {
         h->list_cap = std::max(4, (d.ncomp_max + 3) & ~3);
@@ -287,9 +333,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         if (TG_EVAL_SMEM(m, h->list_cap) > (size_t)maxdyn - 2048) return fail(TG_E_BADARG, "too many Lorentzian components for the shared-memory list of the fused kernel");
         h->max_cpb = m;
         const size_t need = TG_EVAL_SMEM(m, h->list_cap);
-        CK(cudaFuncSetAttribute(tg_k_eval<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
-        CK(cudaFuncSetAttribute(tg_k_eval<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
-        CK(cudaFuncSetAttribute(tg_k_eval<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+        CK(cudaFuncSetAttribute(tg_k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
         const int groups = (C + m - 1) / m;                                               // balanced chain groups of <= max_cpb
         h->chains_per_block = (C + groups - 1) / groups;
     }
@@ -344,15 +388,14 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         const size_t need_tri = ((size_t)d.Nv * (d.Nv + 1) / 2 + d.Nv) * 8;
         h->tri_smem = (need_tri <= budget) ? 1 : 0;
         h->propose_smem = std::max(need_pro, h->tri_smem ? need_tri : (size_t)0);
+        // Nv <= 96: the adaptation works out of registers (tg_spec96, no dynamic shared memory) and its CTAs
+        // ride in the propose grid; larger problems run it as a separate kernel after the propose kernel
+        h->fused_spec = (h->tri_smem && h->smem_matrix && d.Nv <= 96) ? 1 : 0;
         CK(cudaFuncSetAttribute(tg_k_spec, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spec_smem));
-        if (h->propose_smem > 48 * 1024) CK(cudaFuncSetAttribute(tg_k_propose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->propose_smem));
+        CK(cudaFuncSetAttribute(tg_k_propose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->propose_smem));   // static + dynamic may exceed 48 KB
         if (need_pro > 48 * 1024) {
             CK(cudaFuncSetAttribute(tg_k_prologue, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_pro));
         }
-        int lo = 0, hi = 0; CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-        CK(cudaStreamCreateWithPriority(&h->side, cudaStreamNonBlocking, hi));
-        CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     }
     // record ring
     {
@@ -372,7 +415,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(h->stream));
     }
-    if (!(p->flags & TG_F_NO_TILE_ORDER)) { int r = build_tile_order(h); if (r) return r; }
+    { int r = build_items(h, h->sp, C); if (r) return r; }
     return TG_OK;
 }
 
@@ -384,9 +427,6 @@ extern "C" int tg_destroy(tg_handle *h)
     if (h->graph) cudaGraphExecDestroy(h->graph);
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
-    if (h->side) { cudaStreamSynchronize(h->side); cudaStreamDestroy(h->side); }
-    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
-    if (h->ev_join) cudaEventDestroy(h->ev_join);
     for (void *q : h->allocs) cudaFree(q);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -528,6 +568,8 @@ extern "C" int tg_set_state(tg_handle *h, const double *vars, const double *mu, 
         int r = launch_eval_kernels(h, h->sp, h->s.params_cur, (int)C, nullptr, true, true); if (r) return r;
         tg_k_install_current<<<((int)C + 127) / 128, 128, 0, h->stream>>>(h->d, h->s, h->sp.t, h->sp.sums);
         CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(h->stream));
+        { int r = build_items(h, h->sp, (int)C); if (r) return r; }
     }
     CK(cudaStreamSynchronize(h->stream));
     return TG_OK;
@@ -540,24 +582,19 @@ static int launch_step(tg_handle *h, bool begin, bool end, int presummed)
 {
     const int C = h->s.C;
     if (begin) {
-        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}, h->smem_matrix, h->tri_smem};
-        tg_k_propose<<<C, 256, h->propose_smem, h->stream>>>(pa);
+        const int learn = h->m.n_learn > 0, fused = learn && h->fused_spec;
+        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}, h->smem_matrix, h->tri_smem, fused, h->smem_matrix};
+        tg_k_propose<<<dim3(C, fused ? 3 : 1), 256, h->propose_smem, h->stream>>>(pa);
         h->n_launch_total++;
-        if (h->m.n_learn > 0) {
-            // fork: both outcomes of the proposal adaptation (Robbins-Monro update + Cholesky) are prepared
-            // on the high-priority side stream while the fused model+likelihood kernel runs
-            CK(cudaEventRecord(h->ev_fork, h->stream));
-            CK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+        if (learn && !fused) {       // very large Nv: the adaptation candidates get their own launch
             TgSpecArgs sa{h->s, h->m, h->smem_matrix, 0};
-            tg_k_spec<<<dim3(C, 2), 256, h->spec_smem, h->side>>>(sa);
-            CK(cudaEventRecord(h->ev_join, h->side));
+            tg_k_spec<<<dim3(C, 2), 256, h->spec_smem, h->stream>>>(sa);
             h->n_launch_total++;
         }
         int r = launch_eval_kernels(h, h->sp, h->sp.params, C, nullptr, false, presummed != 0); if (r) return r;
     }
     if (end) {
-        if (h->m.n_learn > 0) CK(cudaStreamWaitEvent(h->stream, h->ev_join, 0));
-        TgFinishArgs fa{h->d, h->s, h->m, h->sp.t, h->sp.partials, h->ntiles, h->sp.sums, presummed, h->rec, 1};
+        TgFinishArgs fa{h->d, h->s, h->m, h->sp.t, h->sp.partials, h->nitems, h->sp.sums, presummed, h->rec, 1};
         tg_k_finish<<<C, 256, 0, h->stream>>>(fa);
         h->n_launch_total++;
     }
@@ -590,6 +627,8 @@ extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
 {
     if (!h || nsteps < 0) return fail(TG_E_BADARG, "tg_run: bad argument");
     CK(cudaSetDevice(h->device));
+    if (nsteps >= 64) { int r = build_items(h, h->sp, h->s.C); if (r) return r; }   // follow the windows of the chains (scheduling only)
+    if (h->u_sp.B != h->s.C) { int r = build_units(h, h->u_sp, h->s.C); if (r) return r; }
     long done = 0;
     while (done < nsteps) {
         const long n = std::min(nsteps - done, h->rec.cap);
@@ -611,7 +650,7 @@ extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
                 cudaGraphDestroy(g);
             }
             if (h->graph) {
-                for (; k + G <= n; k += G) { CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += (h->m.n_learn > 0 ? 4L : 3L) * G; h->n_eval_launch += G; }
+                for (; k + G <= n; k += G) { CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += 3L * G; h->n_eval_launch += G; }
             }
         }
         for (; k < n; k++) { int r = launch_step(h, true, true, 0); if (r) return r; }

@@ -5,13 +5,14 @@
 // d=x-nu; p=4*d*d/G^2; res += H*V/(1+p) [* asymmetry]), :453-459 (window accumulate);
 // noise_models.cpp:17-41 (harvey_like); likelihoods.cpp:17-39; model_def.cpp:291-320.
 //
-// Layout: grid.x = bin tiles (TG_THREADS*BPT bins each), grid.y = chain groups.  A CTA loads its
-// tile of x, y, ln x ONCE into registers (coalesced, bin = base + j*TG_THREADS + tid) and reuses it
-// for every chain of its group; per chain it compacts the Lorentzian components whose truncation
-// window intersects the tile into shared memory (order-preserving, so the accumulation order is
-// fixed), accumulates them in registers, adds the noise background, forms y/m and ln m, and
-// reduces them into a per-(chain,tile) fp64 pair.  The model spectrum never goes to HBM (unless
-// the parity/debug pointer is set).
+// Layout: grid.x = work units (item x chain group), costliest first.  An item is a run of sub-tiles of 1024 bins
+// (4 per thread, bin = b0 + j*256 + tid: coalesced): one sub-tile where truncation windows are expected,
+// long runs where only the noise background exists.  Per sub-tile the CTA holds x, y in registers and
+// reuses them for every chain of its group; where windows meet the sub-tile it first compacts, per chain,
+// the components concerned into shared memory (order-preserving, so the accumulation order is fixed).
+// Per chain: Lorentzians accumulated in registers, noise background added, y/m and the product of m
+// folded into per-thread running results; one reduction per (chain, item) at the end.  The model
+// spectrum never goes to HBM (unless the parity/debug pointer is set).
 //
 // FP64-pipe economy (the kernel is bound by the FP64 pipe, not by HBM):
 //  * four components share ONE reciprocal:  sum_k h_k/t_k = N/T with T = t0 t1 t2 t3 and
@@ -26,15 +27,20 @@
 #pragma once
 #include "tg_internal.cuh"
 
+#ifdef TG_PROFILE
+#define TG_DBG_CTAS 8192
+__device__ long long tg_dbg_cta[TG_DBG_CTAS][6];
+__device__ __forceinline__ long long globaltimer_ns() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#endif
+
 struct TgEvalArgs {
     TgDesc        d;
     TgTables      t;
     const double *x, *y, *lnx, *sig;   // [Nx]; sig may be NULL
-    double2      *partials;            // [B][ntiles]  (sum y/m , sum ln m)  or (sum chi2 , 0)
+    double2      *partials;            // [B][nitems]  (sum y/m + slow-path logs , ln of the product of m)  or (sum chi2 , 0)
     double       *model;               // [B][Nx] or NULL
-    const int    *tile_order;          // [ntiles] launch order -> tile (heaviest first) or NULL
-    int           B, ntiles, chains_per_block;
-    int           nsub;                // sub-tiles (TG_THREADS*BPT bins each) per CTA tile
+    const int4   *units;               // [grid] work units in launch order: (first bin, sub-tiles | chains << 16, first chain, item)
+    int           B, nitems, max_group;  // nitems: items (bin runs) = partial sums per chain; max_group: chains per unit at most
     int           list_cap;            // capacity (components) of one chain's list in shared memory, multiple of 4
 };
 
@@ -43,10 +49,14 @@ struct __align__(16) TgComp {       // one Lorentzian m-component clipped to the
     double h; int lo, len;          // height, window start (tile-local), window length
     double ifc, t2;                 // asymmetry extras: 1/fc, (Gamma*asym/(2fc))^2
 };
+#ifndef TG_EVAL_MINBLOCKS
+#define TG_EVAL_MINBLOCKS 2
+#endif
 #define TG_MAXG 8                   // chains per CTA (chain group) at most == warps per CTA
 // dynamic shared memory of tg_k_eval for a group of G chains and a list capacity of cap components:
-// lists, noise tables, per-thread partial results (sum, mantissa product, exponent sum)
-#define TG_EVAL_SMEM(G, cap) ((size_t)(G) * ((size_t)(cap) * sizeof(TgComp) + TG_NOISE_STRIDE * sizeof(double) + TG_THREADS * (2 * sizeof(double) + sizeof(int))))
+// lists, per-quad "covers the whole tile" flags, noise tables, per-thread partial results
+// (sum, mantissa product, exponent sum)
+#define TG_EVAL_SMEM(G, cap) ((size_t)(G) * ((size_t)(cap) * sizeof(TgComp) + (size_t)((cap) / 4 + 2 * TG_MAXH) * sizeof(int) + TG_NOISE_STRIDE * sizeof(double) + TG_THREADS * (2 * sizeof(double) + sizeof(int))))
 
 // height of a component at tile-local bin li: h inside its window, 0 outside
 __device__ __forceinline__ double tg_hsel(double h, int lo, int len, int li)
@@ -54,19 +64,16 @@ __device__ __forceinline__ double tg_hsel(double h, int lo, int len, int li)
     return ((unsigned)(li - lo) < (unsigned)len) ? h : 0.0;
 }
 
+// acc[j] += sum over the list of h_k / (1 + q_k (x_j - nu_k)^2)  [* asymmetry factor], four components
+// per reciprocal.  full[k/4] != 0: the four windows cover the whole tile (no per-bin predicate).
 template <int BPT, bool ASYM>
-__device__ __forceinline__ void tg_accumulate(int n4, const TgComp *L, const double (&x)[BPT], double (&acc)[BPT], double asym, int li0)
+__device__ __forceinline__ void tg_accumulate(int n4, const TgComp *L, const int *full, const double (&x)[BPT], double (&acc)[BPT], double asym, int tid)
 {
-    constexpr int SUB = TG_THREADS * BPT;       // bins of one sub-tile; li0 = tile-local index of this thread's first bin
 #pragma unroll 1
     for (int k = 0; k < n4; k += 4) {
         const double2 a0 = *(const double2 *)&L[k].nu, a1 = *(const double2 *)&L[k + 1].nu, a2 = *(const double2 *)&L[k + 2].nu, a3 = *(const double2 *)&L[k + 3].nu;
         const double h0 = L[k].h, h1 = L[k + 1].h, h2 = L[k + 2].h, h3 = L[k + 3].h;
-        const int2 w0 = *(const int2 *)&L[k].lo, w1 = *(const int2 *)&L[k + 1].lo, w2 = *(const int2 *)&L[k + 2].lo, w3 = *(const int2 *)&L[k + 3].lo;
-        const int s0 = li0 & ~(TG_THREADS - 1) , s1 = s0 + SUB;   // sub-tile range [s0, s1) (li0 = s0 + tid)
-        const bool full = (w0.x <= s0 && w0.x + w0.y >= s1) && (w1.x <= s0 && w1.x + w1.y >= s1) &&
-                          (w2.x <= s0 && w2.x + w2.y >= s1) && (w3.x <= s0 && w3.x + w3.y >= s1);
-        if (full && !ASYM) {                     // CTA-uniform: every bin of the tile is inside all 4 windows
+        if (!ASYM && full[k >> 2]) {             // CTA-uniform
 #pragma unroll
             for (int j = 0; j < BPT; j++) {
                 const double d0 = x[j] - a0.x, d1 = x[j] - a1.x, d2 = x[j] - a2.x, d3 = x[j] - a3.x;
@@ -79,11 +86,12 @@ __device__ __forceinline__ void tg_accumulate(int n4, const TgComp *L, const dou
                 acc[j] = fma(N, tg_rcp_fast(T), acc[j]);
             }
         } else {
+            const int2 w0 = *(const int2 *)&L[k].lo, w1 = *(const int2 *)&L[k + 1].lo, w2 = *(const int2 *)&L[k + 2].lo, w3 = *(const int2 *)&L[k + 3].lo;
             double2 c0, c1, c2, c3;
             if (ASYM) { c0 = *(const double2 *)&L[k].ifc; c1 = *(const double2 *)&L[k + 1].ifc; c2 = *(const double2 *)&L[k + 2].ifc; c3 = *(const double2 *)&L[k + 3].ifc; }
 #pragma unroll
             for (int j = 0; j < BPT; j++) {
-                const int li = li0 + j * TG_THREADS;
+                const int li = tid + j * TG_THREADS;
                 double g0 = tg_hsel(h0, w0.x, w0.y, li), g1 = tg_hsel(h1, w1.x, w1.y, li), g2 = tg_hsel(h2, w2.x, w2.y, li), g3 = tg_hsel(h3, w3.x, w3.y, li);
                 if (ASYM) {                      // build_lorentzian.cpp:94-97: (1+asym(x/fc-1))^2 + (Gamma*asym/(2fc))^2
                     const double e0 = fma(asym, fma(x[j], c0.x, -1.0), 1.0), e1 = fma(asym, fma(x[j], c1.x, -1.0), 1.0);
@@ -136,9 +144,8 @@ __device__ __forceinline__ double tg_exp_nb(double z)
 // t[j] = 1 + (a x_j)^p for one Harvey term and the BPT bins of a thread.  The exponent class is
 // chain-uniform, so the switch sits OUTSIDE the bin loop and every case is straight-line code.
 template <int BPT>
-__device__ __forceinline__ void tg_harvey_t(const double *q, const double (&x)[BPT], const double *lnx, const int (&ii)[BPT], double (&t)[BPT])
+__device__ __forceinline__ void tg_harvey_t(int cls, const double *q, const double (&x)[BPT], const double *lnx, const int (&ii)[BPT], double (&t)[BPT])
 {
-    const int cls = (int)q[TG_H_CLS];
     const double ap = q[TG_H_AP];
     switch (cls) {
     case 0:
@@ -169,33 +176,137 @@ __device__ __forceinline__ void tg_harvey_t(const double *q, const double (&x)[B
     }
 }
 
-template <int BPT>
-__global__ void __launch_bounds__(TG_THREADS) tg_k_eval(TgEvalArgs a)
+struct TgEvalSmem {                 // carved out of the dynamic shared memory
+    TgComp *lists;                  // [G][cap]
+    int    *full;                   // [G][cap/4]   1: the four windows of the quad cover the whole sub-tile
+    int    *cls;                    // [G][TG_MAXH] Harvey exponent classes (ints, so the chain loop has no F2I)
+    int    *nh;                     // [G] .. padded to TG_MAXH
+    double *nz;                     // [G][TG_NOISE_STRIDE]
+    double *sum, *pf;               // [G][TG_THREADS]  running per-thread results of the item
+    int    *pe;                     // [G][TG_THREADS]
+};
+
+// Every chain of the group on NB*TG_THREADS consecutive bins starting at b0, held in registers; no CTA
+// barrier inside, so warps drift apart and hide each other's latencies.  LISTS: the sub-tile meets
+// truncation windows (lists in shared memory); otherwise only the noise background exists there and
+// NB may be 8 (two sub-tiles at once: twice the instruction-level parallelism, half the per-chain
+// overhead).  GEN = false is the interior fast path (all bins inside the spectrum, no model output, no
+// Gaussian test model): no index clamps, no selects.
+template <int NB, bool GEN, bool LISTS>
+__device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalSmem &S, const int *s_tot, int G, int c0, int b0, int tid)
 {
-    constexpr int SUB = TG_THREADS * BPT;
-    constexpr int NW = TG_THREADS / 32;
-    extern __shared__ __align__(16) unsigned char tg_eval_smem[];
-    __shared__ int s_cnt[TG_MAXG][NW];
-    __shared__ int s_tot[TG_MAXG];
+    const int Nx = a.d.Nx, cap = a.list_cap;
+    double x[NB], y[NB];
+    int ii[NB];
+#pragma unroll
+    for (int j = 0; j < NB; j++) {
+        const int idx = b0 + j * TG_THREADS + tid;
+        ii[j] = (!GEN || idx < Nx) ? idx : Nx - 1;
+        x[j] = __ldg(a.x + ii[j]);
+        y[j] = (!GEN || idx < Nx) ? __ldg(a.y + ii[j]) : 0.0;   // bins past the end: y = 0 and (below) m = 1
+    }
+    for (int g = 0; g < G; g++) {
+        const double *nz = S.nz + (size_t)g * TG_NOISE_STRIDE;
+        double acc[NB];
+        if (GEN && nz[TG_N_GAUSS] != 0.0) {       // models.cpp:1977-1978 / :2030-2031 (Gaussian test models always take GEN)
+            const double gA = nz[TG_N_GA], gnu = nz[TG_N_GNU], gs2 = nz[TG_N_GS2];
+#pragma unroll
+            for (int j = 0; j < NB; j++) { const double dd = x[j] - gnu; acc[j] = gA * exp(-0.5 * (dd * dd) / gs2); }
+        } else {
+#pragma unroll
+            for (int j = 0; j < NB; j++) acc[j] = 0.0;
+        }
+        if constexpr (LISTS) {
+            const int n4 = (s_tot[g] + 3) & ~3;
+            const double asym = nz[TG_N_ASYM];
+            if (n4 > 0) {
+                if (asym != 0.0) tg_accumulate<NB, true>(n4, S.lists + (size_t)g * cap, S.full + g * (cap >> 2), x, acc, asym, tid);
+                else             tg_accumulate<NB, false>(n4, S.lists + (size_t)g * cap, S.full + g * (cap >> 2), x, acc, asym, tid);
+            }
+        }
+        // ---- Harvey-like background: y += H/(1+(1e-3*tc*x)^p) ; y += N0  (noise_models.cpp:30-38).
+        //      The prologue lists only the active terms (tc != 0); consecutive pairs share a reciprocal.
+        const int nH = S.nh[g];
+        for (int k = 0; k < nH; k += 2) {
+            double ta[NB], tb[NB];
+            tg_harvey_t<NB>(S.cls[g * TG_MAXH + k], nz + TG_HS * k, x, a.lnx, ii, ta);
+            const double Ha = nz[TG_HS * k + TG_H_H];
+            if (k + 1 < nH) {
+                tg_harvey_t<NB>(S.cls[g * TG_MAXH + k + 1], nz + TG_HS * (k + 1), x, a.lnx, ii, tb);
+                const double Hb = nz[TG_HS * (k + 1) + TG_H_H];
+#pragma unroll
+                for (int j = 0; j < NB; j++) acc[j] = fma(fma(Ha, tb[j], Hb * ta[j]), tg_rcp_fast(ta[j] * tb[j]), acc[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < NB; j++) acc[j] = fma(Ha, tg_rcp_fast(ta[j]), acc[j]);
+            }
+        }
+        const double N0 = nz[TG_N_N0];
+        double m[NB];
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            m[j] = acc[j] + N0;
+            if (GEN) {
+                const int idx = b0 + j * TG_THREADS + tid;
+                if (idx < Nx) { if (a.model) a.model[(size_t)(c0 + g) * Nx + idx] = m[j]; }
+                else m[j] = 1.0;
+            }
+        }
+        // running results of this thread for chain g over the whole item
+        double sum = S.sum[g * TG_THREADS + tid];     // sum y/m (or chi-square) + logs taken the slow way
+        double pf = S.pf[g * TG_THREADS + tid];       // product of the model values: pf * 2^pe, pf in [1,2)
+        int pe = S.pe[g * TG_THREADS + tid];
+        if (a.d.like_case == 0) {                 // likelihoods.cpp:23
+#pragma unroll
+            for (int j0 = 0; j0 < NB; j0 += 4) {
+                double mm[4], yy[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const bool in = (j0 + u < NB);
+                    mm[u] = in ? m[in ? (j0 + u) : 0] : 1.0;
+                    yy[u] = in ? y[in ? (j0 + u) : 0] : 0.0;
+                }
+                const double p01 = mm[0] * mm[1], p23 = mm[2] * mm[3], P = p01 * p23;
+                // all four positive (sign bits clear) and the product a normal number far from the range ends
+                const int sgn = __double2hiint(mm[0]) | __double2hiint(mm[1]) | __double2hiint(mm[2]) | __double2hiint(mm[3]);
+                const int hiP = __double2hiint(P);
+                const int eP = (hiP >> 20) & 0x7ff;
+                if (sgn >= 0 && (unsigned)(eP - 200) < 1646u) {            // 2^-823 < P < 2^823
+                    const double n = fma(fma(yy[0], mm[1], yy[1] * mm[0]), p23, fma(yy[2], mm[3], yy[3] * mm[2]) * p01);
+                    sum = fma(n, tg_rcp_fast(P), sum);
+                    // fold P into the running product; the exponent is kept apart so it can never overflow
+                    pf *= __hiloint2double((hiP & 0x000fffff) | 0x3ff00000, __double2loint(P));      // [1,2) x [1,2)
+                    const int h2 = __double2hiint(pf);
+                    pe += (eP - 1023) + (((h2 >> 20) & 0x7ff) - 1023);
+                    pf = __hiloint2double((h2 & 0x000fffff) | 0x3ff00000, __double2loint(pf));
+                } else {                          // zero / negative / NaN / huge model values: the plain way
+#pragma unroll
+                    for (int u = 0; u < 4; u++) if (j0 + u < NB && (!GEN || b0 + (j0 + u) * TG_THREADS + tid < Nx)) sum += yy[u] * tg_rcp(mm[u]) + log(mm[u]);
+                }
+            }
+        } else {                                  // likelihoods.cpp:36
+#pragma unroll
+            for (int j = 0; j < NB; j++) {
+                const int idx = b0 + j * TG_THREADS + tid;
+                if (!GEN || idx < Nx) {
+                    const double sg = __ldg(a.sig + idx);
+                    const double dd = y[j] - m[j];
+                    sum += (dd * dd) * tg_rcp(sg * sg);
+                }
+            }
+        }
+        S.sum[g * TG_THREADS + tid] = sum; S.pf[g * TG_THREADS + tid] = pf; S.pe[g * TG_THREADS + tid] = pe;
+    }
+}
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = a.tile_order ? __ldg(a.tile_order + blockIdx.x) : blockIdx.x;
-    const int nsub = a.nsub;                      // sub-tiles of SUB bins per CTA tile
-    const int TILE = SUB * nsub;
-    const int base = tile * TILE;
-    const int Nx = a.d.Nx;
-    const int cap = a.list_cap;
-    const int c0 = blockIdx.y * a.chains_per_block;
-    const int G = min(a.B - c0, a.chains_per_block);
-    TgComp *lists = (TgComp *)tg_eval_smem;                                      // [G][cap]
-    double *s_nz  = (double *)(lists + (size_t)a.chains_per_block * cap);        // [G][TG_NOISE_STRIDE]
-    double *s_sum = s_nz + (size_t)a.chains_per_block * TG_NOISE_STRIDE;         // [G][TG_THREADS]
-    double *s_pf  = s_sum + (size_t)a.chains_per_block * TG_THREADS;             // [G][TG_THREADS]
-    int    *s_pe  = (int *)(s_pf + (size_t)a.chains_per_block * TG_THREADS);     // [G][TG_THREADS]
-
-    // ---- phase 1: per-chain lists of the components whose window meets this tile (order-preserving
-    //      ballot compaction, all chains of the group at once), noise tables ----
-    for (int e = tid; e < G * TG_NOISE_STRIDE; e += TG_THREADS) s_nz[e] = a.t.noise[(size_t)c0 * TG_NOISE_STRIDE + e];
+// Per-chain lists of the components whose window meets the sub-tile [b0, b0+SUB): order-preserving
+// ballot compaction for all chains of the group at once, padded to a multiple of four, plus the
+// per-quad "covers the whole sub-tile" flags.  Called by the whole CTA (contains barriers).
+__device__ void tg_build_lists(const TgEvalArgs &a, const TgEvalSmem &S, int (*s_cnt)[TG_THREADS / 32], int *s_tot, int G, int c0, int b0)
+{
+    constexpr int SUB = TG_THREADS * 4, NW = TG_THREADS / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, cap = a.list_cap;
+    __syncthreads();                              // the previous sub-tile's lists are dead
     if (tid < TG_MAXG) s_tot[tid] = 0;
     for (int chunk = 0; chunk < a.d.ncomp_max; chunk += TG_THREADS) {
         const int k = chunk + tid;
@@ -207,12 +318,12 @@ __global__ void __launch_bounds__(TG_THREADS) tg_k_eval(TgEvalArgs a)
             lo[g] = 0; hi[g] = 0;
             if (g < G && k < a.t.ncomp[c0 + g]) {
                 const size_t e = (size_t)(c0 + g) * a.d.ncomp_max + k;
-                lo[g] = a.t.lo[e] - base; hi[g] = a.t.hi[e] - base;
+                lo[g] = a.t.lo[e] - b0; hi[g] = a.t.hi[e] - b0;
             }
         }
 #pragma unroll
         for (int g = 0; g < TG_MAXG; g++) {
-            const bool ov = (lo[g] < TILE) && (hi[g] > 0) && (hi[g] > lo[g]);
+            const bool ov = (lo[g] < SUB) && (hi[g] > 0) && (hi[g] > lo[g]);
             bal[g] = __ballot_sync(0xffffffffu, ov);
             if (lane == 0 && g < G) s_cnt[g][warp] = __popc(bal[g]);
         }
@@ -228,7 +339,7 @@ __global__ void __launch_bounds__(TG_THREADS) tg_k_eval(TgEvalArgs a)
                 q.nu = a.t.nu[e]; q.q = a.t.q[e]; q.h = a.t.h[e];
                 q.lo = max(lo[g], -(1 << 29)); q.len = min(hi[g], 1 << 29) - q.lo;      // keep hi-lo inside int
                 q.ifc = a.t.ifc[e]; q.t2 = a.t.t2sq[e];
-                lists[(size_t)g * cap + off + __popc(bal[g] & ((1u << lane) - 1u))] = q;
+                S.lists[(size_t)g * cap + off + __popc(bal[g] & ((1u << lane) - 1u))] = q;
             }
         }
         __syncthreads();                          // everyone has read s_tot / s_cnt of this pass
@@ -239,111 +350,97 @@ __global__ void __launch_bounds__(TG_THREADS) tg_k_eval(TgEvalArgs a)
         const int g = tid >> 2, u = tid & 3;
         if (g < G) {
             const int total = s_tot[g], n4 = (total + 3) & ~3;
-            if (total + u < n4) { TgComp q; q.nu = 0; q.q = 0; q.h = 0; q.lo = -(1 << 29); q.len = 1 << 30; q.ifc = 0; q.t2 = 0; lists[(size_t)g * cap + total + u] = q; }
+            if (total + u < n4) { TgComp q; q.nu = 0; q.q = 0; q.h = 0; q.lo = -(1 << 29); q.len = 1 << 30; q.ifc = 0; q.t2 = 0; S.lists[(size_t)g * cap + total + u] = q; }
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < G * (cap >> 2); e += TG_THREADS) {
+        const int g = e / (cap >> 2), qd = e - g * (cap >> 2);
+        int f = 0;
+        if (4 * qd < s_tot[g]) {
+            f = 1;
+#pragma unroll
+            for (int u = 0; u < 4; u++) { const TgComp *q = S.lists + (size_t)g * cap + 4 * qd + u; if (!(q->lo <= 0 && q->lo + q->len >= SUB)) f = 0; }
+        }
+        S.full[e] = f;
+    }
+    __syncthreads();
+}
+
+// The fused kernel.  grid.x = work units = (item, chain group); an item is a run of sub-tiles of 1024 bins:
+// ONE sub-tile where truncation windows are expected (few chains per unit), long runs in the noise-only
+// parts of the spectrum (more chains per unit).  The unit table is a scheduling hint only: every sub-tile is classified again from the per-chain
+// window unions of THIS launch, so any partition of the bins gives the same results.
+__global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEvalArgs a)
+{
+    constexpr int SUB = TG_THREADS * 4;
+    constexpr int NW = TG_THREADS / 32;
+    extern __shared__ __align__(16) unsigned char tg_eval_smem[];
+    __shared__ int s_cnt[TG_MAXG][NW];
+    __shared__ int s_tot[TG_MAXG];
+    __shared__ int s_w[2][TG_MAXG];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int4 unit = __ldg(a.units + blockIdx.x);
+    const int2 item = make_int2(unit.x, unit.y & 0xffff);   // (first bin, number of sub-tiles)
+#ifdef TG_PROFILE
+    const int dbg_id = blockIdx.x;
+    if (tid == 0 && dbg_id < TG_DBG_CTAS) { unsigned sm; asm volatile("mov.u32 %0, %smid;" : "=r"(sm)); tg_dbg_cta[dbg_id][0] = clock64(); tg_dbg_cta[dbg_id][3] = ((long long)sm << 32) | (unsigned)item.x; tg_dbg_cta[dbg_id][4] = globaltimer_ns(); }
+#endif
+    const int cap = a.list_cap, cpb = a.max_group, Nx = a.d.Nx;
+    const int c0 = unit.z;
+    const int G = unit.y >> 16;
+    TgEvalSmem S;
+    S.lists = (TgComp *)tg_eval_smem;
+    S.nz    = (double *)(S.lists + (size_t)cpb * cap);
+    S.sum   = S.nz + (size_t)cpb * TG_NOISE_STRIDE;
+    S.pf    = S.sum + (size_t)cpb * TG_THREADS;
+    S.pe    = (int *)(S.pf + (size_t)cpb * TG_THREADS);
+    S.full  = S.pe + (size_t)cpb * TG_THREADS;
+    S.cls   = S.full + (size_t)cpb * (cap >> 2);
+    S.nh    = S.cls + (size_t)cpb * TG_MAXH;
+
+    // ---- phase 0: noise tables, window unions, running results ----
+    for (int e = tid; e < G * TG_NOISE_STRIDE; e += TG_THREADS) S.nz[e] = a.t.noise[(size_t)c0 * TG_NOISE_STRIDE + e];
+    if (tid < G) { s_w[0][tid] = a.t.wlo[c0 + tid]; s_w[1][tid] = a.t.whi[c0 + tid]; }
+    for (int g = 0; g < G; g++) { S.sum[g * TG_THREADS + tid] = 0.0; S.pf[g * TG_THREADS + tid] = 1.0; S.pe[g * TG_THREADS + tid] = 0; }
+    __syncthreads();
+    if (tid < TG_MAXG * TG_MAXH) {                // Harvey exponent classes / counts as ints
+        const int g = tid / TG_MAXH, k = tid % TG_MAXH;
+        if (g < G) {
+            S.cls[g * TG_MAXH + k] = (int)S.nz[(size_t)g * TG_NOISE_STRIDE + TG_HS * k + TG_H_CLS];
+            if (k == 0) S.nh[g] = (int)S.nz[(size_t)g * TG_NOISE_STRIDE + TG_N_NH];
+        }
+    }
+    int wlo = 0x7fffffff, whi = 0;                // union of the group's windows
+    for (int g = 0; g < G; g++) if (s_w[1][g] > s_w[0][g]) { wlo = min(wlo, s_w[0][g]); whi = max(whi, s_w[1][g]); }
+    const bool gen_all = (a.model != nullptr) || (a.d.model_case <= 1);
+    __syncthreads();
+#ifdef TG_PROFILE
+    if (tid == 0 && dbg_id < TG_DBG_CTAS) tg_dbg_cta[dbg_id][1] = clock64();
+#endif
+
+    // ---- phases 1+2 per sub-tile ----
+    for (int sub = 0; sub < item.y; ) {
+        const int b0 = item.x + sub * SUB;
+        if (b0 >= Nx) break;
+        const bool gen = gen_all || (b0 + SUB > Nx);
+        if (wlo < b0 + SUB && whi > b0) {         // truncation windows meet this sub-tile
+            tg_build_lists(a, S, s_cnt, s_tot, G, c0, b0);
+            if (gen) tg_chain_loop<4, true, true>(a, S, s_tot, G, c0, b0, tid);
+            else     tg_chain_loop<4, false, true>(a, S, s_tot, G, c0, b0, tid);
+            sub += 1;
+        } else if (!gen_all && sub + 1 < item.y && b0 + 2 * SUB <= Nx && !(wlo < b0 + 2 * SUB && whi > b0 + SUB)) {
+            tg_chain_loop<8, false, false>(a, S, s_tot, G, c0, b0, tid);    // two noise-only sub-tiles at once
+            sub += 2;
+        } else {
+            if (gen) tg_chain_loop<4, true, false>(a, S, s_tot, G, c0, b0, tid);
+            else     tg_chain_loop<4, false, false>(a, S, s_tot, G, c0, b0, tid);
+            sub += 1;
         }
     }
     __syncthreads();
 
-    // ---- phase 2: every chain of the group x every sub-tile, no CTA barrier inside (warps drift
-    //      apart and hide each other's latencies) ----
-    for (int g = 0; g < G; g++) {
-        const int c = c0 + g;
-        const double *nz = s_nz + (size_t)g * TG_NOISE_STRIDE;
-        const TgComp *L = lists + (size_t)g * cap;
-        const int n4 = (s_tot[g] + 3) & ~3;
-        const double asym = nz[TG_N_ASYM], N0 = nz[TG_N_N0];
-        const int nH = (int)nz[TG_N_NH];
-        const bool gauss = nz[TG_N_GAUSS] != 0.0;
-        double sum = 0.0;                         // sum y/m (or chi-square) + logs taken the slow way
-        double pf = 1.0; int pe = 0;              // running product of model values: pf * 2^pe, pf in [1,2)
-        for (int sub = 0; sub < nsub; sub++) {
-            const int li0 = sub * SUB + tid;
-            double x[BPT], acc[BPT];
-            int ii[BPT];
-            bool any = false;
-#pragma unroll
-            for (int j = 0; j < BPT; j++) {
-                const int idx = base + li0 + j * TG_THREADS;
-                ii[j] = idx < Nx ? idx : Nx - 1;
-                any |= idx < Nx;
-                x[j] = __ldg(a.x + ii[j]);
-                acc[j] = 0.0;
-            }
-            if (base + sub * SUB >= Nx) break;    // whole sub-tile past the end (CTA-uniform)
-            if (gauss) {                          // models.cpp:1977-1978 / :2030-2031
-                const double gA = nz[TG_N_GA], gnu = nz[TG_N_GNU], gs2 = nz[TG_N_GS2];
-#pragma unroll
-                for (int j = 0; j < BPT; j++) { const double dd = x[j] - gnu; acc[j] = gA * exp(-0.5 * (dd * dd) / gs2); }
-            }
-            if (n4 > 0) {
-                if (asym != 0.0) tg_accumulate<BPT, true>(n4, L, x, acc, asym, li0);
-                else             tg_accumulate<BPT, false>(n4, L, x, acc, asym, li0);
-            }
-            // ---- Harvey-like background: y += H/(1+(1e-3*tc*x)^p) ; y += N0  (noise_models.cpp:30-38).
-            //      The prologue lists only the active terms (tc != 0); consecutive pairs share a reciprocal.
-            for (int k = 0; k < nH; k += 2) {
-                double ta[BPT], tb[BPT];
-                tg_harvey_t<BPT>(nz + TG_HS * k, x, a.lnx, ii, ta);
-                const double Ha = nz[TG_HS * k + TG_H_H];
-                if (k + 1 < nH) {
-                    tg_harvey_t<BPT>(nz + TG_HS * (k + 1), x, a.lnx, ii, tb);
-                    const double Hb = nz[TG_HS * (k + 1) + TG_H_H];
-#pragma unroll
-                    for (int j = 0; j < BPT; j++) acc[j] = fma(fma(Ha, tb[j], Hb * ta[j]), tg_rcp_fast(ta[j] * tb[j]), acc[j]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < BPT; j++) acc[j] = fma(Ha, tg_rcp_fast(ta[j]), acc[j]);
-                }
-            }
-            double m[BPT], y[BPT];
-#pragma unroll
-            for (int j = 0; j < BPT; j++) {
-                const int idx = base + li0 + j * TG_THREADS;
-                m[j] = acc[j] + N0;
-                y[j] = __ldg(a.y + ii[j]);
-                if (idx < Nx) { if (a.model) a.model[(size_t)c * Nx + idx] = m[j]; }
-                else { m[j] = 1.0; y[j] = 0.0; }  // bins past the end: ln 1 = 0 and y/m = 0
-            }
-            if (a.d.like_case == 0) {             // likelihoods.cpp:23
-#pragma unroll
-                for (int j0 = 0; j0 < BPT; j0 += 4) {
-                    double mm[4], yy[4];
-#pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const bool in = (j0 + u < BPT);
-                        mm[u] = in ? m[in ? (j0 + u) : 0] : 1.0;
-                        yy[u] = in ? y[in ? (j0 + u) : 0] : 0.0;
-                    }
-                    const double p01 = mm[0] * mm[1], p23 = mm[2] * mm[3], P = p01 * p23;
-                    const int sgn = __double2hiint(mm[0]) | __double2hiint(mm[1]) | __double2hiint(mm[2]) | __double2hiint(mm[3]);
-                    if (sgn >= 0 && P > 1e-250 && P < 1e250) {
-                        const double n = fma(fma(yy[0], mm[1], yy[1] * mm[0]), p23, fma(yy[2], mm[3], yy[3] * mm[2]) * p01);
-                        sum = fma(n, tg_rcp_fast(P), sum);
-                        // fold P into the running product; the exponent is kept apart so it can never overflow
-                        pf *= P;                  // pf in [1,2), P in (1e-250,1e250): no overflow
-                        const int hi = __double2hiint(pf);
-                        pe += ((hi >> 20) & 0x7ff) - 1023;
-                        pf = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(pf));
-                    } else {                      // zero / negative / NaN / huge model values: the plain way
-#pragma unroll
-                        for (int u = 0; u < 4; u++) if (j0 + u < BPT && base + li0 + (j0 + u) * TG_THREADS < Nx) sum += yy[u] * tg_rcp(mm[u]) + log(mm[u]);
-                    }
-                }
-            } else {                              // likelihoods.cpp:36
-#pragma unroll
-                for (int j = 0; j < BPT; j++) {
-                    const int idx = base + li0 + j * TG_THREADS;
-                    if (idx < Nx) {
-                        const double sg = __ldg(a.sig + idx);
-                        const double dd = y[j] - m[j];
-                        sum += (dd * dd) * tg_rcp(sg * sg);
-                    }
-                }
-            }
-        }
-        s_sum[g * TG_THREADS + tid] = sum; s_pf[g * TG_THREADS + tid] = pf; s_pe[g * TG_THREADS + tid] = pe;
-    }
-    __syncthreads();
     // ---- phase 3: warp g reduces chain g (fixed order: 8 strided entries per lane, shuffle tree),
     //      lane 0 takes ONE log of the mantissa product; all chains of the group in parallel ----
     if (warp < G) {
@@ -351,9 +448,9 @@ __global__ void __launch_bounds__(TG_THREADS) tg_k_eval(TgEvalArgs a)
         int pe = 0;
 #pragma unroll
         for (int i = 0; i < NW; i++) {
-            sum += s_sum[warp * TG_THREADS + i * 32 + lane];
-            pf *= s_pf[warp * TG_THREADS + i * 32 + lane];           // 8 mantissas in [1,2): < 2^8
-            pe += s_pe[warp * TG_THREADS + i * 32 + lane];
+            sum += S.sum[warp * TG_THREADS + i * 32 + lane];
+            pf *= S.pf[warp * TG_THREADS + i * 32 + lane];           // 8 mantissas in [1,2): < 2^8
+            pe += S.pe[warp * TG_THREADS + i * 32 + lane];
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {                           // 32 x 2^8 -> < 2^256
@@ -364,9 +461,12 @@ __global__ void __launch_bounds__(TG_THREADS) tg_k_eval(TgEvalArgs a)
         if (lane == 0) {
             double t2 = 0.0;
             if (a.d.like_case == 0) t2 = fma((double)pe, 6.93147180369123816490e-01, fma((double)pe, 1.90821492927058770002e-10, log(pf)));
-            a.partials[(size_t)(c0 + warp) * a.ntiles + tile] = make_double2(sum, t2);
+            a.partials[(size_t)(c0 + warp) * a.nitems + unit.w] = make_double2(sum, t2);
         }
     }
+#ifdef TG_PROFILE
+    if (tid == 0 && dbg_id < TG_DBG_CTAS) { tg_dbg_cta[dbg_id][2] = clock64(); tg_dbg_cta[dbg_id][5] = globaltimer_ns(); }
+#endif
 }
 
 // Sums the per-tile pairs of each chain in a fixed order (thread-strided serial sums, then a

@@ -33,6 +33,7 @@ struct TgTables {
     double *ifc, *t2sq;        // [B][ncomp_max]  asymmetry extras: 1/fc, (0.5*Gamma*asym/fc)^2
     int    *lo, *hi;           // [B][ncomp_max]  window [lo,hi) in LOCAL bin indices
     int    *ncomp;             // [B]
+    int    *wlo, *whi;         // [B]  union [wlo,whi) of all truncation windows in LOCAL bins (empty: wlo >= whi)
     double *noise;             // [B][TG_NOISE_STRIDE] : per ACTIVE Harvey term (H, a=1e-3*tc, p, ln a, a^p clamped, exponent class), then N0, asym, gaussA, gaussNu, gaussS2, flags
     int    *status;            // [B]  TG_ST_* bits
     double *work;              // [B]  L = sum (2l+1)*(hi-lo)

@@ -198,7 +198,7 @@ struct TgProShared {
     double Vl[4];
     double ratios[4][7];
     double work;
-    int    do_amp, status, bad_prior;
+    int    do_amp, status, bad_prior, wlo, whi;
     int    modeStart[5], compStart[5];   // local family: prefix over degrees
 };
 
@@ -222,7 +222,7 @@ __device__ double tg_appwidth_v2(const double *w, double f)
 
 // Writes the 2l+1 components of one mode.  variant 0: a1etaa3, 1: a1l (f_s per degree, c_1m=0).
 __device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff, int l, double fc, double W,
-                             const double *hm, double f_s, double f_s1, double f_s2, int variant, double &work_acc, int &st_acc)
+                             const double *hm, double f_s, double f_s1, double f_s2, int variant, double &work_acc, int &st_acc, int &wlo_acc, int &whi_acc)
 {
     const TgDesc &d = a.d;
     long imin = 0, imax = 0;
@@ -235,6 +235,7 @@ __device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff
         a1 = a1 < 0 ? 0 : (a1 > d.Nx ? d.Nx : a1);
         lo = (int)a0; hi = (int)a1;
         work_acc += (double)(2 * l + 1) * (double)(hi - lo);           // integer-valued: exact, order-free
+        if (hi > lo) { wlo_acc = min(wlo_acc, lo); whi_acc = max(whi_acc, hi); }
     } else {
         st_acc |= st;
     }
@@ -303,7 +304,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     TG_STAMP(4);
     // ---------------- A. chain scalars (thread 0) ----------------
     if (tid == 0) {
-        S.status = 0; S.bad_prior = 0; S.work = 0.0; S.numax = 0; S.a1 = 0; S.inclination = 0;
+        S.status = 0; S.bad_prior = 0; S.wlo = 0x7fffffff; S.whi = 0; S.work = 0.0; S.numax = 0; S.a1 = 0; S.inclination = 0;
         { const double range = d.x_last - d.x_first; S.qmax = 1e70 / (range * range); }
         S.Vl[0] = 1; S.Vl[1] = S.Vl[2] = S.Vl[3] = 0;
         if (fam == 0) {
@@ -400,7 +401,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     if (fam == 2) { nmodes = Nf; ncomp = Nfl0 + 3 * Nfl1 + 5 * Nfl2 + 7 * Nfl3; }
     if (ncomp > d.ncomp_max) { if (tid == 0) S.status |= TG_ST_MODE_OVERFLOW; nmodes = 0; ncomp = 0; }
     double work_acc = 0.0;
-    int st_acc = 0;
+    int st_acc = 0, wlo_acc = 0x7fffffff, whi_acc = 0;
     for (int k = tid; k < nmodes; k += blockDim.x) {
         double hm[7];
         if (fam == 1) {
@@ -421,7 +422,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                     const int pos0 = (l + 1) * n;
                     for (int m = -l; m <= l; m++) { double v = p[iI + pos0 + (m < 0 ? -m : m)]; if (S.do_amp) v = v / (TG_PI * Wl); hm[m + l] = fabs(v); }
                 }
-                tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc);
+                tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
             } else {
                 const double Hl = (l == 0) ? tg_height0(p[n], Wl, S.do_amp) : tg_heightl(p[n], Wl, S.Vl[l], S.do_amp);
                 for (int m = 0; m < 2 * l + 1; m++) hm[m] = Hl * S.ratios[l][m];
@@ -430,9 +431,9 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                     if (mc == 6)      { a11 = fabs(p[iS]); a12 = fabs(p[iS + 6]); }
                     else if (mc == 7) { a11 = fabs(p[iS + 6 + n]); a12 = a11; }
                     else              { a11 = fabs(p[iS + 6 + n]); a12 = fabs(p[iS + 6 + Nmax + n]); }
-                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, 0, a11, a12, 1, work_acc, st_acc);
+                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, 0, a11, a12, 1, work_acc, st_acc, wlo_acc, whi_acc);
                 } else {
-                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc);
+                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
                 }
             }
         } else {                                   // local family, models.cpp:1762-1810 / :1888-1943
@@ -452,14 +453,21 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                     for (int m = -l; m <= l; m++) { double v = p[S.modeStart[l] + pos0 + (m < 0 ? -m : m)]; if (S.do_amp) v = v / (TG_PI * Wl); hm[m + l] = fabs(v); }
                 }
             }
-            tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc);
+            tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
         }
     }
 
     {   // one shared-memory atomic per warp (the sums are integer-valued, hence exact in any order)
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) { work_acc += __shfl_xor_sync(0xffffffffu, work_acc, o); st_acc |= __shfl_xor_sync(0xffffffffu, st_acc, o); }
-        if ((tid & 31) == 0) { if (work_acc != 0.0) atomicAdd(&S.work, work_acc); if (st_acc) atomicOr(&S.status, st_acc); }
+        for (int o = 16; o > 0; o >>= 1) {
+            work_acc += __shfl_xor_sync(0xffffffffu, work_acc, o); st_acc |= __shfl_xor_sync(0xffffffffu, st_acc, o);
+            wlo_acc = min(wlo_acc, __shfl_xor_sync(0xffffffffu, wlo_acc, o)); whi_acc = max(whi_acc, __shfl_xor_sync(0xffffffffu, whi_acc, o));
+        }
+        if ((tid & 31) == 0) {
+            if (work_acc != 0.0) atomicAdd(&S.work, work_acc);
+            if (st_acc) atomicOr(&S.status, st_acc);
+            if (whi_acc > wlo_acc) { atomicMin(&S.wlo, wlo_acc); atomicMax(&S.whi, whi_acc); }
+        }
     }
     TG_STAMP(7);
     // ---------------- D. prior terms, one thread per term ----------------
@@ -553,6 +561,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
         if (blockIdx.x == 0) tg_dbg_clk[9] = clock64();
 #endif
         a.t.ncomp[b] = ncomp;
+        a.t.wlo[b] = S.wlo; a.t.whi[b] = S.whi;
         a.t.work[b] = S.work;
         a.t.status[b] = S.status | (S.bad_prior ? TG_ST_BAD_PRIOR : 0);
     }

@@ -10,49 +10,8 @@
 #pragma once
 #include "tg_internal.cuh"
 #include "tg_prologue.cuh"
+#include "tg_adapt.cuh"
 #include "tg_eval.cuh"
-
-#define TG_TAG_PROP 0x50524f50u
-#define TG_TAG_MH   0x4d485f55u
-#define TG_TAG_PT   0x50545f55u
-#define TG_MAX_LEARN 16
-
-struct TgMala {
-    double c0, eps1, eps2, A1, target;
-    int    n_learn;
-    long   Nt_learn[TG_MAX_LEARN + 1];
-    long   periods[TG_MAX_LEARN];
-    long   dN_mixing;
-    unsigned long long seed;
-    int    flags;
-};
-
-struct TgCtrl {            // lives in device memory so that a captured CUDA graph can be replayed
-    long i;                // current iteration
-    long i0;               // first iteration of the current record chunk
-    unsigned int ticket;   // CTA completion counter of the finish kernel
-    int pad;
-};
-
-struct TgState {
-    int C, E, Ce, Nv, Np;
-    double *vars_cur, *vars_prop;          // [C][Nv]
-    double *params_cur, *params_prop;      // [C][Np]
-    double *logL_cur, *logPrior_cur, *logPost_cur, *Pmove;   // [C]
-    int    *moved;                         // [C]
-    // Adaptive proposal.  (mu, Sigma, chol(Sigma+eps2 I)) live in THREE slots per chain: the live one
-    // and the two candidates of the running step ("proposal rejected" / "proposal accepted"), which the
-    // speculative kernel fills while the fused model+likelihood kernel runs; the finish kernel only
-    // switches live[c].  Slot-major: mu [3][C][Nv], cov / chol [3][C][Nv][Nv] (row-major, lower part of chol).
-    double *mu, *cov, *chol;
-    double *sigma;                         // [C]
-    int    *live;                          // [C]  live slot 0..2
-    int    *chol_fail;                     // [3][C]
-    int    *sticky_status;                 // [C]
-    const int    *index_to_relax;          // [Nv]
-    const double *Tcoefs;                  // [C]
-    TgCtrl *ctrl;
-};
 
 struct TgRecDev {          // device ring of per-step records (drained once per chunk)
     long    cap;           // steps the ring holds
@@ -72,177 +31,48 @@ __device__ __forceinline__ void tg_normal_pair(uint4 r, double *z0, double *z1)
     *z0 = rad * c; *z1 = rad * s;
 }
 
-__device__ __forceinline__ size_t tg_slot_vec(const TgState &s, int slot, int c) { return ((size_t)slot * s.C + c) * s.Nv; }
-__device__ __forceinline__ size_t tg_slot_mat(const TgState &s, int slot, int c) { return ((size_t)slot * s.C + c) * s.Nv * s.Nv; }
-
-// learning zone of iteration it?  (MALA.cpp:641-652)
-__device__ __forceinline__ int tg_learning(const TgMala &m, long it)
-{
-    int learn = 0, which = 0;
-    for (int l = 0; l < m.n_learn; l++) if (it >= m.Nt_learn[l] && it < m.Nt_learn[l + 1]) { learn = 1; which = l; }
-    if (learn && (it % m.periods[which]) != 0) learn = 0;
-    return learn;
-}
-
-// In-CTA Cholesky (lower, right-looking) of the n x n matrix S (leading dimension ld; shared or global
-// memory), 256 threads as a 16x16 grid, ONE barrier per column: while the rank-1 update of column j runs,
-// every thread recomputes the next pivot from the double-buffered diagonal, so the freshly updated
-// entries of column j+1 are scaled in the same pass.  On exit the strictly lower part and the diagonal of
-// S hold L.  work: 4*n doubles (two column buffers, two diagonal buffers).  Returns 1 if a pivot was <= 0 / NaN.
-__device__ int tg_cholesky_inplace(double *S, int n, int ld, double *work)
-{
-    __shared__ int s_fail;
-    const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
-    double *col0 = work, *dg0 = work + 2 * n;     // column buffers col0 + (j&1)*n, diagonal buffers dg0 + (j&1)*n
-    if (tid == 0) s_fail = 0;
-    for (int i = tid; i < n; i += blockDim.x) dg0[i] = S[i * ld + i];
-    __syncthreads();
-    {   // column 0
-        const double pv = dg0[0];
-        const double inv = rsqrt(pv);
-        if (tid == 0) { if (!(pv > 0.0)) s_fail = 1; S[0] = pv * inv; }
-        for (int i = 1 + tid; i < n; i += blockDim.x) { const double v = S[i * ld] * inv; S[i * ld] = v; col0[i] = v; }
-    }
-    __syncthreads();
-    for (int j = 0; j + 1 < n; j++) {
-        const double *cj = col0 + (j & 1) * n; double *cn = col0 + ((j + 1) & 1) * n;
-        const double *dj = dg0 + (j & 1) * n;  double *dn = dg0 + ((j + 1) & 1) * n;
-        // next pivot, recomputed by every thread with the same arithmetic as the diagonal update below
-        const double cnext = cj[j + 1];
-        const double pv = fma(-cnext, cnext, dj[j + 1]);
-        const double inv = rsqrt(pv);
-        if (tid == 0) { if (!(pv > 0.0)) s_fail = 1; S[(j + 1) * ld + (j + 1)] = pv * inv; }
-        for (int t = j + 1 + tid; t < n; t += blockDim.x) { const double c = cj[t]; dn[t] = fma(-c, c, dj[t]); }
-        // strictly-lower trailing update; column j+1 is scaled on the fly
-        const int r = n - j - 1;
-        for (int ii = ty; ii < r; ii += 16) {
-            const int i = j + 1 + ii;
-            const double ci = cj[i];
-            double *row = S + (size_t)i * ld + (j + 1);
-            for (int kk = tx; kk < ii; kk += 16) {
-                double v = fma(-ci, cj[j + 1 + kk], row[kk]);
-                if (kk == 0) { v *= inv; cn[i] = v; }
-                row[kk] = v;
-            }
-        }
-        __syncthreads();
-    }
-    return s_fail;
-}
-
-// One Cholesky job: L = chol(cov + eps2*I) of (slot, chain) -> chol[slot][c]; staged in shared memory
-// when it fits (dyn = shared-memory buffer of Nv*ld + 4*Nv doubles, or NULL: factorise in place in HBM).
-__device__ void tg_factor_slot(const TgState &s, double eps2, int slot, int c, double *dyn, double *work)
-{
-    const int Nv = s.Nv, tid = threadIdx.x, nt = blockDim.x;
-    const double *cv = s.cov + tg_slot_mat(s, slot, c);
-    double *Lg = s.chol + tg_slot_mat(s, slot, c);
-    const int ld = dyn ? (Nv | 1) : Nv;
-    double *L = dyn ? dyn : Lg;
-    for (int e = tid; e < Nv * Nv; e += nt) {
-        const int i = e / Nv, k = e - i * Nv;
-        if (k <= i) L[i * ld + k] = cv[e] + ((i == k) ? eps2 : 0.0);
-    }
-    __syncthreads();
-    const int fail = tg_cholesky_inplace(L, Nv, ld, work);
-    // staged factor goes out PACKED (row i at i(i+1)/2): the propose kernel copies it flat into shared memory
-    if (dyn) for (int i = tid >> 5; i < Nv; i += nt >> 5) for (int k = tid & 31; k <= i; k += 32) Lg[i * (i + 1) / 2 + k] = L[i * ld + k];
-    if (tid == 0) s.chol_fail[slot * s.C + c] = fail;
-}
-
-struct TgSpecArgs {
-    TgState s;
-    TgMala  m;
-    int     smem_matrix;    // 1: the Nv x Nv matrix is staged in shared memory
-    int     init;           // 1: factorise the LIVE slot of every chain (create / restore); 0: speculative step
-};
-
-// K_spec: grid (C, 2).  blockIdx.y = 0: "proposal rejected" candidate (x = vars_cur), 1: "accepted"
-// (x = vars_prop).  Robbins-Monro update of (mu, Sigma) with the p3/p2 truncations (MALA.cpp:292-315,
-// :135-176) from the live slot into candidate slot (live+1+cand)%3, then its Cholesky factor.  Runs on a
-// second stream next to the fused model+likelihood kernel of the same step; the finish kernel selects
-// the candidate that matches the Metropolis decision.  The acceptance only enters sigma (a scalar,
-// applied as sqrt(sigma) at proposal time), so both candidates are exact.  chol layout: packed lower
-// triangle when smem_matrix, else full row-major (factorised in place in HBM).
-__global__ void __launch_bounds__(256) tg_k_spec(TgSpecArgs a)
-{
-    extern __shared__ double tg_dyn_smem[];
-    __shared__ double r1[256];
-    __shared__ double s_scale;
-    const TgState &s = a.s;
-    const int c = blockIdx.x, cand = blockIdx.y, tid = threadIdx.x, nt = blockDim.x;
-    const int Nv = s.Nv;
-    double *dyn = a.smem_matrix ? tg_dyn_smem : nullptr;
-    double *work = a.smem_matrix ? tg_dyn_smem + (size_t)Nv * (Nv | 1) : tg_dyn_smem;
-    const int live = s.live[c];
-    if (a.init) { if (cand == 0) tg_factor_slot(s, a.m.eps2, live, c, dyn, work); return; }
-    const long it = s.ctrl->i;
-    if (!tg_learning(a.m, it)) return;
-    const int slot = (live + 1 + cand) % 3;
-    const double gamma = a.m.c0 / (1.0 + (double)it);
-    const double *xv = (cand ? s.vars_prop : s.vars_cur) + (size_t)c * Nv;
-    const double *mu0 = s.mu + tg_slot_vec(s, live, c), *cov0 = s.cov + tg_slot_mat(s, live, c);
-    double *mu = s.mu + tg_slot_vec(s, slot, c), *cov = s.cov + tg_slot_mat(s, slot, c);
-    // mu <- p3(mu + gamma (x - mu))
-    double part = 0;
-    for (int v = tid; v < Nv; v += nt) { const double m = mu0[v] + gamma * (xv[v] - mu0[v]); mu[v] = m; part += m * m; }
-    r1[tid] = part; __syncthreads();
-    for (int h = 128; h > 0; h >>= 1) { if (tid < h) r1[tid] += r1[tid + h]; __syncthreads(); }
-    if (tid == 0) { const double nrm = sqrt(r1[0]); s_scale = (nrm <= a.m.A1) ? 1.0 : a.m.A1 / nrm; }
-    __syncthreads();
-    if (s_scale != 1.0) for (int v = tid; v < Nv; v += nt) mu[v] = mu[v] * s_scale;
-    __syncthreads();
-    // Sigma <- p2(Sigma + gamma ((x-mu)(x-mu)^T - Sigma))
-    part = 0;
-    for (int e = tid; e < Nv * Nv; e += nt) {
-        const int i = e / Nv, k = e - i * Nv;
-        const double mat = (xv[i] - mu[i]) * (xv[k] - mu[k]);
-        const double cn = cov0[e] + gamma * (mat - cov0[e]);
-        cov[e] = cn; part += cn * cn;
-    }
-    __syncthreads();
-    r1[tid] = part; __syncthreads();
-    for (int h = 128; h > 0; h >>= 1) { if (tid < h) r1[tid] += r1[tid + h]; __syncthreads(); }
-    if (tid == 0) { const double nrm = sqrt(r1[0]); s_scale = (nrm <= a.m.A1) ? 1.0 : a.m.A1 / nrm; }
-    __syncthreads();
-    if (s_scale != 1.0) for (int e = tid; e < Nv * Nv; e += nt) cov[e] = cov[e] * s_scale;
-    __syncthreads();
-    tg_factor_slot(s, a.m.eps2, slot, c, dyn, work);
-}
-
 struct TgProposeArgs {
     TgState   s;
     TgMala    m;
     TgProArgs pro;          // pro.params == s.params_prop
     int       packed;       // 1: chol is stored packed (tg_k_spec staged it in shared memory), 0: full row-major
     int       tri_smem;     // 1: the packed lower triangle of L (Nv(Nv+1)/2 doubles) fits the dynamic shared memory
+    int       fused_spec;   // 1: grid (C, 3): rows 1 and 2 are the speculative adaptation CTAs (tg_adapt.cuh)
+    int       smem_matrix;  // TgSpecArgs.smem_matrix of those CTAs
 };
 
-// K1: one CTA per chain.  Draw z, form x' = x + sqrt(sigma)*L z with L = chol(Sigma+eps2 I) of the live
-// slot (== chol((Sigma+eps2 I)*sigma) z, MALA.cpp:335-353, up to rounding), scatter into params, then run
-// the model prologue + log-prior on the proposed parameter vector.
+// K1, grid (C, 1) or (C, 3).  Row 0, one CTA per chain: draw z, form x' = x + sqrt(sigma)*L z with
+// L = chol(Sigma+eps2 I) of the live slot (== chol((Sigma+eps2 I)*sigma) z, MALA.cpp:335-353, up to
+// rounding), scatter into params, then run the model prologue + log-prior on the proposed parameter
+// vector.  Rows 1 and 2 (fused_spec): the adapted proposal (Robbins-Monro + Cholesky) this chain will
+// use next step if the proposal is rejected / accepted; row 2 recomputes x' itself (same arithmetic,
+// same bits) so that the three CTAs of a chain are independent.
 __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
 {
     extern __shared__ double tg_dyn_smem[];
     __shared__ double s_z[512];
     const TgState &s = a.s;
-    const int c = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    const int c = blockIdx.x, role = blockIdx.y, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
     const long it = s.ctrl->i;
+    if (role != 0) {
+        if (!tg_learning(a.m, it)) return;
+        if (role == 1) { tg_spec_body(s, a.m, a.smem_matrix, 0, c, 0, tg_dyn_smem); return; }
+    }
     const double *L = s.chol + tg_slot_mat(s, s.live[c], c);
     TG_STAMP(0);
     const double sq = sqrt(s.sigma[c]);
     const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PROP, (uint32_t)(a.m.seed >> 32));
     if (a.tri_smem) {
         // ---- fast path: z and the packed lower triangle of L in shared memory, one thread per row ----
-        double *tri = tg_dyn_smem;                                  // row i at i(i+1)/2
+        double *tri = tg_dyn_smem;                                  // packed by columns (tg_colpack)
         double *zz = tri + (size_t)Nv * (Nv + 1) / 2;
         if (a.packed) {
             const int ntri = Nv * (Nv + 1) / 2;
 #pragma unroll 8
             for (int e = tid; e < ntri; e += nt) tri[e] = __ldcg(L + e);
         } else {
-            for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; if (k <= i) tri[i * (i + 1) / 2 + k] = __ldcg(L + e); }
+            for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; if (k <= i) tri[tg_colpack(Nv, k) + i - k] = __ldcg(L + e); }
         }
         for (int v = tid; v < Nv; v += nt) {
             double z0, z1;
@@ -252,12 +82,21 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
         __syncthreads();
         TG_STAMP(1);
         for (int i = tid; i < Nv; i += nt) {
-            const double *row = tri + i * (i + 1) / 2;
+            const double *el = tri + i;                             // L(i,k) = tri[colpack(k) - k + i]: conflict-free across rows
             double a0 = 0.0, a1 = 0.0;                              // fixed order: even / odd columns, then a0 + a1
             int k = 0;
-            for (; k + 1 <= i; k += 2) { a0 = fma(row[k], zz[k], a0); a1 = fma(row[k + 1], zz[k + 1], a1); }
-            if (k <= i) a0 = fma(row[k], zz[k], a0);
-            s.vars_prop[(size_t)c * Nv + i] = s.vars_cur[(size_t)c * Nv + i] + sq * (a0 + a1);
+            for (; k + 1 <= i; k += 2) {
+                a0 = fma(el[0], zz[k], a0); a1 = fma(el[Nv - k - 1], zz[k + 1], a1);
+                el += 2 * (Nv - k) - 3;                             // colpack(k+2)-(k+2) - (colpack(k)-k)
+            }
+            if (k <= i) a0 = fma(el[0], zz[k], a0);
+            const double xp = s.vars_cur[(size_t)c * Nv + i] + sq * (a0 + a1);
+            if (role == 0) s.vars_prop[(size_t)c * Nv + i] = xp; else s_z[i] = xp;
+        }
+        if (role == 2) {                                            // fused_spec implies tri_smem and Nv <= 512
+            __syncthreads();
+            tg_spec_body(s, a.m, a.smem_matrix, 0, c, 1, tg_dyn_smem, s_z);
+            return;
         }
     } else
     // general path (very large Nv): standard normals 512 per pass, rows from HBM

@@ -19,7 +19,7 @@ F_FIX_SWAP_BOOKKEEPING = 1
 
 EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", "tg_eval_upload", "tg_eval_resident",
            "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
-           "tg_step_end", "tg_partials_device_ptr", "tg_sync", "tg_kernel_time", "tg_set_tuning", "tg_set_subtiles",
+           "tg_step_end", "tg_partials_device_ptr", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_event_record", "tg_event_elapsed_ms"]
 
 
@@ -79,8 +79,7 @@ class GpuLibrary:
         L.tg_partials_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int)]
         L.tg_sync.argtypes = [C.c_void_p]
         L.tg_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_double), C.POINTER(C.c_long)]
-        L.tg_set_tuning.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
-        L.tg_set_subtiles.argtypes = [C.c_void_p, C.c_int]
+        L.tg_set_tuning.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
         L.tg_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.tg_event_record.argtypes = [C.c_void_p, C.c_int]
         L.tg_event_elapsed_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
@@ -284,10 +283,8 @@ class GpuModelDef:
     def sync(self):
         self.lib.check(self.lib.lib.tg_sync(self.h))
 
-    def set_tuning(self, chains_per_block=0, bins_per_thread=0, use_graph=-1, nsub=0):
-        self.lib.check(self.lib.lib.tg_set_tuning(self.h, chains_per_block, bins_per_thread, use_graph))
-        if nsub > 0:
-            self.lib.check(self.lib.lib.tg_set_subtiles(self.h, nsub))
+    def set_tuning(self, chains_per_block=0, light_subtiles=0, use_graph=-1, heavy_group=0):
+        self.lib.check(self.lib.lib.tg_set_tuning(self.h, chains_per_block, heavy_group, light_subtiles, use_graph))
 
     def timer_start(self):
         self.lib.check(self.lib.lib.tg_event_record(self.h, 0))
