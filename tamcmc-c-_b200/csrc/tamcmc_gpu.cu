@@ -18,10 +18,19 @@ static int fail(int code, const std::string &msg) { g_err = msg; return code; }
 struct EvalBuf {                 // tables + results for a batch of B parameter vectors
     int       cap = 0;
     TgTables  t{};
+    // inputs and results of a batch are contiguous, laid out for the batch size B of the call:
+    // in = params[B][Np] | T[B];  out = logL[B] | logPrior[B] | logPost[B] | status[B] (int) -- one copy each way
+    double   *in = nullptr, *out = nullptr;
     double   *params = nullptr, *T = nullptr;
     double2  *partials = nullptr, *sums = nullptr;
     double   *logL = nullptr, *logPrior = nullptr, *logPost = nullptr;
     int      *status = nullptr;
+    int       B = 0;               // batch size the pointers above are laid out for
+    double   *pin_in = nullptr, *pin_out = nullptr;    // pinned host staging of the same layout
+    void layout(int b, int Np) {
+        B = b; params = in; T = in + (size_t)b * Np;
+        logL = out; logPrior = out + b; logPost = out + 2 * (size_t)b; status = (int *)(out + 3 * (size_t)b);
+    }
 };
 
 struct tg_handle {
@@ -45,6 +54,7 @@ struct tg_handle {
     std::vector<int4> items_host;          // bin partition: (first bin, sub-tiles, weight = windows crossing, heavy?)
     bool       no_order = false;
     cudaGraphExec_t graph = nullptr;
+    cudaGraphExec_t ev_graph = nullptr; int ev_graph_B = 0;   // tg_eval: copy in, prologue, fused kernel, reduce+finalize, copy out
     // eval-kernel timing
     bool       timing = false;
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
@@ -71,16 +81,27 @@ extern "C" int tg_dbg_specs(long long *out) { return cudaMemcpyFromSymbol(out, t
 extern "C" int tg_dbg_clocks(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_clk, sizeof(long long) * 32) == cudaSuccess ? 0 : -2; }
 #endif
 
+static void drop_graphs(tg_handle *h)
+{
+    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+    if (h->ev_graph) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }
+}
+
 static int alloc_evalbuf(tg_handle *h, EvalBuf &b, int B)
 {
     if (B <= b.cap) return TG_OK;
     const size_t nc = (size_t)B * h->d.ncomp_max;
     b.cap = B;
+    if (h->ev_graph) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }     // the buffers move
     DA(b.t.nu, nc); DA(b.t.h, nc); DA(b.t.q, nc); DA(b.t.ifc, nc); DA(b.t.t2sq, nc); DA(b.t.lo, nc); DA(b.t.hi, nc);
     DA(b.t.ncomp, B); DA(b.t.wlo, B); DA(b.t.whi, B); DA(b.t.noise, (size_t)B * TG_NOISE_STRIDE); DA(b.t.status, B); DA(b.t.work, B); DA(b.t.logprior, B);
-    DA(b.params, (size_t)B * h->d.Np); DA(b.T, B);
+    DA(b.in, (size_t)B * (h->d.Np + 1)); DA(b.out, (size_t)B * 4);
     DA(b.partials, (size_t)B * h->max_items); DA(b.sums, B);
-    DA(b.logL, B); DA(b.logPrior, B); DA(b.logPost, B); DA(b.status, B);
+    if (b.pin_in) cudaFreeHost(b.pin_in);
+    if (b.pin_out) cudaFreeHost(b.pin_out);
+    CK(cudaHostAlloc((void **)&b.pin_in, (size_t)B * (h->d.Np + 1) * 8, cudaHostAllocDefault));
+    CK(cudaHostAlloc((void **)&b.pin_out, (size_t)B * 4 * 8, cudaHostAllocDefault));
+    b.layout(B, h->d.Np);
     return TG_OK;
 }
 
@@ -185,7 +206,7 @@ static int build_items(tg_handle *h, EvalBuf &b, int B)
     h->items_host = items;
     h->nitems = (int)items.size();
     h->u_sp.B = h->u_ev.B = -1;                     // units are rebuilt at the next launch
-    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }     // grid size changed
+    drop_graphs(h);                                 // grid size changed
     return TG_OK;
 }
 
@@ -232,7 +253,7 @@ extern "C" int tg_set_tuning(tg_handle *h, int chains_per_block, int heavy_group
     if (chains_per_block > 0) { h->chains_per_block = std::min(chains_per_block, h->max_cpb); h->u_sp.B = h->u_ev.B = -1; }
     if (heavy_group > 0) { h->heavy_group = heavy_group; h->u_sp.B = h->u_ev.B = -1; }
     if (use_graph >= 0) h->use_graph = use_graph;
-    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
+    drop_graphs(h);
     if (light_subtiles > 0 && light_subtiles != h->light_sub) {
         h->light_sub = std::min(light_subtiles, 4096);
         int r = build_items(h, h->sp, h->s.C); if (r) return r;
@@ -424,10 +445,11 @@ extern "C" int tg_destroy(tg_handle *h)
     if (!h) return TG_OK;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    if (h->graph) cudaGraphExecDestroy(h->graph);
+    drop_graphs(h);
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
     for (void *q : h->allocs) cudaFree(q);
+    for (EvalBuf *b : {&h->sp, &h->ev}) { if (b->pin_in) cudaFreeHost(b->pin_in); if (b->pin_out) cudaFreeHost(b->pin_out); }
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return TG_OK;
@@ -448,16 +470,20 @@ extern "C" int tg_eval_upload(tg_handle *h, const double *params, int B, const d
     if (!h || !params || !T || B < 1) return fail(TG_E_BADARG, "tg_eval_upload: bad argument");
     CK(cudaSetDevice(h->device));
     { int r = alloc_evalbuf(h, h->ev, B); if (r) return r; }
-    CK(cudaMemcpyAsync(h->ev.params, params, (size_t)B * h->d.Np * 8, cudaMemcpyHostToDevice, h->stream));
-    CK(cudaMemcpyAsync(h->ev.T, T, (size_t)B * 8, cudaMemcpyHostToDevice, h->stream));
+    EvalBuf &b = h->ev;
+    if (b.B != B) { CK(cudaStreamSynchronize(h->stream)); b.layout(B, h->d.Np); }
+    // one host->device copy from the pinned staging buffer (a pageable source would make the copy synchronous)
+    memcpy(b.pin_in, params, (size_t)B * h->d.Np * 8);
+    memcpy(b.pin_in + (size_t)B * h->d.Np, T, (size_t)B * 8);
+    CK(cudaMemcpyAsync(b.in, b.pin_in, (size_t)B * (h->d.Np + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     return TG_OK;
 }
 
 static int eval_resident(tg_handle *h, int B, double *model_dev)
 {
-    if (B < 1 || B > h->ev.cap) return fail(TG_E_BADARG, "tg_eval_resident: B exceeds the uploaded batch");
-    int r = launch_eval_kernels(h, h->ev, h->ev.params, B, model_dev, true, true); if (r) return r;
-    tg_k_finalize_eval<<<(B + 127) / 128, 128, 0, h->stream>>>(h->d, h->ev.sums, h->ev.T, h->ev.t, B, h->ev.logL, h->ev.logPrior, h->ev.logPost, h->ev.status);
+    if (B < 1 || B != h->ev.B) return fail(TG_E_BADARG, "tg_eval_resident: B differs from the uploaded batch");
+    int r = launch_eval_kernels(h, h->ev, h->ev.params, B, model_dev, true, false); if (r) return r;
+    tg_k_reduce_finalize<<<B, 256, 0, h->stream>>>(h->d, h->ev.partials, h->nitems, h->ev.sums, h->ev.T, h->ev.t, h->ev.logL, h->ev.logPrior, h->ev.logPost, h->ev.status);
     h->n_launch_total++;
     CK(cudaGetLastError());
     return TG_OK;
@@ -472,19 +498,56 @@ extern "C" int tg_eval_resident(tg_handle *h, int B)
 
 extern "C" int tg_eval_fetch(tg_handle *h, int B, double *logL, double *logPrior, double *logPost, int *status)
 {
-    if (!h || B < 1 || B > h->ev.cap) return fail(TG_E_BADARG, "tg_eval_fetch: bad argument");
+    if (!h || B < 1 || B != h->ev.B) return fail(TG_E_BADARG, "tg_eval_fetch: bad argument");
     CK(cudaSetDevice(h->device));
-    if (logL) CK(cudaMemcpyAsync(logL, h->ev.logL, (size_t)B * 8, cudaMemcpyDeviceToHost, h->stream));
-    if (logPrior) CK(cudaMemcpyAsync(logPrior, h->ev.logPrior, (size_t)B * 8, cudaMemcpyDeviceToHost, h->stream));
-    if (logPost) CK(cudaMemcpyAsync(logPost, h->ev.logPost, (size_t)B * 8, cudaMemcpyDeviceToHost, h->stream));
-    if (status) CK(cudaMemcpyAsync(status, h->ev.status, (size_t)B * 4, cudaMemcpyDeviceToHost, h->stream));
+    EvalBuf &b = h->ev;
+    CK(cudaMemcpyAsync(b.pin_out, b.out, (size_t)B * 28, cudaMemcpyDeviceToHost, h->stream));     // one device->host copy
     CK(cudaStreamSynchronize(h->stream));
+    if (logL) memcpy(logL, b.pin_out, (size_t)B * 8);
+    if (logPrior) memcpy(logPrior, b.pin_out + B, (size_t)B * 8);
+    if (logPost) memcpy(logPost, b.pin_out + 2 * (size_t)B, (size_t)B * 8);
+    if (status) memcpy(status, b.pin_out + 3 * (size_t)B, (size_t)B * 4);
     return TG_OK;
 }
 
 extern "C" int tg_eval(tg_handle *h, const double *params, int B, const double *T,
                        double *logL, double *logPrior, double *logPost, int *status, double *model)
 {
+    if (!h || !params || !T || B < 1) return fail(TG_E_BADARG, "tg_eval: bad argument");
+    if (!model && h->use_graph && !h->timing) {
+        // the whole call as one graph launch: H2D of the packed inputs, prologue, fused kernel, reduce+finalize, D2H of the packed results
+        CK(cudaSetDevice(h->device));
+        { int r = alloc_evalbuf(h, h->ev, B); if (r) return r; }
+        EvalBuf &b = h->ev;
+        if (b.B != B) { CK(cudaStreamSynchronize(h->stream)); b.layout(B, h->d.Np); }
+        if (h->ev_graph && h->ev_graph_B != B) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }
+        if (!h->ev_graph) {
+            if (h->u_ev.B != B) { int r = build_units(h, h->u_ev, B); if (r) return r; }
+            cudaGraph_t g;
+            const long lt = h->n_launch_total, le = h->n_eval_launch;
+            CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+            cudaMemcpyAsync(b.in, b.pin_in, (size_t)B * (h->d.Np + 1) * 8, cudaMemcpyHostToDevice, h->stream);
+            int r = eval_resident(h, B, nullptr);
+            cudaMemcpyAsync(b.pin_out, b.out, (size_t)B * 28, cudaMemcpyDeviceToHost, h->stream);
+            cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
+            h->n_launch_total = lt; h->n_eval_launch = le;
+            if (r) return r;
+            CK(ce);
+            CK(cudaGraphInstantiate(&h->ev_graph, g, 0));
+            cudaGraphDestroy(g);
+            h->ev_graph_B = B;
+        }
+        memcpy(b.pin_in, params, (size_t)B * h->d.Np * 8);
+        memcpy(b.pin_in + (size_t)B * h->d.Np, T, (size_t)B * 8);
+        CK(cudaGraphLaunch(h->ev_graph, h->stream));
+        h->n_launch_total += 3; h->n_eval_launch += 1;
+        CK(cudaStreamSynchronize(h->stream));
+        if (logL) memcpy(logL, b.pin_out, (size_t)B * 8);
+        if (logPrior) memcpy(logPrior, b.pin_out + B, (size_t)B * 8);
+        if (logPost) memcpy(logPost, b.pin_out + 2 * (size_t)B, (size_t)B * 8);
+        if (status) memcpy(status, b.pin_out + 3 * (size_t)B, (size_t)B * 4);
+        return TG_OK;
+    }
     int r = tg_eval_upload(h, params, B, T); if (r) return r;
     double *model_dev = nullptr;
     if (model) CK(cudaMalloc(&model_dev, (size_t)B * h->d.Nx * 8));

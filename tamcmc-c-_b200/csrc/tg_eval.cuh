@@ -507,6 +507,31 @@ __global__ void tg_k_finalize_eval(TgDesc d, const double2 *sums, const double *
     logL[c] = L; logPrior[c] = t.logprior[c]; logPost[c] = L + t.logprior[c]; status[c] = st;
 }
 
+// tg_k_reduce + tg_k_finalize_eval in one launch (the tg_eval call path): CTA c reduces the partials of
+// chain c in the same fixed order as tg_k_reduce, thread 0 finishes the chain.
+__global__ void __launch_bounds__(256) tg_k_reduce_finalize(TgDesc d, const double2 *partials, int ntiles, double2 *sums, const double *T, TgTables t,
+                                                            double *logL, double *logPrior, double *logPost, int *status)
+{
+    __shared__ double r1[256], r2[256];
+    const int c = blockIdx.x, tid = threadIdx.x;
+    double a1 = 0, a2 = 0;
+    for (int k = tid; k < ntiles; k += 256) { const double2 v = partials[(size_t)c * ntiles + k]; a1 += v.x; a2 += v.y; }
+    r1[tid] = a1; r2[tid] = a2;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (tid < s) { r1[tid] += r1[tid + s]; r2[tid] += r2[tid + s]; }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const double2 sm = make_double2(r1[0], r2[0]);
+        sums[c] = sm;
+        int st = t.status[c];
+        const double L = tg_logl_from_sums(d, sm, T[c], st);
+        if (L != L) st |= TG_ST_NAN_LOGL;
+        logL[c] = L; logPrior[c] = t.logprior[c]; logPost[c] = L + t.logprior[c]; status[c] = st;
+    }
+}
+
 __global__ void tg_k_lnx(const double *x, double *lnx, int n)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
