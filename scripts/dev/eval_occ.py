@@ -14,7 +14,7 @@ for name in sys.argv[1:]:
     md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=C), lib=lib)
     md.eval_upload(P, T)
     for cpb in (2, 3, 4, 5):
-        md.set_tuning(cpb, 4, -1); md.kernel_time(reset=1)
+        md.set_tuning(cpb, 8, -1, 2); md.kernel_time(reset=1)
         for _ in range(20): md.eval_resident(C)
         n, ms, tot = md.kernel_time(reset=2)
         print("%-12s cpb=%d: eval kernel %.1f us" % (name, cpb, ms / n * 1e3))

@@ -14,10 +14,10 @@ md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=Cn), lib=lib)
 md.eval_upload(P, T)
 for _ in range(5): md.eval_resident(Cn)
 md.sync()
-buf = (C.c_longlong * (8192 * 6))()
+buf = (C.c_longlong * (8192 * 8))()
 lib.lib.tg_dbg_ctas.argtypes = [C.POINTER(C.c_longlong)]
 lib.lib.tg_dbg_ctas(buf)
-a = np.array(buf, dtype=np.int64).reshape(8192, 6); a = a[a[:, 5] > 0]; a = a[a[:, 4] >= a[:, 4].max() - 150000]   # last launch only
+a = np.array(buf, dtype=np.int64).reshape(8192, 8); a = a[a[:, 5] > 0]; a = a[a[:, 4] >= a[:, 4].max() - 150000]   # last launch only
 t0, t1, t2 = a[:, 0], a[:, 1], a[:, 2]
 sm = a[:, 3] >> 32; tile = a[:, 3] & 0xffffffff
 g0, g1 = a[:, 4], a[:, 5]
@@ -43,3 +43,13 @@ print("heavy CTAs: %d, mean dur %.1f us; light: %d, mean dur %.2f us" % (heavy.s
 # histogram
 h, e = np.histogram(dur, bins=[0, 1, 2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 1000])
 print("hist", list(zip(e[:-1].tolist(), h.tolist())))
+
+# phase breakdown (cycles -> us at 1965 MHz): setup, list building, chain loops, final reduction
+f = 1965.0
+setup = (t1 - t0) / f; lists = a[:, 6] / f; tail = (t2 - a[:, 7]) / f; loops = (a[:, 7] - t1) / f - lists
+for name, sel in (("heavy", heavy), ("light", ~heavy)):
+    tot = dur[sel].sum()
+    print("%s units: n=%d  setup %.2f us (%.1f%%)  lists %.2f (%.1f%%)  loops %.2f (%.1f%%)  final %.2f (%.1f%%)  | mean dur %.2f" % (
+        name, sel.sum(), setup[sel].mean(), 100 * setup[sel].sum() / tot, lists[sel].mean(), 100 * lists[sel].sum() / tot,
+        loops[sel].mean(), 100 * loops[sel].sum() / tot, tail[sel].mean(), 100 * tail[sel].sum() / tot, dur[sel].mean()))
+print("share of all CTA time: heavy %.3f light %.3f" % (dur[heavy].sum() / dur.sum(), dur[~heavy].sum() / dur.sum()))

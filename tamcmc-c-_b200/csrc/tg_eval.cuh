@@ -472,19 +472,29 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
 // Sums the per-tile pairs of each chain in a fixed order (thread-strided serial sums, then a
 // shared-memory tree) -> sums[c] = (sum y/m, sum ln m).  In the bin-sharded variant this is the
 // buffer that is all-reduced across GPUs.
+// Fixed-order sum of one pair per thread over a CTA of 256 (used by every kernel that totals the
+// partials of a chain, so that they agree to the bit): xor-shuffle tree inside each warp, then the eight
+// warp sums in order.  One barrier; s_part is [8] shared double2.
+__device__ __forceinline__ double2 tg_block_sum2(double a1, double a2, double2 *s_part)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a1 += __shfl_xor_sync(0xffffffffu, a1, o); a2 += __shfl_xor_sync(0xffffffffu, a2, o); }
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = make_double2(a1, a2);
+    __syncthreads();
+    double t1 = 0, t2 = 0;
+#pragma unroll
+    for (int w = 0; w < TG_THREADS / 32; w++) { const double2 v = s_part[w]; t1 += v.x; t2 += v.y; }
+    return make_double2(t1, t2);
+}
+
 __global__ void __launch_bounds__(256) tg_k_reduce(const double2 *partials, int ntiles, double2 *sums)
 {
-    __shared__ double r1[256], r2[256];
+    __shared__ double2 s_part[8];
     const int c = blockIdx.x, tid = threadIdx.x;
     double a1 = 0, a2 = 0;
     for (int t = tid; t < ntiles; t += 256) { const double2 v = partials[(size_t)c * ntiles + t]; a1 += v.x; a2 += v.y; }
-    r1[tid] = a1; r2[tid] = a2;
-    __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) {
-        if (tid < s) { r1[tid] += r1[tid + s]; r2[tid] += r2[tid + s]; }
-        __syncthreads();
-    }
-    if (tid == 0) sums[c] = make_double2(r1[0], r2[0]);
+    const double2 sm = tg_block_sum2(a1, a2, s_part);
+    if (tid == 0) sums[c] = sm;
 }
 
 // logL = -p*(s1+s2)/T (likelihoods.cpp:25 + model_def.cpp:302) or -s1/T; logPost = logL + logPrior
@@ -512,18 +522,12 @@ __global__ void tg_k_finalize_eval(TgDesc d, const double2 *sums, const double *
 __global__ void __launch_bounds__(256) tg_k_reduce_finalize(TgDesc d, const double2 *partials, int ntiles, double2 *sums, const double *T, TgTables t,
                                                             double *logL, double *logPrior, double *logPost, int *status)
 {
-    __shared__ double r1[256], r2[256];
+    __shared__ double2 s_part[8];
     const int c = blockIdx.x, tid = threadIdx.x;
     double a1 = 0, a2 = 0;
     for (int k = tid; k < ntiles; k += 256) { const double2 v = partials[(size_t)c * ntiles + k]; a1 += v.x; a2 += v.y; }
-    r1[tid] = a1; r2[tid] = a2;
-    __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) {
-        if (tid < s) { r1[tid] += r1[tid + s]; r2[tid] += r2[tid + s]; }
-        __syncthreads();
-    }
+    const double2 sm = tg_block_sum2(a1, a2, s_part);
     if (tid == 0) {
-        const double2 sm = make_double2(r1[0], r2[0]);
         sums[c] = sm;
         int st = t.status[c];
         const double L = tg_logl_from_sums(d, sm, T[c], st);

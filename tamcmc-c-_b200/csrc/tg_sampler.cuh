@@ -180,66 +180,68 @@ __device__ __forceinline__ void tg_write_record(const TgFinishArgs &a, long slot
 // iteration counter.
 __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
 {
-    __shared__ double r1[256], r2[256];
-    __shared__ int s_accept, s_last, s_learn;
-    __shared__ double s_r;
+    __shared__ double2 s_part[8];
+    __shared__ int s_accept, s_last;
     const TgState &s = a.s;
     const int c = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
+    // Every load that does not depend on the decision is issued up front: the kernel is a chain of
+    // global-memory round trips, so they are kept to the unavoidable ones.
     const long it = s.ctrl->i;
+    double a1 = 0, a2 = 0;
+    if (!a.presummed) for (int t = tid; t < a.ntiles; t += nt) { const double2 v = a.partials[(size_t)c * a.ntiles + t]; a1 += v.x; a2 += v.y; }
+    const bool small = (Nv <= 256 && Np <= 256);   // one element of the proposed point per thread, held in registers
+    double vprop = 0.0, pprop = 0.0;
+    if (small) { if (tid < Nv) vprop = s.vars_prop[(size_t)c * Nv + tid]; if (tid < Np) pprop = s.params_prop[(size_t)c * Np + tid]; }
+    int st = 0, live = 0, fail0 = 0, fail1 = 0;
+    double T = 1.0, logPr = 0.0, logPo_cur = 0.0, sig = 0.0;
+    if (tid == 0) {
+        st = a.t.status[c] | s.sticky_status[c]; T = s.Tcoefs[c]; logPr = a.t.logprior[c]; logPo_cur = s.logPost_cur[c];
+        live = s.live[c]; sig = s.sigma[c];
+        fail0 = s.chol_fail[((live + 1) % 3) * s.C + c]; fail1 = s.chol_fail[((live + 2) % 3) * s.C + c];
+    }
     const long slot = it - s.ctrl->i0;
 
     // 1. logL of the proposed point
-    double2 sum;
-    if (!a.presummed) {
-        double a1 = 0, a2 = 0;
-        for (int t = tid; t < a.ntiles; t += nt) { const double2 v = a.partials[(size_t)c * a.ntiles + t]; a1 += v.x; a2 += v.y; }
-        r1[tid] = a1; r2[tid] = a2;
-        __syncthreads();
-        for (int h = 128; h > 0; h >>= 1) { if (tid < h) { r1[tid] += r1[tid + h]; r2[tid] += r2[tid + h]; } __syncthreads(); }
-        sum = make_double2(r1[0], r2[0]);
-    } else {
-        sum = a.sums[c];
-    }
+    const double2 sum = a.presummed ? a.sums[c] : tg_block_sum2(a1, a2, s_part);
     // 2. Metropolis-Hastings decision (MALA.cpp:475-535)
     if (tid == 0) {
-        int st = a.t.status[c] | s.sticky_status[c];
-        const double T = s.Tcoefs[c];
         const double logL = tg_logl_from_sums(a.d, sum, T, st);
-        const double logPr = a.t.logprior[c];
         const double logPo = logL + logPr;
         double r;
         if (logL != logL) { r = 0.0; st |= TG_ST_NAN_LOGL; }
         else if (logPo == -CUDART_INF) r = 0.0;
-        else { r = exp(logPo - s.logPost_cur[c]); r = (r < 1.0) ? r : 1.0; if (r != r) r = 0.0; }   // NaN ratio: reference is fatal (:504-506); reject here
+        else { r = exp(logPo - logPo_cur); r = (r < 1.0) ? r : 1.0; if (r != r) r = 0.0; }   // NaN ratio: reference is fatal (:504-506); reject here
         const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_MH, (uint32_t)(a.m.seed >> 32));
         const uint4 rn = tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)c, 0u), key);
         const double u = tg_u01(rn.x, rn.y);
         const int acc = (u <= r);
+        s_accept = acc;
         if (acc) { s.logL_cur[c] = logL; s.logPrior_cur[c] = logPr; s.logPost_cur[c] = logPo; }
         s.moved[c] = acc; s.Pmove[c] = r;
-        s_accept = acc; s_r = r;
         if (a.record && slot >= 0 && slot < a.rec.cap) a.rec.status[(size_t)slot * s.C + c] = st;
-        s_learn = tg_learning(a.m, it);
+        // 3. Robbins-Monro update (MALA.cpp:292-315): (mu, Sigma, chol) were prepared for both outcomes by the
+        //    speculative CTAs; select the candidate slot of this outcome and update sigma with the p1 truncation.
+        if (tg_learning(a.m, it)) {
+            const double gamma = a.m.c0 / (1.0 + (double)it);
+            s.live[c] = (live + 1 + acc) % 3;
+            const int sticky = s.sticky_status[c];
+            s.sticky_status[c] = (acc ? fail1 : fail0) ? (sticky | TG_ST_CHOL_FAIL) : (sticky & ~TG_ST_CHOL_FAIL);
+            double sg = sig + gamma * (r - a.m.target);
+            if (sg < a.m.eps1) sg = a.m.eps1;
+            if (sg > a.m.A1) sg = a.m.A1;
+            s.sigma[c] = sg;
+        }
     }
     __syncthreads();
     if (s_accept) {
-        for (int v = tid; v < Nv; v += nt) s.vars_cur[(size_t)c * Nv + v] = s.vars_prop[(size_t)c * Nv + v];
-        for (int i = tid; i < Np; i += nt) s.params_cur[(size_t)c * Np + i] = s.params_prop[(size_t)c * Np + i];
+        if (small) { if (tid < Nv) s.vars_cur[(size_t)c * Nv + tid] = vprop; if (tid < Np) s.params_cur[(size_t)c * Np + tid] = pprop; }
+        else {
+            for (int v = tid; v < Nv; v += nt) s.vars_cur[(size_t)c * Nv + v] = s.vars_prop[(size_t)c * Nv + v];
+            for (int i = tid; i < Np; i += nt) s.params_cur[(size_t)c * Np + i] = s.params_prop[(size_t)c * Np + i];
+        }
     }
     __syncthreads();
-    // 3. Robbins-Monro update (MALA.cpp:292-315): (mu, Sigma, chol) were prepared for both outcomes by
-    //    tg_k_spec; select the candidate slot of this outcome and update sigma with the p1 truncation.
-    if (s_learn && tid == 0) {
-        const double gamma = a.m.c0 / (1.0 + (double)it);
-        const int nl = (s.live[c] + 1 + s_accept) % 3;
-        s.live[c] = nl;
-        if (s.chol_fail[nl * s.C + c]) s.sticky_status[c] |= TG_ST_CHOL_FAIL; else s.sticky_status[c] &= ~TG_ST_CHOL_FAIL;
-        double sg = s.sigma[c] + gamma * (s_r - a.m.target);
-        if (sg < a.m.eps1) sg = a.m.eps1;
-        if (sg > a.m.A1) sg = a.m.A1;
-        s.sigma[c] = sg;
-    }
     if (a.record) tg_write_record(a, slot, c, -1, tid, nt);
 
     // 4. last CTA: tempering swaps (MALA.cpp:381-445, :676-692), then advance the iteration
