@@ -252,54 +252,59 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     if (!s_last) return;
     __threadfence();
     const int attempt = (a.m.dN_mixing > 0) && (it % a.m.dN_mixing == 0) && (it != 0) && (s.Ce >= 2);
-    for (int e0 = 0; e0 < s.E; e0 += nt) {        // decisions, one thread per ensemble
-        const int e = e0 + tid;
-        int doswap = 0, A = -1;
-        double rT = 0.0;
-        if (e < s.E && attempt) {
-            const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PT, (uint32_t)(a.m.seed >> 32));
+    const bool rec_ok = a.record && slot >= 0 && slot < a.rec.cap;
+    if (!attempt) {
+        if (rec_ok) for (int e = tid; e < s.E; e += nt) {
+            const size_t re = (size_t)slot * s.E + e;
+            a.rec.swap_attempt[re] = 0; a.rec.swap_chain0[re] = -1; a.rec.swap_Pswap[re] = 0.0; a.rec.swap_done[re] = 0;
+        }
+    } else {
+        // whole CTA per ensemble; every thread takes the (same) decision from the same loads, and the two rows
+        // that may be exchanged are fetched in the same round trip as the likelihoods (values written by
+        // other CTAs: read through L2)
+        const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PT, (uint32_t)(a.m.seed >> 32));
+        for (int e = 0; e < s.E; e++) {
             const uint4 rn = tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)e, 0u), key);
-            A = (int)(rn.z % (uint32_t)(s.Ce - 1));
+            const int A = (int)(rn.z % (uint32_t)(s.Ce - 1));
             const int gA = e * s.Ce + A, gB = gA + 1;
             const double TA = s.Tcoefs[gA], TB = s.Tcoefs[gB];
-            const double LA = __ldcg(s.logL_cur + gA), LB = __ldcg(s.logL_cur + gB);   // written by other CTAs: read through L2
-            const double LA_TB = LA * TA / TB, LB_TA = LB * TB / TA;
-            rT = exp(LA_TB + LB_TA - LA - LB); rT = (rT < 1.0) ? rT : 1.0;
-            const double u = tg_u01(rn.x, rn.y);
-            doswap = (u <= rT);
-            if (doswap) {
-                const double prA = __ldcg(s.logPrior_cur + gA), prB = __ldcg(s.logPrior_cur + gB);
-                s.logL_cur[gA] = LB_TA; s.logPrior_cur[gA] = prB; s.logPost_cur[gA] = LB_TA + prB;
-                s.logL_cur[gB] = LA_TB; s.logPrior_cur[gB] = prA;
-                // Q8: the reference adds logPrior[ind_A] AFTER it was overwritten with B's prior (MALA.cpp:417,:428)
-                s.logPost_cur[gB] = LA_TB + ((a.m.flags & TG_F_FIX_SWAP_BOOKKEEPING) ? prA : prB);
-                const int mv = __ldcg(s.moved + gA); s.moved[gA] = __ldcg(s.moved + gB); s.moved[gB] = mv;
-                const double pm = __ldcg(s.Pmove + gA); s.Pmove[gA] = __ldcg(s.Pmove + gB); s.Pmove[gB] = pm;
+            const double LA = __ldcg(s.logL_cur + gA), LB = __ldcg(s.logL_cur + gB);
+            double va = 0, vb = 0, pa = 0, pb = 0;
+            if (small) {
+                if (tid < Nv) { va = __ldcg(s.vars_cur + (size_t)gA * Nv + tid); vb = __ldcg(s.vars_cur + (size_t)gB * Nv + tid); }
+                if (tid < Np) { pa = __ldcg(s.params_cur + (size_t)gA * Np + tid); pb = __ldcg(s.params_cur + (size_t)gB * Np + tid); }
             }
-        }
-        if (e < s.E) {
-            // stash the decision in the (now dead) sums buffer of the ensemble's first chain
-            a.sums[e * s.Ce].x = doswap ? (double)(A + 1) : 0.0;
-            if (a.record && slot >= 0 && slot < a.rec.cap) {
+            const double LA_TB = LA * TA / TB, LB_TA = LB * TB / TA;
+            double rT = exp(LA_TB + LB_TA - LA - LB); rT = (rT < 1.0) ? rT : 1.0;
+            const double u = tg_u01(rn.x, rn.y);
+            const int doswap = (u <= rT);
+            if (doswap) {
+                if (tid == 0) {
+                    const double prA = __ldcg(s.logPrior_cur + gA), prB = __ldcg(s.logPrior_cur + gB);
+                    s.logL_cur[gA] = LB_TA; s.logPrior_cur[gA] = prB; s.logPost_cur[gA] = LB_TA + prB;
+                    s.logL_cur[gB] = LA_TB; s.logPrior_cur[gB] = prA;
+                    // Q8: the reference adds logPrior[ind_A] AFTER it was overwritten with B's prior (MALA.cpp:417,:428)
+                    s.logPost_cur[gB] = LA_TB + ((a.m.flags & TG_F_FIX_SWAP_BOOKKEEPING) ? prA : prB);
+                    const int mv = __ldcg(s.moved + gA); s.moved[gA] = __ldcg(s.moved + gB); s.moved[gB] = mv;
+                    const double pm = __ldcg(s.Pmove + gA); s.Pmove[gA] = __ldcg(s.Pmove + gB); s.Pmove[gB] = pm;
+                }
+                if (small) {
+                    if (tid < Nv) { s.vars_cur[(size_t)gA * Nv + tid] = vb; s.vars_cur[(size_t)gB * Nv + tid] = va; }
+                    if (tid < Np) { s.params_cur[(size_t)gA * Np + tid] = pb; s.params_cur[(size_t)gB * Np + tid] = pa; }
+                } else {
+                    for (int v = tid; v < Nv; v += nt) { const double t = __ldcg(s.vars_cur + (size_t)gA * Nv + v); s.vars_cur[(size_t)gA * Nv + v] = __ldcg(s.vars_cur + (size_t)gB * Nv + v); s.vars_cur[(size_t)gB * Nv + v] = t; }
+                    for (int i = tid; i < Np; i += nt) { const double t = __ldcg(s.params_cur + (size_t)gA * Np + i); s.params_cur[(size_t)gA * Np + i] = __ldcg(s.params_cur + (size_t)gB * Np + i); s.params_cur[(size_t)gB * Np + i] = t; }
+                }
+                // the records of the two chains are rewritten by the threads that hold the new values (thread v wrote element v, thread 0 the scalars)
+                if (a.record) { tg_write_record(a, slot, gA, -1, tid, nt); tg_write_record(a, slot, gB, -1, tid, nt); }
+            }
+            if (rec_ok && tid == 0) {
                 const size_t re = (size_t)slot * s.E + e;
-                a.rec.swap_attempt[re] = attempt; a.rec.swap_chain0[re] = attempt ? A : -1;
+                a.rec.swap_attempt[re] = 1; a.rec.swap_chain0[re] = A;
                 a.rec.swap_Pswap[re] = doswap ? rT : 0.0; a.rec.swap_done[re] = doswap;
             }
         }
     }
-    __syncthreads();
-    if (attempt) {
-        for (int e = 0; e < s.E; e++) {           // row exchanges, whole CTA per ensemble
-            const int A1 = (int)a.sums[e * s.Ce].x;
-            if (A1 == 0) continue;
-            const int gA = e * s.Ce + A1 - 1, gB = gA + 1;
-            for (int v = tid; v < Nv; v += nt) { const double t = __ldcg(s.vars_cur + (size_t)gA * Nv + v); s.vars_cur[(size_t)gA * Nv + v] = __ldcg(s.vars_cur + (size_t)gB * Nv + v); s.vars_cur[(size_t)gB * Nv + v] = t; }
-            for (int i = tid; i < Np; i += nt) { const double t = __ldcg(s.params_cur + (size_t)gA * Np + i); s.params_cur[(size_t)gA * Np + i] = __ldcg(s.params_cur + (size_t)gB * Np + i); s.params_cur[(size_t)gB * Np + i] = t; }
-            __syncthreads();
-            if (a.record) { tg_write_record(a, slot, gA, -1, tid, nt); tg_write_record(a, slot, gB, -1, tid, nt); }
-        }
-    }
-    __syncthreads();
     if (tid == 0) { s.ctrl->ticket = 0u; s.ctrl->i = it + 1; }
 }
 
