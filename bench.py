@@ -100,6 +100,14 @@ def run_reference(args, rank, world):
     (MALA.cpp:632), unmodified reference sources (oracle/_ref) -- or the oracle port if absent."""
     if rank != 0:
         return
+    # all the host threads the box has (torchrun exports OMP_NUM_THREADS=1 to its workers)
+    cores = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    try:
+        import ctypes
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(cores)
+    except OSError:
+        pass
     import tamcmc_b200_loader
     tb = tamcmc_b200_loader.load()
     W = tb.workloads
@@ -157,6 +165,8 @@ def main():
     dist = None
     if world > 1:
         import torch.distributed as dist
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = tb.load_library()
     peak_tflops, _ = lib.measure_fp64_peak(local_rank)

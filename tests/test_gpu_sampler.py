@@ -174,3 +174,55 @@ def test_global_fit_runs_and_learns(tb, W, oracle):
     assert out["logL"][-500:, 0].mean() > l0 - 5 * prob.Nv     # stays near the mode of the posterior
     assert np.all(np.diff(out["logL"][-500:].mean(axis=0) * cfg.tcoefs()) < 0)   # hotter chains sit at lower untempered logL
     md.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("norders,path", [(14, "registers (Nv <= 96)"), (18, "shared-memory matrix"), (30, "in place in HBM")])
+def test_adaptation_equals_a_sequential_replay(tb, W, norders, path):
+    """(mu, Sigma, sigma) after N adaptive steps == MALA::update_proposal (MALA.cpp:292-315) replayed on the
+    recorded chain: the speculative two-candidate scheme is exact, on all three factorisation paths."""
+    prob = W.s_global(Nx=100000, step=0.05, norders=norders, numax=2500.0, dnu=120.0)
+    prob.y = np.abs(np.random.default_rng(3).standard_normal(prob.x.size)) + 0.1
+    n0, N = 5, 40
+    cfg = tb.MalaConfig(Nchains=3, Nt_learn=[n0, 10**6], periods_learn=[1], c0=2.0, seed=11, dN_mixing=0)
+    md = tb.GpuModelDef(prob, cfg)
+    Nv = md.Nvars
+    assert (Nv <= 96) == (norders == 14) and (Nv > 170) == (norders == 30), Nv
+    mu, sigma, cov = [a.copy() for a in md.get_proposal()]
+    out = tb.GpuMALA(md).execute(0, N)
+    for i in range(n0, N):
+        gamma = cfg.c0 / (1.0 + i)
+        for c in range(3):
+            x = out["vars"][i, c]
+            mu[c] = mu[c] + gamma * (x - mu[c])
+            d = x - mu[c]
+            cov[c] = cov[c] + gamma * (np.outer(d, d) - cov[c])
+            sigma[c] = min(max(sigma[c] + gamma * (out["Pmove"][i, c] - cfg.target_acceptance), cfg.epsilon1), cfg.A1)
+    mu_g, sigma_g, cov_g = md.get_proposal()
+    assert np.allclose(mu_g, mu, rtol=1e-12, atol=0)
+    assert np.allclose(sigma_g, sigma, rtol=1e-12, atol=0)
+    scale = np.sqrt(np.einsum("cii->ci", cov))
+    # x - mu cancels ~5 digits (frequencies ~2500 with steps ~0.01) and the GPU contracts a + g*(b - a) into an
+    # FMA, so last-ulp differences of mu show up at ~1e-11 of sqrt(S_ii S_kk); a wrong candidate would be O(1)
+    assert np.max(np.abs(cov_g - cov) / (scale[:, :, None] * scale[:, None, :])) < 1e-8
+    assert np.array_equal(cov_g, np.swapaxes(cov_g, 1, 2))                      # kept exactly symmetric
+    assert np.all(out["moved"][n0:].mean(axis=0) > 0.0)                          # the factors are usable: chains move
+    assert np.all((out["status"] & tb.ST_CHOL_FAIL) == 0)
+    md.close()
+
+
+@pytest.mark.gpu
+def test_restore_mirrors_the_lower_triangle(tb, W):
+    """llt() reads the lower triangle only (MALA.cpp:342): a restore file with a garbage upper triangle gives
+    the same chain as the symmetric one."""
+    prob = _gauss(W)
+    cfg = tb.MalaConfig(Nchains=2, Nt_learn=[0, 10**6], periods_learn=[1], c0=2.0, seed=2)
+    a = tb.GpuModelDef(prob, cfg); b = tb.GpuModelDef(prob, cfg)
+    mu, sigma, cov = a.get_proposal()
+    bad = cov.copy()
+    iu = np.triu_indices(cov.shape[1], 1)
+    bad[:, iu[0], iu[1]] += 0.37
+    b.set_state(covarmat=bad)
+    ra = tb.GpuMALA(a).execute(0, 30); rb = tb.GpuMALA(b).execute(0, 30)
+    assert np.array_equal(ra["vars"], rb["vars"])
+    a.close(); b.close()
