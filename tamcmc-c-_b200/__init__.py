@@ -20,5 +20,7 @@ from .build import build_library, LIB_PATH  # noqa: F401
 from .gpu import (GpuLibrary, GpuModelDef, GpuMALA, MalaConfig, TgError, load_library,  # noqa: F401
                   ST_EMPTY_WINDOW, ST_NAN_WINDOW, ST_NAN_LOGL, ST_BAD_PRIOR, ST_CHOL_FAIL, ST_MODE_OVERFLOW)
 
+from . import outputs  # noqa: F401,E402
+
 __all__ = ["workloads", "build_library", "LIB_PATH", "GpuLibrary", "GpuModelDef", "GpuMALA", "MalaConfig",
            "TgError", "load_library"]

@@ -21,6 +21,8 @@ EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", 
            "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
            "tg_step_end", "tg_partials_device_ptr", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_event_record", "tg_event_elapsed_ms"]
+# include/tamcmc_outputs.h (host code in the same library)
+EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_close", "tg_restore_read"]
 
 
 class TgError(RuntimeError):
@@ -83,6 +85,14 @@ class GpuLibrary:
         L.tg_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.tg_event_record.argtypes = [C.c_void_p, C.c_int]
         L.tg_event_elapsed_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.tg_out_last_error.restype = C.c_char_p
+        for name in EXPORTS_OUT[1:]:
+            getattr(L, name).restype = C.c_int
+        L.tg_out_open.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.tg_out_append.argtypes = [C.c_void_p, C.POINTER(_Records), C.c_long, C.c_int]
+        L.tg_out_write_restore.argtypes = [C.c_void_p, C.c_long] + [C.c_void_p] * 4
+        L.tg_out_close.argtypes = [C.c_void_p]
+        L.tg_restore_read.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_long)] + [C.c_void_p] * 4
 
     def check(self, rc):
         if rc != 0:

@@ -226,3 +226,28 @@ def test_restore_mirrors_the_lower_triangle(tb, W):
     ra = tb.GpuMALA(a).execute(0, 30); rb = tb.GpuMALA(b).execute(0, 30)
     assert np.array_equal(ra["vars"], rb["vars"])
     a.close(); b.close()
+
+
+def test_resume_through_the_restore_files(tb, W, tmp_path):
+    """Run 80 steps, write the outputs and the restore triplet in the reference's formats, read them back into
+    a fresh handle and continue: the continuation equals the uninterrupted run bit for bit."""
+    prob = _gauss(W)
+    mk = lambda: tb.MalaConfig(Nchains=4, Nt_learn=[20, 10000], periods_learn=[1], c0=5.0, seed=8, flags=tb.gpu.F_FIX_SWAP_BOOKKEEPING)
+    a = tb.GpuModelDef(prob, mk()); ra = tb.GpuMALA(a).execute(0, 120)
+    b = tb.GpuModelDef(prob, mk()); rb = tb.GpuMALA(b).execute(0, 80)
+    out = tb.outputs.Outputs(prob, b.Tcoefs, str(tmp_path), root="g", Nsamples=120)
+    out.append(rb); out.write_restore(b, 80); out.close()
+    rs = tb.outputs.read_restore(str(tmp_path / "g_restore_"))
+    assert rs["iteration"] == 80 and np.array_equal(rs["vars"], rb["vars"][-1])
+    c = tb.GpuModelDef(prob, mk())
+    c.set_state(vars_=rs["vars"], mu=rs["mu"], sigma=rs["sigma"], covarmat=rs["covarmat"])
+    rc = tb.GpuMALA(c).execute(rs["iteration"], 40)
+    for k in ("vars", "logL", "logPost", "moved", "swap_done", "Pmove"):
+        assert np.array_equal(ra[k][80:], rc[k]), k
+    # and the appended binary files hold the whole chain
+    out2 = tb.outputs.Outputs(prob, b.Tcoefs, str(tmp_path), root="g", Nsamples=120, Nsamples_sofar=80, erase_old_files=False)
+    out2.append(rc); out2.close()
+    v0 = np.fromfile(str(tmp_path / "g_params_chain-0.bin"), dtype=np.float64).reshape(-1, a.Nvars)
+    assert np.array_equal(v0, ra["vars"][:, 0])
+    for m in (a, b, c):
+        m.close()

@@ -1,0 +1,123 @@
+"""On-disk formats of the reference: the files written by csrc/tg_outputs.cpp are
+read back (a) by the reference's own, unmodified tools/read_stats.cpp (oracle/_ref/getstats), (b) by
+independent numpy readers that follow the reference's readers (diagnostics.cpp:677-760, bin2txt_params.cpp)
+and (c) by the restore reader, checked against the keyword grammar of config.cpp:1321-1579."""
+import os
+import subprocess
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GETSTATS = os.path.join(ROOT, "oracle", "_ref", "getstats")
+
+
+def _records(n, Cn, Nv, seed=0):
+    g = np.random.default_rng(seed)
+    return dict(vars=g.standard_normal((n, Cn, Nv)) * 10.0 ** g.integers(-3, 4, (1, 1, Nv)),
+                logL=-1e3 * g.random((n, Cn)), logPrior=-10 * g.random((n, Cn)), logPost=-1e3 * g.random((n, Cn)),
+                Pmove=g.random((n, Cn)), moved=(g.random((n, Cn)) < 0.3).astype(np.uint8),
+                swap_attempt=(np.arange(n)[:, None] % 2 == 0).astype(np.int32), swap_chain0=g.integers(-1, Cn - 1, (n, 1)).astype(np.int32),
+                swap_Pswap=g.random((n, 1)), swap_done=(g.random((n, 1)) < 0.5).astype(np.int32), status=np.zeros((n, Cn), dtype=np.int32))
+
+
+def _hdr(path):
+    d = {}
+    for ln in open(path):
+        if ln.startswith("!"):
+            k, v = ln[1:].split("=", 1)
+            d[k.strip()] = v.strip()
+    return d
+
+
+def test_binary_files_and_headers(tb, W, tmp_path):
+    prob = W.small_global(3, Nx=2000)
+    Cn, Nv = 4, prob.index_to_relax.size
+    T = W.tcoefs(Cn)
+    out = tb.outputs.Outputs(prob, T, str(tmp_path), root="star_A", Nsamples=50)
+    r1, r2 = _records(30, Cn, Nv, 1), _records(20, Cn, Nv, 2)
+    out.append(r1); out.append(r2)
+    out.close()
+    rec = {k: np.concatenate([r1[k], r2[k]]) for k in r1}
+    # params: one raw f64 [sample][Nvars] file per chain (outputs.cpp:1307-1320; reader diagnostics.cpp:677-720)
+    for c in range(Cn):
+        a = np.fromfile(str(tmp_path / ("star_A_params_chain-%d.bin" % c)), dtype=np.float64).reshape(-1, Nv)
+        assert np.array_equal(a, rec["vars"][:, c, :])
+    h = _hdr(str(tmp_path / "star_A_params.hdr"))
+    assert (int(h["Nsamples"]), int(h["Nchains"]), int(h["Nsamples_done"]), int(h["Nvars"])) == (50, Cn, 50, Nv)
+    assert int(h["Ncons"]) == prob.params.size - Nv
+    assert [int(v) for v in h["relax"].split()] == list(prob.relax)
+    assert [int(v) for v in h["plength"].split()] == list(prob.plength)
+    assert h["variable_names"].split() == " ".join(prob.names[i] for i in prob.index_to_relax).split()
+    cons = np.flatnonzero(prob.relax == 0)
+    assert h["constant_names"].split() == " ".join(prob.names[i] for i in cons).split()     # some names contain blanks, as in the reference
+    assert np.allclose([float(v) for v in h["constant_values"].split()], prob.params[cons], rtol=1e-5)
+    # stat criteria: per sample logL[C] | logPrior[C] | logPost[C] (outputs.cpp:1524-1538)
+    s = np.fromfile(str(tmp_path / "star_A_stat_criteria.bin"), dtype=np.float64).reshape(-1, 3, Cn)
+    assert np.array_equal(s[:, 0], rec["logL"]) and np.array_equal(s[:, 1], rec["logPrior"]) and np.array_equal(s[:, 2], rec["logPost"])
+    # parallel tempering: packed {bool, int, double, bool} = 14 bytes per sample (outputs.cpp:1383-1392)
+    dt = np.dtype([("attempt", "u1"), ("chain0", "<i4"), ("Pswitch", "<f8"), ("switched", "u1")])
+    assert dt.itemsize == 14
+    p = np.fromfile(str(tmp_path / "star_A_parallel_tempering.bin"), dtype=dt)
+    assert np.array_equal(p["attempt"], rec["swap_attempt"][:, 0]) and np.array_equal(p["chain0"], rec["swap_chain0"][:, 0])
+    assert np.array_equal(p["Pswitch"], rec["swap_Pswap"][:, 0]) and np.array_equal(p["switched"], rec["swap_done"][:, 0])
+    assert np.allclose([float(v) for v in _hdr(str(tmp_path / "star_A_parallel_tempering.hdr"))["Tcoefs"].split()], T, rtol=1e-5)
+
+
+@pytest.mark.skipif(not os.path.exists(GETSTATS), reason="oracle/_ref/getstats (reference tool) not built")
+def test_reference_getstats_reads_our_stat_file(tb, W, tmp_path):
+    prob = W.small_global(3, Nx=2000)
+    Cn, Nv = 3, prob.index_to_relax.size
+    out = tb.outputs.Outputs(prob, W.tcoefs(Cn), str(tmp_path), root="s", Nsamples=40)
+    rec = _records(40, Cn, Nv, 5)
+    out.append(rec); out.close()
+    for chain in range(Cn):
+        txt = str(tmp_path / ("stats_%d.txt" % chain))
+        r = subprocess.run([GETSTATS, str(tmp_path / "s_stat_criteria"), str(chain), txt], capture_output=True, text=True)
+        assert r.returncode == 0 and "All done successfully" in r.stdout, r.stdout
+        a = np.loadtxt(txt, comments="#")
+        assert a.shape == (40, 3)
+        for k, key in enumerate(("logL", "logPrior", "logPost")):
+            assert np.allclose(a[:, k], rec[key][:, chain], rtol=1e-9, atol=0)      # the tool prints 10 significant digits
+
+
+def test_append_mode_and_restore_round_trip(tb, W, tmp_path):
+    prob = W.small_global(3, Nx=2000)
+    Cn, Nv = 3, prob.index_to_relax.size
+    T = W.tcoefs(Cn)
+    a = tb.outputs.Outputs(prob, T, str(tmp_path), root="r", Nsamples=30)
+    r1 = _records(10, Cn, Nv, 1)
+    a.append(r1)
+    g = np.random.default_rng(9)
+    vars_, mu, sigma = r1["vars"][-1], g.standard_normal((Cn, Nv)), g.random(Cn) + 0.1
+    B = g.standard_normal((Cn, Nv, Nv)); cov = B @ np.swapaxes(B, 1, 2) * 1e-3
+    a.write_restore_arrays(10, vars_, mu, sigma, cov)
+    a.close()
+    # the restore triplet comes back bit for bit (17 significant digits) and carries the iteration
+    rs = tb.outputs.read_restore(str(tmp_path / "r_restore_"))
+    assert rs["iteration"] == 10
+    for k, ref in (("vars", vars_), ("mu", mu), ("sigma", sigma), ("covarmat", cov)):
+        assert np.array_equal(rs[k], ref), k
+    assert tb.outputs.read_restore(str(tmp_path / "r_restore_"), do_restore_last_index=False)["iteration"] == 0
+    # keyword grammar of config.cpp:1321-1579: 6 keywords in file 1, 4 in file 2, 2 in file 3
+    kw = lambda n: [ln.split("=")[0] for ln in open(str(tmp_path / ("r_restore_%d.dat" % n))) if ln.startswith("!")]
+    assert [k for k in kw(1) if k in ("! Nvars", "! Nchains", "! iteration", "! variable_names", "! vars", "! vars_mean")].__len__() == 6
+    assert [k for k in kw(2) if k in ("! sigmas", "! mus", "! sigmas_mean", "! mus_mean")].__len__() == 4
+    assert [k for k in kw(3) if k in ("! covarmats", "! covarmats_mean")].__len__() == 2
+    lines3 = [ln.strip() for ln in open(str(tmp_path / "r_restore_3.dat"))]
+    assert lines3[lines3.index("! covarmats=") + 1] == "*0" and lines3.count("*%d" % (Cn - 1)) == 2
+    # erase_old_files = 0: the data files grow, the headers are left as they were (outputs.cpp:1254)
+    b = tb.outputs.Outputs(prob, T, str(tmp_path), root="r", Nsamples=30, Nsamples_sofar=10, erase_old_files=False)
+    r2 = _records(5, Cn, Nv, 2)
+    b.append(r2); b.close()
+    v0 = np.fromfile(str(tmp_path / "r_params_chain-0.bin"), dtype=np.float64).reshape(-1, Nv)
+    assert np.array_equal(v0, np.concatenate([r1["vars"][:, 0], r2["vars"][:, 0]]))
+    assert int(_hdr(str(tmp_path / "r_params.hdr"))["Nsamples_done"]) == 10
+
+
+def test_header_declares_every_outputs_symbol(tb):
+    import re
+    decl = set(re.findall(r"\b(tg_\w+)\s*\(", open(os.path.join(ROOT, "include", "tamcmc_outputs.h")).read()))
+    lib = tb.load_library()
+    for name in decl:
+        assert hasattr(lib.lib, name), name
+    assert decl == set(tb.gpu.EXPORTS_OUT)
