@@ -5,12 +5,14 @@ import tamcmc_b200_loader
 tb = tamcmc_b200_loader.load()
 W = tb.workloads
 here = os.path.dirname(os.path.abspath(__file__))
-lib = tb.gpu.GpuLibrary(os.path.join(here, "libtamcmc_gpu_prof.so"))
+lib = tb.gpu.GpuLibrary(os.path.join(here, sys.argv[1] if len(sys.argv) > 1 else "libtamcmc_gpu_prof.so"))
 prob = W.s_global(Nx=1000000)
 prob.y = np.abs(np.random.default_rng(1).standard_normal(prob.x.size)) + 0.1
 Cn = 10
 P, T = W.perturbed_params(prob, Cn), W.tcoefs(Cn)
 md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=Cn), lib=lib)
+tune = [int(v) for v in os.environ.get('TG_TUNE', '0,0,0').split(',')]   # chains_per_block, heavy_group, light_subtiles
+md.set_tuning(chains_per_block=tune[0], heavy_group=tune[1], light_subtiles=tune[2])
 md.eval_upload(P, T)
 for _ in range(5): md.eval_resident(Cn)
 md.sync()
@@ -47,9 +49,27 @@ print("hist", list(zip(e[:-1].tolist(), h.tolist())))
 # phase breakdown (cycles -> us at 1965 MHz): setup, list building, chain loops, final reduction
 f = 1965.0
 setup = (t1 - t0) / f; lists = a[:, 6] / f; tail = (t2 - a[:, 7]) / f; loops = (a[:, 7] - t1) / f - lists
-for name, sel in (("heavy", heavy), ("light", ~heavy)):
+for name, sel in (("window", a[:, 6] > 0), ("noise", a[:, 6] == 0)):
     tot = dur[sel].sum()
+    if sel.sum() == 0: continue
     print("%s units: n=%d  setup %.2f us (%.1f%%)  lists %.2f (%.1f%%)  loops %.2f (%.1f%%)  final %.2f (%.1f%%)  | mean dur %.2f" % (
         name, sel.sum(), setup[sel].mean(), 100 * setup[sel].sum() / tot, lists[sel].mean(), 100 * lists[sel].sum() / tot,
         loops[sel].mean(), 100 * loops[sel].sum() / tot, tail[sel].mean(), 100 * tail[sel].sum() / tot, dur[sel].mean()))
 print("share of all CTA time: heavy %.3f light %.3f" % (dur[heavy].sum() / dur.sum(), dur[~heavy].sum() / dur.sum()))
+
+# how many resident CTAs of an SM are inside their chain loops at the same time (clock64 is per SM)
+occ = {}
+for s in np.unique(sm):
+    k = np.where(sm == s)[0]
+    ev = []
+    for i in k:
+        lo_ = t1[i] + a[i, 6]; hi_ = a[i, 7]
+        ev.append((lo_, 1)); ev.append((hi_, -1))
+    ev.sort()
+    n = 0; last = ev[0][0]
+    start_sm = t0[k].min(); end_sm = t2[k].max()
+    occ[0] = occ.get(0, 0) + (ev[0][0] - start_sm) + (end_sm - ev[-1][0])
+    for t, d in ev:
+        occ[n] = occ.get(n, 0) + (t - last); last = t; n += d
+tot = float(sum(occ.values()))
+print("time share with n CTAs of the SM inside the chain loops:", {int(k_): round(v / tot, 3) for k_, v in sorted(occ.items())})

@@ -4,7 +4,7 @@ import tamcmc_b200_loader
 tb = tamcmc_b200_loader.load()
 W = tb.workloads
 lib = tb.gpu.GpuLibrary(os.path.join(os.path.dirname(os.path.abspath(__file__)), "libtamcmc_gpu_prof.so"))
-prob = W.s_global(Nx=1000000, model_case=3, seed=12345, make_y=None) if False else W.s_global(Nx=200000)
+prob = W.s_global(Nx=1000000, model_case=3, seed=12345, make_y=None) if False else W.s_global(Nx=1000000)
 prob.y = np.ones_like(prob.x)
 cfg = tb.MalaConfig(Nchains=10, Nt_learn=[5, 10**9], periods_learn=[1], c0=2.0)
 md = tb.GpuModelDef(prob, cfg, lib=lib)

@@ -36,6 +36,10 @@ struct EvalBuf {                 // tables + results for a batch of B parameter 
 struct tg_handle {
     int        device = 0, n_sm = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t side = nullptr;           // the adaptation candidates of a step run here, beside the proposal and the fused kernel
+    cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
+    bool         side_pending = false;     // a join is owed before the next finish kernel
+    bool         no_split = false, no_side = false;   // developer switches (environment TG_NO_SPLIT_PRIOR / TG_NO_SIDE_STREAM)
     TgDesc     d{};
     TgMala     m{};
     TgState    s{};
@@ -94,7 +98,7 @@ static int alloc_evalbuf(tg_handle *h, EvalBuf &b, int B)
     b.cap = B;
     if (h->ev_graph) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }     // the buffers move
     DA(b.t.nu, nc); DA(b.t.h, nc); DA(b.t.q, nc); DA(b.t.ifc, nc); DA(b.t.t2sq, nc); DA(b.t.lo, nc); DA(b.t.hi, nc);
-    DA(b.t.ncomp, B); DA(b.t.wlo, B); DA(b.t.whi, B); DA(b.t.noise, (size_t)B * TG_NOISE_STRIDE); DA(b.t.status, B); DA(b.t.work, B); DA(b.t.logprior, B);
+    DA(b.t.ncomp, B); DA(b.t.wlo, B); DA(b.t.whi, B); DA(b.t.noise, (size_t)B * TG_NOISE_STRIDE); DA(b.t.status, B); DA(b.t.pstatus, B); DA(b.t.work, B); DA(b.t.logprior, B);
     DA(b.in, (size_t)B * (h->d.Np + 1)); DA(b.out, (size_t)B * 4);
     DA(b.partials, (size_t)B * h->max_items); DA(b.sums, B);
     if (b.pin_in) cudaFreeHost(b.pin_in);
@@ -307,6 +311,10 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, h->device));
     h->n_sm = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
+    h->no_split = getenv("TG_NO_SPLIT_PRIOR") != nullptr; h->no_side = getenv("TG_NO_SIDE_STREAM") != nullptr;
+    CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
 
     TgDesc &d = h->d;
     d.model_case = p->model_case; d.like_case = p->likelihood_case; d.prior_case = p->prior_case;
@@ -450,6 +458,9 @@ extern "C" int tg_destroy(tg_handle *h)
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
     for (void *q : h->allocs) cudaFree(q);
     for (EvalBuf *b : {&h->sp, &h->ev}) { if (b->pin_in) cudaFreeHost(b->pin_in); if (b->pin_out) cudaFreeHost(b->pin_out); }
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->side) cudaStreamDestroy(h->side);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return TG_OK;
@@ -645,18 +656,38 @@ static int launch_step(tg_handle *h, bool begin, bool end, int presummed)
 {
     const int C = h->s.C;
     if (begin) {
+        // The adaptation candidates (Robbins-Monro + Cholesky for both outcomes of the decision) depend on the
+        // state the previous finish kernel left and on nothing of this step (the CTA of the "accepted" outcome
+        // recomputes the proposed point itself), and only the finish kernel needs them: they run on a side stream
+        // next to the proposal, the prologue and the fused kernel (a parallel branch once captured in a graph).
         const int learn = h->m.n_learn > 0, fused = learn && h->fused_spec;
-        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}, h->smem_matrix, h->tri_smem, fused, h->smem_matrix};
-        tg_k_propose<<<dim3(C, fused ? 3 : 1), 256, h->propose_smem, h->stream>>>(pa);
+        const int split = h->tri_smem && !h->no_split;        // the log-prior of the proposed point gets its own CTAs (role 3) on the side stream
+        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}, h->smem_matrix, h->tri_smem, fused, h->smem_matrix, 0,
+                         split ? TG_PRO_MODEL : (TG_PRO_MODEL | TG_PRO_PRIOR)};
+        if (fused || split) {
+            CK(cudaEventRecord(h->ev_fork, h->stream));
+            CK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+            TgProposeArgs ps = pa; ps.role_base = fused ? 1 : 3;
+            tg_k_propose<<<dim3(C, (fused ? 2 : 0) + (split ? 1 : 0)), 256, h->propose_smem, h->no_side ? h->stream : h->side>>>(ps);
+            CK(cudaEventRecord(h->ev_join, h->side));
+            h->side_pending = true;
+            h->n_launch_total++;
+        }
+        tg_k_propose<<<dim3(C, 1), 256, h->propose_smem, h->stream>>>(pa);
         h->n_launch_total++;
-        if (learn && !fused) {       // very large Nv: the adaptation candidates get their own launch
+        if (learn && !fused) {       // very large Nv: the candidates read the proposed point from HBM, so they follow the propose kernel
+            CK(cudaEventRecord(h->ev_fork, h->stream));
+            CK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
             TgSpecArgs sa{h->s, h->m, h->smem_matrix, 0};
-            tg_k_spec<<<dim3(C, 2), 256, h->spec_smem, h->stream>>>(sa);
+            tg_k_spec<<<dim3(C, 2), 256, h->spec_smem, h->side>>>(sa);
+            CK(cudaEventRecord(h->ev_join, h->side));
+            h->side_pending = true;
             h->n_launch_total++;
         }
         int r = launch_eval_kernels(h, h->sp, h->sp.params, C, nullptr, false, presummed != 0); if (r) return r;
     }
     if (end) {
+        if (h->side_pending) { CK(cudaStreamWaitEvent(h->stream, h->ev_join, 0)); h->side_pending = false; }
         TgFinishArgs fa{h->d, h->s, h->m, h->sp.t, h->sp.partials, h->nitems, h->sp.sums, presummed, h->rec, 1};
         tg_k_finish<<<C, 256, 0, h->stream>>>(fa);
         h->n_launch_total++;
@@ -713,7 +744,7 @@ extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
                 cudaGraphDestroy(g);
             }
             if (h->graph) {
-                for (; k + G <= n; k += G) { CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += 3L * G; h->n_eval_launch += G; }
+                for (; k + G <= n; k += G) { CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += ((h->m.n_learn > 0 || (h->tri_smem && !h->no_split)) ? 4L : 3L) * G; h->n_eval_launch += G; }
             }
         }
         for (; k < n; k++) { int r = launch_step(h, true, true, 0); if (r) return r; }

@@ -511,7 +511,7 @@ __global__ void tg_k_finalize_eval(TgDesc d, const double2 *sums, const double *
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= B) return;
-    int st = t.status[c];
+    int st = t.status[c] | t.pstatus[c];
     const double L = tg_logl_from_sums(d, sums[c], T[c], st);
     if (L != L) st |= TG_ST_NAN_LOGL;
     logL[c] = L; logPrior[c] = t.logprior[c]; logPost[c] = L + t.logprior[c]; status[c] = st;
@@ -529,7 +529,7 @@ __global__ void __launch_bounds__(256) tg_k_reduce_finalize(TgDesc d, const doub
     const double2 sm = tg_block_sum2(a1, a2, s_part);
     if (tid == 0) {
         sums[c] = sm;
-        int st = t.status[c];
+        int st = t.status[c] | t.pstatus[c];
         const double L = tg_logl_from_sums(d, sm, T[c], st);
         if (L != L) st |= TG_ST_NAN_LOGL;
         logL[c] = L; logPrior[c] = t.logprior[c]; logPost[c] = L + t.logprior[c]; status[c] = st;

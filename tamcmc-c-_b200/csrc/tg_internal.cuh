@@ -35,7 +35,8 @@ struct TgTables {
     int    *ncomp;             // [B]
     int    *wlo, *whi;         // [B]  union [wlo,whi) of all truncation windows in LOCAL bins (empty: wlo >= whi)
     double *noise;             // [B][TG_NOISE_STRIDE] : per ACTIVE Harvey term (H, a=1e-3*tc, p, ln a, a^p clamped, exponent class), then N0, asym, gaussA, gaussNu, gaussS2, flags
-    int    *status;            // [B]  TG_ST_* bits
+    int    *status;            // [B]  TG_ST_* bits of the model part of the prologue
+    int    *pstatus;           // [B]  TG_ST_BAD_PRIOR or 0, written by the prior part (it may run in another kernel)
     double *work;              // [B]  L = sum (2l+1)*(hi-lo)
     double *logprior;          // [B]
 };

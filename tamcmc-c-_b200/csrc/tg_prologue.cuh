@@ -14,7 +14,7 @@
 
 #ifdef TG_PROFILE
 __device__ long long tg_dbg_clk[32];
-#define TG_STAMP(k) do { __syncthreads(); if (threadIdx.x == 0 && blockIdx.x == 0) tg_dbg_clk[k] = clock64(); } while (0)
+#define TG_STAMP(k) do { __syncthreads(); if (threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0) tg_dbg_clk[k] = clock64(); } while (0)
 #else
 #define TG_STAMP(k) do { } while (0)
 #endif
@@ -220,9 +220,10 @@ __device__ double tg_appwidth_v2(const double *w, double f)
     return exp(lnGamma0 + lnLorentz);
 }
 
-// Writes the 2l+1 components of one mode.  variant 0: a1etaa3, 1: a1l (f_s per degree, c_1m=0).
-__device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff, int l, double fc, double W,
-                             const double *hm, double f_s, double f_s1, double f_s2, int variant, double &work_acc, int &st_acc, int &wlo_acc, int &whi_acc)
+// Writes component m of one mode (one thread per component; the thread of m = -l also accounts for the
+// mode's window in the work / status / union accumulators).  variant 0: a1etaa3, 1: a1l (f_s per degree, c_1m=0).
+__device__ void tg_emit_comp(const TgProArgs &a, TgProShared &S, int b, int coff, int l, int m, double fc, double W,
+                             double hm, double f_s, double f_s1, double f_s2, int variant, double &work_acc, int &st_acc, int &wlo_acc, int &whi_acc)
 {
     const TgDesc &d = a.d;
     long imin = 0, imax = 0;
@@ -234,8 +235,10 @@ __device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff
         a0 = a0 < 0 ? 0 : (a0 > d.Nx ? d.Nx : a0);
         a1 = a1 < 0 ? 0 : (a1 > d.Nx ? d.Nx : a1);
         lo = (int)a0; hi = (int)a1;
-        work_acc += (double)(2 * l + 1) * (double)(hi - lo);           // integer-valued: exact, order-free
-        if (hi > lo) { wlo_acc = min(wlo_acc, lo); whi_acc = max(whi_acc, hi); }
+        if (m == -l) {
+            work_acc += (double)(2 * l + 1) * (double)(hi - lo);       // integer-valued: exact, order-free
+            if (hi > lo) { wlo_acc = min(wlo_acc, lo); whi_acc = max(whi_acc, hi); }
+        }
     } else {
         st_acc |= st;
     }
@@ -244,39 +247,41 @@ __device__ void tg_emit_mode(const TgProArgs &a, TgProShared &S, int b, int coff
     if (q > S.qmax) q = S.qmax;              // keep 1+q*d^2 <= ~1e70: the product of four such terms stays finite (Gamma < ~1e-31 only)
     double ifc = 0.0, t2 = 0.0;              // asymmetry extras (only read by the kernel when asym != 0)
     if (S.asym != 0.0) { ifc = 1.0 / fc; t2 = 0.5 * W * S.asym / fc; }
-    const size_t base = (size_t)b * d.ncomp_max + coff;
-    for (int m = -l; m <= l; m++) {
-        double nu = fc;
-        if (l != 0) {
-            // Q_lm = (l(l+1) - 3m^2) / ((2l-1)(2l+3)): small-integer quotients, folded at compile time with the
-            // same single rounding as the reference's run-time division (build_lorentzian.cpp:77)
-            const int am = m < 0 ? -m : m;
-            const double Qlm = (l == 1) ? (am == 0 ? 2.0 / 5.0 : -1.0 / 5.0)
-                             : (l == 2) ? (am == 0 ? 6.0 / 21.0 : (am == 1 ? 3.0 / 21.0 : -6.0 / 21.0))
-                             :            (am == 0 ? 12.0 / 45.0 : (am == 1 ? 9.0 / 45.0 : (am == 2 ? 0.0 / 45.0 : -15.0 / 45.0)));
-            double clm = 0, fs = f_s;
-            if (variant == 1) {
-                if (l == 1) { clm = 0; fs = f_s1; }
-                if (l == 2) { clm = (double)((5 * m * m * m - 17 * m) / 3); fs = f_s2; }   // exact integers -2,4,0,-4,2
-                if (l == 3) { clm = 0; fs = (f_s1 + f_s2) / 2.; }
-            } else {
-                if (l == 1) clm = m;
-                if (l == 2) clm = (double)((5 * m * m * m - 17 * m) / 3);                  // exact integers -2,4,0,-4,2
-                if (l == 3) clm = 0;
-            }
-            // fc*(1+eta*Q) + m*fs + clm*a3, un-contracted
-            nu = __dadd_rn(__dadd_rn(__dmul_rn(fc, __dadd_rn(1., __dmul_rn(S.eta, Qlm))), __dmul_rn((double)m, fs)), __dmul_rn(clm, S.a3));
+    double nu = fc;
+    if (l != 0) {
+        // Q_lm = (l(l+1) - 3m^2) / ((2l-1)(2l+3)): small-integer quotients, folded at compile time with the
+        // same single rounding as the reference's run-time division (build_lorentzian.cpp:77)
+        const int am = m < 0 ? -m : m;
+        const double Qlm = (l == 1) ? (am == 0 ? 2.0 / 5.0 : -1.0 / 5.0)
+                         : (l == 2) ? (am == 0 ? 6.0 / 21.0 : (am == 1 ? 3.0 / 21.0 : -6.0 / 21.0))
+                         :            (am == 0 ? 12.0 / 45.0 : (am == 1 ? 9.0 / 45.0 : (am == 2 ? 0.0 / 45.0 : -15.0 / 45.0)));
+        double clm = 0, fs = f_s;
+        if (variant == 1) {
+            if (l == 1) { clm = 0; fs = f_s1; }
+            if (l == 2) { clm = (double)((5 * m * m * m - 17 * m) / 3); fs = f_s2; }   // exact integers -2,4,0,-4,2
+            if (l == 3) { clm = 0; fs = (f_s1 + f_s2) / 2.; }
+        } else {
+            if (l == 1) clm = m;
+            if (l == 2) clm = (double)((5 * m * m * m - 17 * m) / 3);                  // exact integers -2,4,0,-4,2
+            if (l == 3) clm = 0;
         }
-        const size_t k = base + (m + l);
-        a.t.nu[k] = nu; a.t.h[k] = hm[m + l]; a.t.q[k] = q;
-        a.t.ifc[k] = ifc; a.t.t2sq[k] = t2 * t2;
-        a.t.lo[k] = lo; a.t.hi[k] = hi;
+        // fc*(1+eta*Q) + m*fs + clm*a3, un-contracted
+        nu = __dadd_rn(__dadd_rn(__dmul_rn(fc, __dadd_rn(1., __dmul_rn(S.eta, Qlm))), __dmul_rn((double)m, fs)), __dmul_rn(clm, S.a3));
     }
+    const size_t k = (size_t)b * d.ncomp_max + coff + (m + l);
+    a.t.nu[k] = nu; a.t.h[k] = hm; a.t.q[k] = q;
+    a.t.ifc[k] = ifc; a.t.t2sq[k] = t2 * t2;
+    a.t.lo[k] = lo; a.t.hi[k] = hi;
 }
 
 // Body shared by the stand-alone prologue kernel (tg_eval path) and the sampler's propose kernel.
 // sm_terms: [Np + 5*TG_MAXORD] doubles of shared memory for the prior terms.  Any blockDim.x >= 32.
-__device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_terms)
+// parts: TG_PRO_MODEL (component table, noise constants, window union: what the fused kernel reads) and/or
+// TG_PRO_PRIOR (log-prior: only the accept decision reads it, so the sampler runs it in another CTA, off the
+// path to the fused kernel).  staged: the caller already put the parameter vector into sm_terms[0..Np).
+#define TG_PRO_MODEL 1
+#define TG_PRO_PRIOR 2
+__device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_terms, const int parts = TG_PRO_MODEL | TG_PRO_PRIOR, const bool staged = false)
 {
     __shared__ TgProShared S;
     __shared__ double s_red[256];
@@ -287,8 +292,9 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     {
         const double *pg = a.params + (size_t)b * d.Np;
         double *nzg = a.t.noise + (size_t)b * TG_NOISE_STRIDE;
-        for (int i = tid; i < d.Np; i += blockDim.x) sp[i] = pg[i];
-        for (int k = tid; k < TG_NOISE_STRIDE; k += blockDim.x) nzg[k] = 0.0;
+        if (!staged) for (int i = tid; i < d.Np; i += blockDim.x) sp[i] = pg[i];
+        if (parts & TG_PRO_MODEL) for (int k = tid; k < TG_NOISE_STRIDE; k += blockDim.x) nzg[k] = 0.0;
+        if (tid == 0) { S.status = 0; S.bad_prior = 0; }
     }
     __syncthreads();
     const double *p = sp;
@@ -303,8 +309,8 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
 
     TG_STAMP(4);
     // ---------------- A. chain scalars (thread 0) ----------------
-    if (tid == 0) {
-        S.status = 0; S.bad_prior = 0; S.wlo = 0x7fffffff; S.whi = 0; S.work = 0.0; S.numax = 0; S.a1 = 0; S.inclination = 0;
+    if ((parts & TG_PRO_MODEL) && tid == 0) {
+        S.wlo = 0x7fffffff; S.whi = 0; S.work = 0.0; S.numax = 0; S.a1 = 0; S.inclination = 0;
         { const double range = d.x_last - d.x_first; S.qmax = 1e70 / (range * range); }
         S.Vl[0] = 1; S.Vl[1] = S.Vl[2] = S.Vl[3] = 0;
         if (fam == 0) {
@@ -373,7 +379,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
 
     TG_STAMP(5);
     // ---------------- B. inclination -> height ratios (15 threads) ----------------
-    if (fam != 0 && tid < 16) {
+    if ((parts & TG_PRO_MODEL) && fam != 0 && tid < 16) {
         // tid -> (l, m): l=0:{0} l=1:{1..3} l=2:{4..8} l=3:{9..15}
         const int l = tid == 0 ? 0 : (tid < 4 ? 1 : (tid < 9 ? 2 : 3));
         const int m = tid - l * l - l;
@@ -395,18 +401,20 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     __syncthreads();
 
     TG_STAMP(6);
-    // ---------------- C. one thread per mode ----------------
+    // ---------------- C. one thread per component (the mode-level quantities are recomputed by the 2l+1
+    //                    threads of a mode: redundant arithmetic, but no serial loop over m) ----------------
     int nmodes = 0, ncomp = 0;
     if (fam == 1) { const int L1 = (lmax > 3 ? 3 : lmax) + 1; nmodes = Nmax * L1; ncomp = Nmax * L1 * L1; }
     if (fam == 2) { nmodes = Nf; ncomp = Nfl0 + 3 * Nfl1 + 5 * Nfl2 + 7 * Nfl3; }
     if (ncomp > d.ncomp_max) { if (tid == 0) S.status |= TG_ST_MODE_OVERFLOW; nmodes = 0; ncomp = 0; }
     double work_acc = 0.0;
     int st_acc = 0, wlo_acc = 0x7fffffff, whi_acc = 0;
-    for (int k = tid; k < nmodes; k += blockDim.x) {
-        double hm[7];
+    for (int j = tid; j < ((parts & TG_PRO_MODEL) ? ncomp : 0); j += blockDim.x) {
         if (fam == 1) {
-            const int L1 = (lmax > 3 ? 3 : lmax) + 1;
-            const int n = k / L1, l = k % L1;
+            const int L1 = (lmax > 3 ? 3 : lmax) + 1, L2 = L1 * L1;
+            const int n = j / L2, r = j - n * L2;
+            const int l = (r >= 9) ? 3 : ((r >= 4) ? 2 : ((r >= 1) ? 1 : 0));
+            const int m = r - l * l - l;
             const int foff = Nmax + lmax + (l >= 1 ? Nfl0 : 0) + (l >= 2 ? Nfl1 : 0) + (l >= 3 ? Nfl2 : 0);
             const double fl = p[foff + n];
             const double *fl0_all = p + Nmax + lmax, *Wl0_all = p + iW;
@@ -415,45 +423,41 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
             else if (mc == 10) Wl = tg_appwidth_v2(p + iW, fl);
             else if (l == 0)   Wl = fabs(Wl0_all[n]);
             else               Wl = fabs(tg_lin_interpol(fl0_all, Wl0_all, Nfl0 < Nmax ? Nfl0 : Nmax, fl));
-            const int coff = n * L1 * L1 + l * l;
+            const int coff = n * L2 + l * l;
             if (mc == 13) {                        // models.cpp:1185-1237
-                if (l == 0) hm[0] = tg_height0(p[n], Wl, S.do_amp);
-                else {
-                    const int pos0 = (l + 1) * n;
-                    for (int m = -l; m <= l; m++) { double v = p[iI + pos0 + (m < 0 ? -m : m)]; if (S.do_amp) v = v / (TG_PI * Wl); hm[m + l] = fabs(v); }
-                }
-                tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
+                double hm;
+                if (l == 0) hm = tg_height0(p[n], Wl, S.do_amp);
+                else { double v = p[iI + (l + 1) * n + (m < 0 ? -m : m)]; if (S.do_amp) v = v / (TG_PI * Wl); hm = fabs(v); }
+                tg_emit_comp(a, S, b, coff, l, m, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
             } else {
                 const double Hl = (l == 0) ? tg_height0(p[n], Wl, S.do_amp) : tg_heightl(p[n], Wl, S.Vl[l], S.do_amp);
-                for (int m = 0; m < 2 * l + 1; m++) hm[m] = Hl * S.ratios[l][m];
+                const double hm = Hl * S.ratios[l][m + l];
                 if (mc == 6 || mc == 7 || mc == 8) {
                     double a11, a12;
                     if (mc == 6)      { a11 = fabs(p[iS]); a12 = fabs(p[iS + 6]); }
                     else if (mc == 7) { a11 = fabs(p[iS + 6 + n]); a12 = a11; }
                     else              { a11 = fabs(p[iS + 6 + n]); a12 = fabs(p[iS + 6 + Nmax + n]); }
-                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, 0, a11, a12, 1, work_acc, st_acc, wlo_acc, whi_acc);
+                    tg_emit_comp(a, S, b, coff, l, m, fl, Wl, hm, 0, a11, a12, 1, work_acc, st_acc, wlo_acc, whi_acc);
                 } else {
-                    tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
+                    tg_emit_comp(a, S, b, coff, l, m, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
                 }
             }
         } else {                                   // local family, models.cpp:1762-1810 / :1888-1943
             int l = 0;
-            while (l < 3 && k >= S.modeStart[l + 1]) l++;
-            const int n = k - S.modeStart[l];
+            while (l < 3 && j >= S.compStart[l + 1]) l++;
+            const int r = j - S.compStart[l];
+            const int n = r / (2 * l + 1), m = r - n * (2 * l + 1) - l;
             const double fl = p[iF + S.modeStart[l] + n];
             const double Wl = fabs(p[iW + S.modeStart[l] + n]);
             const int coff = S.compStart[l] + n * (2 * l + 1);
+            double hm;
             if (mc == 11) {
-                const double Hl = tg_height0(p[S.modeStart[l] + n], Wl, S.do_amp);
-                for (int m = 0; m < 2 * l + 1; m++) hm[m] = Hl * S.ratios[l][m];
+                hm = tg_height0(p[S.modeStart[l] + n], Wl, S.do_amp) * S.ratios[l][m + l];
             } else {
-                if (l == 0) hm[0] = tg_height0(p[n], Wl, S.do_amp);
-                else {
-                    const int pos0 = (l + 1) * n;
-                    for (int m = -l; m <= l; m++) { double v = p[S.modeStart[l] + pos0 + (m < 0 ? -m : m)]; if (S.do_amp) v = v / (TG_PI * Wl); hm[m + l] = fabs(v); }
-                }
+                if (l == 0) hm = tg_height0(p[n], Wl, S.do_amp);
+                else { double v = p[S.modeStart[l] + (l + 1) * n + (m < 0 ? -m : m)]; if (S.do_amp) v = v / (TG_PI * Wl); hm = fabs(v); }
             }
-            tg_emit_mode(a, S, b, coff, l, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
+            tg_emit_comp(a, S, b, coff, l, m, fl, Wl, hm, S.a1, 0, 0, 0, work_acc, st_acc, wlo_acc, whi_acc);
         }
     }
 
@@ -470,6 +474,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
         }
     }
     TG_STAMP(7);
+    const bool do_prior = (parts & TG_PRO_PRIOR) != 0;
     // ---------------- D. prior terms, one thread per term ----------------
     int bad = 0;
     double *ex = terms + d.Np;                     // extra terms: [0..MAXORD) d02, then 4 x MAXORD smoothness
@@ -477,10 +482,10 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     // the prior terms go to the threads in REVERSE order: the low threads are busy with the modes (C),
     // and there is no barrier between C and D
     const int rt = blockDim.x - 1 - tid;
-    for (int i = rt; i < d.Np; i += blockDim.x) { const int swi = a.sw[i]; ssw[i] = swi; terms[i] = tg_generic_prior(swi, a.pri + 4 * i, p[i], &bad); }
+    if (do_prior) for (int i = rt; i < d.Np; i += blockDim.x) { const int swi = a.sw[i]; ssw[i] = swi; terms[i] = tg_generic_prior(swi, a.pri + 4 * i, p[i], &bad); }
     if (bad) atomicOr(&S.bad_prior, 1);
     double Dnu = 0;
-    if (d.prior_case == 2) {
+    if (do_prior && d.prior_case == 2) {
         // Dnu = SUM of the adaptive first derivative of fl0 (priors_calc.cpp:87-88)
         const double *f0 = p + Nmax + lmax;
         if (Nfl0 >= 2) {
@@ -516,7 +521,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
     TG_STAMP(8);
     // ---------------- E. sum of all terms (fixed-order block tree; the reference sums sequentially in
     //                    long double -- same value to ~1e-15 relative), then thread 0 applies the hard limits ----
-    {
+    if (do_prior) {
         double part = 0.0;
         for (int i = tid; i < d.Np; i += blockDim.x) part += terms[i];
         if (d.prior_case == 2) {
@@ -530,7 +535,7 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
         if ((tid & 31) == 0) s_red[tid >> 5] = part;
         __syncthreads();
     }
-    if (tid == 0) {
+    if (tid == 0 && do_prior) {
         double f = 0.0;
         for (int w = 0; w < (int)(blockDim.x >> 5); w++) f += s_red[w];
         if (d.prior_case == 2) {            // priors_MS_Global, priors_calc.cpp:24-172
@@ -557,13 +562,16 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
             if ((ssw[iI] != 0) && (p[iI] < 0)) f = tg_ninf();
         }
         a.t.logprior[b] = f;
+        a.t.pstatus[b] = S.bad_prior ? TG_ST_BAD_PRIOR : 0;
+    }
+    if (tid == 0 && (parts & TG_PRO_MODEL)) {
 #ifdef TG_PROFILE
-        if (blockIdx.x == 0) tg_dbg_clk[9] = clock64();
+        if (blockIdx.x == 0 && blockIdx.y == 0) tg_dbg_clk[9] = clock64();
 #endif
         a.t.ncomp[b] = ncomp;
         a.t.wlo[b] = S.wlo; a.t.whi[b] = S.whi;
         a.t.work[b] = S.work;
-        a.t.status[b] = S.status | (S.bad_prior ? TG_ST_BAD_PRIOR : 0);
+        a.t.status[b] = S.status;
     }
 }
 

@@ -39,23 +39,26 @@ struct TgProposeArgs {
     int       tri_smem;     // 1: the packed lower triangle of L (Nv(Nv+1)/2 doubles) fits the dynamic shared memory
     int       fused_spec;   // 1: grid (C, 3): rows 1 and 2 are the speculative adaptation CTAs (tg_adapt.cuh)
     int       smem_matrix;  // TgSpecArgs.smem_matrix of those CTAs
+    int       role_base;    // role of grid row 0: 0 = proposal (main stream), 1 or 3 = side-stream grid (roles 1,2 adaptation, role 3 log-prior)
+    int       parts;        // role 0: TG_PRO_MODEL, or TG_PRO_MODEL | TG_PRO_PRIOR when no role-3 CTA computes the prior
 };
 
-// K1, grid (C, 1) or (C, 3).  Row 0, one CTA per chain: draw z, form x' = x + sqrt(sigma)*L z with
+// K1, role = blockIdx.y + role_base.  Role 0, one CTA per chain: draw z, form x' = x + sqrt(sigma)*L z with
 // L = chol(Sigma+eps2 I) of the live slot (== chol((Sigma+eps2 I)*sigma) z, MALA.cpp:335-353, up to
 // rounding), scatter into params, then run the model prologue + log-prior on the proposed parameter
-// vector.  Rows 1 and 2 (fused_spec): the adapted proposal (Robbins-Monro + Cholesky) this chain will
-// use next step if the proposal is rejected / accepted; row 2 recomputes x' itself (same arithmetic,
-// same bits) so that the three CTAs of a chain are independent.
+// vector.  Roles 1 and 2 (fused_spec): the adapted proposal (Robbins-Monro + Cholesky) this chain will
+// use next step if the proposal is rejected / accepted; role 2 recomputes x' itself (same arithmetic,
+// same bits) so that the three CTAs of a chain are independent -- the host launches roles 1 and 2 as their
+// own grid on a side stream, concurrent with role 0 and the fused kernel.
 __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
 {
     extern __shared__ double tg_dyn_smem[];
     __shared__ double s_z[512];
     const TgState &s = a.s;
-    const int c = blockIdx.x, role = blockIdx.y, tid = threadIdx.x, nt = blockDim.x;
+    const int c = blockIdx.x, role = blockIdx.y + a.role_base, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
     const long it = s.ctrl->i;
-    if (role != 0) {
+    if (role == 1 || role == 2) {
         if (!tg_learning(a.m, it)) return;
         if (role == 1) { tg_spec_body(s, a.m, a.smem_matrix, 0, c, 0, tg_dyn_smem); return; }
     }
@@ -96,6 +99,14 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
         if (role == 2) {                                            // fused_spec implies tri_smem and Nv <= 512
             __syncthreads();
             tg_spec_body(s, a.m, a.smem_matrix, 0, c, 1, tg_dyn_smem, s_z);
+            return;
+        }
+        if (role == 3) {                                            // log-prior of the proposed point, off the path to the fused kernel
+            __syncthreads();                                        // the triangle is dead: its memory becomes the parameter vector
+            for (int i = tid; i < Np; i += nt) tg_dyn_smem[i] = s.params_cur[(size_t)c * Np + i];
+            __syncthreads();
+            for (int v = tid; v < Nv; v += nt) tg_dyn_smem[s.index_to_relax[v]] = s_z[v];
+            tg_prologue_body(a.pro, c, tg_dyn_smem, TG_PRO_PRIOR, true);
             return;
         }
     } else
@@ -147,7 +158,7 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
     for (int v = tid; v < Nv; v += nt) s.params_prop[(size_t)c * Np + s.index_to_relax[v]] = s.vars_prop[(size_t)c * Nv + v];
     __syncthreads();
     TG_STAMP(3);
-    tg_prologue_body(a.pro, c, tg_dyn_smem);
+    tg_prologue_body(a.pro, c, tg_dyn_smem, a.parts);
 }
 
 struct TgFinishArgs {
@@ -196,7 +207,7 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     int st = 0, live = 0, fail0 = 0, fail1 = 0;
     double T = 1.0, logPr = 0.0, logPo_cur = 0.0, sig = 0.0;
     if (tid == 0) {
-        st = a.t.status[c] | s.sticky_status[c]; T = s.Tcoefs[c]; logPr = a.t.logprior[c]; logPo_cur = s.logPost_cur[c];
+        st = a.t.status[c] | a.t.pstatus[c] | s.sticky_status[c]; T = s.Tcoefs[c]; logPr = a.t.logprior[c]; logPo_cur = s.logPost_cur[c];
         live = s.live[c]; sig = s.sigma[c];
         fail0 = s.chol_fail[((live + 1) % 3) * s.C + c]; fail1 = s.chol_fail[((live + 2) % 3) * s.C + c];
     }
@@ -322,7 +333,7 @@ __global__ void tg_k_install_current(TgDesc d, TgState s, TgTables t, const doub
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= s.C) return;
-    const double L = tg_logl_from_sums(d, sums[c], s.Tcoefs[c], t.status[c]);
+    const double L = tg_logl_from_sums(d, sums[c], s.Tcoefs[c], t.status[c] | t.pstatus[c]);
     s.logL_cur[c] = L; s.logPrior_cur[c] = t.logprior[c]; s.logPost_cur[c] = L + t.logprior[c];
     s.Pmove[c] = 0.0; s.moved[c] = 0;
 }
