@@ -13,8 +13,8 @@ __global__ void __launch_bounds__(TG_THREADS, 2) k_noise(TgEvalArgs a, int G, in
     TgEvalSmem S;
     S.lists = (TgComp *)sm;
     S.nz = (double *)sm;
-    S.sum = S.nz + G * TG_NOISE_STRIDE; S.pf = S.sum + G * TG_THREADS; S.pfd = S.pf + G * TG_THREADS; S.pe = (int *)(S.pfd + G * TG_THREADS); S.ped = S.pe + G * TG_THREADS;
-    S.full = S.ped + G * TG_THREADS; S.cls = S.full; S.nh = S.cls + G * TG_MAXH;
+    S.sum = S.nz + G * TG_NOISE_STRIDE; S.pf = S.sum + G * TG_THREADS; S.pe = (int *)(S.pf + G * TG_THREADS);
+    S.full = S.pe + G * TG_THREADS; S.cls = S.full; S.nh = S.cls + G * TG_MAXH;
     for (int e = tid; e < G * TG_NOISE_STRIDE; e += TG_THREADS) S.nz[e] = 0.0;
     __syncthreads();
     if (tid < G) {
@@ -24,16 +24,14 @@ __global__ void __launch_bounds__(TG_THREADS, 2) k_noise(TgEvalArgs a, int G, in
         nz[TG_N_N0] = 0.13; nz[TG_N_NH] = 2.0;
         S.cls[tid * TG_MAXH + 0] = 4; S.cls[tid * TG_MAXH + 1] = 2; S.nh[tid] = 2;
     }
-    for (int g = 0; g < G; g++) { S.sum[g * TG_THREADS + tid] = 0.0; S.pf[g * TG_THREADS + tid] = 1.0; S.pfd[g * TG_THREADS + tid] = 1.0; S.pe[g * TG_THREADS + tid] = 0; S.ped[g * TG_THREADS + tid] = 0; }
+    for (int g = 0; g < G; g++) { S.sum[g * TG_THREADS + tid] = 0.0; S.pf[g * TG_THREADS + tid] = 1.0; S.pe[g * TG_THREADS + tid] = 0; }
     __syncthreads();
     const int b0 = blockIdx.x * NB * TG_THREADS;
     for (int r = 0; r < reps; r++) {
-        double x[NB], y[NB];
-        tg_load_xy<NB, false>(a, b0, tid, x, y);
-        tg_chain_loop<NB, false, false>(a, S, s_tot, G, 0, b0, tid, x, y);
+        tg_chain_loop<NB, false, false>(a, S, s_tot, G, 0, b0, tid);
     }
     double s = 0;
-    for (int g = 0; g < G; g++) s += S.sum[g * TG_THREADS + tid] + S.pf[g * TG_THREADS + tid] + S.pe[g * TG_THREADS + tid] + S.pfd[g * TG_THREADS + tid] + S.ped[g * TG_THREADS + tid];
+    for (int g = 0; g < G; g++) s += S.sum[g * TG_THREADS + tid] + S.pf[g * TG_THREADS + tid] + S.pe[g * TG_THREADS + tid];
     out[blockIdx.x * TG_THREADS + tid] = s;
 }
 
