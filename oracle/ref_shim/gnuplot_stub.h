@@ -4,8 +4,19 @@
 // Test infrastructure only; no plotting happens anywhere in this repo.
 #pragma once
 #include <ostream>
+#include <unistd.h>
 namespace gnuplotio {
 template <typename T> struct TextSender {
     static void send(std::ostream &, const T &) {}
 };
 }
+// diagnostics.cpp drives gnuplot through this class; here every command is dropped (no plotting).
+class Gnuplot {
+public:
+    Gnuplot() {}
+    template <typename T> Gnuplot &operator<<(const T &) { return *this; }
+    Gnuplot &operator<<(std::ostream &(*)(std::ostream &)) { return *this; }
+    template <typename T> Gnuplot &send1d(const T &) { return *this; }
+    template <typename T> std::string file1d(const T &) { return std::string(); }
+    template <typename T> std::string file1d(const T &, const std::string &) { return std::string(); }
+};
