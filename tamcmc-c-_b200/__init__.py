@@ -21,6 +21,8 @@ from .gpu import (GpuLibrary, GpuModelDef, GpuMALA, MalaConfig, TgError, load_li
                   ST_EMPTY_WINDOW, ST_NAN_WINDOW, ST_NAN_LOGL, ST_BAD_PRIOR, ST_CHOL_FAIL, ST_MODE_OVERFLOW)
 
 from . import outputs  # noqa: F401,E402
+from . import frontend  # noqa: F401,E402
+from . import config_tree  # noqa: F401,E402
 
 __all__ = ["workloads", "build_library", "LIB_PATH", "GpuLibrary", "GpuModelDef", "GpuMALA", "MalaConfig",
            "TgError", "load_library"]

@@ -5,9 +5,10 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libtamcmc_gpu.so")
-SOURCES = ["tamcmc_gpu.cu", "tg_outputs.cpp"]
+SOURCES = ["tamcmc_gpu.cu", "tg_outputs.cpp", "tg_frontend.cpp"]
 HEADERS = ["tg_internal.cuh", "tg_prologue.cuh", "tg_eval.cuh", "tg_adapt.cuh", "tg_sampler.cuh",
-           os.path.join("..", "..", "include", "tamcmc_gpu.h"), os.path.join("..", "..", "include", "tamcmc_outputs.h")]
+           os.path.join("..", "..", "include", "tamcmc_gpu.h"), os.path.join("..", "..", "include", "tamcmc_outputs.h"),
+           os.path.join("..", "..", "include", "tamcmc_frontend.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]

@@ -25,6 +25,11 @@ EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", 
 EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_close", "tg_restore_read"]
 
 
+# include/tamcmc_frontend.h (host code in the same library)
+EXPORTS_FE = ["tg_fe_last_error", "tg_fe_open", "tg_fe_close", "tg_fe_counts", "tg_fe_nslices", "tg_fe_setup", "tg_fe_problem",
+              "tg_fe_run_info", "tg_fe_input_name", "tg_fe_prior_name", "tg_fe_dump", "tg_evidence", "tg_acceptance"]
+
+
 class TgError(RuntimeError):
     pass
 
@@ -93,6 +98,25 @@ class GpuLibrary:
         L.tg_out_write_restore.argtypes = [C.c_void_p, C.c_long] + [C.c_void_p] * 4
         L.tg_out_close.argtypes = [C.c_void_p]
         L.tg_restore_read.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_long)] + [C.c_void_p] * 4
+        L.tg_fe_last_error.restype = C.c_char_p
+        for name in ("tg_fe_open", "tg_fe_counts", "tg_fe_nslices", "tg_fe_setup", "tg_fe_problem", "tg_fe_run_info", "tg_evidence", "tg_acceptance"):
+            getattr(L, name).restype = C.c_int
+        L.tg_fe_close.restype = None
+        L.tg_fe_input_name.restype = C.c_char_p
+        L.tg_fe_prior_name.restype = C.c_char_p
+        L.tg_fe_dump.restype = C.c_long
+        L.tg_fe_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+        L.tg_fe_close.argtypes = [C.c_void_p]
+        L.tg_fe_counts.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 4
+        L.tg_fe_nslices.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.tg_fe_setup.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.tg_fe_problem.argtypes = [C.c_void_p, C.POINTER(_Problem)]
+        L.tg_fe_run_info.argtypes = [C.c_void_p, C.c_void_p]
+        L.tg_fe_input_name.argtypes = [C.c_void_p, C.c_int]
+        L.tg_fe_prior_name.argtypes = [C.c_void_p, C.c_int]
+        L.tg_fe_dump.argtypes = [C.c_void_p, C.c_char_p, C.c_long]
+        L.tg_evidence.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_long, C.c_int, C.c_void_p, C.POINTER(C.c_double)]
+        L.tg_acceptance.argtypes = [C.c_void_p, C.c_long, C.c_int, C.c_long, C.c_long, C.c_long, C.c_void_p, C.POINTER(C.c_double)]
 
     def check(self, rc):
         if rc != 0:
