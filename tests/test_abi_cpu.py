@@ -10,8 +10,8 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def header_symbols():
-    txt = open(os.path.join(ROOT, "include", "tamcmc_gpu.h")).read()
+def header_symbols(name="tamcmc_gpu.h"):
+    txt = open(os.path.join(ROOT, "include", name)).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
     return sorted(set(re.findall(r"\b(tg_[a-z0-9_]+)\s*\(", txt)))
 
@@ -24,8 +24,14 @@ def test_library_builds_and_exports_header_symbols(tb):
     assert len(syms) >= 18
     for s in syms:
         assert hasattr(lib, s), "header declares %s but the library does not export it" % s
-    from tamcmc_b200.gpu import EXPORTS
+    from tamcmc_b200.gpu import EXPORTS, EXPORTS_OUT, EXPORTS_FE
     assert sorted(EXPORTS) == syms, "python binding and header disagree"
+    # the host-code headers of the same library: outputs / restore formats and the input front end
+    for hdr, exp in (("tamcmc_outputs.h", EXPORTS_OUT), ("tamcmc_frontend.h", EXPORTS_FE)):
+        hs = header_symbols(hdr)
+        for sname in hs:
+            assert hasattr(lib, sname), "%s declares %s but the library does not export it" % (hdr, sname)
+        assert sorted(exp) == hs, "python binding and %s disagree" % hdr
 
 
 def test_library_is_sm100a_only(tb):
