@@ -142,6 +142,10 @@ int tg_sizes(tg_handle *h, int *Nv, int *Np, int *C, int *E, long *Nx);
 int tg_step_begin(tg_handle *h, long i);
 int tg_step_end(tg_handle *h, long i);
 int tg_partials_device_ptr(tg_handle *h, void **ptr, int *count);
+/* Bin-sharded variant only: tg_create / tg_set_state evaluate the CURRENT points on this shard's bins and leave their
+ * partial sums in the same buffer; all-reduce it, then call this to install the logL / logPosterior of the current
+ * points from the reduced sums (Model_def constructor, model_def.cpp:139-143). */
+int tg_shard_install_current(tg_handle *h);
 int tg_sync(tg_handle *h);
 
 /* Kernel timing of the dominant kernel (CUDA events on the handle's stream), accumulated since

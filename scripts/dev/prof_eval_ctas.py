@@ -16,10 +16,10 @@ md.set_tuning(chains_per_block=tune[0], heavy_group=tune[1], light_subtiles=tune
 md.eval_upload(P, T)
 for _ in range(5): md.eval_resident(Cn)
 md.sync()
-buf = (C.c_longlong * (8192 * 8))()
+buf = (C.c_longlong * (8192 * 6))()
 lib.lib.tg_dbg_ctas.argtypes = [C.POINTER(C.c_longlong)]
 lib.lib.tg_dbg_ctas(buf)
-a = np.array(buf, dtype=np.int64).reshape(8192, 8); a = a[a[:, 5] > 0]; a = a[a[:, 4] >= a[:, 4].max() - 150000]   # last launch only
+a = np.array(buf, dtype=np.int64).reshape(8192, 6); a = a[a[:, 5] > 0]; a = a[a[:, 4] >= a[:, 4].max() - 150000]   # last launch only
 t0, t1, t2 = a[:, 0], a[:, 1], a[:, 2]
 sm = a[:, 3] >> 32; tile = a[:, 3] & 0xffffffff
 g0, g1 = a[:, 4], a[:, 5]
@@ -46,30 +46,12 @@ print("heavy CTAs: %d, mean dur %.1f us; light: %d, mean dur %.2f us" % (heavy.s
 h, e = np.histogram(dur, bins=[0, 1, 2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 1000])
 print("hist", list(zip(e[:-1].tolist(), h.tolist())))
 
-# phase breakdown (cycles -> us at 1965 MHz): setup, list building, chain loops, final reduction
 f = 1965.0
-setup = (t1 - t0) / f; lists = a[:, 6] / f; tail = (t2 - a[:, 7]) / f; loops = (a[:, 7] - t1) / f - lists
-for name, sel in (("window", a[:, 6] > 0), ("noise", a[:, 6] == 0)):
-    tot = dur[sel].sum()
-    if sel.sum() == 0: continue
-    print("%s units: n=%d  setup %.2f us (%.1f%%)  lists %.2f (%.1f%%)  loops %.2f (%.1f%%)  final %.2f (%.1f%%)  | mean dur %.2f" % (
-        name, sel.sum(), setup[sel].mean(), 100 * setup[sel].sum() / tot, lists[sel].mean(), 100 * lists[sel].sum() / tot,
-        loops[sel].mean(), 100 * loops[sel].sum() / tot, tail[sel].mean(), 100 * tail[sel].sum() / tot, dur[sel].mean()))
-print("share of all CTA time: heavy %.3f light %.3f" % (dur[heavy].sum() / dur.sum(), dur[~heavy].sum() / dur.sum()))
-
-# how many resident CTAs of an SM are inside their chain loops at the same time (clock64 is per SM)
-occ = {}
-for s in np.unique(sm):
-    k = np.where(sm == s)[0]
-    ev = []
-    for i in k:
-        lo_ = t1[i] + a[i, 6]; hi_ = a[i, 7]
-        ev.append((lo_, 1)); ev.append((hi_, -1))
-    ev.sort()
-    n = 0; last = ev[0][0]
-    start_sm = t0[k].min(); end_sm = t2[k].max()
-    occ[0] = occ.get(0, 0) + (ev[0][0] - start_sm) + (end_sm - ev[-1][0])
-    for t, d in ev:
-        occ[n] = occ.get(n, 0) + (t - last); last = t; n += d
-tot = float(sum(occ.values()))
-print("time share with n CTAs of the SM inside the chain loops:", {int(k_): round(v / tot, 3) for k_, v in sorted(occ.items())})
+setup = (t1 - t0) / f
+print("setup (phase 0) us: mean %.2f  share of CTA time %.3f" % (setup.mean(), setup.sum() / dur.sum()))
+start = (g0 - g0.min()) / 1e3; end = (g1 - g0.min()) / 1e3
+print("CTA start times us: first wave (<1us) %d CTAs, last start %.1f; last end %.1f" % ((start < 1).sum(), start.max(), end.max()))
+slots_busy = dur.sum() / (148 * 2)
+print("sum of CTA durations / 296 slots = %.1f us  (efficiency vs span %.3f)" % (slots_busy, slots_busy / end.max()))
+# idle tail per SM: span - finish time of the SM
+print("idle tail per SM us: mean %.2f max %.2f" % ((end.max() - last).mean(), (end.max() - last).max()))

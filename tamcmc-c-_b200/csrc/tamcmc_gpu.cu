@@ -49,7 +49,7 @@ struct tg_handle {
     int       *index_to_relax = nullptr; double *Tcoefs = nullptr;
     EvalBuf    ev;               // tg_eval batches
     EvalBuf    sp;               // sampler's proposed points (cap == C)
-    int        nitems = 0, max_items = 0, light_sub = 8, chains_per_block = 0, heavy_group = 2, use_graph = 1, steps_per_graph = 16;
+    int        nitems = 0, max_items = 0, light_sub = 8, heavy_sub = 2, chains_per_block = 0, heavy_group = 2, use_graph = 1, steps_per_graph = 16;
     int        smem_matrix = 0, tri_smem = 0; size_t propose_smem = 0, spec_smem = 0; int fused_spec = 0;
     double    *stage_mu = nullptr, *stage_cov = nullptr;   // tg_get_state staging ([C][Nv], [C][Nv][Nv])
     int        list_cap = 4, max_cpb = 1;
@@ -80,7 +80,7 @@ template <typename T> static int dalloc(tg_handle *h, T **p, size_t n)
 extern "C" const char *tg_last_error(void) { return g_err.c_str(); }
 extern "C" int tg_version(void) { return 100; }
 #ifdef TG_PROFILE
-extern "C" int tg_dbg_ctas(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_cta, sizeof(long long) * TG_DBG_CTAS * 8) == cudaSuccess ? 0 : -2; }
+extern "C" int tg_dbg_ctas(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_cta, sizeof(long long) * TG_DBG_CTAS * 6) == cudaSuccess ? 0 : -2; }
 extern "C" int tg_dbg_specs(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_spec, sizeof(long long) * 16) == cudaSuccess ? 0 : -2; }
 extern "C" int tg_dbg_clocks(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_clk, sizeof(long long) * 32) == cudaSuccess ? 0 : -2; }
 #endif
@@ -201,7 +201,8 @@ static int build_items(tg_handle *h, EvalBuf &b, int B)
         for (int t = 0, c = 0; t < nt; t++) { c += diff[t]; w[t] = c; }
         const int L = std::max(1, h->light_sub);
         for (int t = 0; t < t0; t += L) items.push_back(make_int4(t * SUB, std::min(L, t0 - t), 0, 0));
-        for (int t = t0; t < t1; t++) items.push_back(make_int4(t * SUB, 1, w[t], 1));
+        const int Hs = std::max(1, h->heavy_sub);   // sub-tiles per item where windows are expected (2: the kernel takes them 8 bins per thread)
+        for (int t = t0; t < t1; t += Hs) { int wm = 0; for (int q = t; q < std::min(t + Hs, t1); q++) wm = std::max(wm, w[q]); items.push_back(make_int4(t * SUB, std::min(Hs, t1 - t), wm, 1)); }
         for (int t = t1; t < nt; t += L) items.push_back(make_int4(t * SUB, std::min(L, nt - t), 0, 0));
     }
     bool same = items.size() == h->items_host.size();
@@ -365,6 +366,9 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         CK(cudaFuncSetAttribute(tg_k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
         const int groups = (C + m - 1) / m;                                               // balanced chain groups of <= max_cpb
         h->chains_per_block = (C + groups - 1) / groups;
+        // developer knobs for scheduling experiments (never change results)
+        if (const char *e = getenv("TG_HEAVY_SUB")) h->heavy_sub = std::max(1, atoi(e));
+        if (const char *e = getenv("TG_HEAVY_GROUP")) h->heavy_group = std::max(1, atoi(e));
     }
 
     // ---- MALA configuration ----
@@ -768,6 +772,15 @@ extern "C" int tg_step_end(tg_handle *h, long i)
     if (!h) return fail(TG_E_BADARG, "null handle");
     CK(cudaSetDevice(h->device));
     return launch_step(h, false, true, 1);
+}
+extern "C" int tg_shard_install_current(tg_handle *h)
+{
+    if (!h) return fail(TG_E_BADARG, "null handle");
+    CK(cudaSetDevice(h->device));
+    tg_k_install_current<<<(h->s.C + 127) / 128, 128, 0, h->stream>>>(h->d, h->s, h->sp.t, h->sp.sums);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(h->stream));
+    return TG_OK;
 }
 extern "C" int tg_partials_device_ptr(tg_handle *h, void **ptr, int *count)
 {

@@ -299,12 +299,12 @@ __device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalS
     }
 }
 
-// Per-chain lists of the components whose window meets the sub-tile [b0, b0+SUB): order-preserving
+// Per-chain lists of the components whose window meets the tile [b0, b0+SUB) (SUB = one or two sub-tiles): order-preserving
 // ballot compaction for all chains of the group at once, padded to a multiple of four, plus the
 // per-quad "covers the whole sub-tile" flags.  Called by the whole CTA (contains barriers).
-__device__ void tg_build_lists(const TgEvalArgs &a, const TgEvalSmem &S, int (*s_cnt)[TG_THREADS / 32], int *s_tot, int G, int c0, int b0)
+__device__ void tg_build_lists(const TgEvalArgs &a, const TgEvalSmem &S, int (*s_cnt)[TG_THREADS / 32], int *s_tot, int G, int c0, int b0, const int SUB)
 {
-    constexpr int SUB = TG_THREADS * 4, NW = TG_THREADS / 32;
+    constexpr int NW = TG_THREADS / 32;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, cap = a.list_cap;
     __syncthreads();                              // the previous sub-tile's lists are dead
     if (tid < TG_MAXG) s_tot[tid] = 0;
@@ -425,8 +425,14 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
         const int b0 = item.x + sub * SUB;
         if (b0 >= Nx) break;
         const bool gen = gen_all || (b0 + SUB > Nx);
-        if (wlo < b0 + SUB && whi > b0) {         // truncation windows meet this sub-tile
-            tg_build_lists(a, S, s_cnt, s_tot, G, c0, b0);
+        if (!gen_all && sub + 1 < item.y && b0 + 2 * SUB <= Nx && wlo < b0 + 2 * SUB && whi > b0) {
+            // truncation windows meet this pair of sub-tiles: 8 bins per thread against one list (half the list traffic and
+            // loop overhead per bin, twice the independent work per warp behind every reciprocal)
+            tg_build_lists(a, S, s_cnt, s_tot, G, c0, b0, 2 * SUB);
+            tg_chain_loop<8, false, true>(a, S, s_tot, G, c0, b0, tid);
+            sub += 2;
+        } else if (wlo < b0 + SUB && whi > b0) {  // truncation windows meet this sub-tile
+            tg_build_lists(a, S, s_cnt, s_tot, G, c0, b0, SUB);
             if (gen) tg_chain_loop<4, true, true>(a, S, s_tot, G, c0, b0, tid);
             else     tg_chain_loop<4, false, true>(a, S, s_tot, G, c0, b0, tid);
             sub += 1;

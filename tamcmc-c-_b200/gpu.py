@@ -19,7 +19,7 @@ F_FIX_SWAP_BOOKKEEPING = 1
 
 EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", "tg_eval_upload", "tg_eval_resident",
            "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
-           "tg_step_end", "tg_partials_device_ptr", "tg_sync", "tg_kernel_time", "tg_set_tuning",
+           "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_event_record", "tg_event_elapsed_ms"]
 # include/tamcmc_outputs.h (host code in the same library)
 EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_close", "tg_restore_read"]
@@ -84,6 +84,7 @@ class GpuLibrary:
         L.tg_step_begin.argtypes = [C.c_void_p, C.c_long]
         L.tg_step_end.argtypes = [C.c_void_p, C.c_long]
         L.tg_partials_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int)]
+        L.tg_shard_install_current.argtypes = [C.c_void_p]
         L.tg_sync.argtypes = [C.c_void_p]
         L.tg_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_double), C.POINTER(C.c_long)]
         L.tg_set_tuning.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
@@ -368,6 +369,11 @@ class GpuMALA:
 
     def step_end(self, i):
         self.model.lib.check(self.model.lib.lib.tg_step_end(self.model.h, i))
+
+    def install_current(self):
+        """Bin-sharded variant: install the current logL from the (all-reduced) partials buffer."""
+        self.model.lib.check(self.model.lib.lib.tg_shard_install_current(self.model.h))
+        self.model.refresh_from_device()
 
     def partials_ptr(self):
         p, n = C.c_void_p(), C.c_int()
