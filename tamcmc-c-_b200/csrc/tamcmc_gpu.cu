@@ -366,6 +366,10 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         CK(cudaFuncSetAttribute(tg_k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
         const int groups = (C + m - 1) / m;                                               // balanced chain groups of <= max_cpb
         h->chains_per_block = (C + groups - 1) / groups;
+        // where truncation windows lie: items of two sub-tiles (taken 8 bins per thread); one chain per unit for a single
+        // ensemble (more, smaller units: better tail of the grid), three when many chains fill the GPU anyway
+        h->heavy_sub = 2;
+        h->heavy_group = (C >= 24) ? 3 : 1;
         // developer knobs for scheduling experiments (never change results)
         if (const char *e = getenv("TG_HEAVY_SUB")) h->heavy_sub = std::max(1, atoi(e));
         if (const char *e = getenv("TG_HEAVY_GROUP")) h->heavy_group = std::max(1, atoi(e));
