@@ -39,6 +39,7 @@ struct tg_handle {
     cudaStream_t side = nullptr;           // the adaptation candidates of a step run here, beside the proposal and the fused kernel
     cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
     bool         side_pending = false;     // a join is owed before the next finish kernel
+    bool         pdl = true;                           // programmatic dependent launch between the step kernels (environment TG_PDL=0 turns it off)
     bool         no_split = false, no_side = false;   // developer switches (environment TG_NO_SPLIT_PRIOR / TG_NO_SIDE_STREAM)
     TgDesc     d{};
     TgMala     m{};
@@ -120,6 +121,20 @@ static int ncomp_for(const tg_problem *p, int *ncomp, int *nmodes)
     return TG_OK;
 }
 
+// Launch with (pdl) or without the programmatic-serialization attribute: with it the kernel may become resident while its
+// predecessor in the stream still runs and synchronises on it with tg_pdl_wait() (tg_internal.cuh).
+template <class Arg>
+static cudaError_t launch_k(void (*kern)(Arg), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, const Arg &arg)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, arg);
+}
+
 static cudaEvent_t next_event(tg_handle *h)
 {
     if (h->ev_used == h->ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); h->ev_pool.push_back(e); }
@@ -142,7 +157,7 @@ static int harvest_events(tg_handle *h)
 static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B);
 
 // prologue (optional) + fused kernel + per-chain reduction for B points
-static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_dev, int B, double *model, bool do_prologue, bool do_reduce)
+static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_dev, int B, double *model, bool do_prologue, bool do_reduce, bool pdl = false)
 {
     if (do_prologue) {
         TgProArgs pa{h->d, b.t, params_dev, h->pri, h->sw};
@@ -158,7 +173,7 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
         if (h->ev_used >= 8192) { int r = harvest_events(h); if (r) return r; }
         cudaEventRecord(next_event(h), h->stream);
     }
-    tg_k_eval<<<grid, TG_THREADS, esm, h->stream>>>(ea);
+    CK(launch_k(tg_k_eval, grid, dim3(TG_THREADS), esm, h->stream, pdl && !h->timing, ea));
     if (h->timing) cudaEventRecord(next_event(h), h->stream);
     h->n_eval_launch++; h->n_launch_total++;
     if (do_reduce) { tg_k_reduce<<<B, 256, 0, h->stream>>>(b.partials, h->nitems, b.sums); h->n_launch_total++; }
@@ -314,6 +329,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
     h->no_split = getenv("TG_NO_SPLIT_PRIOR") != nullptr; h->no_side = getenv("TG_NO_SIDE_STREAM") != nullptr;
+    if (const char *e = getenv("TG_PDL")) h->pdl = atoi(e) != 0;
     CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
 
@@ -681,7 +697,7 @@ static int launch_step(tg_handle *h, bool begin, bool end, int presummed)
             h->side_pending = true;
             h->n_launch_total++;
         }
-        tg_k_propose<<<dim3(C, 1), 256, h->propose_smem, h->stream>>>(pa);
+        CK(launch_k(tg_k_propose, dim3(C, 1), dim3(256), h->propose_smem, h->stream, h->pdl && !h->timing, pa));
         h->n_launch_total++;
         if (learn && !fused) {       // very large Nv: the candidates read the proposed point from HBM, so they follow the propose kernel
             CK(cudaEventRecord(h->ev_fork, h->stream));
@@ -692,12 +708,12 @@ static int launch_step(tg_handle *h, bool begin, bool end, int presummed)
             h->side_pending = true;
             h->n_launch_total++;
         }
-        int r = launch_eval_kernels(h, h->sp, h->sp.params, C, nullptr, false, presummed != 0); if (r) return r;
+        int r = launch_eval_kernels(h, h->sp, h->sp.params, C, nullptr, false, presummed != 0, h->pdl); if (r) return r;
     }
     if (end) {
         if (h->side_pending) { CK(cudaStreamWaitEvent(h->stream, h->ev_join, 0)); h->side_pending = false; }
         TgFinishArgs fa{h->d, h->s, h->m, h->sp.t, h->sp.partials, h->nitems, h->sp.sums, presummed, h->rec, 1};
-        tg_k_finish<<<C, 256, 0, h->stream>>>(fa);
+        CK(launch_k(tg_k_finish, dim3(C), dim3(256), 0, h->stream, h->pdl && !presummed && !h->timing, fa));
         h->n_launch_total++;
     }
     CK(cudaGetLastError());
@@ -738,18 +754,21 @@ extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
         long k = 0;
         if (h->use_graph && !h->timing) {
             const int G = h->steps_per_graph;
-            if (!h->graph && n >= G) {
-                cudaGraph_t g;
+            for (int attempt = 0; !h->graph && n >= G && attempt < 2; attempt++) {
+                cudaGraph_t g = nullptr;
                 const long lt = h->n_launch_total, le = h->n_eval_launch;
                 CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
                 int r = TG_OK;
                 for (int q = 0; q < G && r == TG_OK; q++) r = launch_step(h, true, true, 0);
                 cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
-                h->n_launch_total = lt; h->n_eval_launch = le;
-                if (r) return r;
-                CK(ce);
-                CK(cudaGraphInstantiate(&h->graph, g, 0));
-                cudaGraphDestroy(g);
+                h->n_launch_total = lt; h->n_eval_launch = le; h->side_pending = false;
+                if (ce == cudaSuccess && r == TG_OK) ce = cudaGraphInstantiate(&h->graph, g, 0);
+                if (g) cudaGraphDestroy(g);
+                if (ce == cudaSuccess && r == TG_OK) break;
+                h->graph = nullptr;
+                if (!h->pdl || attempt == 1) { if (r) return r; CK(ce); }
+                cudaGetLastError();                  // a driver that cannot capture programmatic edges: same graph with full dependencies
+                h->pdl = false;
             }
             if (h->graph) {
                 for (; k + G <= n; k += G) { CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += ((h->m.n_learn > 0 || (h->tri_smem && !h->no_split)) ? 4L : 3L) * G; h->n_eval_launch += G; }

@@ -401,9 +401,11 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
     S.nh    = S.cls + (size_t)cpb * TG_MAXH;
 
     // ---- phase 0: noise tables, window unions, running results ----
+    for (int g = 0; g < G; g++) { S.sum[g * TG_THREADS + tid] = 0.0; S.pf[g * TG_THREADS + tid] = 1.0; S.pe[g * TG_THREADS + tid] = 0; }
+    tg_pdl_wait();                                // everything above (unit table, shared-memory set-up) may overlap the proposal kernel
+    tg_pdl_trigger();
     for (int e = tid; e < G * TG_NOISE_STRIDE; e += TG_THREADS) S.nz[e] = a.t.noise[(size_t)c0 * TG_NOISE_STRIDE + e];
     if (tid < G) { s_w[0][tid] = a.t.wlo[c0 + tid]; s_w[1][tid] = a.t.whi[c0 + tid]; }
-    for (int g = 0; g < G; g++) { S.sum[g * TG_THREADS + tid] = 0.0; S.pf[g * TG_THREADS + tid] = 1.0; S.pe[g * TG_THREADS + tid] = 0; }
     __syncthreads();
     if (tid < TG_MAXG * TG_MAXH) {                // Harvey exponent classes / counts as ints
         const int g = tid / TG_MAXH, k = tid % TG_MAXH;

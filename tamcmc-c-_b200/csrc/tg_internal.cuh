@@ -59,6 +59,14 @@ struct TgTables {
 // ---------------------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------------------
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-serialization attribute may become
+// resident while its predecessor in the stream still runs; tg_pdl_wait() blocks until the predecessor grid has completed
+// and its writes are visible (a no-op for a kernel launched without the attribute); tg_pdl_trigger() lets the successor
+// become resident (every CTA must call it or exit).  All three step kernels trigger only AFTER their own wait, so at most
+// one kernel runs ahead and nothing of a successor executes past its wait before the predecessor is complete.
+__device__ __forceinline__ void tg_pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void tg_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Reciprocal: MUFU.RCP64H seed (2^-23 rel. error) + 2 Newton steps = full fp64 precision
 // (<= 1 ulp; not IEEE-exact, which the 1e-10 parity budget does not need).  Special values:
 // t=inf -> 0, t=0 -> inf, NaN -> NaN come out right because the seed is already exact there

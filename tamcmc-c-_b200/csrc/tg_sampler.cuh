@@ -57,6 +57,8 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
     const TgState &s = a.s;
     const int c = blockIdx.x, role = blockIdx.y + a.role_base, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
+    tg_pdl_wait();                                                  // role 0 may be resident before the previous finish kernel is done
+    if (role == 0) tg_pdl_trigger();                                // the side-stream roles complete in full before the finish kernel starts
     const long it = s.ctrl->i;
     if (role == 1 || role == 2) {
         if (!tg_learning(a.m, it)) return;
@@ -198,20 +200,28 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     const int Nv = s.Nv, Np = s.Np;
     // Every load that does not depend on the decision is issued up front: the kernel is a chain of
     // global-memory round trips, so they are kept to the unavoidable ones.
+    // Under programmatic dependent launch this kernel becomes resident while the fused kernel drains: the proposal kernel and
+    // the adaptation candidates are complete by then (the fused kernel triggers after its own wait; the candidates are a full
+    // dependency), so everything but the partial sums is loaded before the wait.
     const long it = s.ctrl->i;
-    double a1 = 0, a2 = 0;
-    if (!a.presummed) for (int t = tid; t < a.ntiles; t += nt) { const double2 v = a.partials[(size_t)c * a.ntiles + t]; a1 += v.x; a2 += v.y; }
     const bool small = (Nv <= 256 && Np <= 256);   // one element of the proposed point per thread, held in registers
     double vprop = 0.0, pprop = 0.0;
     if (small) { if (tid < Nv) vprop = s.vars_prop[(size_t)c * Nv + tid]; if (tid < Np) pprop = s.params_prop[(size_t)c * Np + tid]; }
     int st = 0, live = 0, fail0 = 0, fail1 = 0;
     double T = 1.0, logPr = 0.0, logPo_cur = 0.0, sig = 0.0;
     if (tid == 0) {
-        st = a.t.status[c] | a.t.pstatus[c] | s.sticky_status[c]; T = s.Tcoefs[c]; logPr = a.t.logprior[c]; logPo_cur = s.logPost_cur[c];
+        st = a.t.status[c] | s.sticky_status[c]; T = s.Tcoefs[c]; logPo_cur = s.logPost_cur[c];
         live = s.live[c]; sig = s.sigma[c];
-        fail0 = s.chol_fail[((live + 1) % 3) * s.C + c]; fail1 = s.chol_fail[((live + 2) % 3) * s.C + c];
     }
     const long slot = it - s.ctrl->i0;
+    tg_pdl_wait();
+    tg_pdl_trigger();
+    if (tid == 0) {                                                 // products of the side-stream CTAs: only after the wait
+        st |= a.t.pstatus[c]; logPr = a.t.logprior[c];
+        fail0 = s.chol_fail[((live + 1) % 3) * s.C + c]; fail1 = s.chol_fail[((live + 2) % 3) * s.C + c];
+    }
+    double a1 = 0, a2 = 0;
+    if (!a.presummed) for (int t = tid; t < a.ntiles; t += nt) { const double2 v = a.partials[(size_t)c * a.ntiles + t]; a1 += v.x; a2 += v.y; }
 
     // 1. logL of the proposed point
     const double2 sum = a.presummed ? a.sums[c] : tg_block_sum2(a1, a2, s_part);

@@ -74,6 +74,23 @@ def test_graph_and_direct_launch_agree(tb, W):
     a.close(); b.close()
 
 
+@pytest.mark.parametrize("case", ["gauss", "local", "global"])
+def test_programmatic_dependent_launch_changes_nothing(tb, W, case, monkeypatch):
+    """The step kernels overlap their launch with the predecessor's tail (griddepcontrol, tg_internal.cuh); the records of
+    a run must be the same bits with the overlap turned off (TG_PDL=0 is read when the handle is created)."""
+    prob = {"gauss": lambda: _gauss(W), "local": lambda: W.s_local(), "global": lambda: W.s_global(Nx=100000, step=0.05, norders=4, numax=2500.0, dnu=120.0)}[case]()
+    cfg = tb.MalaConfig(Nchains=10, Nt_learn=[20, 10000], periods_learn=[1], c0=2.0, dN_mixing=1, seed=77)
+    res = []
+    for pdl in ("0", "1"):
+        monkeypatch.setenv("TG_PDL", pdl)
+        md = tb.GpuModelDef(prob, cfg)
+        res.append(tb.GpuMALA(md).execute(0, 160))
+        md.close()
+    for k in res[0]:
+        assert np.array_equal(res[0][k], res[1][k], equal_nan=res[0][k].dtype.kind == "f"), k
+    assert np.all(np.isfinite(res[1]["logPost"][:, 0]))
+
+
 def _cpu_sampler(oracle, prob, cfg, nsteps, rng):
     """MALA.cpp:608-692 with numpy RNG and the oracle as generate_model."""
     C = cfg.Nchains
