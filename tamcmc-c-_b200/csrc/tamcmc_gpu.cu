@@ -5,6 +5,8 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <limits>
+#include <cmath>
 #include <algorithm>
 #include "tg_internal.cuh"
 #include "tg_prologue.cuh"
@@ -46,6 +48,8 @@ struct tg_handle {
     TgState    s{};
     TgRecDev   rec{};
     double    *x = nullptr, *y = nullptr, *lnx = nullptr, *sig = nullptr;
+    double    *mom = nullptr; int mom_sub = 4, mom_run = 16; int *mom_fail = nullptr; long n_mom_tiles = 0;
+    int       *mom_note = nullptr;                      // pinned, mapped: the kernel stores 1 when it flags a tile for the first time          // Chebyshev moments of the data over aligned tiles (tg_eval.cuh), NULL = off
     double    *pri = nullptr; int *sw = nullptr;
     int       *index_to_relax = nullptr; double *Tcoefs = nullptr;
     EvalBuf    ev;               // tg_eval batches
@@ -121,6 +125,46 @@ static int ncomp_for(const tg_problem *p, int *ncomp, int *nmodes)
     return TG_OK;
 }
 
+// Moment buffer of the background-only path (tg_eval.cuh, tg_moment_tiles): the interpolation matrices, then for every
+// aligned tile of mt_bins bins ST_k = sum_i T_k(t_i) and YT_k = sum_i y_i T_k(t_i), k < TG_MD, t_i = (x_i - xm) / xh with
+// xm, xh the centre and half-width of the tile (the kernel forms them from the same two abscissae).  Extended precision on
+// the host; a tile whose abscissae do not increase across it gets ST_0 = NaN and is never used.
+static void build_moments(const double *x, const double *y, long Nx, int mt_bins, std::vector<double> &out)
+{
+    const int n = TG_MD, nc = TG_MCHK;
+    const long nt = Nx / mt_bins;
+    out.assign((size_t)TG_MOM_HDR + (size_t)nt * 2 * n, 0.0);
+    const long double pi = 3.141592653589793238462643383279502884L;
+    long double tn[TG_MD + TG_MCHK];
+    for (int j = 0; j < n; j++) tn[j] = cosl(pi * (j + 0.5L) / n);                 // roots of T_n
+    { const int ext[TG_MCHK] = {0, 2, 4, 6, 9}; for (int c = 0; c < nc; c++) tn[n + c] = cosl(pi * ext[c] / n); }   // extrema of T_n: the node polynomial peaks there
+    long double W[TG_MD][TG_MD];
+    for (int k = 0; k < n; k++) for (int j = 0; j < n; j++) W[k][j] = (k == 0 ? 1.0L : 2.0L) / n * cosl(pi * k * (j + 0.5L) / n);
+    for (int k = 0; k < n; k++) for (int j = 0; j < n; j++) out[(size_t)k * n + j] = (double)W[k][j];
+    for (int c = 0; c < nc; c++) for (int j = 0; j < n; j++) {
+        long double e = 0.0L;
+        for (int k = 0; k < n; k++) e += W[k][j] * cosl(k * acosl(tn[n + c]));
+        out[(size_t)(n + c) * n + j] = (double)e;
+    }
+    for (int j = 0; j < n + nc; j++) out[(size_t)(n + nc) * n + j] = (double)tn[j];
+    for (long t = 0; t < nt; t++) {
+        const double *xs = x + t * mt_bins, *ys = y + t * mt_bins;
+        const double xa = xs[0], xb = xs[mt_bins - 1], xm = 0.5 * (xa + xb), xh = 0.5 * (xb - xa);
+        long double S[TG_MD] = {0}, Y[TG_MD] = {0};
+        bool good = (xh > 0.0) && std::isfinite(xm) && std::isfinite(xh);
+        for (int i = 0; i < mt_bins && good; i++) {
+            const long double tt = ((long double)xs[i] - xm) / xh;
+            if (!(tt >= -1.0L - 1e-12L && tt <= 1.0L + 1e-12L) || !std::isfinite(ys[i])) { good = false; break; }
+            long double T0 = 1.0L, T1 = tt;
+            S[0] += 1.0L; Y[0] += ys[i]; S[1] += T1; Y[1] += ys[i] * T1;
+            for (int k = 2; k < n; k++) { const long double T2 = 2.0L * tt * T1 - T0; S[k] += T2; Y[k] += ys[i] * T2; T0 = T1; T1 = T2; }
+        }
+        double *o = out.data() + TG_MOM_HDR + (size_t)t * 2 * n;
+        for (int k = 0; k < n; k++) { o[k] = (double)S[k]; o[n + k] = (double)Y[k]; }
+        if (!good) o[0] = std::numeric_limits<double>::quiet_NaN();
+    }
+}
+
 // Launch with (pdl) or without the programmatic-serialization attribute: with it the kernel may become resident while its
 // predecessor in the stream still runs and synchronises on it with tg_pdl_wait() (tg_internal.cuh).
 template <class Arg>
@@ -167,7 +211,7 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
     tg_handle::UnitTable &u = (&b == &h->sp) ? h->u_sp : h->u_ev;
     if (B != u.B) { int r = build_units(h, u, B); if (r) return r; }     // never inside a graph capture: tg_run builds u_sp first
     const size_t esm = TG_EVAL_SMEM(h->chains_per_block, h->list_cap);
-    TgEvalArgs ea{h->d, b.t, h->x, h->y, h->lnx, h->sig, b.partials, model, u.dev, B, h->nitems, h->chains_per_block, h->list_cap};
+    TgEvalArgs ea{h->d, b.t, h->x, h->y, h->lnx, h->sig, b.partials, model, u.dev, B, h->nitems, h->chains_per_block, h->list_cap, h->mom, h->mom_sub, h->mom_fail, h->mom_note};
     dim3 grid(u.n);
     if (h->timing) {
         if (h->ev_used >= 8192) { int r = harvest_events(h); if (r) return r; }
@@ -215,13 +259,33 @@ static int build_items(tg_handle *h, EvalBuf &b, int B)
         }
         for (int t = 0, c = 0; t < nt; t++) { c += diff[t]; w[t] = c; }
         const int L = std::max(1, h->light_sub);
-        for (int t = 0; t < t0; t += L) items.push_back(make_int4(t * SUB, std::min(L, t0 - t), 0, 0));
+        // background-only stretches: runs of aligned moment tiles the kernel evaluates through the moments of the data (kind 2, cheap),
+        // bin-by-bin runs (kind 0) for misaligned ends and for the tiles earlier launches flagged (their polynomial check failed)
+        const int ms = h->mom ? h->mom_sub : 0;
+        std::vector<int> flag((size_t)std::max<long>(h->n_mom_tiles, 1), 0);
+        if (ms > 0 && h->n_mom_tiles > 0) CK(cudaMemcpy(flag.data(), h->mom_fail, (size_t)h->n_mom_tiles * 4, cudaMemcpyDeviceToHost));
+        auto usable = [&](int t, int tb) { return ms > 0 && t % ms == 0 && t + ms <= tb && (long)(t + ms) * SUB <= (long)h->d.Nx && !flag[t / ms]; };
+        auto light_region = [&](int ta, int tb) {
+            int t = ta;
+            while (t < tb) {
+                if (usable(t, tb)) {
+                    int n = 1;
+                    while (n < h->mom_run && usable(t + n * ms, tb)) n++;
+                    items.push_back(make_int4(t * SUB, n * ms, 0, 2)); t += n * ms;
+                } else {
+                    int e = t + 1;
+                    while (e < tb && e - t < L && !usable(e, tb)) e++;
+                    items.push_back(make_int4(t * SUB, e - t, 0, 0)); t = e;
+                }
+            }
+        };
+        light_region(0, t0);
         const int Hs = std::max(1, h->heavy_sub);   // sub-tiles per item where windows are expected (2: the kernel takes them 8 bins per thread)
         for (int t = t0; t < t1; t += Hs) { int wm = 0; for (int q = t; q < std::min(t + Hs, t1); q++) wm = std::max(wm, w[q]); items.push_back(make_int4(t * SUB, std::min(Hs, t1 - t), wm, 1)); }
-        for (int t = t1; t < nt; t += L) items.push_back(make_int4(t * SUB, std::min(L, nt - t), 0, 0));
+        light_region(t1, nt);
     }
     bool same = items.size() == h->items_host.size();
-    for (size_t k = 0; same && k < items.size(); k++) same = items[k].x == h->items_host[k].x && items[k].y == h->items_host[k].y && items[k].z == h->items_host[k].z;
+    for (size_t k = 0; same && k < items.size(); k++) same = items[k].x == h->items_host[k].x && items[k].y == h->items_host[k].y && items[k].z == h->items_host[k].z && items[k].w == h->items_host[k].w;
     if (same) return TG_OK;
     h->items_host = items;
     h->nitems = (int)items.size();
@@ -239,12 +303,12 @@ static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B)
     const int gl = std::max(1, h->chains_per_block), gh = std::max(1, std::min(h->heavy_group, gl));
     for (size_t k = 0; k < h->items_host.size(); k++) {
         const int4 it = h->items_host[k];
-        const int gmax = (it.w && !h->no_order) ? gh : gl;
+        const int gmax = (it.w == 1 && !h->no_order) ? gh : gl;
         const int groups = (B + gmax - 1) / gmax, g = (B + groups - 1) / groups;      // balanced
         for (int c0 = 0; c0 < B; c0 += g) {
             const int G = std::min(g, B - c0);
             units.push_back(make_int4(it.x, it.y | (G << 16), c0, (int)k));
-            cost.push_back((double)G * it.y * (20.0 + 6.25 * it.z) + 15.0);
+            cost.push_back(it.w == 2 ? (double)G * (it.y / std::max(1, h->mom_sub)) * 8.0 + 15.0 : (double)G * it.y * (20.0 + 6.25 * it.z) + 15.0);
         }
     }
     if (!h->no_order) {
@@ -265,6 +329,16 @@ static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B)
     CK(cudaMemcpy(u.dev, units.data(), units.size() * sizeof(int4), cudaMemcpyHostToDevice));
     u.n = (int)units.size(); u.B = B;
     return TG_OK;
+}
+
+// The fused kernel flagged background-only tiles whose polynomial check failed since the work items were built: rebuild the
+// items around them (they cost a bin-by-bin evaluation; left inside a long run of cheap moment tiles they would be the tail
+// of the launch).  Results never depend on the items.
+static int refresh_items_if_flagged(tg_handle *h)
+{
+    if (!h->mom_note || !*(volatile int *)h->mom_note) return TG_OK;
+    *(volatile int *)h->mom_note = 0;
+    return build_items(h, h->sp, h->s.C);
 }
 
 extern "C" int tg_set_tuning(tg_handle *h, int chains_per_block, int heavy_group, int light_subtiles, int use_graph)
@@ -355,6 +429,22 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     CK(cudaMemcpyAsync(h->y, p->y, Nx * 8, cudaMemcpyHostToDevice, h->stream));
     if (p->sigma_y) { DA(h->sig, Nx); CK(cudaMemcpyAsync(h->sig, p->sigma_y, Nx * 8, cudaMemcpyHostToDevice, h->stream)); }
     tg_k_lnx<<<(unsigned)((Nx + 255) / 256), 256, 0, h->stream>>>(h->x, h->lnx, (int)Nx);
+    {   // moments of the data for the background-only stretches (chi22p likelihood only; TG_MOMENTS=0 turns the path off)
+        const char *e = getenv("TG_MOMENTS"), *e2 = getenv("TG_MOM_SUB");
+        if (e2) h->mom_sub = std::max(1, std::min(8, atoi(e2)));
+        if (const char *e3 = getenv("TG_MOM_RUN")) h->mom_run = std::max(1, atoi(e3));
+        if (!(e && atoi(e) == 0) && p->likelihood_case == 0 && (long)Nx >= (long)h->mom_sub * TG_THREADS * 4) {
+            std::vector<double> mom;
+            build_moments(p->x, p->y, (long)Nx, h->mom_sub * TG_THREADS * 4, mom);
+            DA(h->mom, mom.size());
+            CK(cudaMemcpy(h->mom, mom.data(), mom.size() * 8, cudaMemcpyHostToDevice));
+            h->n_mom_tiles = (long)Nx / (h->mom_sub * TG_THREADS * 4);
+            DA(h->mom_fail, (size_t)h->n_mom_tiles);
+            CK(cudaMemset(h->mom_fail, 0, (size_t)h->n_mom_tiles * 4));
+            CK(cudaHostAlloc((void **)&h->mom_note, sizeof(int), cudaHostAllocMapped));
+            *h->mom_note = 0;
+        }
+    }
     DA(h->pri, (size_t)4 * p->Np); DA(h->sw, p->Np); DA(h->index_to_relax, d.Nv); DA(h->Tcoefs, p->Nchains);
     CK(cudaMemcpyAsync(h->pri, p->priors, (size_t)4 * p->Np * 8, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->sw, p->priors_switch, (size_t)p->Np * 4, cudaMemcpyHostToDevice, h->stream));
@@ -482,6 +572,7 @@ extern "C" int tg_destroy(tg_handle *h)
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
     for (void *q : h->allocs) cudaFree(q);
     for (EvalBuf *b : {&h->sp, &h->ev}) { if (b->pin_in) cudaFreeHost(b->pin_in); if (b->pin_out) cudaFreeHost(b->pin_out); }
+    if (h->mom_note) cudaFreeHost(h->mom_note);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->side) cudaStreamDestroy(h->side);
@@ -528,6 +619,7 @@ extern "C" int tg_eval_resident(tg_handle *h, int B)
 {
     if (!h) return fail(TG_E_BADARG, "null handle");
     CK(cudaSetDevice(h->device));
+    { int r = refresh_items_if_flagged(h); if (r) return r; }
     return eval_resident(h, B, nullptr);
 }
 
@@ -549,6 +641,7 @@ extern "C" int tg_eval(tg_handle *h, const double *params, int B, const double *
                        double *logL, double *logPrior, double *logPost, int *status, double *model)
 {
     if (!h || !params || !T || B < 1) return fail(TG_E_BADARG, "tg_eval: bad argument");
+    { int r = refresh_items_if_flagged(h); if (r) return r; }
     if (!model && h->use_graph && !h->timing) {
         // the whole call as one graph launch: H2D of the packed inputs, prologue, fused kernel, reduce+finalize, D2H of the packed results
         CK(cudaSetDevice(h->device));
@@ -745,7 +838,8 @@ extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
 {
     if (!h || nsteps < 0) return fail(TG_E_BADARG, "tg_run: bad argument");
     CK(cudaSetDevice(h->device));
-    if (nsteps >= 64) { int r = build_items(h, h->sp, h->s.C); if (r) return r; }   // follow the windows of the chains (scheduling only)
+    if (nsteps >= 64) { if (h->mom_note) *(volatile int *)h->mom_note = 0; int r = build_items(h, h->sp, h->s.C); if (r) return r; }   // follow the windows of the chains (scheduling only)
+    else { int r = refresh_items_if_flagged(h); if (r) return r; }
     if (h->u_sp.B != h->s.C) { int r = build_units(h, h->u_sp, h->s.C); if (r) return r; }
     long done = 0;
     while (done < nsteps) {
@@ -786,6 +880,8 @@ extern "C" int tg_step_begin(tg_handle *h, long i)
 {
     if (!h) return fail(TG_E_BADARG, "null handle");
     CK(cudaSetDevice(h->device));
+    { int r = refresh_items_if_flagged(h); if (r) return r; }
+    if (h->u_sp.B != h->s.C) { int r = build_units(h, h->u_sp, h->s.C); if (r) return r; }
     { int r = set_ctrl(h, i, i); if (r) return r; }
     return launch_step(h, true, false, 1);
 }

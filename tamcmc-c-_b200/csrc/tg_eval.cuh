@@ -42,7 +42,29 @@ struct TgEvalArgs {
     const int4   *units;               // [grid] work units in launch order: (first bin, sub-tiles | chains << 16, first chain, item)
     int           B, nitems, max_group;  // nitems: items (bin runs) = partial sums per chain; max_group: chains per unit at most
     int           list_cap;            // capacity (components) of one chain's list in shared memory, multiple of 4
+    const double *mom;                 // [Nx / mom_bins][2][TG_MD] Chebyshev moments of the data over aligned tiles (tg_moment_tiles), or NULL
+    int           mom_sub;             // sub-tiles of 1024 bins per moment tile
+    int          *mom_fail;            // [Nx / mom_bins] set to 1 when a tile failed its check for some chain (scheduling hint for the host)
+    int          *mom_note;            // pinned host word: set to 1 when a tile is flagged for the first time
 };
+
+// ---- background-only stretches of the spectrum through Chebyshev moments of the data ------------------------------
+// Outside every truncation window the model is the smooth background b(x) = N0 + sum_k H_k / (1 + (a_k x)^p_k), and over
+// a tile of a few thousand bins both 1/b and ln b are polynomials of degree 8 in x to rounding error (the poles of the
+// Harvey profiles are hundreds of tile widths away above a few hundred microHz).  With c, d the Chebyshev coefficients of 1/b and
+// ln b on the tile, the likelihood terms of the tile are
+//     sum_i y_i / b(x_i) = sum_k c_k YT_k ,   sum_i ln b(x_i) = sum_k d_k ST_k ,
+// YT_k = sum_i y_i T_k(t_i), ST_k = sum_i T_k(t_i): moments of the DATA, computed once when the spectrum is loaded.  Per
+// (tile, chain) that is 9 exact evaluations of b at the Chebyshev nodes instead of one per bin.  Nothing is assumed: five
+// more exact evaluations at extrema of T_9 (where the interpolation error peaks) check both polynomials against b, and
+// a tile whose check exceeds TG_MOM_TOL for a chain (low frequencies, exotic parameters, NaN, b <= 0) is evaluated bin by
+// bin for that chain as before.
+#define TG_MD      9                   // Chebyshev coefficients per function (degree 8)
+#define TG_MCHK    5                   // check points
+#define TG_MOM_TOL 2.0e-14
+#define TG_MOM_HDR ((TG_MD + TG_MCHK) * TG_MD + TG_MD + TG_MCHK)   // doubles at the head of the moment buffer: the matrix that takes
+                                       // the values at the nodes to the coefficients (TG_MD rows) and to the interpolant at the check
+                                       // points (TG_MCHK rows), then the nodes and check points in [-1, 1]
 
 struct __align__(16) TgComp {       // one Lorentzian m-component clipped to the tile, 48 bytes
     double nu, q;                   // centre, 4/Gamma^2
@@ -193,7 +215,7 @@ struct TgEvalSmem {                 // carved out of the dynamic shared memory
 // overhead).  GEN = false is the interior fast path (all bins inside the spectrum, no model output, no
 // Gaussian test model): no index clamps, no selects.
 template <int NB, bool GEN, bool LISTS>
-__device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalSmem &S, const int *s_tot, int G, int c0, int b0, int tid)
+__device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalSmem &S, const int *s_tot, int G, int c0, int b0, int tid, unsigned gmask = 0xffffffffu)
 {
     const int Nx = a.d.Nx, cap = a.list_cap;
     double x[NB], y[NB];
@@ -206,6 +228,7 @@ __device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalS
         y[j] = (!GEN || idx < Nx) ? __ldg(a.y + ii[j]) : 0.0;   // bins past the end: y = 0 and (below) m = 1
     }
     for (int g = 0; g < G; g++) {
+        if (!((gmask >> g) & 1u)) continue;       // CTA-uniform: chains of the group this call is not for
         const double *nz = S.nz + (size_t)g * TG_NOISE_STRIDE;
         double acc[NB];
         if (GEN && nz[TG_N_GAUSS] != 0.0) {       // models.cpp:1977-1978 / :2030-2031 (Gaussian test models always take GEN)
@@ -299,6 +322,73 @@ __device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalS
     }
 }
 
+// Exact background at one abscissa (noise table of one chain in shared memory): N0 + sum_k H_k / (1 + (a_k x)^p_k)
+__device__ __noinline__ double tg_background_at(const double *nz, const int *cls, int nH, double x)
+{
+    double acc = 0.0;
+    for (int k = 0; k < nH; k++) {
+        const double *q = nz + TG_HS * k;
+        const double ap = q[TG_H_AP];
+        double t;
+        switch (cls[k]) {
+        case 0: t = 2.0; break;
+        case 1: t = fma(ap, x, 1.0); break;
+        case 2: t = fma(ap * x, x, 1.0); break;
+        case 3: t = fma((ap * x) * x, x, 1.0); break;
+        case 4: { const double x2 = x * x; t = fma(ap * x2, x2, 1.0); break; }
+        default: t = tg_exp_nb(q[TG_H_P] * (q[TG_H_LNA] + log(x))) + 1.0; break;
+        }
+        acc = fma(q[TG_H_H], tg_rcp(t), acc);
+    }
+    return acc + nz[TG_N_N0];
+}
+
+// n_mt background-only moment tiles starting at bin b0 (aligned) for the G chains of the unit: warp w takes the pairs
+// (tile, chain) = w, w + 8, ...; lanes 0..8 evaluate the background at the nodes, lanes 9..13 at the check points.  A pair
+// that passes adds its two sums to the running results of the chain (lane 0's slot of S.sum, s_lw[g][warp]); a pair that
+// fails sets bit g of s_fail[tile] and is evaluated bin by bin by the caller.  No barrier inside.
+__device__ void tg_moment_tiles(const TgEvalArgs &a, const TgEvalSmem &S, const double (*s_WE)[TG_MD], const double *s_tn,
+                                double (*s_lw)[TG_THREADS / 32], unsigned *s_fail, int G, int b0, int n_mt)
+{
+    constexpr int NW = TG_THREADS / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int mtb = a.mom_sub * (TG_THREADS * 4);
+    for (int p = warp; p < n_mt * G; p += NW) {
+        const int mt = p / G, g = p - mt * G;
+        const int bb = b0 + mt * mtb;
+        const double xa = __ldg(a.x + bb), xb = __ldg(a.x + bb + mtb - 1);
+        const double xm = 0.5 * (xa + xb), xh = 0.5 * (xb - xa);
+        const double *mo = a.mom + TG_MOM_HDR + (size_t)(bb / mtb) * 2 * TG_MD;
+        double r = 0.0, l = 0.0, mom_s = 0.0, mom_y = 0.0;
+        bool ok = (xh > 0.0);
+        if (lane < TG_MD) { mom_s = __ldg(mo + lane); mom_y = __ldg(mo + TG_MD + lane); }
+        if (lane == 0) ok = ok && (mom_s == (double)mtb);       // ST_0 = number of bins; NaN marks a tile the host could not use
+        if (lane < TG_MD + TG_MCHK) {
+            const double b = tg_background_at(S.nz + (size_t)g * TG_NOISE_STRIDE, S.cls + g * TG_MAXH, S.nh[g], fma(xh, s_tn[lane], xm));
+            ok = ok && (b > 0.0) && (b < 1.0e300);              // false for NaN
+            r = tg_rcp(b); l = log(b);
+        }
+        const int row = (lane < TG_MD + TG_MCHK) ? lane : 0;
+        double cr = 0.0, cl = 0.0;                              // lanes 0..8: coefficients; lanes 9..13: interpolants at the check points
+#pragma unroll
+        for (int j = 0; j < TG_MD; j++) {
+            const double w = s_WE[row][j];
+            cr = fma(w, __shfl_sync(0xffffffffu, r, j), cr);
+            cl = fma(w, __shfl_sync(0xffffffffu, l, j), cl);
+        }
+        if (lane >= TG_MD && lane < TG_MD + TG_MCHK)
+            ok = ok && (fabs(cr - r) <= TG_MOM_TOL * fabs(r)) && (fabs(cl - l) <= TG_MOM_TOL * fmax(1.0, fabs(l)));
+        double ps = (lane < TG_MD) ? cr * mom_y : 0.0, pl = (lane < TG_MD) ? cl * mom_s : 0.0;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) { ps += __shfl_down_sync(0xffffffffu, ps, o); pl += __shfl_down_sync(0xffffffffu, pl, o); }
+        const bool all_ok = __all_sync(0xffffffffu, ok);
+        if (lane == 0) {
+            if (all_ok) { S.sum[g * TG_THREADS + tid] += ps; s_lw[g][warp] += pl; }
+            else atomicOr(s_fail + mt, 1u << g);
+        }
+    }
+}
+
 // Per-chain lists of the components whose window meets the tile [b0, b0+SUB) (SUB = one or two sub-tiles): order-preserving
 // ballot compaction for all chains of the group at once, padded to a multiple of four, plus the
 // per-quad "covers the whole sub-tile" flags.  Called by the whole CTA (contains barriers).
@@ -379,6 +469,10 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
     __shared__ int s_cnt[TG_MAXG][NW];
     __shared__ int s_tot[TG_MAXG];
     __shared__ int s_w[2][TG_MAXG];
+    __shared__ double s_WE[TG_MD + TG_MCHK][TG_MD];   // moment path: node values -> coefficients / check interpolants
+    __shared__ double s_tn[TG_MD + TG_MCHK];
+    __shared__ double s_lw[TG_MAXG][NW];              // moment path: sum of ln b per chain and warp
+    __shared__ unsigned s_fail[32];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int4 unit = __ldg(a.units + blockIdx.x);
@@ -402,6 +496,12 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
 
     // ---- phase 0: noise tables, window unions, running results ----
     for (int g = 0; g < G; g++) { S.sum[g * TG_THREADS + tid] = 0.0; S.pf[g * TG_THREADS + tid] = 1.0; S.pe[g * TG_THREADS + tid] = 0; }
+    const bool use_mom = (a.mom != nullptr) && (a.d.like_case == 0) && (a.model == nullptr) && (a.d.model_case > 1);
+    if (tid < TG_MAXG * NW) (&s_lw[0][0])[tid] = 0.0;
+    if (use_mom) {                                // constants of the spectrum, not of the step
+        if (tid < (TG_MD + TG_MCHK) * TG_MD) (&s_WE[0][0])[tid] = a.mom[tid];
+        if (tid < TG_MD + TG_MCHK) s_tn[tid] = a.mom[(TG_MD + TG_MCHK) * TG_MD + tid];
+    }
     tg_pdl_wait();                                // everything above (unit table, shared-memory set-up) may overlap the proposal kernel
     tg_pdl_trigger();
     for (int e = tid; e < G * TG_NOISE_STRIDE; e += TG_THREADS) S.nz[e] = a.t.noise[(size_t)c0 * TG_NOISE_STRIDE + e];
@@ -427,6 +527,26 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
         const int b0 = item.x + sub * SUB;
         if (b0 >= Nx) break;
         const bool gen = gen_all || (b0 + SUB > Nx);
+        if (use_mom) {                            // aligned background-only tiles ahead: through the moments of the data
+            const int mtb = a.mom_sub * SUB;
+            int n_mt = 0;
+            if (b0 % mtb == 0)
+                while (n_mt < 32 && sub + (n_mt + 1) * a.mom_sub <= item.y && b0 + (n_mt + 1) * mtb <= Nx && !(wlo < b0 + (n_mt + 1) * mtb && whi > b0 + n_mt * mtb)) n_mt++;
+            if (n_mt > 0) {
+                __syncthreads();                  // s_fail of the previous round has been read
+                if (tid < 32) s_fail[tid] = 0u;
+                __syncthreads();
+                tg_moment_tiles(a, S, s_WE, s_tn, s_lw, s_fail, G, b0, n_mt);
+                __syncthreads();
+                for (int t = 0; t < n_mt; t++) {
+                    const unsigned fm = s_fail[t];
+                    if (fm && tid == 0 && atomicExch(a.mom_fail + b0 / mtb + t, 1) == 0) *(volatile int *)a.mom_note = 1;
+                    if (fm) for (int s2 = 0; s2 < a.mom_sub; s2++) tg_chain_loop<4, false, false>(a, S, s_tot, G, c0, b0 + (t * a.mom_sub + s2) * SUB, tid, fm);
+                }
+                sub += n_mt * a.mom_sub;
+                continue;
+            }
+        }
         if (!gen_all && sub + 1 < item.y && b0 + 2 * SUB <= Nx && wlo < b0 + 2 * SUB && whi > b0) {
             // truncation windows meet this pair of sub-tiles: 8 bins per thread against one list (half the list traffic and
             // loop overhead per bin, twice the independent work per warp behind every reciprocal)
@@ -468,7 +588,11 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
         }
         if (lane == 0) {
             double t2 = 0.0;
-            if (a.d.like_case == 0) t2 = fma((double)pe, 6.93147180369123816490e-01, fma((double)pe, 1.90821492927058770002e-10, log(pf)));
+            if (a.d.like_case == 0) {
+                t2 = fma((double)pe, 6.93147180369123816490e-01, fma((double)pe, 1.90821492927058770002e-10, log(pf)));
+#pragma unroll
+                for (int w = 0; w < NW; w++) t2 += s_lw[warp][w];
+            }
             a.partials[(size_t)(c0 + warp) * a.nitems + unit.w] = make_double2(sum, t2);
         }
     }

@@ -187,3 +187,34 @@ def test_cfg3_full_size_vs_oracle_and_properties(tb, W, oracle):
     m = md.call_model_explicit(P[3:4])
     assert relerr(m, oracle.model(prob.model_case, P[3], prob.plength, prob.x)[1]) < TOL
     md.close()
+
+
+@pytest.mark.parametrize("case", ["cfg3", "general_p", "sharp_knee"])
+def test_background_moments_equal_the_bin_by_bin_path(tb, W, oracle, case, monkeypatch):
+    """Outside every truncation window the fused kernel takes sum y/b and sum ln b of a tile from Chebyshev moments of the
+    data (tg_eval.cuh: tg_moment_tiles) whenever its polynomial check passes, and bin by bin otherwise.  The two paths must
+    agree to rounding, and both with the oracle -- for integer Harvey exponents, for non-integer ones (the exp/log branch)
+    and for a background whose knee is so sharp that most tiles must fail the check."""
+    prob = W.s_global(Nx=400000, step=0.02)
+    ip = [i for i, n in enumerate(prob.names) if n == "Harvey-Noise_p"]
+    itc = [i for i, n in enumerate(prob.names) if n == "Harvey-Noise_tc"]
+    if case == "general_p":
+        prob.params[ip[1]], prob.params[ip[2]] = 3.37, 1.83
+    if case == "sharp_knee":
+        prob.params[ip[2]] = 40.0                    # (x / 4000 microHz)^40: a cliff in the middle of the background-only part
+        prob.params[itc[2]] = 0.25
+    prob = _with_y(prob, oracle, W, seed=5)
+    C = 6
+    P, T = W.perturbed_params(prob, C, scale=1.0), W.tcoefs(C, 1.3)
+    res = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("TG_MOMENTS", mode)
+        md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=C))
+        md.evaluate(P, T)                            # first launch flags the tiles whose check fails ...
+        md.set_tuning(light_subtiles=9); md.set_tuning(light_subtiles=8)       # ... the work items are rebuilt around them
+        res[mode] = md.evaluate(P, T)
+        md.close()
+    ref = oracle.generate_models(prob, P, T)
+    assert np.array_equal(res["0"]["status"], res["1"]["status"])
+    assert relerr(res["1"]["logL"], res["0"]["logL"]) < 2e-14
+    assert relerr(res["1"]["logL"], ref["logL"]) < TOL and relerr(res["0"]["logL"], ref["logL"]) < TOL
