@@ -280,6 +280,33 @@ def main():
            "call": "tg_eval == batched Model_def::generate_model, pinned host params in, logL/logPrior/logPost/status out",
            "steps": Ke}
 
+    # ---- the other single-GPU configurations of BASELINE.json, same device-resident sampler, short runs (N=1 only;
+    #      reported beside the headline, not part of it) ----
+    other = None
+    if rank == 0 and world == 1:
+        other = {}
+
+        def short_run(p, c, warm, steps):
+            m2 = tb.GpuModelDef(p, c, device=local_rank)
+            ml = tb.GpuMALA(m2)
+            ml.execute(0, warm, record=False)
+            m2.sync(); m2.timer_start()
+            ml.execute(warm, steps, record=False)
+            t_ms = m2.timer_stop_ms()
+            m2.kernel_time(reset=1)
+            ml.execute(warm + steps, min(steps, 64), record=False)
+            n2, ms2, _ = m2.kernel_time(reset=2)
+            m2.close()
+            return t_ms / steps, ms2 / max(n2, 1)
+        p1 = W.s_local(make_y=make_y)
+        ms1, k1 = short_run(p1, tb.MalaConfig(Nchains=10, lambda_temp=1.7, c0=2.0, Nt_learn=[100, 10**9], periods_learn=[1], dN_mixing=1, seed=7), 200, 2000)
+        other["configs[1] S-local: model_MS_local_basic, 10k bins, 10 chains"] = {"chain_steps_per_s": 10 / (ms1 * 1e-3), "ms_per_step": ms1, "fused_kernel_us": k1 * 1e3}
+        C4 = 1024
+        ms4, k4 = short_run(prob, tb.MalaConfig(Nchains=C4, chains_per_ensemble=8, lambda_temp=1.7, c0=2.0, Nt_learn=[20, 10**9], periods_learn=[1], dN_mixing=1, seed=11), 32, 64)
+        other["configs[3] S-global with 1024 batched chains (128 tempered ensembles of 8)"] = {
+            "chain_steps_per_s": C4 / (ms4 * 1e-3), "ms_per_step": ms4, "fused_kernel_us": k4 * 1e3,
+            "roofline_frac": F_launch / C_CHAINS * C4 / (k4 * 1e-3) / 1e12 / peak_tflops}
+
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only; bounded sample) ----
     cpu = None
     if rank == 0 and world == 1:
@@ -310,7 +337,7 @@ def main():
                            "l2": "x, y = 16 MB per launch (< L2) but the timed kernel is FP64-bound; no L2 flush (steady-state MCMC reuses the spectrum every step by design)",
                            "per_gpu": "one independent tempered ensemble (star) per GPU, no collective"},
                 "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-                "bin_evals_per_s": value * NX}
+                "bin_evals_per_s": value * NX, "other_configs": other}
         print(json.dumps(line), flush=True)
     md.close()
     if dist is not None:
