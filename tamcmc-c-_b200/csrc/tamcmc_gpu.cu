@@ -48,7 +48,7 @@ struct tg_handle {
     TgState    s{};
     TgRecDev   rec{};
     double    *x = nullptr, *y = nullptr, *lnx = nullptr, *sig = nullptr;
-    double    *mom = nullptr; int mom_sub = 4, mom_run = 16; int *mom_fail = nullptr; long n_mom_tiles = 0;
+    double    *mom = nullptr; int mom_sub = 4, mom_run = 16; int *mom_fail = nullptr; long n_mom_tiles = 0; bool mom_probed = false;
     int       *mom_note = nullptr;                      // pinned, mapped: the kernel stores 1 when it flags a tile for the first time          // Chebyshev moments of the data over aligned tiles (tg_eval.cuh), NULL = off
     double    *pri = nullptr; int *sw = nullptr;
     int       *index_to_relax = nullptr; double *Tcoefs = nullptr;
@@ -477,6 +477,9 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         // background-only tiles on the moment path: one chain per unit is best up to ~100 chains, 3.9 vs 4.0 us per chain at 80)
         h->heavy_sub = 2;
         h->heavy_group = (C >= 128) ? 3 : 1;
+        // a spectrum so short that pairs of sub-tiles would not even fill the GPU once (S-local: 10k bins, 10 chains): single
+        // sub-tiles, twice the units (25.7 vs 29.9 us per step there)
+        if ((long)((d.Nx + TG_THREADS * 4 - 1) / (TG_THREADS * 4)) * C < 4L * 296) h->heavy_sub = 1;
         // developer knobs for scheduling experiments (never change results)
         if (const char *e = getenv("TG_HEAVY_SUB")) h->heavy_sub = std::max(1, atoi(e));
         if (const char *e = getenv("TG_HEAVY_GROUP")) h->heavy_group = std::max(1, atoi(e));
@@ -560,6 +563,11 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         CK(cudaStreamSynchronize(h->stream));
     }
     { int r = build_items(h, h->sp, C); if (r) return r; }
+    if (h->mom_note) {   // once more with the real work items: flags the background-only tiles whose polynomial check fails at the start
+        int r = launch_eval_kernels(h, h->sp, s.params_cur, C, nullptr, false, true); if (r) return r;
+        CK(cudaStreamSynchronize(h->stream));
+        r = refresh_items_if_flagged(h); if (r) return r;
+    }
     return TG_OK;
 }
 
@@ -847,7 +855,7 @@ extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
         const long n = std::min(nsteps - done, h->rec.cap);
         { int r = set_ctrl(h, i0 + done, i0 + done); if (r) return r; }
         long k = 0;
-        if (h->use_graph && !h->timing) {
+        for (int pass = 0; pass < 2 && h->use_graph && !h->timing; pass++) {
             const int G = h->steps_per_graph;
             for (int attempt = 0; !h->graph && n >= G && attempt < 2; attempt++) {
                 cudaGraph_t g = nullptr;
@@ -865,9 +873,24 @@ extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
                 cudaGetLastError();                  // a driver that cannot capture programmatic edges: same graph with full dependencies
                 h->pdl = false;
             }
+            bool again = false;
             if (h->graph) {
-                for (; k + G <= n; k += G) { CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += ((h->m.n_learn > 0 || (h->tri_smem && !h->no_split)) ? 4L : 3L) * G; h->n_eval_launch += G; }
+                for (; k + G <= n; k += G) {
+                    CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += ((h->m.n_learn > 0 || (h->tri_smem && !h->no_split)) ? 4L : 3L) * G; h->n_eval_launch += G;
+                    if (h->mom_note && !h->mom_probed) {
+                        // first steps of this handle: which background-only tiles fail their polynomial check is known now; without
+                        // this look the rest of the call would run with those tiles inside long cheap items (2x slower launches)
+                        h->mom_probed = true;
+                        CK(cudaStreamSynchronize(h->stream));
+                        if (*(volatile int *)h->mom_note) {
+                            int r = refresh_items_if_flagged(h); if (r) return r;
+                            if (h->u_sp.B != h->s.C) { r = build_units(h, h->u_sp, h->s.C); if (r) return r; }
+                            if (!h->graph) { k += G; again = true; break; }
+                        }
+                    }
+                }
             }
+            if (!again) break;
         }
         for (; k < n; k++) { int r = launch_step(h, true, true, 0); if (r) return r; }
         { int r = drain_records(h, rec, done, n); if (r) return r; }
