@@ -86,6 +86,7 @@ extern "C" const char *tg_last_error(void) { return g_err.c_str(); }
 extern "C" int tg_version(void) { return 100; }
 #ifdef TG_PROFILE
 extern "C" int tg_dbg_ctas(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_cta, sizeof(long long) * TG_DBG_CTAS * 6) == cudaSuccess ? 0 : -2; }
+extern "C" int tg_dbg_timeline(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_tl, sizeof(long long) * 8) == cudaSuccess ? 0 : -2; }
 extern "C" int tg_dbg_specs(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_spec, sizeof(long long) * 16) == cudaSuccess ? 0 : -2; }
 extern "C" int tg_dbg_clocks(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_clk, sizeof(long long) * 32) == cudaSuccess ? 0 : -2; }
 #endif

@@ -480,6 +480,6 @@ __device__ void tg_spec_body(const TgState &s, const TgMala &m, const int smem_m
 // stand-alone launch: grid (C, 2) speculative step, or (C, 1) with init = 1 (create / restore)
 __global__ void __launch_bounds__(256) tg_k_spec(TgSpecArgs a)
 {
-    extern __shared__ double tg_dyn_smem[];
+    extern __shared__ __align__(16) double tg_dyn_smem[];
     tg_spec_body(a.s, a.m, a.smem_matrix, a.init, blockIdx.x, blockIdx.y, tg_dyn_smem);
 }

@@ -30,6 +30,7 @@
 #ifdef TG_PROFILE
 #define TG_DBG_CTAS 8192
 __device__ long long tg_dbg_cta[TG_DBG_CTAS][6];
+__device__ long long tg_dbg_tl[8];     // step timeline (globaltimer): propose start/end, finish entry/after wait/end, side start/end, previous finish end
 __device__ __forceinline__ long long globaltimer_ns() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #endif
 

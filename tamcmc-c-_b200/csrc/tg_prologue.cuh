@@ -357,12 +357,8 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
             // noise: |noise_params| ; Nharvey=(Nnoise-1)/3 (global) or 0 (local)
             const int nH = (fam == 1) ? (Nnoise - 1) / 3 : 0;
             if (nH > TG_MAXH) S.status |= TG_ST_MODE_OVERFLOW;
-            int na = 0;                    // only the ACTIVE terms (tc != 0, noise_models.cpp:31) are listed, in order
-            for (int k = 0; k < nH && k < TG_MAXH; k++) {
-                if (fabs(p[iN + 3 * k + 1]) == 0.0) continue;
-                tg_set_harvey(nz, na, fabs(p[iN + 3 * k]), 1e-3 * fabs(p[iN + 3 * k + 1]), fabs(p[iN + 3 * k + 2]), d.x_last);
-                na++;
-            }
+            int na = 0;                    // only the ACTIVE terms (tc != 0, noise_models.cpp:31) are listed, in order;
+            for (int k = 0; k < nH && k < TG_MAXH; k++) if (fabs(p[iN + 3 * k + 1]) != 0.0) na++;   // their tables: threads 32.. below
             nz[TG_N_N0] = fabs(p[iN + Nnoise - 1]);
             nz[TG_N_NH] = na;
             nz[TG_N_ASYM] = S.asym;
@@ -373,6 +369,15 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
                 for (int l = 0; l < 4; l++) { S.modeStart[l] = ms; S.compStart[l] = cs; ms += nfl[l]; cs += nfl[l] * (2 * l + 1); }
                 S.modeStart[4] = ms; S.compStart[4] = cs;
             }
+        }
+    }
+    if ((parts & TG_PRO_MODEL) && fam == 1 && tid >= 32 && tid < 32 + TG_MAXH) {
+        // one thread per Harvey term (log, powers: ~1 us each when thread 0 did them one after the other), next to thread 0's scalars
+        const int nH = (Nnoise - 1) / 3, k = tid - 32;
+        if (k < nH && fabs(p[iN + 3 * k + 1]) != 0.0) {
+            int slot = 0;
+            for (int j = 0; j < k; j++) if (fabs(p[iN + 3 * j + 1]) != 0.0) slot++;
+            tg_set_harvey(nz, slot, fabs(p[iN + 3 * k]), 1e-3 * fabs(p[iN + 3 * k + 1]), fabs(p[iN + 3 * k + 2]), d.x_last);
         }
     }
     __syncthreads();
@@ -579,6 +584,6 @@ __device__ void tg_prologue_body(const TgProArgs &a, const int b, double *sm_ter
 
 __global__ void __launch_bounds__(TG_PRO_THREADS) tg_k_prologue(TgProArgs a)
 {
-    extern __shared__ double tg_dyn_smem[];
+    extern __shared__ __align__(16) double tg_dyn_smem[];
     tg_prologue_body(a, blockIdx.x, tg_dyn_smem);
 }

@@ -52,19 +52,26 @@ struct TgProposeArgs {
 // own grid on a side stream, concurrent with role 0 and the fused kernel.
 __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
 {
-    extern __shared__ double tg_dyn_smem[];
+    extern __shared__ __align__(16) double tg_dyn_smem[];
     __shared__ double s_z[512];
     const TgState &s = a.s;
     const int c = blockIdx.x, role = blockIdx.y + a.role_base, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
     tg_pdl_wait();                                                  // role 0 may be resident before the previous finish kernel is done
-    if (role == 0) tg_pdl_trigger();                                // the side-stream roles complete in full before the finish kernel starts
+    if (role == 0) tg_pdl_trigger();
+#ifdef TG_PROFILE
+    if (tid == 0 && c == 0 && blockIdx.y == 0) { if (role == 0) { tg_dbg_tl[7] = tg_dbg_tl[4]; tg_dbg_tl[0] = globaltimer_ns(); } else tg_dbg_tl[5] = globaltimer_ns(); }
+#endif                                // the side-stream roles complete in full before the finish kernel starts
     const long it = s.ctrl->i;
     if (role == 1 || role == 2) {
         if (!tg_learning(a.m, it)) return;
         if (role == 1) { tg_spec_body(s, a.m, a.smem_matrix, 0, c, 0, tg_dyn_smem); return; }
     }
     const double *L = s.chol + tg_slot_mat(s, s.live[c], c);
+    // role 0, fast path: the proposed parameter vector is assembled in shared memory and handed to the prologue there (no
+    // round trip through global memory between the proposal and the prologue); its ingredients are requested now
+    double pc0 = 0.0; int ir0 = 0;
+    if (role == 0 && a.tri_smem) { if (tid < Np) pc0 = s.params_cur[(size_t)c * Np + tid]; if (tid < Nv) ir0 = s.index_to_relax[tid]; }
     TG_STAMP(0);
     const double sq = sqrt(s.sigma[c]);
     const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PROP, (uint32_t)(a.m.seed >> 32));
@@ -72,10 +79,21 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
         // ---- fast path: z and the packed lower triangle of L in shared memory, one thread per row ----
         double *tri = tg_dyn_smem;                                  // packed by columns (tg_colpack)
         double *zz = tri + (size_t)Nv * (Nv + 1) / 2;
+        bool async_copy = false;
         if (a.packed) {
             const int ntri = Nv * (Nv + 1) / 2;
+            if ((((size_t)L) & 15) == 0) {
+                // all of the triangle in flight at once (16-byte asynchronous copies through L2, no registers), under the normals
+                const unsigned sb = (unsigned)__cvta_generic_to_shared(tri);
+                for (int e = 2 * tid; e + 1 < ntri; e += 2 * nt)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sb + 8u * (unsigned)e), "l"(L + e) : "memory");
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                if ((ntri & 1) && tid == 0) tri[ntri - 1] = __ldcg(L + ntri - 1);
+                async_copy = true;
+            } else {
 #pragma unroll 8
-            for (int e = tid; e < ntri; e += nt) tri[e] = __ldcg(L + e);
+                for (int e = tid; e < ntri; e += nt) tri[e] = __ldcg(L + e);
+            }
         } else {
             for (int e = tid; e < Nv * Nv; e += nt) { const int i = e / Nv, k = e - i * Nv; if (k <= i) tri[tg_colpack(Nv, k) + i - k] = __ldcg(L + e); }
         }
@@ -84,6 +102,7 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
             tg_normal_pair(tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)c, (uint32_t)(v >> 1)), key), &z0, &z1);
             zz[v] = (v & 1) ? z1 : z0;
         }
+        if (async_copy) asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
         TG_STAMP(1);
         for (int i = tid; i < Nv; i += nt) {
@@ -96,7 +115,8 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
             }
             if (k <= i) a0 = fma(el[0], zz[k], a0);
             const double xp = s.vars_cur[(size_t)c * Nv + i] + sq * (a0 + a1);
-            if (role == 0) s.vars_prop[(size_t)c * Nv + i] = xp; else s_z[i] = xp;
+            s_z[i] = xp;
+            if (role == 0) s.vars_prop[(size_t)c * Nv + i] = xp;
         }
         if (role == 2) {                                            // fused_spec implies tri_smem and Nv <= 512
             __syncthreads();
@@ -111,6 +131,20 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
             tg_prologue_body(a.pro, c, tg_dyn_smem, TG_PRO_PRIOR, true);
             return;
         }
+        // role 0: params_prop = params_cur with the free variables replaced (Model_def::update_params_with_vars), in shared memory
+        TG_STAMP(2);
+        __syncthreads();                                            // the triangle is dead
+        for (int i = tid; i < Np; i += nt) tg_dyn_smem[i] = (i == tid) ? pc0 : s.params_cur[(size_t)c * Np + i];
+        __syncthreads();
+        for (int v = tid; v < Nv; v += nt) tg_dyn_smem[(v == tid) ? ir0 : s.index_to_relax[v]] = s_z[v];
+        __syncthreads();
+        for (int i = tid; i < Np; i += nt) s.params_prop[(size_t)c * Np + i] = tg_dyn_smem[i];
+        TG_STAMP(3);
+        tg_prologue_body(a.pro, c, tg_dyn_smem, a.parts, true);
+#ifdef TG_PROFILE
+        __syncthreads(); if (tid == 0 && c == 0) tg_dbg_tl[1] = globaltimer_ns();
+#endif
+        return;
     } else
     // general path (very large Nv): standard normals 512 per pass, rows from HBM
     for (int v0 = 0; v0 < Nv; v0 += 512) {
@@ -203,6 +237,9 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     // Under programmatic dependent launch this kernel becomes resident while the fused kernel drains: the proposal kernel and
     // the adaptation candidates are complete by then (the fused kernel triggers after its own wait; the candidates are a full
     // dependency), so everything but the partial sums is loaded before the wait.
+#ifdef TG_PROFILE
+    if (tid == 0 && c == 0) tg_dbg_tl[2] = globaltimer_ns();
+#endif
     const long it = s.ctrl->i;
     const bool small = (Nv <= 256 && Np <= 256);   // one element of the proposed point per thread, held in registers
     double vprop = 0.0, pprop = 0.0;
@@ -216,6 +253,9 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     const long slot = it - s.ctrl->i0;
     tg_pdl_wait();
     tg_pdl_trigger();
+#ifdef TG_PROFILE
+    if (tid == 0 && c == 0) tg_dbg_tl[3] = globaltimer_ns();
+#endif
     if (tid == 0) {                                                 // products of the side-stream CTAs: only after the wait
         st |= a.t.pstatus[c]; logPr = a.t.logprior[c];
         fail0 = s.chol_fail[((live + 1) % 3) * s.C + c]; fail1 = s.chol_fail[((live + 2) % 3) * s.C + c];
@@ -327,6 +367,9 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
         }
     }
     if (tid == 0) { s.ctrl->ticket = 0u; s.ctrl->i = it + 1; }
+#ifdef TG_PROFILE
+    if (tid == 0) tg_dbg_tl[4] = globaltimer_ns();
+#endif
 }
 
 // Live (mu, Sigma) of every chain -> contiguous [C][Nv], [C][Nv][Nv] (restore files / tg_get_state)
