@@ -38,6 +38,7 @@ def main():
     ap.add_argument("--check-steps", type=int, default=40)
     ap.add_argument("--chains", type=int, default=10)
     ap.add_argument("--equal-length", action="store_true", help="equal-length shards instead of cost-balanced ones")
+    ap.add_argument("--heavy-weight", type=float, default=17.0, help="cost of a bin under truncation windows in units of a background-only bin (measured: 17 .. 2000 give the same step time on 2 GPUs)")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -51,7 +52,7 @@ def main():
     prob = W.s_global(Nx=a.nx, step=8500.0 / a.nx)
     full_x, full_y = prob.x, prob.y
     # contiguous bin ranges of equal estimated cost (the truncation windows of the modes make some bins ~17x dearer)
-    desc, sl = (S.balanced_shard_descriptor(prob, world, rank) if not a.equal_length else S.shard_descriptor(full_x, world, rank))
+    desc, sl = (S.balanced_shard_descriptor(prob, world, rank, a.heavy_weight) if not a.equal_length else S.shard_descriptor(full_x, world, rank))
     cfg = tb.MalaConfig(Nchains=a.chains, Nt_learn=[10, 1000000], periods_learn=[1], c0=1.7, seed=2024)
     import copy
     sub = copy.copy(prob)
