@@ -499,10 +499,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
     for (int g = 0; g < G; g++) { S.sum[g * TG_THREADS + tid] = 0.0; S.pf[g * TG_THREADS + tid] = 1.0; S.pe[g * TG_THREADS + tid] = 0; }
     const bool use_mom = (a.mom != nullptr) && (a.d.like_case == 0) && (a.model == nullptr) && (a.d.model_case > 1);
     if (tid < TG_MAXG * NW) (&s_lw[0][0])[tid] = 0.0;
-    if (use_mom) {                                // constants of the spectrum, not of the step
-        if (tid < (TG_MD + TG_MCHK) * TG_MD) (&s_WE[0][0])[tid] = a.mom[tid];
-        if (tid < TG_MD + TG_MCHK) s_tn[tid] = a.mom[(TG_MD + TG_MCHK) * TG_MD + tid];
-    }
+    bool we_loaded = false;                       // the interpolation matrices are staged by the first moment tile of the unit (most units have none)
     tg_pdl_wait();                                // everything above (unit table, shared-memory set-up) may overlap the proposal kernel
     tg_pdl_trigger();
     for (int e = tid; e < G * TG_NOISE_STRIDE; e += TG_THREADS) S.nz[e] = a.t.noise[(size_t)c0 * TG_NOISE_STRIDE + e];
@@ -536,6 +533,11 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
             if (n_mt > 0) {
                 __syncthreads();                  // s_fail of the previous round has been read
                 if (tid < 32) s_fail[tid] = 0u;
+                if (!we_loaded) {                 // constants of the spectrum, not of the step
+                    if (tid < (TG_MD + TG_MCHK) * TG_MD) (&s_WE[0][0])[tid] = a.mom[tid];
+                    if (tid < TG_MD + TG_MCHK) s_tn[tid] = a.mom[(TG_MD + TG_MCHK) * TG_MD + tid];
+                    we_loaded = true;
+                }
                 __syncthreads();
                 tg_moment_tiles(a, S, s_WE, s_tn, s_lw, s_fail, G, b0, n_mt);
                 __syncthreads();
