@@ -81,3 +81,34 @@ def test_partitioning(tb):
         assert all(cuts[r][1] == cuts[r + 1][0] for r in range(G - 1))
         sizes = [b - a for a, b in cuts]
         assert max(sizes) - min(sizes) <= 1
+
+
+def test_background_moment_identity_and_its_check():
+    """The identity behind the fused kernel's background-only path (tg_eval.cuh, tg_moment_tiles), restated in numpy:
+    with c the Chebyshev coefficients of 1/b on a tile, sum_i y_i / b(x_i) = sum_k c_k * sum_i y_i T_k(t_i) to rounding
+    when b is resolved by degree 8 -- and when it is not, the check points (extrema of T_9) see an error of the size of
+    the true one, so the kernel falls back to the bin-by-bin sum."""
+    n, nb = 9, 4096
+    tn = np.cos(np.pi * (np.arange(n) + 0.5) / n)
+    Wm = (2.0 / n) * np.cos(np.outer(np.arange(n), np.pi * (np.arange(n) + 0.5) / n)); Wm[0] *= 0.5
+    tc = np.cos(np.pi * np.array([0, 2, 4, 6, 9]) / n)
+    cheb = lambda c, t: c @ np.cos(np.outer(np.arange(n), np.arccos(np.clip(t, -1, 1))))
+    b = lambda x: 0.134 + 11.05 / (1 + (0.04967 * x) ** 4) + 0.9357 / (1 + (0.0013516 * x) ** 2)
+    g = np.random.default_rng(3)
+    for x0, resolved in ((2000.0, True), (600.0, True), (10.0, False)):
+        x = x0 + 0.0085 * np.arange(nb)
+        y = b(x) * g.exponential(size=nb)
+        xm, xh = 0.5 * (x[0] + x[-1]), 0.5 * (x[-1] - x[0])
+        t = (x - xm) / xh
+        T = np.cos(np.outer(np.arange(n), np.arccos(np.clip(t, -1, 1))))
+        YT, ST = T @ y, T.sum(axis=1)
+        bn = b(xm + xh * tn)
+        cr, cl = Wm @ (1.0 / bn), Wm @ np.log(bn)
+        s1, s2 = np.sum(y / b(x)), np.sum(np.log(b(x)))
+        e1, e2 = abs(cr @ YT - s1) / abs(s1), abs(cl @ ST - s2) / abs(s2)
+        bc = b(xm + xh * tc)
+        chk = max(np.max(np.abs(cheb(cr, tc) - 1.0 / bc) * bc), np.max(np.abs(cheb(cl, tc) - np.log(bc)) / np.maximum(1.0, np.abs(np.log(bc)))))
+        if resolved:
+            assert e1 < 5e-15 and e2 < 5e-15 and chk < 2e-14, (x0, e1, e2, chk)
+        else:
+            assert chk > 1e-10 and chk > 0.05 * max(e1, e2), (x0, e1, e2, chk)      # the check fires: this tile goes bin by bin
