@@ -49,6 +49,7 @@ struct tg_handle {
     TgRecDev   rec{};
     double    *x = nullptr, *y = nullptr, *lnx = nullptr, *sig = nullptr;
     double    *mom = nullptr; int mom_sub = 4, mom_run = 16; int *mom_fail = nullptr; long n_mom_tiles = 0; bool mom_probed = false;
+    int        hybrid_pct = 0, hybrid_group = 2;
     int       *mom_note = nullptr;                      // pinned, mapped: the kernel stores 1 when it flags a tile for the first time          // Chebyshev moments of the data over aligned tiles (tg_eval.cuh), NULL = off
     double    *pri = nullptr; int *sw = nullptr;
     int       *index_to_relax = nullptr; double *Tcoefs = nullptr;
@@ -302,9 +303,19 @@ static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B)
     std::vector<int4> units;
     std::vector<double> cost;
     const int gl = std::max(1, h->chains_per_block), gh = std::max(1, std::min(h->heavy_group, gl));
+    // hybrid: the costliest hybrid_pct percent of the window-region items take hybrid_group chains per unit (set-up and
+    // list building shared by the chains of a unit), the rest heavy_group (small units for the tail of the grid)
+    std::vector<char> big(h->items_host.size(), 0);
+    if (h->hybrid_pct > 0 && !h->no_order) {
+        std::vector<int> hv;
+        for (size_t k = 0; k < h->items_host.size(); k++) if (h->items_host[k].w == 1) hv.push_back((int)k);
+        std::stable_sort(hv.begin(), hv.end(), [&](int a, int b2) { const int4 &p = h->items_host[a], &q = h->items_host[b2]; return p.y * (20.0 + 6.25 * p.z) > q.y * (20.0 + 6.25 * q.z); });
+        const size_t nb = hv.size() * (size_t)std::min(100, h->hybrid_pct) / 100;
+        for (size_t k = 0; k < nb; k++) big[hv[k]] = 1;
+    }
     for (size_t k = 0; k < h->items_host.size(); k++) {
         const int4 it = h->items_host[k];
-        const int gmax = (it.w == 1 && !h->no_order) ? gh : gl;
+        const int gmax = (it.w == 1 && !h->no_order) ? (big[k] ? std::max(1, std::min(h->hybrid_group, gl)) : gh) : gl;
         const int groups = (B + gmax - 1) / gmax, g = (B + groups - 1) / groups;      // balanced
         for (int c0 = 0; c0 < B; c0 += g) {
             const int G = std::min(g, B - c0);
@@ -482,6 +493,12 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         // sub-tiles, twice the units (25.7 vs 29.9 us per step there)
         if ((long)((d.Nx + TG_THREADS * 4 - 1) / (TG_THREADS * 4)) * C < 4L * 296) h->heavy_sub = 1;
         // developer knobs for scheduling experiments (never change results)
+        // the costliest window-region items take three chains per unit (set-up and list building shared), the rest one chain
+        // (small units for the tail): 70 % of them at 10 chains (49.0 -> 48.1 us), all of them from 32 chains on (-7 %)
+        h->hybrid_group = 3;
+        h->hybrid_pct = (C < 16) ? 70 : ((C < 32) ? 80 : 100);
+        if (const char *e = getenv("TG_HYBRID_PCT")) h->hybrid_pct = atoi(e);
+        if (const char *e = getenv("TG_HYBRID_GROUP")) h->hybrid_group = std::max(1, atoi(e));
         if (const char *e = getenv("TG_HEAVY_SUB")) h->heavy_sub = std::max(1, atoi(e));
         if (const char *e = getenv("TG_HEAVY_GROUP")) h->heavy_group = std::max(1, atoi(e));
     }
