@@ -495,7 +495,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         // developer knobs for scheduling experiments (never change results)
         // the costliest window-region items take three chains per unit (set-up and list building shared), the rest one chain
         // (small units for the tail): 70 % of them at 10 chains (49.0 -> 48.1 us), all of them from 32 chains on (-7 %)
-        h->hybrid_group = 3;
+        h->hybrid_group = (C < 64) ? 3 : ((C < 128) ? 4 : 5);
         h->hybrid_pct = (C < 16) ? 70 : ((C < 32) ? 80 : 100);
         if (const char *e = getenv("TG_HYBRID_PCT")) h->hybrid_pct = atoi(e);
         if (const char *e = getenv("TG_HYBRID_GROUP")) h->hybrid_group = std::max(1, atoi(e));
