@@ -491,12 +491,13 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         h->heavy_group = (C >= 128) ? 3 : 1;
         // a spectrum so short that pairs of sub-tiles would not even fill the GPU once (S-local: 10k bins, 10 chains): single
         // sub-tiles, twice the units (25.7 vs 29.9 us per step there)
-        if ((long)((d.Nx + TG_THREADS * 4 - 1) / (TG_THREADS * 4)) * C < 4L * 296) h->heavy_sub = 1;
+        const bool short_spectrum = (long)((d.Nx + TG_THREADS * 4 - 1) / (TG_THREADS * 4)) * C < 4L * 296;
+        if (short_spectrum) h->heavy_sub = 1;
         // developer knobs for scheduling experiments (never change results)
         // the costliest window-region items take three chains per unit (set-up and list building shared), the rest one chain
         // (small units for the tail): 70 % of them at 10 chains (49.0 -> 48.1 us), all of them from 32 chains on (-7 %)
         h->hybrid_group = (C < 64) ? 3 : ((C < 128) ? 4 : 5);
-        h->hybrid_pct = (C < 16) ? 70 : ((C < 32) ? 80 : 100);
+        h->hybrid_pct = short_spectrum ? 0 : ((C < 16) ? 70 : ((C < 32) ? 80 : 100));      // short spectra: as many units as possible
         if (const char *e = getenv("TG_HYBRID_PCT")) h->hybrid_pct = atoi(e);
         if (const char *e = getenv("TG_HYBRID_GROUP")) h->hybrid_group = std::max(1, atoi(e));
         if (const char *e = getenv("TG_HEAVY_SUB")) h->heavy_sub = std::max(1, atoi(e));
