@@ -498,6 +498,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         // (small units for the tail): 70 % of them at 10 chains (49.0 -> 48.1 us), all of them from 32 chains on (-7 %)
         h->hybrid_group = (C < 64) ? 3 : ((C < 128) ? 4 : 5);
         h->hybrid_pct = short_spectrum ? 0 : ((C < 16) ? 70 : ((C < 32) ? 80 : 100));      // short spectra: as many units as possible
+        if (const char *e = getenv("TG_GRAPH_STEPS")) h->steps_per_graph = std::max(1, std::min(256, atoi(e)));
         if (const char *e = getenv("TG_HYBRID_PCT")) h->hybrid_pct = atoi(e);
         if (const char *e = getenv("TG_HYBRID_GROUP")) h->hybrid_group = std::max(1, atoi(e));
         if (const char *e = getenv("TG_HEAVY_SUB")) h->heavy_sub = std::max(1, atoi(e));
