@@ -8,9 +8,14 @@ prior, Metropolis accept, Robbins-Monro adaptation, tempering swap.  N>1: one in
 ensemble (a different synthetic star) per GPU, no data-path collective (weak scaling).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                    [--config cfg3|cfg2|cfg4|cfg5] [--stars-per-gpu S] [--no-cfg5] [--extra-out PATH]
 
 Prints ONE JSON line (rank 0).  ``--impl reference`` times the reference's own CPU implementation
 of the path (oracle/_ref: unmodified reference sources, OpenMP over chains) on the host cores.
+
+The default line is cfg3 (the headline) and carries, under "cfg5_8_stars_per_gpu", the same metric with EIGHT stars of
+10 chains per GPU advanced as one launch group (configs[4] of BASELINE.json: 64 stars over 8 GPUs).  ``--config`` selects
+another configuration of BASELINE.json as the line's workload (builder runs, committed under profiles/).
 """
 import argparse
 import json
@@ -27,28 +32,41 @@ sys.path.insert(0, ROOT)
 
 C_CHAINS = 10
 NX = 1_000_000
+STEPS_PER_GRAPH = 16
 METRIC = "tempered chain-steps/s (model_MS_Global 1M-bin spectrum, 10 chains per ensemble)"
 
 
-def synth_problem(W, make_y, rank=0):
-    """S-global; rank r gets another star (seed, numax/Dnu jitter) -- cfg5's recipe."""
-    g = np.random.Generator(np.random.Philox(key=777 + rank))
-    jit = (1.0 + 0.1 * (2 * g.random(2) - 1)) if rank > 0 else np.ones(2)
-    return W.s_global(Nx=NX, model_case=3, seed=12345 + rank, make_y=make_y, numax=2700.0 * jit[0], dnu=120.186 * jit[1])
+def synth_problem(W, make_y, star=0):
+    """S-global; star s > 0 is another star (seed, numax/Dnu jitter) -- cfg5's recipe."""
+    g = np.random.Generator(np.random.Philox(key=777 + star))
+    jit = (1.0 + 0.1 * (2 * g.random(2) - 1)) if star > 0 else np.ones(2)
+    return W.s_global(Nx=NX, model_case=3, seed=12345 + star, make_y=make_y, numax=2700.0 * jit[0], dnu=120.186 * jit[1])
+
+
+def workload_config(nv, stars_per_gpu=1):
+    """config of the JSON line -- the same dict in both arms."""
+    return {"workload": "cfg3 S-global: model_MS_Global_a1etaa3_HarveyLike_Classic, 106 params (%d free), Nx=1000000, C=10 chains per star, "
+                        "%d star(s) per GPU, lambda=1.7, learning on" % (nv, stars_per_gpu),
+            "step": "one MCMC iteration of every chain; the reference arm and e2e time its dominant part, generate_model (model+logL+prior) for the chains of one iteration",
+            "l2": "x, y = 16 MB per launch and star (< L2) but the timed kernel is FP64-bound; no L2 flush (steady-state MCMC reuses the spectrum every step by design)",
+            "per_gpu": "independent tempered ensembles (stars) per GPU, no collective"}
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (recipe of B200_PROFILING.md)."""
+    """nvidia-smi clocks / throttle reasons during the timed region (recipe of B200_PROFILING.md); one sampler per node."""
 
     Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
-    def __init__(self, gpu_index):
+    def __init__(self, gpu_index, enabled=True):
         self.rows = []
         self.proc = None
         self.idx = gpu_index
+        self.enabled = enabled
 
     def start(self):
+        if not self.enabled:
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                           "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -63,7 +81,7 @@ class ClockSampler:
 
     def stop(self):
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["not sampled on this rank" if not self.enabled else "nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
         try:
@@ -117,21 +135,22 @@ def run_reference(args, rank, world):
     P, T = W.perturbed_params(prob, C_CHAINS), W.tcoefs(C_CHAINS)
     kind = "reference" if R.available else "port"
     fn = (lambda: R.generate_models(prob, P, T)) if R.available else (lambda: O.generate_models(prob, P, T))
-    cores = os.cpu_count() or 1
-    for _ in range(args.warmup):
+    # bounded sample: a step is ~0.5 s of all-core CPU work; the driver's --steps 20 --warmup 5 run as given
+    steps, warm = min(args.steps, 60), min(args.warmup, 10)
+    for _ in range(warm):
         fn()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         fn()
     dt = time.perf_counter() - t0
-    val = C_CHAINS * args.steps / dt
+    val = C_CHAINS * steps / dt
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "chain-steps/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / steps * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "cfg3 S-global: model_MS_Global_a1etaa3_HarveyLike_Classic, 106 params, Nx=1000000, C=10 chains",
-                       "step": "generate_model (model+logL+prior) for the 10 chains of one MCMC iteration"},
+            "config": workload_config(prob.Nv),
             "cpu_baseline": {"value": val, "unit": "chain-steps/s", "cores": min(cores, C_CHAINS), "kind": kind,
-                             "sample": "%d full steps (10 chains x 1M bins each), OpenMP over chains, %d host cores" % (args.steps, cores)},
+                             "sample": "%d full steps after %d warm-up steps (10 chains x 1M bins each: generate_model of one star), OpenMP over chains as in MALA.cpp:632, %d host cores; "
+                                       "unmodified reference sources compiled against the repo's Eigen-API shim" % (steps, warm, cores)},
             "e2e": {"value": val, "unit": "chain-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "bin_evals_per_s": val * NX}
     print(json.dumps(line), flush=True)
@@ -144,14 +163,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=200)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--cpu-steps", type=int, default=4)
+    ap.add_argument("--config", default="cfg3", choices=["cfg2", "cfg3", "cfg4", "cfg5"])
+    ap.add_argument("--stars-per-gpu", type=int, default=0, help="cfg5: stars (tempered ensembles of 10 chains, each its own spectrum) per GPU as one launch group")
+    ap.add_argument("--no-cfg5", action="store_true", help="skip the 8-stars-per-GPU measurement carried by the default line")
+    ap.add_argument("--extra-out", default=None, help="also write the JSON line to this file")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        if args.steps > 60:
-            args.steps = 60          # bounded sample: each step is ~1 s of all-core CPU work
-        args.warmup = min(args.warmup, 3)
         run_reference(args, rank, world)
         return
 
@@ -170,61 +190,95 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = tb.load_library()
     peak_tflops, _ = lib.measure_fp64_peak(local_rank)
+    props = torch.cuda.get_device_properties(local_rank)
 
-    # ---- synthetic star of this rank: y = m_true * Exp(1), m_true from the GPU model path itself ----
+    # ---- synthetic stars of this rank: y = m_true * Exp(1), m_true from the GPU model path itself ----
     def make_y(p):
         tmp = tb.GpuModelDef(p, tb.MalaConfig(Nchains=1), device=local_rank)
         m = tmp.call_model(0)
         tmp.close()
         return m
-    prob = synth_problem(W, make_y, rank)
-    cfg = tb.MalaConfig(Nchains=C_CHAINS, lambda_temp=1.7, c0=2.0, Nt_learn=[100, 10**9], periods_learn=[1],
-                        dN_mixing=1, seed=4242 + rank)
-    md = tb.GpuModelDef(prob, cfg, device=local_rank)
-    mala = tb.GpuMALA(md)
-    W_steps, K = max(args.warmup, 3), args.steps
 
-    def barrier():
+    def mala_cfg(C, seed, per_ensemble=0):
+        # learning on from the first step (Learning phase of the reference, MALA.cpp:641-652): 4 launches per step,
+        # the adaptation CTAs run beside the proposal and the fused kernel
+        return tb.MalaConfig(Nchains=C, chains_per_ensemble=per_ensemble, lambda_temp=1.7, c0=2.0, Nt_learn=[0, 10**9], periods_learn=[1],
+                             dN_mixing=1, seed=seed)
+
+    cfg_name = args.config
+    S = args.stars_per_gpu if args.stars_per_gpu > 0 else (8 if cfg_name == "cfg5" else 1)
+    if S > 1:
+        cfg_name = "cfg5"
+    C_star = {"cfg2": 10, "cfg3": C_CHAINS, "cfg4": 1024, "cfg5": C_CHAINS}[cfg_name]
+    nx_star = 10000 if cfg_name == "cfg2" else NX
+    W_run, K = max(args.warmup, 2 * STEPS_PER_GRAPH), args.steps       # warm-up covers two whole step graphs
+
+    def build_group(n_stars, first_star):
+        mds = []
+        for s in range(n_stars):
+            star = first_star + s
+            if cfg_name == "cfg2":
+                p = W.s_local(make_y=make_y)
+            else:
+                p = synth_problem(W, make_y, star)
+            mds.append(tb.GpuModelDef(p, mala_cfg(C_star, 4242 + star, 8 if cfg_name == "cfg4" else 0), device=local_rank))
+        return mds, (tb.GpuBatch(mds) if n_stars > 1 else None)
+
+    def barrier(md):
         md.sync()
         if dist is not None:
             dist.barrier()
         md.sync()
 
-    # ---- warm-up (learning on from i=100, as in the Learning phase of the reference) ----
-    mala.execute(0, W_steps, record=False)
-    i0 = W_steps
-    # ---- timed region 1: `value` -- device-resident loop, nothing crosses PCIe ----
-    clocks = ClockSampler(local_rank)
-    clocks.start()
-    md.kernel_time(reset=2)
-    barrier()
-    md.timer_start()
-    mala.execute(i0, K, record=False)
-    ms = md.timer_stop_ms()
-    barrier()
-    n_eval, _, launches = md.kernel_time(reset=0)
-    i0 += K
-    clk = clocks.stop()
-    if dist is not None:
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    value = world * C_CHAINS * K / (ms * 1e-3)
+    def timed_run(mds, grp, warm, steps, clock_rank=False):
+        """warm-up, then `steps` steps timed on the device (CUDA events on the group's stream), max over ranks."""
+        md0 = mds[0]
+        runner = grp if grp is not None else tb.GpuMALA(md0)
+        runner.execute(0, warm, record=False)
+        clocks = ClockSampler(local_rank, enabled=clock_rank)
+        clocks.start()
+        (grp or md0).kernel_time(reset=2)
+        barrier(md0)
+        (grp or md0).timer_start()
+        runner.execute(warm, steps, record=False)
+        ms = (grp or md0).timer_stop_ms()
+        barrier(md0)
+        _, _, launches = (grp or md0).kernel_time(reset=0)
+        clk = clocks.stop()
+        if dist is not None:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        # the same steps with CUDA events around every launch of the fused kernel
+        (grp or md0).kernel_time(reset=1)
+        Kr = min(steps, 200)
+        runner.execute(warm + steps, Kr, record=False)
+        n_ev, ms_ev, _ = (grp or md0).kernel_time(reset=2)
+        return ms, launches, clk, ms_ev / max(n_ev, 1) * 1e-3, n_ev
 
-    # ---- timed region 2: same steps with CUDA events around every launch of the fused kernel ----
-    md.kernel_time(reset=1)
-    Kr = min(K, 500)
-    mala.execute(i0, Kr, record=False)
-    n_ev, ms_ev, _ = md.kernel_time(reset=2)
-    i0 += Kr
-    t_kernel = ms_ev / max(n_ev, 1) * 1e-3
-    fin = md.evaluate(md.params, md.Tcoefs)
-    Lw, Kh = md.last_work(C_CHAINS)
-    F_chain = 8.0 * Lw + NX * (5.0 * Kh + 5.0)                 # F = 8L + Nx(5K+1+4), asym == 0
-    F_launch = float(F_chain.sum())
+    def algorithmic_work(mds):
+        """F = 8 L + Nx (5 K + 5) per chain (asym == 0); executed: the background term only where bins are taken one by one."""
+        F = Fx = 0.0
+        Lm, Kh = [], 0
+        for md in mds:
+            md.evaluate(md.params, md.Tcoefs)
+            Lw, Kh = md.last_work(md.Nmodels)
+            bins_direct, mom_tiles, _ = md.work_profile()
+            F += float((8.0 * Lw + md.Nx * (5.0 * Kh + 5.0)).sum())
+            Fx += float((8.0 * Lw + bins_direct * (5.0 * Kh + 5.0) + mom_tiles * (14 * (5.0 * Kh + 5.0) + 2 * 2 * 14 * 9 + 4 * 9)).sum())
+            Lm.append(float(Lw.mean()))
+        return F, Fx, float(np.mean(Lm)), Kh
+
+    mds, grp = build_group(S, rank * S)
+    md = mds[0]
+    ms, launches, clk, t_kernel, n_ev = timed_run(mds, grp, W_run, K, clock_rank=(local_rank == 0))
+    chains_gpu = S * C_star
+    value = world * chains_gpu * K / (ms * 1e-3)
+    F_launch, F_exec, L_mean, Kh = algorithmic_work(mds)
     achieved = F_launch / t_kernel / 1e12
-    # x and y once per launch (ln x is only read for non-integer Harvey exponents; cfg3 has p = 4, 2) + per-chain tables
-    hbm_bytes = 16.0 * NX + C_CHAINS * (md.Nparams * 8 + 224 * 48 + 44 * 8)
+    peak_nominal = props.multi_processor_count * 64 * 2 * (clk.get("sm_max_mhz") or 1965.0) * 1e6 / 1e12     # SMs x 64 DFMA lanes x 2 flop x clock
+    # x and y once per launch and star (ln x is only read for non-integer Harvey exponents; cfg3 has p = 4, 2) + per-chain tables
+    hbm_bytes = S * 16.0 * nx_star + chains_gpu * (md.Nparams * 8 + 224 * 48 + 44 * 8)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -232,41 +286,45 @@ def main():
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     roofline = {"bound": "fp64", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
+                "frac_executed": F_exec / t_kernel / 1e12 / peak_tflops, "peak_nominal": peak_nominal, "frac_of_nominal": achieved / peak_nominal,
                 "traffic": load_traffic(), "kernel": "tg_k_eval", "avg_launch_us": t_kernel * 1e6, "launches_timed": n_ev,
-                "algorithmic_flop_per_launch": F_launch, "L_component_bins_per_chain": float(Lw.mean()), "K_harvey": Kh,
+                "algorithmic_flop_per_launch": F_launch, "executed_flop_per_launch": F_exec,
+                "L_component_bins_per_chain": L_mean, "K_harvey": Kh,
                 "kernel_share_of_step": t_kernel / (ms * 1e-3 / K),
-                "peak_source": "DFMA microkernel measured in this run (MEASURED_PEAKS.json has no FP64 figure)",
+                "peak_source": "DFMA microkernel measured in this run (MEASURED_PEAKS.json has no FP64 figure); peak_nominal = SMs x 64 lanes x 2 x max SM clock",
+                "frac_executed_note": "algorithmic flops of the work the kernel runs: the Nx(5K+5) background term only over bins taken one by one, "
+                                      "14 exact background evaluations per (moment tile, chain) elsewhere",
                 "hbm": {"achieved": hbm_bytes / t_kernel / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": hbm_bytes / t_kernel / 1e9 / hbm_peak, "algorithmic_bytes_per_launch": hbm_bytes,
                         "peak_source": "MEASURED_PEAKS.json" if "hbm_gbs" in peaks else "fallback"}}
 
-    # ---- e2e: the reference-facing call (batched Model_def::generate_model) with HOST buffers ----
+    # ---- e2e: the reference-facing call (batched Model_def::generate_model) with HOST buffers, star after star ----
     g = np.random.Generator(np.random.Philox(key=99 + rank))
-    idx = md.index_to_relax
-    err = prob.init_errors()
-    Pcur = md.params.copy()
-    Ke = min(K, 400)
-    # the host sampler's proposals for every step, in pinned host memory (what an unmodified host-side
-    # MALA::execute would hand to generate_model); every call copies its own C x Np block to the device
-    pin_params = torch.empty((Ke + 3, C_CHAINS, md.Nparams), dtype=torch.float64).pin_memory()
-    pin_T = torch.from_numpy(md.Tcoefs.copy()).pin_memory()
-    Ph, Th = pin_params.numpy(), pin_T.numpy()
-    Ph[:] = Pcur[None, :, :]
-    Ph[:, :, idx] += 0.05 * err[None, None, :] * g.standard_normal((Ke + 3, C_CHAINS, idx.size))
-    outs = [np.empty(C_CHAINS) for _ in range(3)]
-    st = np.zeros(C_CHAINS, dtype=np.int32)
-    step_bytes = C_CHAINS * md.Nparams * 8
-    p0, pT = Ph.ctypes.data, Th.ctypes.data
-    po = [o.ctypes.data for o in outs] + [st.ctypes.data]
+    Ke = min(K, 400) if S == 1 else min(K, 100)
     tg_eval = lib.lib.tg_eval
+    calls = []
+    for m_ in mds:
+        idx = m_.index_to_relax
+        err = m_.prob.init_errors()
+        # the host sampler's proposals for every step, in pinned host memory (what an unmodified host-side
+        # MALA::execute would hand to generate_model); every call copies its own C x Np block to the device
+        pin_params = torch.empty((Ke + 3, m_.Nmodels, m_.Nparams), dtype=torch.float64).pin_memory()
+        pin_T = torch.from_numpy(m_.Tcoefs.copy()).pin_memory()
+        Ph, Th = pin_params.numpy(), pin_T.numpy()
+        Ph[:] = m_.params[None, :, :]
+        Ph[:, :, idx] += 0.05 * err[None, None, :] * g.standard_normal((Ke + 3, m_.Nmodels, idx.size))
+        outs = [np.empty(m_.Nmodels) for _ in range(3)]
+        st = np.zeros(m_.Nmodels, dtype=np.int32)
+        calls.append((m_.h, Ph.ctypes.data, m_.Nmodels * m_.Nparams * 8, m_.Nmodels, Th.ctypes.data, [o.ctypes.data for o in outs] + [st.ctypes.data], (pin_params, pin_T, outs, st)))
 
     def host_step(k):
-        rc = tg_eval(md.h, p0 + k * step_bytes, C_CHAINS, pT, po[0], po[1], po[2], po[3], None)
-        if rc != 0:
-            lib.check(rc)
+        for (h, p0, nb, cn, pT, po, _) in calls:
+            rc = tg_eval(h, p0 + k * nb, cn, pT, po[0], po[1], po[2], po[3], None)
+            if rc != 0:
+                lib.check(rc)
     for k in range(3):
         host_step(k)
-    barrier()
+    barrier(md)
     t0 = time.perf_counter()
     for k in range(Ke):
         host_step(3 + k)
@@ -275,43 +333,44 @@ def main():
         t = torch.tensor([dt_e2e], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt_e2e = float(t.item())
-    e2e = {"value": world * C_CHAINS * Ke / dt_e2e, "unit": "chain-steps/s",
-           "h2d_bytes_per_step": C_CHAINS * md.Nparams * 8 + C_CHAINS * 8, "d2h_bytes_per_step": C_CHAINS * (3 * 8 + 4),
-           "call": "tg_eval == batched Model_def::generate_model, pinned host params in, logL/logPrior/logPost/status out",
+    e2e = {"value": world * chains_gpu * Ke / dt_e2e, "unit": "chain-steps/s",
+           "h2d_bytes_per_step": chains_gpu * md.Nparams * 8 + chains_gpu * 8, "d2h_bytes_per_step": chains_gpu * (3 * 8 + 4),
+           "call": "tg_eval == batched Model_def::generate_model, pinned host params in, logL/logPrior/logPost/status out, one call per star and step",
            "steps": Ke}
+    nv = md.Nvars
+    for m_ in mds:
+        m_.sync()
 
-    # ---- the other single-GPU configurations of BASELINE.json, same device-resident sampler, short runs (N=1 only;
-    #      reported beside the headline, not part of it) ----
-    other = None
-    if rank == 0 and world == 1:
-        other = {}
-
-        def short_run(p, c, warm, steps):
-            m2 = tb.GpuModelDef(p, c, device=local_rank)
-            ml = tb.GpuMALA(m2)
-            ml.execute(0, warm, record=False)
-            m2.sync(); m2.timer_start()
-            ml.execute(warm, steps, record=False)
-            t_ms = m2.timer_stop_ms()
-            m2.kernel_time(reset=1)
-            ml.execute(warm + steps, min(steps, 64), record=False)
-            n2, ms2, _ = m2.kernel_time(reset=2)
-            m2.close()
-            return t_ms / steps, ms2 / max(n2, 1)
-        p1 = W.s_local(make_y=make_y)
-        ms1, k1 = short_run(p1, tb.MalaConfig(Nchains=10, lambda_temp=1.7, c0=2.0, Nt_learn=[100, 10**9], periods_learn=[1], dN_mixing=1, seed=7), 200, 2000)
-        other["configs[1] S-local: model_MS_local_basic, 10k bins, 10 chains"] = {"chain_steps_per_s": 10 / (ms1 * 1e-3), "ms_per_step": ms1, "fused_kernel_us": k1 * 1e3}
-        C4 = 1024
-        ms4, k4 = short_run(prob, tb.MalaConfig(Nchains=C4, chains_per_ensemble=8, lambda_temp=1.7, c0=2.0, Nt_learn=[20, 10**9], periods_learn=[1], dN_mixing=1, seed=11), 32, 64)
-        other["configs[3] S-global with 1024 batched chains (128 tempered ensembles of 8)"] = {
-            "chain_steps_per_s": C4 / (ms4 * 1e-3), "ms_per_step": ms4, "fused_kernel_us": k4 * 1e3,
-            "roofline_frac": F_launch / C_CHAINS * C4 / (k4 * 1e-3) / 1e12 / peak_tflops}
+    # ---- cfg5 beside the headline: EIGHT stars of 10 chains per GPU as one launch group (same run, same GPU) ----
+    cfg5 = None
+    if cfg_name == "cfg3" and not args.no_cfg5:
+        if grp is not None:
+            grp.close()
+        for m_ in mds:
+            m_.close()
+        S5 = 8
+        mds5, grp5 = build_group(S5, 1000 + rank * S5)
+        ms5, launches5, _, tk5, n5 = timed_run(mds5, grp5, 2 * STEPS_PER_GRAPH, max(K, 4 * STEPS_PER_GRAPH))
+        K5 = max(K, 4 * STEPS_PER_GRAPH)
+        F5, Fx5, _, _ = algorithmic_work(mds5)
+        cfg5 = {"value": world * S5 * C_CHAINS * K5 / (ms5 * 1e-3), "unit": "chain-steps/s", "stars_per_gpu": S5, "chains_per_gpu": S5 * C_CHAINS,
+                "steps": K5, "ms_per_step": ms5 / K5, "fused_kernel_us": tk5 * 1e6, "units_per_launch": grp5.sizes()[2],
+                "roofline_frac": F5 / tk5 / 1e12 / peak_tflops, "roofline_frac_executed": Fx5 / tk5 / 1e12 / peak_tflops,
+                "kernel_share_of_step": tk5 / (ms5 * 1e-3 / K5), "per_gpu_vs_one_star": (S5 * C_CHAINS * K5 / (ms5 * 1e-3)) / (chains_gpu * K / (ms * 1e-3)),
+                "gpu_launches": int(launches5),
+                "what": "configs[4] of BASELINE.json: 8 different synthetic stars (own spectrum, parameters, Philox key) x 10 tempered chains per GPU, "
+                        "ONE proposal / fused / decision launch per step for all of them (tg_batch_run)"}
+        grp5.close()
+        for m_ in mds5:
+            m_.close()
+        mds, grp = [], None
 
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only; bounded sample) ----
     cpu = None
-    if rank == 0 and world == 1:
+    if rank == 0 and world == 1 and cfg_name in ("cfg3", "cfg5"):
         from oracle.oracle import Oracle, RefLib
         O, R = Oracle(), RefLib()
+        prob = synth_problem(W, make_y=lambda p: O.model(p.model_case, p.params, p.plength, p.x)[1])
         Pc, Tc = W.perturbed_params(prob, C_CHAINS), W.tcoefs(C_CHAINS)
         fn = (lambda: R.generate_models(prob, Pc, Tc)) if R.available else (lambda: O.generate_models(prob, Pc, Tc))
         fn()
@@ -326,20 +385,31 @@ def main():
         ncpu = os.cpu_count() or 1
         cpu = {"value": C_CHAINS * args.cpu_steps / dtc, "unit": "chain-steps/s", "cores": min(ncpu, C_CHAINS),
                "kind": "reference" if R.available else "port",
-               "sample": "%d full steps (10 chains x 1M bins), generate_model under OpenMP over chains, box has %d cores" % (args.cpu_steps, ncpu),
+               "sample": "%d full steps (10 chains x 1M bins), generate_model under OpenMP over chains, box has %d cores; unmodified reference sources "
+                         "compiled against the repo's Eigen-API shim (lean_port_value: the repo's plain-C restatement of the same arithmetic, same threads)" % (args.cpu_steps, ncpu),
                "lean_port_value": C_CHAINS * args.cpu_steps / dtp}
 
     if rank == 0:
-        line = {"metric": METRIC, "value": value, "unit": "chain-steps/s", "n_gpus": world, "steps": K, "warmup": W_steps,
+        config = workload_config(nv, S)
+        if cfg_name == "cfg2":
+            config["workload"] = "cfg2 S-local: model_MS_local_basic, 10k bins, 10 chains, learning on"
+        if cfg_name == "cfg4":
+            config["workload"] = "cfg4 S-global with 1024 batched chains (128 replicated tempered ensembles of 8), Nx=1000000, learning on"
+        config["warmup_steps_run"] = W_run
+        line = {"metric": METRIC, "value": value, "unit": "chain-steps/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-                "data": "synthetic",
-                "config": {"workload": "cfg3 S-global: model_MS_Global_a1etaa3_HarveyLike_Classic, 106 params (%d free), Nx=1000000, C=10 chains per GPU, lambda=1.7, learning on" % md.Nvars,
-                           "l2": "x, y = 16 MB per launch (< L2) but the timed kernel is FP64-bound; no L2 flush (steady-state MCMC reuses the spectrum every step by design)",
-                           "per_gpu": "one independent tempered ensemble (star) per GPU, no collective"},
+                "data": "synthetic", "config": config,
                 "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-                "bin_evals_per_s": value * NX, "other_configs": other}
-        print(json.dumps(line), flush=True)
-    md.close()
+                "bin_evals_per_s": value * nx_star, "cfg5_8_stars_per_gpu": cfg5}
+        txt = json.dumps(line)
+        print(txt, flush=True)
+        if args.extra_out:
+            with open(args.extra_out, "w") as f:
+                f.write(txt + "\n")
+    if grp is not None:
+        grp.close()
+    for m_ in mds:
+        m_.close()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

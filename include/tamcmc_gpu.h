@@ -71,6 +71,10 @@ typedef struct tg_problem {
     unsigned long long seed;      /* Philox key (reference: time(NULL), MALA.cpp:62)                      */
     int           device;         /* CUDA device ordinal                                                  */
     int           flags;          /* TG_F_* */
+    /* Offsets added to the chain / ensemble indices in the Philox counters: ensemble e of a handle that batches many replicated
+     * ensembles (chains_per_ensemble) draws the same numbers as a single-ensemble handle with philox_chain0 = e*chains_per_ensemble,
+     * philox_ensemble0 = e and the same seed.  0 for ordinary use. */
+    int           philox_chain0, philox_ensemble0;
 } tg_problem;
 
 #define TG_F_NO_TILE_ORDER        2 /* one work item per 1024-bin sub-tile in index order instead of heaviest-first + long noise-only items (scheduling only; results identical) */
@@ -133,6 +137,20 @@ int tg_set_state(tg_handle *h, const double *vars, const double *mu, const doubl
  * No per-step host transfer; the per-step records are drained into rec (may be NULL) at the end. */
 int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec);
 
+/* Launch group (configs[4] of BASELINE.json: several stars -- independent tempered ensembles with their own spectrum, parameters
+ * and priors -- per GPU; the reference runs stars as an array of independent processes, scripts/slurm/job_array.sh:8,24 and
+ * main.cpp:111-127).  The stars stay independent handles; tg_batch_run advances all of them by nsteps iterations with ONE
+ * proposal, ONE fused model+likelihood and ONE decision launch per step (the work-unit table of the fused kernel spans every
+ * star, costliest first).  Each star's trajectory is the same, bit for bit, as tg_run on its handle alone.  All handles on one
+ * device; they must outlive the group; recs[k] (may be NULL, as may recs) receives the records of star k. */
+typedef struct tg_batch tg_batch;
+int tg_batch_create(tg_handle **handles, int n, tg_batch **out);
+int tg_batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs);
+int tg_batch_destroy(tg_batch *b);
+int tg_batch_sizes(tg_batch *b, int *nstars, int *Ctot, int *units);
+int tg_batch_kernel_time(tg_batch *b, int reset, long *launches, double *ms_eval, long *total_launches);
+int tg_batch_event_record(tg_batch *b, int which);   /* stopwatch on the group's stream; read with tg_event_elapsed_ms(handles[0]) */
+
 /* Sizes implied by the problem. */
 int tg_sizes(tg_handle *h, int *Nv, int *Np, int *C, int *E, long *Nx);
 
@@ -155,6 +173,11 @@ int tg_kernel_time(tg_handle *h, int reset, long *launches, double *ms_eval, lon
  * unit where truncation windows are expected, sub-tiles of 1024 bins per unit in the noise-only parts of the
  * spectrum, CUDA-graph replay of tg_run. */
 int tg_set_tuning(tg_handle *h, int chains_per_block, int heavy_group, int light_subtiles, int use_graph);
+
+/* How the fused kernel covers the spectrum for the sampler's chains at present (scheduling only, results never depend on it):
+ * bins evaluated bin by bin, background-only tiles of mom_sub*1024 bins taken through the Chebyshev moments of the data
+ * (14 exact evaluations of the background per tile and chain instead of one per bin), work units per launch. */
+int tg_work_profile(tg_handle *h, long *bins_direct, long *moment_tiles, int *units);
 
 /* Device-side stopwatch on the handle's stream (CUDA events): which = 0 start, 1 stop. */
 int tg_event_record(tg_handle *h, int which);

@@ -17,12 +17,12 @@ present the calls raise.
 from . import workloads  # noqa: F401
 from . import sharding  # noqa: F401
 from .build import build_library, LIB_PATH  # noqa: F401
-from .gpu import (GpuLibrary, GpuModelDef, GpuMALA, MalaConfig, TgError, load_library,  # noqa: F401
+from .gpu import (GpuLibrary, GpuModelDef, GpuMALA, GpuBatch, MalaConfig, TgError, load_library,  # noqa: F401
                   ST_EMPTY_WINDOW, ST_NAN_WINDOW, ST_NAN_LOGL, ST_BAD_PRIOR, ST_CHOL_FAIL, ST_MODE_OVERFLOW)
 
 from . import outputs  # noqa: F401,E402
 from . import frontend  # noqa: F401,E402
 from . import config_tree  # noqa: F401,E402
 
-__all__ = ["workloads", "build_library", "LIB_PATH", "GpuLibrary", "GpuModelDef", "GpuMALA", "MalaConfig",
+__all__ = ["workloads", "build_library", "LIB_PATH", "GpuLibrary", "GpuModelDef", "GpuMALA", "GpuBatch", "MalaConfig",
            "TgError", "load_library"]

@@ -29,26 +29,28 @@ struct EvalBuf {                 // tables + results for a batch of B parameter 
     int      *status = nullptr;
     int       B = 0;               // batch size the pointers above are laid out for
     double   *pin_in = nullptr, *pin_out = nullptr;    // pinned host staging of the same layout
+    TgEvalArgs *d_args = nullptr;                      // the fused kernel reads its arguments from device memory (tg_load_args)
+    TgEvalArgs  h_args;                                // what d_args holds
+    bool        args_valid = false;
     void layout(int b, int Np) {
         B = b; params = in; T = in + (size_t)b * Np;
         logL = out; logPrior = out + b; logPost = out + 2 * (size_t)b; status = (int *)(out + 3 * (size_t)b);
     }
 };
 
+struct tg_batch;
 struct tg_handle {
     int        device = 0, n_sm = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t side = nullptr;           // the adaptation candidates of a step run here, beside the proposal and the fused kernel
-    cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
-    bool         side_pending = false;     // a join is owed before the next finish kernel
-    bool         pdl = true;                           // programmatic dependent launch between the step kernels (environment TG_PDL=0 turns it off)
-    bool         no_split = false, no_side = false;   // developer switches (environment TG_NO_SPLIT_PRIOR / TG_NO_SIDE_STREAM)
+    tg_batch    *self = nullptr;           // the sampler steps of a handle run as a batch of one star (tg_run == tg_batch_run of it)
+    long         items_version = 0;        // bumped whenever the work items change (batches rebuild their unit tables)
+    bool         no_split = false;         // developer switch (environment TG_NO_SPLIT_PRIOR)
     TgDesc     d{};
     TgMala     m{};
     TgState    s{};
     TgRecDev   rec{};
     double    *x = nullptr, *y = nullptr, *lnx = nullptr, *sig = nullptr;
-    double    *mom = nullptr; int mom_sub = 4, mom_run = 16; int *mom_fail = nullptr; long n_mom_tiles = 0; bool mom_probed = false;
+    double    *mom = nullptr; int mom_sub = 4, mom_run = 16; int *mom_fail = nullptr; long n_mom_tiles = 0;
     int        hybrid_pct = 0, hybrid_group = 2;
     int       *mom_note = nullptr;                      // pinned, mapped: the kernel stores 1 when it flags a tile for the first time          // Chebyshev moments of the data over aligned tiles (tg_eval.cuh), NULL = off
     double    *pri = nullptr; int *sw = nullptr;
@@ -63,7 +65,6 @@ struct tg_handle {
     UnitTable  u_sp, u_ev;                 // work units of the fused kernel in launch order: sampler (B = C), tg_eval batches
     std::vector<int4> items_host;          // bin partition: (first bin, sub-tiles, weight = windows crossing, heavy?)
     bool       no_order = false;
-    cudaGraphExec_t graph = nullptr;
     cudaGraphExec_t ev_graph = nullptr; int ev_graph_B = 0;   // tg_eval: copy in, prologue, fused kernel, reduce+finalize, copy out
     // eval-kernel timing
     bool       timing = false;
@@ -71,6 +72,39 @@ struct tg_handle {
     long       n_eval_launch = 0, n_launch_total = 0; double ms_eval = 0;
     std::vector<void *> allocs;
     cudaEvent_t watch[2] = {nullptr, nullptr};
+    void       *nccl_comm = nullptr;       // bin-sharded variant: ncclComm_t of the shard group (tg_shard_attach)
+};
+
+// A launch group: the sampler steps of several stars (handles on the same GPU) as ONE propose / fused / finish launch per
+// step -- cfg5 of BASELINE.json (several tempered ensembles of different spectra per GPU).  The stars stay independent
+// (own spectrum, parameters, priors, Philox key, iteration counter, records); only the grids are shared: the unit table of
+// the fused kernel spans all stars, costliest first.  A handle on its own is a batch of one.
+struct tg_batch {
+    std::vector<tg_handle *> hs;
+    int          device = 0, Ctot = 0;
+    cudaStream_t stream = nullptr;         // == hs[0]->stream
+    cudaStream_t side = nullptr;           // the adaptation candidates of a step run here, beside the proposal and the fused kernel
+    cudaEvent_t  ev_fork = nullptr, ev_join = nullptr;
+    bool         side_pending = false;     // a join is owed before the next finish kernel
+    bool         pdl = true;               // programmatic dependent launch between the step kernels (environment TG_PDL=0 turns it off)
+    bool         no_side = false;          // developer switch (environment TG_NO_SIDE_STREAM)
+    int          use_graph = 1, steps_per_graph = 16, presummed = 0;
+    // per-star argument records of the three step kernels + the chain map, host copies and device arrays
+    std::vector<TgEvalArgs>    h_ev;   TgEvalArgs    *d_ev = nullptr;
+    std::vector<TgProposeArgs> h_pm, h_ps; TgProposeArgs *d_pm = nullptr, *d_ps = nullptr;
+    std::vector<TgFinishArgs>  h_fin;  TgFinishArgs  *d_fin = nullptr;
+    int2        *d_cmap = nullptr;
+    bool         args_valid = false;
+    int          side_rows = 0; size_t propose_smem = 0, eval_smem = 0;
+    tg_handle::UnitTable units;            // work units of the fused kernel over all stars, costliest first
+    std::vector<long> units_version;       // items_version of every star the table was built from
+    cudaGraphExec_t graph = nullptr;
+    bool         probed = false;           // the look at the flagged background tiles after the first graph of a long run
+    // eval-kernel timing
+    bool         timing = false;
+    std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
+    long         n_eval_launch = 0, n_launch_total = 0; double ms_eval = 0;
+    std::vector<void *> allocs;
 };
 
 template <typename T> static int dalloc(tg_handle *h, T **p, size_t n)
@@ -83,6 +117,22 @@ template <typename T> static int dalloc(tg_handle *h, T **p, size_t n)
 }
 #define DA(ptr, n) do { int r_ = dalloc(h, &(ptr), (n)); if (r_) return r_; } while (0)
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of the function, not of a handle: only ever raised
+static int raise_dyn_smem(const void *func, size_t bytes)
+{
+    static std::vector<std::pair<std::pair<const void *, int>, size_t>> seen;   // (function, device) -> bytes
+    int dev = 0; CK(cudaGetDevice(&dev));
+    const std::pair<const void *, int> key(func, dev);
+    for (auto &e : seen) if (e.first == key) {
+        if (bytes <= e.second) return TG_OK;
+        CK(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        e.second = bytes; return TG_OK;
+    }
+    CK(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    seen.push_back({key, bytes});
+    return TG_OK;
+}
+
 extern "C" const char *tg_last_error(void) { return g_err.c_str(); }
 extern "C" int tg_version(void) { return 100; }
 #ifdef TG_PROFILE
@@ -94,8 +144,8 @@ extern "C" int tg_dbg_clocks(long long *out) { return cudaMemcpyFromSymbol(out, 
 
 static void drop_graphs(tg_handle *h)
 {
-    if (h->graph) { cudaGraphExecDestroy(h->graph); h->graph = nullptr; }
     if (h->ev_graph) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }
+    h->items_version++;                                   // batches holding this star re-capture their step graph
 }
 
 static int alloc_evalbuf(tg_handle *h, EvalBuf &b, int B)
@@ -169,8 +219,8 @@ static void build_moments(const double *x, const double *y, long Nx, int mt_bins
 
 // Launch with (pdl) or without the programmatic-serialization attribute: with it the kernel may become resident while its
 // predecessor in the stream still runs and synchronises on it with tg_pdl_wait() (tg_internal.cuh).
-template <class Arg>
-static cudaError_t launch_k(void (*kern)(Arg), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, const Arg &arg)
+template <class... Arg>
+static cudaError_t launch_k(void (*kern)(Arg...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, Arg... arg)
 {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
@@ -178,7 +228,7 @@ static cudaError_t launch_k(void (*kern)(Arg), dim3 grid, dim3 block, size_t sme
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, kern, arg);
+    return cudaLaunchKernelEx(&cfg, kern, arg...);
 }
 
 static cudaEvent_t next_event(tg_handle *h)
@@ -202,7 +252,23 @@ static int harvest_events(tg_handle *h)
 
 static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B);
 
-// prologue (optional) + fused kernel + per-chain reduction for B points
+// The argument record of the fused kernel for the points held in `b` -> device memory (uploaded only when it changed; never
+// called with a change pending inside a stream capture: the callers bring it up to date before they begin one).
+static int sync_eval_args(tg_handle *h, EvalBuf &b, double *model, int B)
+{
+    TgEvalArgs ea; memset(&ea, 0, sizeof(ea));
+    ea.d = h->d; ea.t = b.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = b.partials; ea.model = model;
+    ea.B = B; ea.nitems = h->nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
+    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note;
+    if (b.d_args && b.args_valid && memcmp(&ea, &b.h_args, sizeof(ea)) == 0) return TG_OK;
+    if (!b.d_args) DA(b.d_args, 1);
+    memcpy(&b.h_args, &ea, sizeof(ea));
+    CK(cudaMemcpyAsync(b.d_args, &b.h_args, sizeof(ea), cudaMemcpyHostToDevice, h->stream));
+    b.args_valid = true;
+    return TG_OK;
+}
+
+// prologue (optional) + fused kernel + per-chain reduction for B points of ONE handle (tg_eval, create / restore)
 static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_dev, int B, double *model, bool do_prologue, bool do_reduce, bool pdl = false)
 {
     if (do_prologue) {
@@ -211,15 +277,15 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
         h->n_launch_total++;
     }
     tg_handle::UnitTable &u = (&b == &h->sp) ? h->u_sp : h->u_ev;
-    if (B != u.B) { int r = build_units(h, u, B); if (r) return r; }     // never inside a graph capture: tg_run builds u_sp first
+    if (B != u.B) { int r = build_units(h, u, B); if (r) return r; }     // never inside a graph capture
+    { int r = sync_eval_args(h, b, model, B); if (r) return r; }
     const size_t esm = TG_EVAL_SMEM(h->chains_per_block, h->list_cap);
-    TgEvalArgs ea{h->d, b.t, h->x, h->y, h->lnx, h->sig, b.partials, model, u.dev, B, h->nitems, h->chains_per_block, h->list_cap, h->mom, h->mom_sub, h->mom_fail, h->mom_note};
     dim3 grid(u.n);
     if (h->timing) {
         if (h->ev_used >= 8192) { int r = harvest_events(h); if (r) return r; }
         cudaEventRecord(next_event(h), h->stream);
     }
-    CK(launch_k(tg_k_eval, grid, dim3(TG_THREADS), esm, h->stream, pdl && !h->timing, ea));
+    CK(launch_k(tg_k_eval, grid, dim3(TG_THREADS), esm, h->stream, pdl && !h->timing, (const TgEvalArgs *)b.d_args, (const int4 *)u.dev));
     if (h->timing) cudaEventRecord(next_event(h), h->stream);
     h->n_eval_launch++; h->n_launch_total++;
     if (do_reduce) { tg_k_reduce<<<B, 256, 0, h->stream>>>(b.partials, h->nitems, b.sums); h->n_launch_total++; }
@@ -297,11 +363,10 @@ static int build_items(tg_handle *h, EvalBuf &b, int B)
 }
 
 // Units = items x chain groups: few chains per unit where windows are expected (an item there costs
-// 5-10x a noise-only sub-tile), up to chains_per_block elsewhere; costliest first (LPT scheduling).
-static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B)
+// 5-10x a noise-only sub-tile), up to chains_per_block elsewhere.  Appends the units of star `star` (B points) with their
+// estimated costs; host side only.
+static void make_units(tg_handle *h, int B, int star, std::vector<int4> &units, std::vector<double> &cost)
 {
-    std::vector<int4> units;
-    std::vector<double> cost;
     const int gl = std::max(1, h->chains_per_block), gh = std::max(1, std::min(h->heavy_group, gl));
     // hybrid: the costliest hybrid_pct percent of the window-region items take hybrid_group chains per unit (set-up and
     // list building shared by the chains of a unit), the rest heavy_group (small units for the tail of the grid)
@@ -319,11 +384,16 @@ static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B)
         const int groups = (B + gmax - 1) / gmax, g = (B + groups - 1) / groups;      // balanced
         for (int c0 = 0; c0 < B; c0 += g) {
             const int G = std::min(g, B - c0);
-            units.push_back(make_int4(it.x, it.y | (G << 16), c0, (int)k));
+            units.push_back(make_int4(it.x, it.y | (G << 16), c0, (int)k | (star << TG_UNIT_STAR_SHIFT)));
             cost.push_back(it.w == 2 ? (double)G * (it.y / std::max(1, h->mom_sub)) * 8.0 + 15.0 : (double)G * it.y * (20.0 + 6.25 * it.z) + 15.0);
         }
     }
-    if (!h->no_order) {
+}
+
+// costliest first (LPT scheduling) unless the tile order is forced, then to the device
+static int upload_units(std::vector<void *> &allocs, cudaStream_t stream, tg_handle::UnitTable &u, std::vector<int4> &units, const std::vector<double> &cost, bool keep_order)
+{
+    if (!keep_order) {
         std::vector<int> idx(units.size());
         for (size_t k = 0; k < idx.size(); k++) idx[k] = (int)k;
         std::stable_sort(idx.begin(), idx.end(), [&](int a, int b2) { return cost[a] > cost[b2]; });
@@ -334,12 +404,22 @@ static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B)
     if ((int)units.size() > u.cap) {
         void *q = nullptr;
         CK(cudaMalloc(&q, units.size() * sizeof(int4)));
-        h->allocs.push_back(q);                     // the old (smaller) table is released with the handle
+        allocs.push_back(q);                        // the old (smaller) table is released with its owner
         u.dev = (int4 *)q; u.cap = (int)units.size();
     }
-    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaStreamSynchronize(stream));
     CK(cudaMemcpy(u.dev, units.data(), units.size() * sizeof(int4), cudaMemcpyHostToDevice));
-    u.n = (int)units.size(); u.B = B;
+    u.n = (int)units.size();
+    return TG_OK;
+}
+
+static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B)
+{
+    std::vector<int4> units;
+    std::vector<double> cost;
+    make_units(h, B, 0, units, cost);
+    int r = upload_units(h->allocs, h->stream, u, units, cost, h->no_order); if (r) return r;
+    u.B = B;
     return TG_OK;
 }
 
@@ -353,21 +433,28 @@ static int refresh_items_if_flagged(tg_handle *h)
     return build_items(h, h->sp, h->s.C);
 }
 
+static int batch_refresh(tg_batch *b);
+static void batch_drop_graph(tg_batch *b);
+
 extern "C" int tg_set_tuning(tg_handle *h, int chains_per_block, int heavy_group, int light_subtiles, int use_graph)
 {
     if (!h) return fail(TG_E_BADARG, "null handle");
+    CK(cudaSetDevice(h->device));
     if (chains_per_block > 0) { h->chains_per_block = std::min(chains_per_block, h->max_cpb); h->u_sp.B = h->u_ev.B = -1; }
     if (heavy_group > 0) { h->heavy_group = heavy_group; h->u_sp.B = h->u_ev.B = -1; }
-    if (use_graph >= 0) h->use_graph = use_graph;
+    if (use_graph >= 0) { h->use_graph = use_graph; if (h->self) { h->self->use_graph = use_graph; batch_drop_graph(h->self); } }
     drop_graphs(h);
     if (light_subtiles > 0 && light_subtiles != h->light_sub) {
         h->light_sub = std::min(light_subtiles, 4096);
         int r = build_items(h, h->sp, h->s.C); if (r) return r;
     }
-    return TG_OK;
+    return h->self ? batch_refresh(h->self) : TG_OK;
 }
 
 static int create_impl(const tg_problem *p, tg_handle *h);
+static int batch_create(tg_handle **hs, int n, tg_batch **out);
+static int batch_destroy(tg_batch *b);
+extern "C" int tg_event_record(tg_handle *h, int which);
 
 extern "C" int tg_destroy(tg_handle *h);
 
@@ -413,11 +500,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, h->device));
     h->n_sm = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    CK(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
-    h->no_split = getenv("TG_NO_SPLIT_PRIOR") != nullptr; h->no_side = getenv("TG_NO_SIDE_STREAM") != nullptr;
-    if (const char *e = getenv("TG_PDL")) h->pdl = atoi(e) != 0;
-    CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
-    CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+    h->no_split = getenv("TG_NO_SPLIT_PRIOR") != nullptr;
 
     TgDesc &d = h->d;
     d.model_case = p->model_case; d.like_case = p->likelihood_case; d.prior_case = p->prior_case;
@@ -481,7 +564,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         if (TG_EVAL_SMEM(m, h->list_cap) > (size_t)maxdyn - 2048) return fail(TG_E_BADARG, "too many Lorentzian components for the shared-memory list of the fused kernel");
         h->max_cpb = m;
         const size_t need = TG_EVAL_SMEM(m, h->list_cap);
-        CK(cudaFuncSetAttribute(tg_k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need));
+        { int r = raise_dyn_smem((const void *)tg_k_eval, need); if (r) return r; }
         const int groups = (C + m - 1) / m;                                               // balanced chain groups of <= max_cpb
         h->chains_per_block = (C + groups - 1) / groups;
         // where truncation windows lie: items of two sub-tiles (taken 8 bins per thread); one chain per unit for a single
@@ -512,6 +595,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     for (int l = 0; l < p->n_learn; l++) { m.Nt_learn[l] = p->Nt_learn[l]; m.periods[l] = p->periods_learn[l]; }
     if (p->n_learn > 0) m.Nt_learn[p->n_learn] = p->Nt_learn[p->n_learn];
     m.dN_mixing = p->dN_mixing; m.seed = p->seed; m.flags = p->flags;
+    m.chain0 = p->philox_chain0; m.ens0 = p->philox_ensemble0;
 
     // ---- sampler state (MALA::MALA + init_proposal, Model_def ctor) ----
     TgState &s = h->s;
@@ -522,7 +606,8 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     DA(s.logL_cur, C); DA(s.logPrior_cur, C); DA(s.logPost_cur, C); DA(s.Pmove, C); DA(s.moved, C);
     DA(s.mu, 3 * C * Nv); DA(s.sigma, C); DA(s.cov, 3 * C * Nv * Nv); DA(s.chol, 3 * C * Nv * Nv); DA(s.live, C); DA(s.chol_fail, 3 * C); DA(s.sticky_status, C);
     DA(h->stage_mu, C * Nv); DA(h->stage_cov, C * Nv * Nv);
-    DA(s.ctrl, 1);
+    DA(s.ctrl, 1); DA(s.ens_ticket, s.E);
+    CK(cudaMemsetAsync(s.ens_ticket, 0, (size_t)s.E * 4, h->stream));
     s.index_to_relax = h->index_to_relax; s.Tcoefs = h->Tcoefs;
     {
         std::vector<double> vars(C * Nv), params(C * Np), sigma(C), cov(C * Nv * Nv, 0.0);
@@ -558,11 +643,9 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         // Nv <= 96: the adaptation works out of registers (tg_spec96, no dynamic shared memory) and its CTAs
         // ride in the propose grid; larger problems run it as a separate kernel after the propose kernel
         h->fused_spec = (h->tri_smem && h->smem_matrix && d.Nv <= 96) ? 1 : 0;
-        CK(cudaFuncSetAttribute(tg_k_spec, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->spec_smem));
-        CK(cudaFuncSetAttribute(tg_k_propose, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->propose_smem));   // static + dynamic may exceed 48 KB
-        if (need_pro > 48 * 1024) {
-            CK(cudaFuncSetAttribute(tg_k_prologue, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need_pro));
-        }
+        { int r = raise_dyn_smem((const void *)tg_k_spec, h->spec_smem); if (r) return r; }
+        { int r = raise_dyn_smem((const void *)tg_k_propose, h->propose_smem); if (r) return r; }   // static + dynamic may exceed 48 KB
+        if (need_pro > 48 * 1024) { int r = raise_dyn_smem((const void *)tg_k_prologue, need_pro); if (r) return r; }
     }
     // record ring
     {
@@ -588,7 +671,9 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         CK(cudaStreamSynchronize(h->stream));
         r = refresh_items_if_flagged(h); if (r) return r;
     }
-    return TG_OK;
+    // the handle's own launch group: unit table, argument records and the step graph are ready when tg_create returns
+    { tg_handle *one[1] = {h}; int r = batch_create(one, 1, &h->self); if (r) return r; }
+    return batch_refresh(h->self);
 }
 
 extern "C" int tg_destroy(tg_handle *h)
@@ -596,15 +681,13 @@ extern "C" int tg_destroy(tg_handle *h)
     if (!h) return TG_OK;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->self) { batch_destroy(h->self); h->self = nullptr; }
     drop_graphs(h);
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
     for (void *q : h->allocs) cudaFree(q);
     for (EvalBuf *b : {&h->sp, &h->ev}) { if (b->pin_in) cudaFreeHost(b->pin_in); if (b->pin_out) cudaFreeHost(b->pin_out); }
     if (h->mom_note) cudaFreeHost(h->mom_note);
-    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
-    if (h->ev_join) cudaEventDestroy(h->ev_join);
-    if (h->side) cudaStreamDestroy(h->side);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return TG_OK;
@@ -680,6 +763,7 @@ extern "C" int tg_eval(tg_handle *h, const double *params, int B, const double *
         if (h->ev_graph && h->ev_graph_B != B) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }
         if (!h->ev_graph) {
             if (h->u_ev.B != B) { int r = build_units(h, h->u_ev, B); if (r) return r; }
+            { int r = sync_eval_args(h, b, nullptr, B); if (r) return r; }        // not inside the capture
             cudaGraph_t g;
             const long lt = h->n_launch_total, le = h->n_eval_launch;
             CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
@@ -792,149 +876,373 @@ extern "C" int tg_set_state(tg_handle *h, const double *vars, const double *mu, 
         { int r = build_items(h, h->sp, (int)C); if (r) return r; }
     }
     CK(cudaStreamSynchronize(h->stream));
-    return TG_OK;
+    return h->self ? batch_refresh(h->self) : TG_OK;
 }
 
 // ------------------------------------------------------------------------------------------
-// MALA::execute on the device
+// MALA::execute on the device: launch groups (a handle is a group of one star)
 // ------------------------------------------------------------------------------------------
-static int launch_step(tg_handle *h, bool begin, bool end, int presummed)
+static void batch_drop_graph(tg_batch *b)
 {
-    const int C = h->s.C;
-    if (begin) {
-        // The adaptation candidates (Robbins-Monro + Cholesky for both outcomes of the decision) depend on the
-        // state the previous finish kernel left and on nothing of this step (the CTA of the "accepted" outcome
-        // recomputes the proposed point itself), and only the finish kernel needs them: they run on a side stream
-        // next to the proposal, the prologue and the fused kernel (a parallel branch once captured in a graph).
+    if (b->graph) { cudaGraphExecDestroy(b->graph); b->graph = nullptr; }
+}
+
+static cudaEvent_t batch_next_event(tg_batch *b)
+{
+    if (b->ev_used == b->ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); b->ev_pool.push_back(e); }
+    return b->ev_pool[b->ev_used++];
+}
+
+static int batch_harvest_events(tg_batch *b)
+{
+    if (b->ev_used == 0) return TG_OK;
+    CK(cudaStreamSynchronize(b->stream));
+    for (size_t k = 0; k + 1 < b->ev_used; k += 2) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, b->ev_pool[k], b->ev_pool[k + 1]));
+        b->ms_eval += ms;
+    }
+    b->ev_used = 0;
+    return TG_OK;
+}
+
+template <class T> static int batch_dalloc(tg_batch *b, T **p, size_t n)
+{
+    void *q = nullptr;
+    CK(cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T)));
+    b->allocs.push_back(q);
+    *p = (T *)q;
+    return TG_OK;
+}
+
+static int batch_destroy(tg_batch *b)
+{
+    if (!b) return TG_OK;
+    cudaSetDevice(b->device);
+    if (b->stream) cudaStreamSynchronize(b->stream);
+    if (b->side) cudaStreamSynchronize(b->side);
+    batch_drop_graph(b);
+    for (auto e : b->ev_pool) cudaEventDestroy(e);
+    for (void *q : b->allocs) cudaFree(q);
+    if (b->ev_fork) cudaEventDestroy(b->ev_fork);
+    if (b->ev_join) cudaEventDestroy(b->ev_join);
+    if (b->side) cudaStreamDestroy(b->side);
+    delete b;
+    return TG_OK;
+}
+
+static int batch_create(tg_handle **hs, int n, tg_batch **out)
+{
+    if (!hs || n < 1 || n >= (1 << (31 - TG_UNIT_STAR_SHIFT)) || !out) return fail(TG_E_BADARG, "tg_batch_create: bad argument");
+    for (int k = 0; k < n; k++) {
+        if (!hs[k]) return fail(TG_E_BADARG, "tg_batch_create: null handle");
+        if (hs[k]->device != hs[0]->device) return fail(TG_E_BADARG, "tg_batch_create: the stars of a launch group live on one GPU");
+        if (hs[k]->nccl_comm && n > 1) return fail(TG_E_BADARG, "tg_batch_create: a bin-sharded handle runs on its own");
+        for (int j = 0; j < k; j++) if (hs[j] == hs[k]) return fail(TG_E_BADARG, "tg_batch_create: handle listed twice");
+    }
+    tg_batch *b = new tg_batch();
+    b->hs.assign(hs, hs + n);
+    b->device = hs[0]->device; b->stream = hs[0]->stream;
+    b->use_graph = hs[0]->use_graph; b->steps_per_graph = hs[0]->steps_per_graph;
+    b->units_version.assign(n, -1);
+    int r = TG_OK;
+    auto bail = [&](int code) { const std::string keep = g_err; batch_destroy(b); g_err = keep; return code; };
+    if (cudaSetDevice(b->device) != cudaSuccess) return bail(fail(TG_E_CUDA, "cudaSetDevice"));
+    if (cudaStreamCreateWithFlags(&b->side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&b->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&b->ev_join, cudaEventDisableTiming) != cudaSuccess) return bail(fail(TG_E_CUDA, "tg_batch_create: stream / events"));
+    b->no_side = getenv("TG_NO_SIDE_STREAM") != nullptr;
+    if (const char *e = getenv("TG_PDL")) b->pdl = atoi(e) != 0;
+    std::vector<int2> cmap;
+    for (int k = 0; k < n; k++) for (int c = 0; c < hs[k]->s.C; c++) cmap.push_back(make_int2(k, c));
+    b->Ctot = (int)cmap.size();
+    if ((r = batch_dalloc(b, &b->d_cmap, cmap.size())) || (r = batch_dalloc(b, &b->d_ev, n)) || (r = batch_dalloc(b, &b->d_pm, n)) ||
+        (r = batch_dalloc(b, &b->d_ps, n)) || (r = batch_dalloc(b, &b->d_fin, n))) return bail(r);
+    for (int k = 0; k < n; k++) if (cudaStreamSynchronize(hs[k]->stream) != cudaSuccess) return bail(fail(TG_E_CUDA, "tg_batch_create: sync"));
+    if (cudaMemcpy(b->d_cmap, cmap.data(), cmap.size() * sizeof(int2), cudaMemcpyHostToDevice) != cudaSuccess) return bail(fail(TG_E_CUDA, "tg_batch_create: chain map"));
+    *out = b;
+    return TG_OK;
+}
+
+// Argument records of the three step kernels for every star -> device arrays (uploaded when something changed)
+static int batch_sync_args(tg_batch *b)
+{
+    const size_t n = b->hs.size();
+    std::vector<TgEvalArgs> ev(n); std::vector<TgProposeArgs> pm(n), ps(n); std::vector<TgFinishArgs> fin(n);
+    memset(ev.data(), 0, n * sizeof(TgEvalArgs)); memset(pm.data(), 0, n * sizeof(TgProposeArgs));
+    memset(ps.data(), 0, n * sizeof(TgProposeArgs)); memset(fin.data(), 0, n * sizeof(TgFinishArgs));
+    int rows = 0; size_t psm = 0, esm = 0;
+    for (size_t k = 0; k < n; k++) {
+        tg_handle *h = b->hs[k];
+        TgEvalArgs &ea = ev[k];
+        ea.d = h->d; ea.t = h->sp.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = h->sp.partials; ea.model = nullptr;
+        ea.B = h->s.C; ea.nitems = h->nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
+        ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note;
+        // The adaptation candidates (Robbins-Monro + Cholesky for both outcomes of the decision) depend on the state the previous
+        // finish kernel left and on nothing of this step (the CTA of the "accepted" outcome recomputes the proposed point itself),
+        // and only the finish kernel needs them: they run on a side stream next to the proposal, the prologue and the fused kernel.
         const int learn = h->m.n_learn > 0, fused = learn && h->fused_spec;
         const int split = h->tri_smem && !h->no_split;        // the log-prior of the proposed point gets its own CTAs (role 3) on the side stream
-        TgProposeArgs pa{h->s, h->m, TgProArgs{h->d, h->sp.t, h->sp.params, h->pri, h->sw}, h->smem_matrix, h->tri_smem, fused, h->smem_matrix, 0,
-                         split ? TG_PRO_MODEL : (TG_PRO_MODEL | TG_PRO_PRIOR)};
-        if (fused || split) {
-            CK(cudaEventRecord(h->ev_fork, h->stream));
-            CK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
-            TgProposeArgs ps = pa; ps.role_base = fused ? 1 : 3;
-            tg_k_propose<<<dim3(C, (fused ? 2 : 0) + (split ? 1 : 0)), 256, h->propose_smem, h->no_side ? h->stream : h->side>>>(ps);
-            CK(cudaEventRecord(h->ev_join, h->side));
-            h->side_pending = true;
-            h->n_launch_total++;
+        TgProposeArgs &a = pm[k];
+        a.s = h->s; a.m = h->m; a.pro.d = h->d; a.pro.t = h->sp.t; a.pro.params = h->sp.params; a.pro.pri = h->pri; a.pro.sw = h->sw;
+        a.packed = h->smem_matrix; a.tri_smem = h->tri_smem; a.fused_spec = fused; a.smem_matrix = h->smem_matrix;
+        a.role_base = 0; a.parts = split ? TG_PRO_MODEL : (TG_PRO_MODEL | TG_PRO_PRIOR); a.nroles = 1;
+        ps[k] = a; ps[k].role_base = fused ? 1 : 3; ps[k].nroles = (fused ? 2 : 0) + (split ? 1 : 0);
+        rows = std::max(rows, ps[k].nroles);
+        psm = std::max(psm, h->propose_smem); esm = std::max(esm, TG_EVAL_SMEM(h->chains_per_block, h->list_cap));
+        TgFinishArgs &f = fin[k];
+        f.d = h->d; f.s = h->s; f.m = h->m; f.t = h->sp.t; f.partials = h->sp.partials; f.ntiles = h->nitems; f.sums = h->sp.sums;
+        f.presummed = b->presummed; f.rec = h->rec; f.record = 1;
+    }
+    b->side_rows = rows; b->propose_smem = psm; b->eval_smem = esm;
+    const bool same = b->args_valid && b->h_ev.size() == n && memcmp(ev.data(), b->h_ev.data(), n * sizeof(TgEvalArgs)) == 0 &&
+                      memcmp(pm.data(), b->h_pm.data(), n * sizeof(TgProposeArgs)) == 0 && memcmp(ps.data(), b->h_ps.data(), n * sizeof(TgProposeArgs)) == 0 &&
+                      memcmp(fin.data(), b->h_fin.data(), n * sizeof(TgFinishArgs)) == 0;
+    if (same) return TG_OK;
+    b->h_ev.swap(ev); b->h_pm.swap(pm); b->h_ps.swap(ps); b->h_fin.swap(fin);
+    CK(cudaStreamSynchronize(b->stream));
+    CK(cudaMemcpy(b->d_ev, b->h_ev.data(), n * sizeof(TgEvalArgs), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(b->d_pm, b->h_pm.data(), n * sizeof(TgProposeArgs), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(b->d_ps, b->h_ps.data(), n * sizeof(TgProposeArgs), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(b->d_fin, b->h_fin.data(), n * sizeof(TgFinishArgs), cudaMemcpyHostToDevice));
+    b->args_valid = true;
+    return TG_OK;
+}
+
+static int batch_build_units(tg_batch *b)
+{
+    std::vector<int4> units; std::vector<double> cost;
+    bool keep_order = false;
+    for (size_t k = 0; k < b->hs.size(); k++) { make_units(b->hs[k], b->hs[k]->s.C, (int)k, units, cost); keep_order = keep_order || b->hs[k]->no_order; }
+    int r = upload_units(b->allocs, b->stream, b->units, units, cost, keep_order); if (r) return r;
+    for (size_t k = 0; k < b->hs.size(); k++) b->units_version[k] = b->hs[k]->items_version;
+    return TG_OK;
+}
+
+// NCCL for the bin-sharded variant comes from the library torch ships (dlopen, tg_shard_attach)
+typedef int (*tg_nccl_allreduce_t)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+static tg_nccl_allreduce_t g_nccl_allreduce = nullptr;
+
+// One MCMC step of every star of the group: begin = proposal + prologue + fused kernel, end = decision + swaps.
+static int batch_launch_step(tg_batch *b, bool begin, bool end)
+{
+    const int Ct = b->Ctot;
+    if (begin) {
+        if (b->side_rows > 0) {
+            CK(cudaEventRecord(b->ev_fork, b->stream));
+            CK(cudaStreamWaitEvent(b->side, b->ev_fork, 0));
+            tg_k_propose<<<dim3(Ct, b->side_rows), 256, b->propose_smem, b->no_side ? b->stream : b->side>>>(b->d_ps, b->d_cmap);
+            CK(cudaEventRecord(b->ev_join, b->side));
+            b->side_pending = true;
+            b->n_launch_total++;
         }
-        CK(launch_k(tg_k_propose, dim3(C, 1), dim3(256), h->propose_smem, h->stream, h->pdl && !h->timing, pa));
-        h->n_launch_total++;
-        if (learn && !fused) {       // very large Nv: the candidates read the proposed point from HBM, so they follow the propose kernel
-            CK(cudaEventRecord(h->ev_fork, h->stream));
-            CK(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+        CK(launch_k(tg_k_propose, dim3(Ct, 1), dim3(256), b->propose_smem, b->stream, b->pdl && !b->timing, (const TgProposeArgs *)b->d_pm, (const int2 *)b->d_cmap));
+        b->n_launch_total++;
+        for (tg_handle *h : b->hs) if (h->m.n_learn > 0 && !h->fused_spec) {
+            // very large Nv: the candidates read the proposed point from HBM, so they follow the propose kernel
+            CK(cudaEventRecord(b->ev_fork, b->stream));
+            CK(cudaStreamWaitEvent(b->side, b->ev_fork, 0));
             TgSpecArgs sa{h->s, h->m, h->smem_matrix, 0};
-            tg_k_spec<<<dim3(C, 2), 256, h->spec_smem, h->side>>>(sa);
-            CK(cudaEventRecord(h->ev_join, h->side));
-            h->side_pending = true;
-            h->n_launch_total++;
+            tg_k_spec<<<dim3(h->s.C, 2), 256, h->spec_smem, b->side>>>(sa);
+            CK(cudaEventRecord(b->ev_join, b->side));
+            b->side_pending = true;
+            b->n_launch_total++;
         }
-        int r = launch_eval_kernels(h, h->sp, h->sp.params, C, nullptr, false, presummed != 0, h->pdl); if (r) return r;
+        if (b->timing) {
+            if (b->ev_used >= 8192) { int r = batch_harvest_events(b); if (r) return r; }
+            cudaEventRecord(batch_next_event(b), b->stream);
+        }
+        CK(launch_k(tg_k_eval, dim3(b->units.n), dim3(TG_THREADS), b->eval_smem, b->stream, b->pdl && !b->timing, (const TgEvalArgs *)b->d_ev, (const int4 *)b->units.dev));
+        if (b->timing) cudaEventRecord(batch_next_event(b), b->stream);
+        b->n_eval_launch++; b->n_launch_total++;
+        if (b->presummed) for (tg_handle *h : b->hs) {
+            tg_k_reduce<<<h->s.C, 256, 0, b->stream>>>(h->sp.partials, h->nitems, h->sp.sums); b->n_launch_total++;
+            if (h->nccl_comm) {       // bin-sharded variant: per-chain partial sums of all shards, part of the step's graph
+                const int rc = g_nccl_allreduce(h->sp.sums, h->sp.sums, (size_t)2 * h->s.C, /*ncclDouble*/ 8, /*ncclSum*/ 0, h->nccl_comm, b->stream);
+                if (rc != 0) return fail(TG_E_CUDA, "ncclAllReduce failed (" + std::to_string(rc) + ")");
+                b->n_launch_total++;
+            }
+        }
     }
     if (end) {
-        if (h->side_pending) { CK(cudaStreamWaitEvent(h->stream, h->ev_join, 0)); h->side_pending = false; }
-        TgFinishArgs fa{h->d, h->s, h->m, h->sp.t, h->sp.partials, h->nitems, h->sp.sums, presummed, h->rec, 1};
-        CK(launch_k(tg_k_finish, dim3(C), dim3(256), 0, h->stream, h->pdl && !presummed && !h->timing, fa));
-        h->n_launch_total++;
+        if (b->side_pending) { CK(cudaStreamWaitEvent(b->stream, b->ev_join, 0)); b->side_pending = false; }
+        CK(launch_k(tg_k_finish, dim3(Ct), dim3(256), 0, b->stream, b->pdl && !b->presummed && !b->timing, (const TgFinishArgs *)b->d_fin, (const int2 *)b->d_cmap));
+        b->n_launch_total++;
     }
     CK(cudaGetLastError());
     return TG_OK;
 }
 
-static int set_ctrl(tg_handle *h, long i, long i0)
+// Capture + instantiate the graph of steps_per_graph steps (never inside a caller's timed loop: batch_refresh runs at create,
+// after a restore, and at the END of a run when the work items moved)
+static int batch_capture(tg_batch *b)
 {
-    TgCtrl c{i, i0, 0u, 0};
-    CK(cudaMemcpyAsync(h->s.ctrl, &c, sizeof(c), cudaMemcpyHostToDevice, h->stream));
+    const int G = b->steps_per_graph;
+    for (int attempt = 0; !b->graph && attempt < 2; attempt++) {
+        cudaGraph_t g = nullptr;
+        const long lt = b->n_launch_total, le = b->n_eval_launch;
+        CK(cudaStreamBeginCapture(b->stream, cudaStreamCaptureModeThreadLocal));
+        int r = TG_OK;
+        for (int q = 0; q < G && r == TG_OK; q++) r = batch_launch_step(b, true, true);
+        cudaError_t ce = cudaStreamEndCapture(b->stream, &g);
+        b->n_launch_total = lt; b->n_eval_launch = le; b->side_pending = false;
+        if (ce == cudaSuccess && r == TG_OK) ce = cudaGraphInstantiate(&b->graph, g, 0);
+        if (g) cudaGraphDestroy(g);
+        if (ce == cudaSuccess && r == TG_OK) { cudaGraphUpload(b->graph, b->stream); break; }
+        b->graph = nullptr;
+        if (!b->pdl || attempt == 1) { if (r) return r; CK(ce); }
+        cudaGetLastError();                  // a driver that cannot capture programmatic edges: same graph with full dependencies
+        b->pdl = false;
+    }
     return TG_OK;
 }
 
-static int drain_records(tg_handle *h, tg_records *rec, long done, long n)
+// Brings the group up to date with its stars: work items around freshly flagged background tiles, unit table, argument
+// records, step graph.  Cheap when nothing changed.
+static int batch_refresh(tg_batch *b)
+{
+    for (tg_handle *h : b->hs) { int r = refresh_items_if_flagged(h); if (r) return r; }
+    bool stale = false;
+    for (size_t k = 0; k < b->hs.size(); k++) stale = stale || (b->units_version[k] != b->hs[k]->items_version);
+    if (stale) { batch_drop_graph(b); int r = batch_build_units(b); if (r) return r; }
+    { int r = batch_sync_args(b); if (r) return r; }
+    if (b->use_graph && !b->timing && !b->graph) { int r = batch_capture(b); if (r) return r; }
+    return TG_OK;
+}
+
+static int batch_set_ctrl(tg_batch *b, long i, long i0)
+{
+    for (tg_handle *h : b->hs) {
+        TgCtrl c{i, i0, 0u, 0};
+        CK(cudaMemcpyAsync(h->s.ctrl, &c, sizeof(c), cudaMemcpyHostToDevice, b->stream));
+    }
+    return TG_OK;
+}
+
+static int drain_records(tg_handle *h, cudaStream_t st, tg_records *rec, long done, long n)
 {
     if (!rec || n <= 0) return TG_OK;
     const size_t C = h->s.C, Nv = h->s.Nv, E = h->s.E;
     const TgRecDev &r = h->rec;
-#define CP(dst, src, per, T) if (rec->dst) CK(cudaMemcpyAsync(rec->dst + (size_t)done * (per), r.src, (size_t)n * (per) * sizeof(T), cudaMemcpyDeviceToHost, h->stream))
+#define CP(dst, src, per, T) if (rec->dst) CK(cudaMemcpyAsync(rec->dst + (size_t)done * (per), r.src, (size_t)n * (per) * sizeof(T), cudaMemcpyDeviceToHost, st))
     CP(vars, vars, C * Nv, double); CP(logL, logL, C, double); CP(logPrior, logPrior, C, double); CP(logPost, logPost, C, double);
     CP(Pmove, Pmove, C, double); CP(moved, moved, C, unsigned char); CP(status, status, C, int);
     CP(swap_attempt, swap_attempt, E, int); CP(swap_chain0, swap_chain0, E, int); CP(swap_done, swap_done, E, int); CP(swap_Pswap, swap_Pswap, E, double);
 #undef CP
-    CK(cudaStreamSynchronize(h->stream));
     return TG_OK;
+}
+
+static int batch_launches_per_step(const tg_batch *b)
+{
+    int n = 3 + (b->side_rows > 0 ? 1 : 0);
+    for (tg_handle *h : b->hs) { if (h->m.n_learn > 0 && !h->fused_spec) n++; if (b->presummed) n += 1 + (h->nccl_comm ? 1 : 0); }
+    return n;
+}
+
+static int batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs)
+{
+    CK(cudaSetDevice(b->device));
+    { int r = batch_refresh(b); if (r) return r; }
+    long cap = b->hs[0]->rec.cap;
+    for (tg_handle *h : b->hs) cap = std::min(cap, h->rec.cap);
+    const int G = b->steps_per_graph;
+    long done = 0;
+    while (done < nsteps) {
+        const long n = std::min(nsteps - done, cap);
+        { int r = batch_set_ctrl(b, i0 + done, i0 + done); if (r) return r; }
+        long k = 0;
+        while (b->graph && b->use_graph && !b->timing && k + G <= n) {
+            CK(cudaGraphLaunch(b->graph, b->stream)); b->n_launch_total += (long)batch_launches_per_step(b) * G; b->n_eval_launch += G;
+            k += G;
+            if (!b->probed && nsteps >= 8L * G) {
+                // first steps of a long run: which background-only tiles fail their polynomial check at the proposed points is known
+                // now; without this look the rest of the call would run with those tiles inside long cheap items
+                b->probed = true;
+                CK(cudaStreamSynchronize(b->stream));
+                int r = batch_refresh(b); if (r) return r;
+            }
+        }
+        for (; k < n; k++) { int r = batch_launch_step(b, true, true); if (r) return r; }
+        for (size_t s2 = 0; s2 < b->hs.size(); s2++) { int r = drain_records(b->hs[s2], b->stream, recs ? recs[s2] : nullptr, done, n); if (r) return r; }
+        CK(cudaStreamSynchronize(b->stream));
+        done += n;
+    }
+    CK(cudaStreamSynchronize(b->stream));
+    // maintenance for the NEXT call, outside any timed loop of the caller's steps: follow the windows of the chains (scheduling
+    // only) after a long run, rebuild around flagged tiles, re-capture the graph if the grid changed
+    if (nsteps >= 64) for (tg_handle *h : b->hs) { if (h->mom_note) *(volatile int *)h->mom_note = 0; int r = build_items(h, h->sp, h->s.C); if (r) return r; }
+    return batch_refresh(b);
 }
 
 extern "C" int tg_run(tg_handle *h, long i0, long nsteps, tg_records *rec)
 {
-    if (!h || nsteps < 0) return fail(TG_E_BADARG, "tg_run: bad argument");
-    CK(cudaSetDevice(h->device));
-    if (nsteps >= 64) { if (h->mom_note) *(volatile int *)h->mom_note = 0; int r = build_items(h, h->sp, h->s.C); if (r) return r; }   // follow the windows of the chains (scheduling only)
-    else { int r = refresh_items_if_flagged(h); if (r) return r; }
-    if (h->u_sp.B != h->s.C) { int r = build_units(h, h->u_sp, h->s.C); if (r) return r; }
-    long done = 0;
-    while (done < nsteps) {
-        const long n = std::min(nsteps - done, h->rec.cap);
-        { int r = set_ctrl(h, i0 + done, i0 + done); if (r) return r; }
-        long k = 0;
-        for (int pass = 0; pass < 2 && h->use_graph && !h->timing; pass++) {
-            const int G = h->steps_per_graph;
-            for (int attempt = 0; !h->graph && n >= G && attempt < 2; attempt++) {
-                cudaGraph_t g = nullptr;
-                const long lt = h->n_launch_total, le = h->n_eval_launch;
-                CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-                int r = TG_OK;
-                for (int q = 0; q < G && r == TG_OK; q++) r = launch_step(h, true, true, 0);
-                cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
-                h->n_launch_total = lt; h->n_eval_launch = le; h->side_pending = false;
-                if (ce == cudaSuccess && r == TG_OK) ce = cudaGraphInstantiate(&h->graph, g, 0);
-                if (g) cudaGraphDestroy(g);
-                if (ce == cudaSuccess && r == TG_OK) break;
-                h->graph = nullptr;
-                if (!h->pdl || attempt == 1) { if (r) return r; CK(ce); }
-                cudaGetLastError();                  // a driver that cannot capture programmatic edges: same graph with full dependencies
-                h->pdl = false;
-            }
-            bool again = false;
-            if (h->graph) {
-                for (; k + G <= n; k += G) {
-                    CK(cudaGraphLaunch(h->graph, h->stream)); h->n_launch_total += ((h->m.n_learn > 0 || (h->tri_smem && !h->no_split)) ? 4L : 3L) * G; h->n_eval_launch += G;
-                    if (h->mom_note && !h->mom_probed) {
-                        // first steps of this handle: which background-only tiles fail their polynomial check is known now; without
-                        // this look the rest of the call would run with those tiles inside long cheap items (2x slower launches)
-                        h->mom_probed = true;
-                        CK(cudaStreamSynchronize(h->stream));
-                        if (*(volatile int *)h->mom_note) {
-                            int r = refresh_items_if_flagged(h); if (r) return r;
-                            if (h->u_sp.B != h->s.C) { r = build_units(h, h->u_sp, h->s.C); if (r) return r; }
-                            if (!h->graph) { k += G; again = true; break; }
-                        }
-                    }
-                }
-            }
-            if (!again) break;
-        }
-        for (; k < n; k++) { int r = launch_step(h, true, true, 0); if (r) return r; }
-        { int r = drain_records(h, rec, done, n); if (r) return r; }
-        done += n;
-    }
-    CK(cudaStreamSynchronize(h->stream));
-    return TG_OK;
+    if (!h || nsteps < 0 || !h->self) return fail(TG_E_BADARG, "tg_run: bad argument");
+    tg_records *recs[1] = {rec};
+    return batch_run(h->self, i0, nsteps, recs);
 }
 
+extern "C" int tg_batch_create(tg_handle **handles, int n, tg_batch **out)
+{
+    if (out) *out = nullptr;
+    tg_batch *b = nullptr;
+    int r = batch_create(handles, n, &b); if (r) return r;
+    r = batch_refresh(b);
+    if (r) { const std::string keep = g_err; batch_destroy(b); g_err = keep; return r; }
+    *out = b;
+    return TG_OK;
+}
+extern "C" int tg_batch_destroy(tg_batch *b) { return batch_destroy(b); }
+extern "C" int tg_batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs)
+{
+    if (!b || nsteps < 0) return fail(TG_E_BADARG, "tg_batch_run: bad argument");
+    return batch_run(b, i0, nsteps, recs);
+}
+extern "C" int tg_batch_sizes(tg_batch *b, int *nstars, int *Ctot, int *units)
+{
+    if (!b) return fail(TG_E_BADARG, "null batch");
+    if (nstars) *nstars = (int)b->hs.size(); if (Ctot) *Ctot = b->Ctot; if (units) *units = b->units.n;
+    return TG_OK;
+}
+static int batch_kernel_time(tg_batch *b, int reset, long *launches, double *ms_eval, long *total_launches)
+{
+    CK(cudaSetDevice(b->device));
+    { int r = batch_harvest_events(b); if (r) return r; }
+    if (launches) *launches = b->n_eval_launch;
+    if (ms_eval) *ms_eval = b->ms_eval;
+    if (total_launches) *total_launches = b->n_launch_total;
+    if (reset == 1) { b->n_eval_launch = 0; b->ms_eval = 0; b->n_launch_total = 0; b->timing = true; }
+    if (reset == 2) { b->n_eval_launch = 0; b->ms_eval = 0; b->n_launch_total = 0; b->timing = false; return batch_refresh(b); }
+    return TG_OK;
+}
+extern "C" int tg_batch_kernel_time(tg_batch *b, int reset, long *launches, double *ms_eval, long *total_launches)
+{
+    if (!b) return fail(TG_E_BADARG, "null batch");
+    return batch_kernel_time(b, reset, launches, ms_eval, total_launches);
+}
+// device-side stopwatch on the group's stream: which = 0 start, 1 stop (then the elapsed time is read with tg_event_elapsed_ms of the first star)
+extern "C" int tg_batch_event_record(tg_batch *b, int which)
+{
+    if (!b) return fail(TG_E_BADARG, "null batch");
+    return tg_event_record(b->hs[0], which);
+}
+
+// Bin-sharded variant, host-driven form: the caller all-reduces the partial sums between the two halves of a step
 extern "C" int tg_step_begin(tg_handle *h, long i)
 {
-    if (!h) return fail(TG_E_BADARG, "null handle");
+    if (!h || !h->self) return fail(TG_E_BADARG, "null handle");
     CK(cudaSetDevice(h->device));
-    { int r = refresh_items_if_flagged(h); if (r) return r; }
-    if (h->u_sp.B != h->s.C) { int r = build_units(h, h->u_sp, h->s.C); if (r) return r; }
-    { int r = set_ctrl(h, i, i); if (r) return r; }
-    return launch_step(h, true, false, 1);
+    tg_batch *b = h->self;
+    if (!b->presummed) { b->presummed = 1; batch_drop_graph(b); }
+    { int r = batch_refresh(b); if (r) return r; }
+    { int r = batch_set_ctrl(b, i, i); if (r) return r; }
+    return batch_launch_step(b, true, false);
 }
 extern "C" int tg_step_end(tg_handle *h, long i)
 {
     (void)i;
-    if (!h) return fail(TG_E_BADARG, "null handle");
+    if (!h || !h->self) return fail(TG_E_BADARG, "null handle");
     CK(cudaSetDevice(h->device));
-    return launch_step(h, false, true, 1);
+    return batch_launch_step(h->self, false, true);
 }
 extern "C" int tg_shard_install_current(tg_handle *h)
 {
@@ -964,11 +1272,28 @@ extern "C" int tg_kernel_time(tg_handle *h, int reset, long *launches, double *m
     if (!h) return fail(TG_E_BADARG, "null handle");
     CK(cudaSetDevice(h->device));
     { int r = harvest_events(h); if (r) return r; }
-    if (launches) *launches = h->n_eval_launch;
-    if (ms_eval) *ms_eval = h->ms_eval;
-    if (total_launches) *total_launches = h->n_launch_total;
+    long bl = 0, bt = 0; double bms = 0;
+    if (h->self) { int r = batch_kernel_time(h->self, 0, &bl, &bms, &bt); if (r) return r; }
+    if (launches) *launches = h->n_eval_launch + bl;
+    if (ms_eval) *ms_eval = h->ms_eval + bms;
+    if (total_launches) *total_launches = h->n_launch_total + bt;
     if (reset == 1) { h->n_eval_launch = 0; h->ms_eval = 0; h->n_launch_total = 0; h->timing = true; }
     if (reset == 2) { h->n_eval_launch = 0; h->ms_eval = 0; h->n_launch_total = 0; h->timing = false; }
+    if (reset && h->self) return batch_kernel_time(h->self, reset, nullptr, nullptr, nullptr);
+    return TG_OK;
+}
+
+extern "C" int tg_work_profile(tg_handle *h, long *bins_direct, long *moment_tiles, int *units)
+{
+    if (!h) return fail(TG_E_BADARG, "null handle");
+    long bd = 0, mt = 0;
+    for (const int4 &it : h->items_host) {
+        if (it.w == 2) mt += it.y / std::max(1, h->mom_sub);
+        else bd += std::min<long>((long)it.y * TG_THREADS * 4, (long)h->d.Nx - it.x);
+    }
+    if (bins_direct) *bins_direct = bd;
+    if (moment_tiles) *moment_tiles = mt;
+    if (units) *units = h->self ? h->self->units.n : 0;
     return TG_OK;
 }
 

@@ -25,6 +25,8 @@ struct TgMala {
     long   dN_mixing;
     unsigned long long seed;
     int    flags;
+    int    chain0, ens0;   // offsets of the chain / ensemble indices in the Philox counters (tg_problem.philox_chain0 / philox_ensemble0)
+    int    pad_;
 };
 
 struct TgCtrl {            // lives in device memory so that a captured CUDA graph can be replayed
@@ -49,6 +51,7 @@ struct TgState {
     int    *live;                          // [C]  live slot 0..2
     int    *chol_fail;                     // [3][C]
     int    *sticky_status;                 // [C]
+    unsigned int *ens_ticket;              // [E]  CTA completion counters of the finish kernel, one per ensemble
     const int    *index_to_relax;          // [Nv]
     const double *Tcoefs;                  // [C]
     TgCtrl *ctrl;

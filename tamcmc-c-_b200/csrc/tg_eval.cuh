@@ -40,7 +40,6 @@ struct TgEvalArgs {
     const double *x, *y, *lnx, *sig;   // [Nx]; sig may be NULL
     double2      *partials;            // [B][nitems]  (sum y/m + slow-path logs , ln of the product of m)  or (sum chi2 , 0)
     double       *model;               // [B][Nx] or NULL
-    const int4   *units;               // [grid] work units in launch order: (first bin, sub-tiles | chains << 16, first chain, item)
     int           B, nitems, max_group;  // nitems: items (bin runs) = partial sums per chain; max_group: chains per unit at most
     int           list_cap;            // capacity (components) of one chain's list in shared memory, multiple of 4
     const double *mom;                 // [Nx / mom_bins][2][TG_MD] Chebyshev moments of the data over aligned tiles (tg_moment_tiles), or NULL
@@ -462,7 +461,10 @@ __device__ void tg_build_lists(const TgEvalArgs &a, const TgEvalSmem &S, int (*s
 // ONE sub-tile where truncation windows are expected (few chains per unit), long runs in the noise-only
 // parts of the spectrum (more chains per unit).  The unit table is a scheduling hint only: every sub-tile is classified again from the per-chain
 // window unions of THIS launch, so any partition of the bins gives the same results.
-__global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEvalArgs a)
+// units [grid]: work units in launch order, (first bin, sub-tiles | chains << 16, first chain, item | star << TG_UNIT_STAR_SHIFT);
+// argv [stars]: the argument record of every star the launch spans (one for a single handle).
+#define TG_UNIT_STAR_SHIFT 21
+__global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const TgEvalArgs *__restrict__ argv, const int4 *__restrict__ units)
 {
     constexpr int SUB = TG_THREADS * 4;
     constexpr int NW = TG_THREADS / 32;
@@ -475,8 +477,12 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
     __shared__ double s_lw[TG_MAXG][NW];              // moment path: sum of ln b per chain and warp
     __shared__ unsigned s_fail[32];
 
+    __shared__ __align__(16) TgEvalArgs s_args;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int4 unit = __ldg(a.units + blockIdx.x);
+    const int4 unit = __ldg(units + blockIdx.x);
+    tg_load_args(&s_args, argv + ((unsigned)unit.w >> TG_UNIT_STAR_SHIFT));
+    const TgEvalArgs &a = s_args;
+    const int item_index = unit.w & ((1 << TG_UNIT_STAR_SHIFT) - 1);
     const int2 item = make_int2(unit.x, unit.y & 0xffff);   // (first bin, number of sub-tiles)
 #ifdef TG_PROFILE
     const int dbg_id = blockIdx.x;
@@ -596,7 +602,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(TgEva
 #pragma unroll
                 for (int w = 0; w < NW; w++) t2 += s_lw[warp][w];
             }
-            a.partials[(size_t)(c0 + warp) * a.nitems + unit.w] = make_double2(sum, t2);
+            a.partials[(size_t)(c0 + warp) * a.nitems + item_index] = make_double2(sum, t2);
         }
     }
 #ifdef TG_PROFILE

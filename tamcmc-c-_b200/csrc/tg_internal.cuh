@@ -67,6 +67,18 @@ struct TgTables {
 __device__ __forceinline__ void tg_pdl_wait()    { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void tg_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// Per-star kernel arguments live in DEVICE memory, one array per kernel indexed by star (a launch may span several stars:
+// cfg5, several tempered ensembles of different spectra per GPU); a CTA copies the record of its star into shared memory.
+// The arrays are written by the host long before the launch, never by a kernel, so they may be read before tg_pdl_wait().
+template <class A> __device__ __forceinline__ void tg_load_args(A *dst, const A *src)
+{
+    static_assert(sizeof(A) % 8 == 0, "argument records are copied in 8-byte words");
+    const unsigned long long *s = (const unsigned long long *)src;
+    unsigned long long *d = (unsigned long long *)dst;
+    for (int i = threadIdx.x; i < (int)(sizeof(A) / 8); i += blockDim.x) d[i] = __ldg(s + i);
+    __syncthreads();
+}
+
 // Reciprocal: MUFU.RCP64H seed (2^-23 rel. error) + 2 Newton steps = full fp64 precision
 // (<= 1 ulp; not IEEE-exact, which the 1e-10 parity budget does not need).  Special values:
 // t=inf -> 0, t=0 -> inf, NaN -> NaN come out right because the seed is already exact there

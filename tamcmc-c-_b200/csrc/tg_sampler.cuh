@@ -41,6 +41,8 @@ struct TgProposeArgs {
     int       smem_matrix;  // TgSpecArgs.smem_matrix of those CTAs
     int       role_base;    // role of grid row 0: 0 = proposal (main stream), 1 or 3 = side-stream grid (roles 1,2 adaptation, role 3 log-prior)
     int       parts;        // role 0: TG_PRO_MODEL, or TG_PRO_MODEL | TG_PRO_PRIOR when no role-3 CTA computes the prior
+    int       nroles;       // grid rows this star uses (a launch that spans several stars has as many rows as its most demanding star)
+    int       pad_;
 };
 
 // K1, role = blockIdx.y + role_base.  Role 0, one CTA per chain: draw z, form x' = x + sqrt(sigma)*L z with
@@ -50,13 +52,20 @@ struct TgProposeArgs {
 // use next step if the proposal is rejected / accepted; role 2 recomputes x' itself (same arithmetic,
 // same bits) so that the three CTAs of a chain are independent -- the host launches roles 1 and 2 as their
 // own grid on a side stream, concurrent with role 0 and the fused kernel.
-__global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
+// grid.x = every chain of the launch; cmap[blockIdx.x] = (star, chain of that star), argv[star] = its argument record.
+__global__ void __launch_bounds__(256) tg_k_propose(const TgProposeArgs *__restrict__ argv, const int2 *__restrict__ cmap)
 {
     extern __shared__ __align__(16) double tg_dyn_smem[];
     __shared__ double s_z[512];
+    __shared__ __align__(16) TgProposeArgs s_args;
+    const int2 cm = __ldg(cmap + blockIdx.x);
+    tg_load_args(&s_args, argv + cm.x);
+    const TgProposeArgs &a = s_args;
+    if ((int)blockIdx.y >= a.nroles) return;
     const TgState &s = a.s;
-    const int c = blockIdx.x, role = blockIdx.y + a.role_base, tid = threadIdx.x, nt = blockDim.x;
+    const int c = cm.y, role = blockIdx.y + a.role_base, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
+    const uint32_t cid = (uint32_t)(c + a.m.chain0);              // chain index of the Philox counters
     tg_pdl_wait();                                                  // role 0 may be resident before the previous finish kernel is done
     if (role == 0) tg_pdl_trigger();
 #ifdef TG_PROFILE
@@ -99,7 +108,7 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
         }
         for (int v = tid; v < Nv; v += nt) {
             double z0, z1;
-            tg_normal_pair(tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)c, (uint32_t)(v >> 1)), key), &z0, &z1);
+            tg_normal_pair(tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), cid, (uint32_t)(v >> 1)), key), &z0, &z1);
             zz[v] = (v & 1) ? z1 : z0;
         }
         if (async_copy) asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -151,7 +160,7 @@ __global__ void __launch_bounds__(256) tg_k_propose(TgProposeArgs a)
         __syncthreads();
         for (int v = v0 + tid; v < Nv && v < v0 + 512; v += nt) {
             double z0, z1;
-            tg_normal_pair(tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)c, (uint32_t)(v >> 1)), key), &z0, &z1);
+            tg_normal_pair(tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), cid, (uint32_t)(v >> 1)), key), &z0, &z1);
             s_z[v - v0] = (v & 1) ? z1 : z0;
         }
         __syncthreads();
@@ -222,15 +231,20 @@ __device__ __forceinline__ void tg_write_record(const TgFinishArgs &a, long slot
     }
 }
 
-// K3: one CTA per chain: likelihood reduction -> MH accept -> Robbins-Monro update -> record;
-// the last CTA to finish performs the tempering swaps of every ensemble and advances the
-// iteration counter.
-__global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
+// K3: one CTA per chain: likelihood reduction -> MH accept -> Robbins-Monro update -> record; the last CTA of an
+// ensemble to finish performs that ensemble's tempering swap (ensembles in parallel), and the last ensemble of the star
+// advances the star's iteration counter.  grid.x = every chain of the launch (cmap / argv as in tg_k_propose).
+__global__ void __launch_bounds__(256) tg_k_finish(const TgFinishArgs *__restrict__ argv, const int2 *__restrict__ cmap)
 {
     __shared__ double2 s_part[8];
-    __shared__ int s_accept, s_last;
+    __shared__ int s_accept, s_last, s_swap;
+    __shared__ double s_sw[3];
+    __shared__ __align__(16) TgFinishArgs s_args;
+    const int2 cm = __ldg(cmap + blockIdx.x);
+    tg_load_args(&s_args, argv + cm.x);
+    const TgFinishArgs &a = s_args;
     const TgState &s = a.s;
-    const int c = blockIdx.x, tid = threadIdx.x, nt = blockDim.x;
+    const int c = cm.y, tid = threadIdx.x, nt = blockDim.x;
     const int Nv = s.Nv, Np = s.Np;
     // Every load that does not depend on the decision is issued up front: the kernel is a chain of
     // global-memory round trips, so they are kept to the unavoidable ones.
@@ -238,7 +252,7 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     // the adaptation candidates are complete by then (the fused kernel triggers after its own wait; the candidates are a full
     // dependency), so everything but the partial sums is loaded before the wait.
 #ifdef TG_PROFILE
-    if (tid == 0 && c == 0) tg_dbg_tl[2] = globaltimer_ns();
+    if (tid == 0 && blockIdx.x == 0) tg_dbg_tl[2] = globaltimer_ns();
 #endif
     const long it = s.ctrl->i;
     const bool small = (Nv <= 256 && Np <= 256);   // one element of the proposed point per thread, held in registers
@@ -254,7 +268,7 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     tg_pdl_wait();
     tg_pdl_trigger();
 #ifdef TG_PROFILE
-    if (tid == 0 && c == 0) tg_dbg_tl[3] = globaltimer_ns();
+    if (tid == 0 && blockIdx.x == 0) tg_dbg_tl[3] = globaltimer_ns();
 #endif
     if (tid == 0) {                                                 // products of the side-stream CTAs: only after the wait
         st |= a.t.pstatus[c]; logPr = a.t.logprior[c];
@@ -274,7 +288,7 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
         else if (logPo == -CUDART_INF) r = 0.0;
         else { r = exp(logPo - logPo_cur); r = (r < 1.0) ? r : 1.0; if (r != r) r = 0.0; }   // NaN ratio: reference is fatal (:504-506); reject here
         const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_MH, (uint32_t)(a.m.seed >> 32));
-        const uint4 rn = tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)c, 0u), key);
+        const uint4 rn = tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)(c + a.m.chain0), 0u), key);
         const double u = tg_u01(rn.x, rn.y);
         const int acc = (u <= r);
         s_accept = acc;
@@ -305,68 +319,75 @@ __global__ void __launch_bounds__(256) tg_k_finish(TgFinishArgs a)
     __syncthreads();
     if (a.record) tg_write_record(a, slot, c, -1, tid, nt);
 
-    // 4. last CTA: tempering swaps (MALA.cpp:381-445, :676-692), then advance the iteration
+    // 4. last CTA of the ensemble: its tempering swap (MALA.cpp:381-445, :676-692)
+    const int e = c / s.Ce;
     __threadfence();
     __syncthreads();
-    if (tid == 0) { const unsigned t = atomicAdd(&s.ctrl->ticket, 1u); s_last = (t == (unsigned)(s.C - 1)); }
+    if (tid == 0) { const unsigned t = atomicAdd(s.ens_ticket + e, 1u); s_last = (t == (unsigned)(s.Ce - 1)); }
     __syncthreads();
     if (!s_last) return;
     __threadfence();
     const int attempt = (a.m.dN_mixing > 0) && (it % a.m.dN_mixing == 0) && (it != 0) && (s.Ce >= 2);
     const bool rec_ok = a.record && slot >= 0 && slot < a.rec.cap;
+    const size_t re = (size_t)(rec_ok ? slot : 0) * s.E + e;
     if (!attempt) {
-        if (rec_ok) for (int e = tid; e < s.E; e += nt) {
-            const size_t re = (size_t)slot * s.E + e;
-            a.rec.swap_attempt[re] = 0; a.rec.swap_chain0[re] = -1; a.rec.swap_Pswap[re] = 0.0; a.rec.swap_done[re] = 0;
-        }
+        if (rec_ok && tid == 0) { a.rec.swap_attempt[re] = 0; a.rec.swap_chain0[re] = -1; a.rec.swap_Pswap[re] = 0.0; a.rec.swap_done[re] = 0; }
     } else {
-        // whole CTA per ensemble; every thread takes the (same) decision from the same loads, and the two rows
-        // that may be exchanged are fetched in the same round trip as the likelihoods (values written by
-        // other CTAs: read through L2)
+        // The pair is a function of the counter alone, so every thread knows it and fetches its elements of the two rows in the
+        // same round trip in which thread 0 fetches the likelihoods (values written by other CTAs: read through L2).  ONE thread
+        // takes the decision and publishes it through shared memory: nobody re-reads a likelihood that thread 0 may already have
+        // overwritten.
         const uint2 key = make_uint2((uint32_t)a.m.seed ^ TG_TAG_PT, (uint32_t)(a.m.seed >> 32));
-        for (int e = 0; e < s.E; e++) {
-            const uint4 rn = tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)e, 0u), key);
-            const int A = (int)(rn.z % (uint32_t)(s.Ce - 1));
-            const int gA = e * s.Ce + A, gB = gA + 1;
+        const uint4 rn = tg_philox(make_uint4((uint32_t)it, (uint32_t)(it >> 32), (uint32_t)(e + a.m.ens0), 0u), key);
+        const int A = (int)(rn.z % (uint32_t)(s.Ce - 1));
+        const int gA = e * s.Ce + A, gB = gA + 1;
+        double va = 0, vb = 0, pa = 0, pb = 0;
+        if (small) {
+            if (tid < Nv) { va = __ldcg(s.vars_cur + (size_t)gA * Nv + tid); vb = __ldcg(s.vars_cur + (size_t)gB * Nv + tid); }
+            if (tid < Np) { pa = __ldcg(s.params_cur + (size_t)gA * Np + tid); pb = __ldcg(s.params_cur + (size_t)gB * Np + tid); }
+        }
+        if (tid == 0) {
             const double TA = s.Tcoefs[gA], TB = s.Tcoefs[gB];
             const double LA = __ldcg(s.logL_cur + gA), LB = __ldcg(s.logL_cur + gB);
-            double va = 0, vb = 0, pa = 0, pb = 0;
-            if (small) {
-                if (tid < Nv) { va = __ldcg(s.vars_cur + (size_t)gA * Nv + tid); vb = __ldcg(s.vars_cur + (size_t)gB * Nv + tid); }
-                if (tid < Np) { pa = __ldcg(s.params_cur + (size_t)gA * Np + tid); pb = __ldcg(s.params_cur + (size_t)gB * Np + tid); }
-            }
             const double LA_TB = LA * TA / TB, LB_TA = LB * TB / TA;
             double rT = exp(LA_TB + LB_TA - LA - LB); rT = (rT < 1.0) ? rT : 1.0;
             const double u = tg_u01(rn.x, rn.y);
-            const int doswap = (u <= rT);
-            if (doswap) {
-                if (tid == 0) {
-                    const double prA = __ldcg(s.logPrior_cur + gA), prB = __ldcg(s.logPrior_cur + gB);
-                    s.logL_cur[gA] = LB_TA; s.logPrior_cur[gA] = prB; s.logPost_cur[gA] = LB_TA + prB;
-                    s.logL_cur[gB] = LA_TB; s.logPrior_cur[gB] = prA;
-                    // Q8: the reference adds logPrior[ind_A] AFTER it was overwritten with B's prior (MALA.cpp:417,:428)
-                    s.logPost_cur[gB] = LA_TB + ((a.m.flags & TG_F_FIX_SWAP_BOOKKEEPING) ? prA : prB);
-                    const int mv = __ldcg(s.moved + gA); s.moved[gA] = __ldcg(s.moved + gB); s.moved[gB] = mv;
-                    const double pm = __ldcg(s.Pmove + gA); s.Pmove[gA] = __ldcg(s.Pmove + gB); s.Pmove[gB] = pm;
-                }
-                if (small) {
-                    if (tid < Nv) { s.vars_cur[(size_t)gA * Nv + tid] = vb; s.vars_cur[(size_t)gB * Nv + tid] = va; }
-                    if (tid < Np) { s.params_cur[(size_t)gA * Np + tid] = pb; s.params_cur[(size_t)gB * Np + tid] = pa; }
-                } else {
-                    for (int v = tid; v < Nv; v += nt) { const double t = __ldcg(s.vars_cur + (size_t)gA * Nv + v); s.vars_cur[(size_t)gA * Nv + v] = __ldcg(s.vars_cur + (size_t)gB * Nv + v); s.vars_cur[(size_t)gB * Nv + v] = t; }
-                    for (int i = tid; i < Np; i += nt) { const double t = __ldcg(s.params_cur + (size_t)gA * Np + i); s.params_cur[(size_t)gA * Np + i] = __ldcg(s.params_cur + (size_t)gB * Np + i); s.params_cur[(size_t)gB * Np + i] = t; }
-                }
-                // the records of the two chains are rewritten by the threads that hold the new values (thread v wrote element v, thread 0 the scalars)
-                if (a.record) { tg_write_record(a, slot, gA, -1, tid, nt); tg_write_record(a, slot, gB, -1, tid, nt); }
+            s_swap = (u <= rT); s_sw[0] = rT; s_sw[1] = LA_TB; s_sw[2] = LB_TA;
+        }
+        __syncthreads();
+        const int doswap = s_swap;
+        if (doswap) {
+            if (tid == 0) {
+                const double LA_TB = s_sw[1], LB_TA = s_sw[2];
+                const double prA = __ldcg(s.logPrior_cur + gA), prB = __ldcg(s.logPrior_cur + gB);
+                s.logL_cur[gA] = LB_TA; s.logPrior_cur[gA] = prB; s.logPost_cur[gA] = LB_TA + prB;
+                s.logL_cur[gB] = LA_TB; s.logPrior_cur[gB] = prA;
+                // Q8: the reference adds logPrior[ind_A] AFTER it was overwritten with B's prior (MALA.cpp:417,:428)
+                s.logPost_cur[gB] = LA_TB + ((a.m.flags & TG_F_FIX_SWAP_BOOKKEEPING) ? prA : prB);
+                const int mv = __ldcg(s.moved + gA); s.moved[gA] = __ldcg(s.moved + gB); s.moved[gB] = mv;
+                const double pm = __ldcg(s.Pmove + gA); s.Pmove[gA] = __ldcg(s.Pmove + gB); s.Pmove[gB] = pm;
             }
-            if (rec_ok && tid == 0) {
-                const size_t re = (size_t)slot * s.E + e;
-                a.rec.swap_attempt[re] = 1; a.rec.swap_chain0[re] = A;
-                a.rec.swap_Pswap[re] = doswap ? rT : 0.0; a.rec.swap_done[re] = doswap;
+            if (small) {
+                if (tid < Nv) { s.vars_cur[(size_t)gA * Nv + tid] = vb; s.vars_cur[(size_t)gB * Nv + tid] = va; }
+                if (tid < Np) { s.params_cur[(size_t)gA * Np + tid] = pb; s.params_cur[(size_t)gB * Np + tid] = pa; }
+            } else {
+                for (int v = tid; v < Nv; v += nt) { const double t = __ldcg(s.vars_cur + (size_t)gA * Nv + v); s.vars_cur[(size_t)gA * Nv + v] = __ldcg(s.vars_cur + (size_t)gB * Nv + v); s.vars_cur[(size_t)gB * Nv + v] = t; }
+                for (int i = tid; i < Np; i += nt) { const double t = __ldcg(s.params_cur + (size_t)gA * Np + i); s.params_cur[(size_t)gA * Np + i] = __ldcg(s.params_cur + (size_t)gB * Np + i); s.params_cur[(size_t)gB * Np + i] = t; }
             }
+            // the records of the two chains are rewritten by the threads that hold the new values (thread v wrote element v, thread 0 the scalars)
+            if (a.record) { tg_write_record(a, slot, gA, -1, tid, nt); tg_write_record(a, slot, gB, -1, tid, nt); }
+        }
+        if (rec_ok && tid == 0) {
+            a.rec.swap_attempt[re] = 1; a.rec.swap_chain0[re] = A;
+            a.rec.swap_Pswap[re] = doswap ? s_sw[0] : 0.0; a.rec.swap_done[re] = doswap;
         }
     }
-    if (tid == 0) { s.ctrl->ticket = 0u; s.ctrl->i = it + 1; }
+    // 5. the last ensemble of the star advances the iteration
+    if (tid == 0) {
+        s.ens_ticket[e] = 0u;
+        const unsigned t2 = atomicAdd(&s.ctrl->ticket, 1u);
+        if (t2 == (unsigned)(s.E - 1)) { s.ctrl->ticket = 0u; s.ctrl->i = it + 1; }
+    }
 #ifdef TG_PROFILE
     if (tid == 0) tg_dbg_tl[4] = globaltimer_ns();
 #endif

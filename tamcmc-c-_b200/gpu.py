@@ -20,7 +20,8 @@ F_FIX_SWAP_BOOKKEEPING = 1
 EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", "tg_eval_upload", "tg_eval_resident",
            "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
            "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_sync", "tg_kernel_time", "tg_set_tuning",
-           "tg_measure_fp64_peak", "tg_event_record", "tg_event_elapsed_ms"]
+           "tg_measure_fp64_peak", "tg_work_profile", "tg_event_record", "tg_event_elapsed_ms",
+           "tg_batch_create", "tg_batch_run", "tg_batch_destroy", "tg_batch_sizes", "tg_batch_kernel_time", "tg_batch_event_record"]
 # include/tamcmc_outputs.h (host code in the same library)
 EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_close", "tg_restore_read"]
 
@@ -48,6 +49,7 @@ class _Problem(C.Structure):
         ("target_acceptance", C.c_double),
         ("n_learn", C.c_int), ("Nt_learn", C.c_void_p), ("periods_learn", C.c_void_p), ("dN_mixing", C.c_long),
         ("init_err", C.c_void_p), ("seed", C.c_ulonglong), ("device", C.c_int), ("flags", C.c_int),
+        ("philox_chain0", C.c_int), ("philox_ensemble0", C.c_int),
     ]
 
 
@@ -91,6 +93,13 @@ class GpuLibrary:
         L.tg_measure_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.tg_event_record.argtypes = [C.c_void_p, C.c_int]
         L.tg_event_elapsed_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.tg_work_profile.argtypes = [C.c_void_p, C.POINTER(C.c_long), C.POINTER(C.c_long), C.POINTER(C.c_int)]
+        L.tg_batch_create.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_void_p)]
+        L.tg_batch_run.argtypes = [C.c_void_p, C.c_long, C.c_long, C.POINTER(C.POINTER(_Records))]
+        L.tg_batch_destroy.argtypes = [C.c_void_p]
+        L.tg_batch_sizes.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 3
+        L.tg_batch_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_double), C.POINTER(C.c_long)]
+        L.tg_batch_event_record.argtypes = [C.c_void_p, C.c_int]
         L.tg_out_last_error.restype = C.c_char_p
         for name in EXPORTS_OUT[1:]:
             getattr(L, name).restype = C.c_int
@@ -158,6 +167,8 @@ class MalaConfig:
     dN_mixing: int = 1
     seed: int = 12345
     flags: int = 0
+    philox_chain0: int = 0          # offsets of the chain / ensemble indices in the Philox counters (include/tamcmc_gpu.h)
+    philox_ensemble0: int = 0
 
     def tcoefs(self):
         if self.Tcoefs is not None:
@@ -204,6 +215,7 @@ class GpuModelDef:
         P.dN_mixing = m.dN_mixing
         P.init_err = _p(f64(prob.init_errors())) if prob.err_frac is not None else None
         P.seed, P.device, P.flags = m.seed, device, m.flags
+        P.philox_chain0, P.philox_ensemble0 = m.philox_chain0, m.philox_ensemble0
         self.Tcoefs = T
         h = C.c_void_p()
         self.lib.check(self.lib.lib.tg_create(C.byref(P), C.byref(h)))
@@ -331,6 +343,12 @@ class GpuModelDef:
         self.lib.check(self.lib.lib.tg_event_elapsed_ms(self.h, C.byref(ms)))
         return ms.value
 
+    def work_profile(self):
+        """(bins evaluated bin by bin, background-only moment tiles, work units) of the sampler's launches."""
+        b, m, u = C.c_long(0), C.c_long(0), C.c_int(0)
+        self.lib.check(self.lib.lib.tg_work_profile(self.h, C.byref(b), C.byref(m), C.byref(u)))
+        return b.value, m.value, u.value
+
     def kernel_time(self, reset=0):
         n, ms, tot = C.c_long(0), C.c_double(0), C.c_long(0)
         self.lib.check(self.lib.lib.tg_kernel_time(self.h, reset, C.byref(n), C.byref(ms), C.byref(tot)))
@@ -345,21 +363,26 @@ class GpuMALA:
         self.Nchains = model_current.Nmodels
         self.Tcoefs = model_current.Tcoefs
 
+    @staticmethod
+    def _records(md, nsteps, record_vars=True):
+        Cn, Nv, E = md.Nmodels, md.Nvars, md.Nensembles
+        out = dict(
+            vars=np.empty((nsteps, Cn, Nv)) if record_vars else None,
+            logL=np.empty((nsteps, Cn)), logPrior=np.empty((nsteps, Cn)), logPost=np.empty((nsteps, Cn)),
+            Pmove=np.empty((nsteps, Cn)), moved=np.empty((nsteps, Cn), dtype=np.uint8),
+            swap_attempt=np.empty((nsteps, E), dtype=np.int32), swap_chain0=np.empty((nsteps, E), dtype=np.int32),
+            swap_Pswap=np.empty((nsteps, E)), swap_done=np.empty((nsteps, E), dtype=np.int32),
+            status=np.empty((nsteps, Cn), dtype=np.int32))
+        rec = _Records(*[_p(out[k]) for k in ("vars", "logL", "logPrior", "logPost", "Pmove", "moved",
+                                               "swap_attempt", "swap_chain0", "swap_Pswap", "swap_done", "status")])
+        return out, rec
+
     def execute(self, i0, nsteps, record=True, record_vars=True):
         md = self.model
-        Cn, Nv, E = md.Nmodels, md.Nvars, md.Nensembles
         out = None
         rec = None
         if record:
-            out = dict(
-                vars=np.empty((nsteps, Cn, Nv)) if record_vars else None,
-                logL=np.empty((nsteps, Cn)), logPrior=np.empty((nsteps, Cn)), logPost=np.empty((nsteps, Cn)),
-                Pmove=np.empty((nsteps, Cn)), moved=np.empty((nsteps, Cn), dtype=np.uint8),
-                swap_attempt=np.empty((nsteps, E), dtype=np.int32), swap_chain0=np.empty((nsteps, E), dtype=np.int32),
-                swap_Pswap=np.empty((nsteps, E)), swap_done=np.empty((nsteps, E), dtype=np.int32),
-                status=np.empty((nsteps, Cn), dtype=np.int32))
-            rec = _Records(*[_p(out[k]) for k in ("vars", "logL", "logPrior", "logPost", "Pmove", "moved",
-                                                   "swap_attempt", "swap_chain0", "swap_Pswap", "swap_done", "status")])
+            out, rec = self._records(md, nsteps, record_vars)
         md.lib.check(md.lib.lib.tg_run(md.h, i0, nsteps, C.byref(rec) if rec is not None else None))
         md.refresh_from_device()
         return out
@@ -379,3 +402,60 @@ class GpuMALA:
         p, n = C.c_void_p(), C.c_int()
         self.model.lib.check(self.model.lib.lib.tg_partials_device_ptr(self.model.h, C.byref(p), C.byref(n)))
         return p.value, n.value
+
+
+class GpuBatch:
+    """Launch group of several stars on one GPU (tg_batch_*): the reference runs stars as independent processes
+    (scripts/slurm/job_array.sh:8,24, main.cpp:111-127); here every step of all of them is one proposal, one fused
+    model+likelihood and one decision launch.  ``models`` are GpuModelDef objects on the same device; they stay usable."""
+
+    def __init__(self, models):
+        self.models = list(models)
+        self.lib = self.models[0].lib
+        arr = (C.c_void_p * len(self.models))(*[m.h for m in self.models])
+        b = C.c_void_p()
+        self.lib.check(self.lib.lib.tg_batch_create(arr, len(self.models), C.byref(b)))
+        self.b = b
+
+    def close(self):
+        if getattr(self, "b", None):
+            self.lib.lib.tg_batch_destroy(self.b)
+            self.b = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sizes(self):
+        n, c, u = C.c_int(), C.c_int(), C.c_int()
+        self.lib.check(self.lib.lib.tg_batch_sizes(self.b, C.byref(n), C.byref(c), C.byref(u)))
+        return n.value, c.value, u.value
+
+    def execute(self, i0, nsteps, record=True, record_vars=True):
+        """MALA::execute for every star of the group; returns the list of per-star record dicts (or None)."""
+        outs, arr = None, None
+        if record:
+            pairs = [GpuMALA._records(m, nsteps, record_vars) for m in self.models]
+            outs = [p[0] for p in pairs]
+            self._recs = [p[1] for p in pairs]
+            arr = (C.POINTER(_Records) * len(pairs))(*[C.pointer(r) for r in self._recs])
+        self.lib.check(self.lib.lib.tg_batch_run(self.b, i0, nsteps, arr))
+        for m in self.models:
+            m.refresh_from_device()
+        return outs
+
+    def kernel_time(self, reset=0):
+        n, ms, tot = C.c_long(0), C.c_double(0), C.c_long(0)
+        self.lib.check(self.lib.lib.tg_batch_kernel_time(self.b, reset, C.byref(n), C.byref(ms), C.byref(tot)))
+        return n.value, ms.value, tot.value
+
+    def timer_start(self):
+        self.lib.check(self.lib.lib.tg_batch_event_record(self.b, 0))
+
+    def timer_stop_ms(self):
+        self.lib.check(self.lib.lib.tg_batch_event_record(self.b, 1))
+        ms = C.c_double(0)
+        self.lib.check(self.lib.lib.tg_event_elapsed_ms(self.models[0].h, C.byref(ms)))
+        return ms.value
