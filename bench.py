@@ -33,6 +33,8 @@ sys.path.insert(0, ROOT)
 C_CHAINS = 10
 NX = 1_000_000
 STEPS_PER_GRAPH = 16
+I0 = 10000          # first iteration of the bench: a run restored into its Learning phase (gamma = c0/(1+i) = 2e-4, MALA.cpp:641-652); at i = 0
+                    # gamma would be 2 and the first Robbins-Monro updates would leave an indefinite covariance
 METRIC = "tempered chain-steps/s (model_MS_Global 1M-bin spectrum, 10 chains per ensemble)"
 
 
@@ -46,7 +48,7 @@ def synth_problem(W, make_y, star=0):
 def workload_config(nv, stars_per_gpu=1):
     """config of the JSON line -- the same dict in both arms."""
     return {"workload": "cfg3 S-global: model_MS_Global_a1etaa3_HarveyLike_Classic, 106 params (%d free), Nx=1000000, C=10 chains per star, "
-                        "%d star(s) per GPU, lambda=1.7, learning on" % (nv, stars_per_gpu),
+                        "%d star(s) per GPU, lambda=1.7, learning on (iterations from %d)" % (nv, stars_per_gpu, I0),
             "step": "one MCMC iteration of every chain; the reference arm and e2e time its dominant part, generate_model (model+logL+prior) for the chains of one iteration",
             "l2": "x, y = 16 MB per launch and star (< L2) but the timed kernel is FP64-bound; no L2 flush (steady-state MCMC reuses the spectrum every step by design)",
             "per_gpu": "independent tempered ensembles (stars) per GPU, no collective"}
@@ -234,13 +236,13 @@ def main():
         """warm-up, then `steps` steps timed on the device (CUDA events on the group's stream), max over ranks."""
         md0 = mds[0]
         runner = grp if grp is not None else tb.GpuMALA(md0)
-        runner.execute(0, warm, record=False)
+        runner.execute(I0, warm, record=False)
         clocks = ClockSampler(local_rank, enabled=clock_rank)
         clocks.start()
         (grp or md0).kernel_time(reset=2)
         barrier(md0)
         (grp or md0).timer_start()
-        runner.execute(warm, steps, record=False)
+        runner.execute(I0 + warm, steps, record=False)
         ms = (grp or md0).timer_stop_ms()
         barrier(md0)
         _, _, launches = (grp or md0).kernel_time(reset=0)
@@ -252,7 +254,7 @@ def main():
         # the same steps with CUDA events around every launch of the fused kernel
         (grp or md0).kernel_time(reset=1)
         Kr = min(steps, 200)
-        runner.execute(warm + steps, Kr, record=False)
+        runner.execute(I0 + warm + steps, Kr, record=False)
         n_ev, ms_ev, _ = (grp or md0).kernel_time(reset=2)
         return ms, launches, clk, ms_ev / max(n_ev, 1) * 1e-3, n_ev
 

@@ -348,7 +348,7 @@ __device__ __noinline__ double tg_background_at(const double *nz, const int *cls
 // that passes adds its two sums to the running results of the chain (lane 0's slot of S.sum, s_lw[g][warp]); a pair that
 // fails sets bit g of s_fail[tile] and is evaluated bin by bin by the caller.  No barrier inside.
 __device__ void tg_moment_tiles(const TgEvalArgs &a, const TgEvalSmem &S, const double (*s_WE)[TG_MD], const double *s_tn,
-                                double (*s_lw)[TG_THREADS / 32], unsigned *s_fail, int G, int b0, int n_mt)
+                                double (*s_lw)[TG_THREADS / 32], unsigned *s_fail, unsigned *s_flag, int G, int b0, int n_mt)
 {
     constexpr int NW = TG_THREADS / 32;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -360,14 +360,18 @@ __device__ void tg_moment_tiles(const TgEvalArgs &a, const TgEvalSmem &S, const 
         const double xm = 0.5 * (xa + xb), xh = 0.5 * (xb - xa);
         const double *mo = a.mom + TG_MOM_HDR + (size_t)(bb / mtb) * 2 * TG_MD;
         double r = 0.0, l = 0.0, mom_s = 0.0, mom_y = 0.0;
-        bool ok = (xh > 0.0);
+        bool ok = (xh > 0.0), bval = true;
         if (lane < TG_MD) { mom_s = __ldg(mo + lane); mom_y = __ldg(mo + TG_MD + lane); }
         if (lane == 0) ok = ok && (mom_s == (double)mtb);       // ST_0 = number of bins; NaN marks a tile the host could not use
         if (lane < TG_MD + TG_MCHK) {
             const double b = tg_background_at(S.nz + (size_t)g * TG_NOISE_STRIDE, S.cls + g * TG_MAXH, S.nh[g], fma(xh, s_tn[lane], xm));
-            ok = ok && (b > 0.0) && (b < 1.0e300);              // false for NaN
+            bval = (b > 0.0) && (b < 1.0e300);                  // false for NaN
+            ok = ok && bval;
             r = tg_rcp(b); l = log(b);
         }
+        // a background that is not a positive finite number at the nodes (NaN parameters of a failed proposal, ...) is no
+        // statement about the tile: it is evaluated bin by bin like any failure, but the tile is not flagged for the host
+        const bool sane = __all_sync(0xffffffffu, bval);
         const int row = (lane < TG_MD + TG_MCHK) ? lane : 0;
         double cr = 0.0, cl = 0.0;                              // lanes 0..8: coefficients; lanes 9..13: interpolants at the check points
 #pragma unroll
@@ -384,7 +388,7 @@ __device__ void tg_moment_tiles(const TgEvalArgs &a, const TgEvalSmem &S, const 
         const bool all_ok = __all_sync(0xffffffffu, ok);
         if (lane == 0) {
             if (all_ok) { S.sum[g * TG_THREADS + tid] += ps; s_lw[g][warp] += pl; }
-            else atomicOr(s_fail + mt, 1u << g);
+            else { atomicOr(s_fail + mt, 1u << g); if (sane) atomicOr(s_flag + mt, 1u << g); }
         }
     }
 }
@@ -475,7 +479,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
     __shared__ double s_WE[TG_MD + TG_MCHK][TG_MD];   // moment path: node values -> coefficients / check interpolants
     __shared__ double s_tn[TG_MD + TG_MCHK];
     __shared__ double s_lw[TG_MAXG][NW];              // moment path: sum of ln b per chain and warp
-    __shared__ unsigned s_fail[32];
+    __shared__ unsigned s_fail[32], s_flag[32];       // moment path: chains that take the tile bin by bin / that flag it for the host
 
     __shared__ __align__(16) TgEvalArgs s_args;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -538,18 +542,18 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
                 while (n_mt < 32 && sub + (n_mt + 1) * a.mom_sub <= item.y && b0 + (n_mt + 1) * mtb <= Nx && !(wlo < b0 + (n_mt + 1) * mtb && whi > b0 + n_mt * mtb)) n_mt++;
             if (n_mt > 0) {
                 __syncthreads();                  // s_fail of the previous round has been read
-                if (tid < 32) s_fail[tid] = 0u;
+                if (tid < 32) { s_fail[tid] = 0u; s_flag[tid] = 0u; }
                 if (!we_loaded) {                 // constants of the spectrum, not of the step
                     if (tid < (TG_MD + TG_MCHK) * TG_MD) (&s_WE[0][0])[tid] = a.mom[tid];
                     if (tid < TG_MD + TG_MCHK) s_tn[tid] = a.mom[(TG_MD + TG_MCHK) * TG_MD + tid];
                     we_loaded = true;
                 }
                 __syncthreads();
-                tg_moment_tiles(a, S, s_WE, s_tn, s_lw, s_fail, G, b0, n_mt);
+                tg_moment_tiles(a, S, s_WE, s_tn, s_lw, s_fail, s_flag, G, b0, n_mt);
                 __syncthreads();
                 for (int t = 0; t < n_mt; t++) {
                     const unsigned fm = s_fail[t];
-                    if (fm && tid == 0 && atomicExch(a.mom_fail + b0 / mtb + t, 1) == 0) *(volatile int *)a.mom_note = 1;
+                    if (s_flag[t] && tid == 0 && atomicExch(a.mom_fail + b0 / mtb + t, 1) == 0) *(volatile int *)a.mom_note = 1;
                     if (fm) for (int s2 = 0; s2 < a.mom_sub; s2++) tg_chain_loop<4, false, false>(a, S, s_tot, G, c0, b0 + (t * a.mom_sub + s2) * SUB, tid, fm);
                 }
                 sub += n_mt * a.mom_sub;

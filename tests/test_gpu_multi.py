@@ -166,17 +166,28 @@ def test_ensemble_of_a_batched_handle_equals_a_single_ensemble_handle(tb, W, ora
     big.close()
 
 
-def test_multi_ensemble_resume_is_bit_exact(tb, W, oracle):
+def test_multi_ensemble_resume(tb, W, oracle):
+    """Resume of a multi-ensemble handle from (vars, mu, sigma, covarmat), the content of the restore triplet.  Like the
+    reference (model_def.cpp:104-128) the restore re-evaluates the current points, so the likelihood a swapped chain carried
+    (L*T_B/T_A, MALA.cpp:405-410) comes back as -p*sum/T_A: a last-bit difference that enters sigma through Pmove.  Every
+    decision is the same; the continuous records agree to rounding.  (With quirk Q8 replicated the resumed run would also
+    lose the stale logPosterior of swapped chains, as the reference does -- hence the flag.)"""
     Ce, E = 8, 4
     prob = _small(W, oracle, seed=5)
-    mk = lambda: tb.MalaConfig(Nchains=Ce * E, chains_per_ensemble=Ce, Nt_learn=[5, 10**6], periods_learn=[1], c0=2.0, dN_mixing=2, seed=9)
+    mk = lambda: tb.MalaConfig(Nchains=Ce * E, chains_per_ensemble=Ce, Nt_learn=[5, 10**6], periods_learn=[1], c0=2.0, dN_mixing=2, seed=9,
+                               flags=tb.gpu.F_FIX_SWAP_BOOKKEEPING)
     a = tb.GpuModelDef(prob, mk()); ra = tb.GpuMALA(a).execute(0, 90)
-    b = tb.GpuModelDef(prob, mk()); tb.GpuMALA(b).execute(0, 50)
+    b = tb.GpuModelDef(prob, mk()); rb = tb.GpuMALA(b).execute(0, 50)
+    for k in ra:
+        assert np.array_equal(ra[k][:50], rb[k], equal_nan=ra[k].dtype.kind == "f"), k      # same seed, same bits
     mu, sg, cov = b.get_proposal()
     c = tb.GpuModelDef(prob, mk()); c.set_state(vars_=b.vars, mu=mu, sigma=sg, covarmat=cov)
     rc = tb.GpuMALA(c).execute(50, 40)
-    for k in ("vars", "logL", "logPost", "moved", "swap_done", "swap_chain0", "Pmove"):
+    assert ra["swap_done"][50:].sum() > 3 and ra["moved"][50:].mean() > 0.02
+    for k in ("moved", "swap_done", "swap_chain0", "swap_attempt", "status"):
         assert np.array_equal(ra[k][50:], rc[k]), k
+    for k in ("vars", "logL", "logPrior", "logPost", "Pmove"):
+        assert np.allclose(ra[k][50:], rc[k], rtol=1e-9, atol=1e-9), k
     for m in (a, b, c):
         m.close()
 
