@@ -113,6 +113,25 @@ int tg_destroy(tg_handle *h);
 int tg_eval(tg_handle *h, const double *params, int B, const double *T,
             double *logL, double *logPrior, double *logPost, int *status, double *model);
 
+/* tg_eval for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments, meaning
+ * and results as tg_eval without the model pointer (HOST buffers in and out), but the call performs no cudaMalloc / cudaFree /
+ * cudaHostAlloc or any other allocating routine: the scratch of the fused kernel (argument record, work-unit table,
+ * per-(vector, work item) partial sums, per-vector totals) lives in ONE file-scope __device__ array of
+ * 4 KiB + TG_NOALLOC_MAX_UNITS*16 + TG_NOALLOC_MAX_PAIRS*16 + TG_NOALLOC_MAX_B*16 bytes (about 5.1 MiB) that every GPU loading
+ * the library holds until the process exits; the per-vector tables and the pinned staging buffers are the ones tg_create (or an
+ * earlier, larger tg_eval) allocated for the handle.  Limits, each rejected with TG_E_BADARG and a message naming it:
+ * B <= the vectors the handle's tables hold (Nchains of tg_create unless a larger tg_eval grew them), B <= TG_NOALLOC_MAX_B,
+ * B x work items of the spectrum <= TG_NOALLOC_MAX_PAIRS, work units of the launch <= TG_NOALLOC_MAX_UNITS.
+ * The array is shared by every call on a device and keeps the last call's contents (the call overwrites the record and the table
+ * and clears the sums it uses): calls that overlap on the GPU -- two handles on one device driven from two host threads -- race
+ * on it; calls on one handle, or serialised by the caller, do not. */
+#define TG_NOALLOC_MAX_UNITS  65536
+#define TG_NOALLOC_MAX_PAIRS  262144
+#define TG_NOALLOC_MAX_B      4096
+int tg_eval_noalloc(tg_handle *h, const double *params, int B, const double *T,
+                    double *logL, double *logPrior, double *logPost, int *status);
+
 /* Same evaluation with the parameter vectors already resident in HBM (uploaded once by
  * tg_eval_upload); nothing crosses PCIe.  Results stay on the device until tg_eval_fetch. */
 int tg_eval_upload(tg_handle *h, const double *params, int B, const double *T);

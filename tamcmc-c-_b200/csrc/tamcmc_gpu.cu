@@ -1340,3 +1340,94 @@ extern "C" int tg_event_elapsed_ms(tg_handle *h, double *ms)
     *ms = f;
     return TG_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// tg_eval_noalloc: batched generate_model for callers that may not allocate (include/tamcmc_gpu.h).  The scratch of the fused
+// kernel -- its argument record, its work-unit table, the per-(chain, item) partial sums and the per-chain totals -- lives in
+// ONE file-scope device array of fixed size instead of cudaMalloc'd buffers.  Every GPU that loads the library holds the
+// array until the process exits; every call on a device shares it and finds the previous call's contents in it.
+// ------------------------------------------------------------------------------------------
+#define TG_NA_ARGS_BYTES 4096                                   // the argument record of tg_k_eval
+static_assert(sizeof(TgEvalArgs) <= TG_NA_ARGS_BYTES, "argument record outgrew its slot of the static scratch");
+#define TG_NA_OFF_UNITS  ((size_t)TG_NA_ARGS_BYTES)
+#define TG_NA_OFF_PAIRS  (TG_NA_OFF_UNITS + (size_t)TG_NOALLOC_MAX_UNITS * sizeof(int4))
+#define TG_NA_OFF_SUMS   (TG_NA_OFF_PAIRS + (size_t)TG_NOALLOC_MAX_PAIRS * sizeof(double2))
+#define TG_NA_BYTES      (TG_NA_OFF_SUMS + (size_t)TG_NOALLOC_MAX_B * sizeof(double2))     // 4 KiB + 1 MiB + 4 MiB + 64 KiB
+static __device__ __align__(256) unsigned char tg_na_scratch[TG_NA_BYTES];
+
+// In host code `tg_na_scratch` is only the host-side stand-in of the symbol, not a device address: the address a kernel can
+// use comes from cudaGetSymbolAddress, asked once per device with that device current.
+static int na_scratch(int device, unsigned char **out)
+{
+    static unsigned char *ptr[64] = {};
+    if (device < 0 || device >= 64) return fail(TG_E_BADARG, "tg_eval_noalloc: device ordinal out of range");
+    if (!ptr[device]) {
+        CK(cudaSetDevice(device));
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, tg_na_scratch));
+        if (!p) return fail(TG_E_CUDA, "tg_eval_noalloc: cudaGetSymbolAddress returned a null address");
+        ptr[device] = (unsigned char *)p;
+    }
+    *out = ptr[device];
+    return TG_OK;
+}
+
+extern "C" int tg_eval_noalloc(tg_handle *h, const double *params, int B, const double *T,
+                               double *logL, double *logPrior, double *logPost, int *status)
+{
+    if (!h || !params || !T || B < 1) return fail(TG_E_BADARG, "tg_eval_noalloc: bad argument");
+    CK(cudaSetDevice(h->device));
+    EvalBuf &b = h->ev;
+    if (B > b.cap) return fail(TG_E_BADARG, "tg_eval_noalloc: B = " + std::to_string(B) + " parameter vectors, but this handle's tables hold " + std::to_string(b.cap) +
+                               " (tg_create sizes them for Nchains, a larger tg_eval call grows them; this entry point never allocates)");
+    if (B > TG_NOALLOC_MAX_B) return fail(TG_E_BADARG, "tg_eval_noalloc: B = " + std::to_string(B) + " exceeds TG_NOALLOC_MAX_B = " + std::to_string(TG_NOALLOC_MAX_B));
+    const int nitems = h->nitems;
+    if ((long)B * nitems > (long)TG_NOALLOC_MAX_PAIRS)
+        return fail(TG_E_BADARG, "tg_eval_noalloc: B x work items = " + std::to_string(B) + " x " + std::to_string(nitems) + " partial sums exceed the static scratch (TG_NOALLOC_MAX_PAIRS = " +
+                                 std::to_string(TG_NOALLOC_MAX_PAIRS) + "); use tg_eval");
+    std::vector<int4> units; std::vector<double> cost;              // host memory only
+    make_units(h, B, 0, units, cost);
+    if (units.size() > (size_t)TG_NOALLOC_MAX_UNITS)
+        return fail(TG_E_BADARG, "tg_eval_noalloc: " + std::to_string(units.size()) + " work units exceed the static scratch (TG_NOALLOC_MAX_UNITS = " + std::to_string(TG_NOALLOC_MAX_UNITS) + "); use tg_eval");
+    if (!h->no_order) {                                             // costliest first, like upload_units
+        std::vector<int> idx(units.size());
+        for (size_t k = 0; k < idx.size(); k++) idx[k] = (int)k;
+        std::stable_sort(idx.begin(), idx.end(), [&](int a, int b2) { return cost[a] > cost[b2]; });
+        std::vector<int4> u2(units.size());
+        for (size_t k = 0; k < idx.size(); k++) u2[k] = units[idx[k]];
+        units.swap(u2);
+    }
+    unsigned char *base = nullptr;
+    { int r = na_scratch(h->device, &base); if (r) return r; }
+    TgEvalArgs *d_args = (TgEvalArgs *)base;
+    int4 *d_units = (int4 *)(base + TG_NA_OFF_UNITS);
+    double2 *d_pairs = (double2 *)(base + TG_NA_OFF_PAIRS), *d_sums = (double2 *)(base + TG_NA_OFF_SUMS);
+    if (b.B != B) { CK(cudaStreamSynchronize(h->stream)); b.layout(B, h->d.Np); }
+    // inputs through the handle's pinned staging buffer (allocated by tg_create), one copy
+    memcpy(b.pin_in, params, (size_t)B * h->d.Np * 8);
+    memcpy(b.pin_in + (size_t)B * h->d.Np, T, (size_t)B * 8);
+    CK(cudaMemcpyAsync(b.in, b.pin_in, (size_t)B * (h->d.Np + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+    TgEvalArgs ea; memset(&ea, 0, sizeof(ea));
+    ea.d = h->d; ea.t = b.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = d_pairs; ea.model = nullptr;
+    ea.B = B; ea.nitems = nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
+    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note;
+    // the scratch keeps the last call's contents: the record and the table are overwritten, the partial sums start at zero
+    // (pageable sources: the runtime stages them before the call returns, so the locals may die)
+    CK(cudaMemcpyAsync(d_args, &ea, sizeof(ea), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_units, units.data(), units.size() * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemsetAsync(d_pairs, 0, (size_t)B * nitems * sizeof(double2), h->stream));
+    CK(cudaMemsetAsync(d_sums, 0, (size_t)B * sizeof(double2), h->stream));
+    TgProArgs pa{h->d, b.t, b.params, h->pri, h->sw};
+    tg_k_prologue<<<B, TG_PRO_THREADS, TG_PRO_SMEM(h->d.Np), h->stream>>>(pa);
+    tg_k_eval<<<(unsigned)units.size(), TG_THREADS, TG_EVAL_SMEM(h->chains_per_block, h->list_cap), h->stream>>>((const TgEvalArgs *)d_args, (const int4 *)d_units);
+    tg_k_reduce_finalize<<<B, 256, 0, h->stream>>>(h->d, d_pairs, nitems, d_sums, b.T, b.t, b.logL, b.logPrior, b.logPost, b.status);
+    CK(cudaGetLastError());
+    h->n_launch_total += 3; h->n_eval_launch += 1;
+    CK(cudaMemcpyAsync(b.pin_out, b.out, (size_t)B * 28, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (logL) memcpy(logL, b.pin_out, (size_t)B * 8);
+    if (logPrior) memcpy(logPrior, b.pin_out + B, (size_t)B * 8);
+    if (logPost) memcpy(logPost, b.pin_out + 2 * (size_t)B, (size_t)B * 8);
+    if (status) memcpy(status, b.pin_out + 3 * (size_t)B, (size_t)B * 4);
+    return TG_OK;
+}
