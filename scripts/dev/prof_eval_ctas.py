@@ -8,7 +8,7 @@ here = os.path.dirname(os.path.abspath(__file__))
 lib = tb.gpu.GpuLibrary(os.path.join(here, sys.argv[1] if len(sys.argv) > 1 else "libtamcmc_gpu_prof.so"))
 prob = W.s_global(Nx=1000000)
 prob.y = np.abs(np.random.default_rng(1).standard_normal(prob.x.size)) + 0.1
-Cn = 10
+Cn = int(os.environ.get('TG_C', '10'))
 P, T = W.perturbed_params(prob, Cn), W.tcoefs(Cn)
 md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=Cn), lib=lib)
 tune = [int(v) for v in os.environ.get('TG_TUNE', '0,0,0').split(',')]   # chains_per_block, heavy_group, light_subtiles
@@ -16,10 +16,11 @@ md.set_tuning(chains_per_block=tune[0], heavy_group=tune[1], light_subtiles=tune
 md.eval_upload(P, T)
 for _ in range(5): md.eval_resident(Cn)
 md.sync()
+lib.lib.tg_sync(md.h)
 buf = (C.c_longlong * (8192 * 6))()
 lib.lib.tg_dbg_ctas.argtypes = [C.POINTER(C.c_longlong)]
 lib.lib.tg_dbg_ctas(buf)
-a = np.array(buf, dtype=np.int64).reshape(8192, 6); a = a[a[:, 5] > 0]; a = a[a[:, 4] >= a[:, 4].max() - 150000]   # last launch only
+a = np.array(buf, dtype=np.int64).reshape(8192, 6); a = a[a[:, 5] > 0]; a = a[a[:, 4] >= a[:, 4].max() - 2000000]   # last launch only
 t0, t1, t2 = a[:, 0], a[:, 1], a[:, 2]
 sm = a[:, 3] >> 32; tile = a[:, 3] & 0xffffffff
 g0, g1 = a[:, 4], a[:, 5]
@@ -55,3 +56,20 @@ slots_busy = dur.sum() / (148 * 2)
 print("sum of CTA durations / 296 slots = %.1f us  (efficiency vs span %.3f)" % (slots_busy, slots_busy / end.max()))
 # idle tail per SM: span - finish time of the SM
 print("idle tail per SM us: mean %.2f max %.2f" % ((end.max() - last).mean(), (end.max() - last).max()))
+# far-field path: where a heavy unit's time goes, and how much of the list is still evaluated exactly
+try:
+    fb = (C.c_longlong * (8192 * 4))()
+    lib.lib.tg_dbg_ffstats.argtypes = [C.POINTER(C.c_longlong)]
+    lib.lib.tg_dbg_ffstats(fb)
+    ffs = np.array(fb, dtype=np.int64).reshape(8192, 4)
+    full = np.array(buf, dtype=np.int64).reshape(8192, 6)
+    ok = (full[:, 5] > 0) & (ffs[:, 3] > 0)
+    hv = ffs[ok]; dd = (full[ok, 5] - full[ok, 4]) / 1e3
+    alld = (full[full[:, 5] > 0, 5] - full[full[:, 5] > 0, 4]) / 1e3
+    oth = (full[:, 5] > 0) & (ffs[:, 3] == 0)
+    do = (full[oth, 5] - full[oth, 4]) / 1e3
+    print("slot time: far-field units %.0f us in %d units, other units %.0f us in %d units (mean %.2f, max %.2f)" % (dd.sum(), ok.sum(), do.sum(), oth.sum(), do.mean() if oth.sum() else 0, do.max() if oth.sum() else 0))
+    print("far-field units: %d, duration mean %.2f us; lists %.2f us, ff set-up %.2f us; exact (quad, micro-tile) pairs %.1f of %.1f per unit (%.1f %%)" % (
+        ok.sum(), dd.mean(), hv[:, 0].mean() / f, hv[:, 1].mean() / f, hv[:, 2].mean(), hv[:, 3].mean(), 100.0 * hv[:, 2].sum() / hv[:, 3].sum()))
+except Exception as e:
+    print("no far-field stats:", e)

@@ -111,6 +111,6 @@ def write_model_file(path, modes, ranges, model_fullname, Dnu, C_l=0.0, noise=((
         f.write("   Splitting_a1   Uniform   %.6f   0.0   %.6f\n   Asphericity_eta   Fix_Auto   1.0\n   Splitting_a3   Fix   0.0\n   Asymetry   Fix   0.0\n" % (a1, max(3.0 * a1, 1.5)))
         f.write("   Inclination   Uniform   %.6f   0.0   90.0\n" % inclination)
         f.write("   Visibility_l1   Gaussian   1.5   1.5   0.15\n   Visibility_l2   Gaussian   0.53   0.53   0.05\n   Visibility_l3   Gaussian   0.08   0.08   0.02\n")
-        f.write("   Height   %s   %.6f   %.6f   %.6f\n   Width   Fix_Auto   1.0\n" % height_prior)
+        f.write("   Height   %s   %s\n   Width   Fix_Auto   1.0\n" % (height_prior[0], "   ".join("%.6f" % v for v in height_prior[1:])))
         for line in extra_common:
             f.write("   %s\n" % line)

@@ -51,6 +51,7 @@ struct tg_handle {
     TgRecDev   rec{};
     double    *x = nullptr, *y = nullptr, *lnx = nullptr, *sig = nullptr;
     double    *mom = nullptr; int mom_sub = 4, mom_run = 16; int *mom_fail = nullptr; long n_mom_tiles = 0;
+    double    *ffw = nullptr; double ff_r2 = 30.25;    // far-field path of the fused kernel (tg_ff_setup): matrix + nodes, (pole distance / half-width)^2 from which a component is far
     int        hybrid_pct = 0, hybrid_group = 2;
     int       *mom_note = nullptr;                      // pinned, mapped: the kernel stores 1 when it flags a tile for the first time          // Chebyshev moments of the data over aligned tiles (tg_eval.cuh), NULL = off
     double    *pri = nullptr; int *sw = nullptr;
@@ -98,7 +99,8 @@ struct tg_batch {
     int          side_rows = 0; size_t propose_smem = 0, eval_smem = 0;
     tg_handle::UnitTable units;            // work units of the fused kernel over all stars, costliest first
     std::vector<long> units_version;       // items_version of every star the table was built from
-    cudaGraphExec_t graph = nullptr;
+    cudaGraphExec_t graph = nullptr;       // steps_per_graph steps
+    cudaGraphExec_t graph_small[2] = {nullptr, nullptr};   // 4 steps and 1 step: the remainder of a call is replayed too, never launched kernel by kernel
     bool         probed = false;           // the look at the flagged background tiles after the first graph of a long run
     // eval-kernel timing
     bool         timing = false;
@@ -137,6 +139,7 @@ extern "C" const char *tg_last_error(void) { return g_err.c_str(); }
 extern "C" int tg_version(void) { return 100; }
 #ifdef TG_PROFILE
 extern "C" int tg_dbg_ctas(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_cta, sizeof(long long) * TG_DBG_CTAS * 6) == cudaSuccess ? 0 : -2; }
+extern "C" int tg_dbg_ffstats(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_ff, sizeof(long long) * TG_DBG_CTAS * 4) == cudaSuccess ? 0 : -2; }
 extern "C" int tg_dbg_timeline(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_tl, sizeof(long long) * 8) == cudaSuccess ? 0 : -2; }
 extern "C" int tg_dbg_specs(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_spec, sizeof(long long) * 16) == cudaSuccess ? 0 : -2; }
 extern "C" int tg_dbg_clocks(long long *out) { return cudaMemcpyFromSymbol(out, tg_dbg_clk, sizeof(long long) * 32) == cudaSuccess ? 0 : -2; }
@@ -259,7 +262,7 @@ static int sync_eval_args(tg_handle *h, EvalBuf &b, double *model, int B)
     TgEvalArgs ea; memset(&ea, 0, sizeof(ea));
     ea.d = h->d; ea.t = b.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = b.partials; ea.model = model;
     ea.B = B; ea.nitems = h->nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
-    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note;
+    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ffw = h->ffw; ea.ff_r2 = h->ff_r2;
     if (b.d_args && b.args_valid && memcmp(&ea, &b.h_args, sizeof(ea)) == 0) return TG_OK;
     if (!b.d_args) DA(b.d_args, 1);
     memcpy(&b.h_args, &ea, sizeof(ea));
@@ -540,6 +543,21 @@ static int create_impl(const tg_problem *p, tg_handle *h)
             *h->mom_note = 0;
         }
     }
+    {   // far-field path under the truncation windows (TG_FARFIELD=0 turns it off): needs abscissae that increase
+        const char *e = getenv("TG_FARFIELD");
+        bool inc = true;
+        for (size_t i = 1; i < Nx && inc; i++) inc = p->x[i] > p->x[i - 1];
+        if (e && atoi(e) == 1 && inc && p->model_case >= 2) {      // experimental in this commit: opt-in
+            if (const char *e2 = getenv("TG_FF_R2")) h->ff_r2 = std::max(4.0, atof(e2));
+            std::vector<double> w((size_t)TG_FF_HDR);
+            const long double pi = 3.141592653589793238462643383279502884L;
+            for (int k = 0; k < TG_FF_N; k++) for (int i = 0; i < TG_FF_N; i++)
+                w[(size_t)k * TG_FF_N + i] = (double)((k == 0 ? 1.0L : 2.0L) / TG_FF_N * cosl(pi * k * (i + 0.5L) / TG_FF_N));
+            for (int i = 0; i < TG_FF_N; i++) w[(size_t)TG_FF_N * TG_FF_N + i] = (double)cosl(pi * (i + 0.5L) / TG_FF_N);
+            DA(h->ffw, w.size());
+            CK(cudaMemcpy(h->ffw, w.data(), w.size() * 8, cudaMemcpyHostToDevice));
+        }
+    }
     DA(h->pri, (size_t)4 * p->Np); DA(h->sw, p->Np); DA(h->index_to_relax, d.Nv); DA(h->Tcoefs, p->Nchains);
     CK(cudaMemcpyAsync(h->pri, p->priors, (size_t)4 * p->Np * 8, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->sw, p->priors_switch, (size_t)p->Np * 4, cudaMemcpyHostToDevice, h->stream));
@@ -570,7 +588,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         // where truncation windows lie: items of two sub-tiles (taken 8 bins per thread); one chain per unit for a single
         // ensemble (more, smaller units: better tail of the grid), three when many chains fill the GPU anyway (measured with the
         // background-only tiles on the moment path: one chain per unit is best up to ~100 chains, 3.9 vs 4.0 us per chain at 80)
-        h->heavy_sub = 2;
+        h->heavy_sub = h->ffw ? 2 * TG_FF_MAXP : 2;       // far-field path: up to four pairs share one list and one set-up
         h->heavy_group = (C >= 128) ? 3 : 1;
         // a spectrum so short that pairs of sub-tiles would not even fill the GPU once (S-local: 10k bins, 10 chains): single
         // sub-tiles, twice the units (25.7 vs 29.9 us per step there)
@@ -885,6 +903,7 @@ extern "C" int tg_set_state(tg_handle *h, const double *vars, const double *mu, 
 static void batch_drop_graph(tg_batch *b)
 {
     if (b->graph) { cudaGraphExecDestroy(b->graph); b->graph = nullptr; }
+    for (int k = 0; k < 2; k++) if (b->graph_small[k]) { cudaGraphExecDestroy(b->graph_small[k]); b->graph_small[k] = nullptr; }
 }
 
 static cudaEvent_t batch_next_event(tg_batch *b)
@@ -977,7 +996,7 @@ static int batch_sync_args(tg_batch *b)
         TgEvalArgs &ea = ev[k];
         ea.d = h->d; ea.t = h->sp.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = h->sp.partials; ea.model = nullptr;
         ea.B = h->s.C; ea.nitems = h->nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
-        ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note;
+        ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ffw = h->ffw; ea.ff_r2 = h->ff_r2;
         // The adaptation candidates (Robbins-Monro + Cholesky for both outcomes of the decision) depend on the state the previous
         // finish kernel left and on nothing of this step (the CTA of the "accepted" outcome recomputes the proposed point itself),
         // and only the finish kernel needs them: they run on a side stream next to the proposal, the prologue and the fused kernel.
@@ -1073,26 +1092,37 @@ static int batch_launch_step(tg_batch *b, bool begin, bool end)
     return TG_OK;
 }
 
-// Capture + instantiate the graph of steps_per_graph steps (never inside a caller's timed loop: batch_refresh runs at create,
+// Capture + instantiate the graphs of steps_per_graph, 4 and 1 steps (never inside a caller's timed loop: batch_refresh runs at create,
 // after a restore, and at the END of a run when the work items moved)
-static int batch_capture(tg_batch *b)
+static int batch_capture_one(tg_batch *b, int nsteps, cudaGraphExec_t *out)
 {
-    const int G = b->steps_per_graph;
-    for (int attempt = 0; !b->graph && attempt < 2; attempt++) {
+    for (int attempt = 0; !*out && attempt < 2; attempt++) {
         cudaGraph_t g = nullptr;
         const long lt = b->n_launch_total, le = b->n_eval_launch;
         CK(cudaStreamBeginCapture(b->stream, cudaStreamCaptureModeThreadLocal));
         int r = TG_OK;
-        for (int q = 0; q < G && r == TG_OK; q++) r = batch_launch_step(b, true, true);
+        for (int q = 0; q < nsteps && r == TG_OK; q++) r = batch_launch_step(b, true, true);
         cudaError_t ce = cudaStreamEndCapture(b->stream, &g);
         b->n_launch_total = lt; b->n_eval_launch = le; b->side_pending = false;
-        if (ce == cudaSuccess && r == TG_OK) ce = cudaGraphInstantiate(&b->graph, g, 0);
+        if (ce == cudaSuccess && r == TG_OK) ce = cudaGraphInstantiate(out, g, 0);
         if (g) cudaGraphDestroy(g);
-        if (ce == cudaSuccess && r == TG_OK) { cudaGraphUpload(b->graph, b->stream); break; }
-        b->graph = nullptr;
+        if (ce == cudaSuccess && r == TG_OK) { cudaGraphUpload(*out, b->stream); break; }
+        *out = nullptr;
         if (!b->pdl || attempt == 1) { if (r) return r; CK(ce); }
-        cudaGetLastError();                  // a driver that cannot capture programmatic edges: same graph with full dependencies
+        cudaGetLastError();                  // a driver that cannot capture programmatic edges: the same graphs with full dependencies
         b->pdl = false;
+        batch_drop_graph(b);                 // (the ones captured so far carry programmatic edges; batch_capture takes a second pass)
+    }
+    return TG_OK;
+}
+static const int TG_SMALL_GRAPH[2] = {4, 1};
+static int batch_capture(tg_batch *b)
+{
+    for (int pass = 0; pass < 2; pass++) {   // a second pass if programmatic edges had to be given up half way
+        const bool pdl0 = b->pdl;
+        if (!b->graph) { int r = batch_capture_one(b, b->steps_per_graph, &b->graph); if (r) return r; }
+        for (int k = 0; k < 2; k++) if (!b->graph_small[k] && TG_SMALL_GRAPH[k] < b->steps_per_graph) { int r = batch_capture_one(b, TG_SMALL_GRAPH[k], &b->graph_small[k]); if (r) return r; }
+        if (b->pdl == pdl0) break;
     }
     return TG_OK;
 }
@@ -1160,6 +1190,13 @@ static int batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs)
                 b->probed = true;
                 CK(cudaStreamSynchronize(b->stream));
                 int r = batch_refresh(b); if (r) return r;
+            }
+        }
+        for (int q = 0; q < 2; q++) {          // the remainder: graphs of 4 steps and of 1 step
+            const int gs = TG_SMALL_GRAPH[q];
+            while (b->graph_small[q] && b->use_graph && !b->timing && k + gs <= n) {
+                CK(cudaGraphLaunch(b->graph_small[q], b->stream)); b->n_launch_total += (long)batch_launches_per_step(b) * gs; b->n_eval_launch += gs;
+                k += gs;
             }
         }
         for (; k < n; k++) { int r = batch_launch_step(b, true, true); if (r) return r; }
@@ -1410,7 +1447,7 @@ extern "C" int tg_eval_noalloc(tg_handle *h, const double *params, int B, const 
     TgEvalArgs ea; memset(&ea, 0, sizeof(ea));
     ea.d = h->d; ea.t = b.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = d_pairs; ea.model = nullptr;
     ea.B = B; ea.nitems = nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
-    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note;
+    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ffw = h->ffw; ea.ff_r2 = h->ff_r2;
     // the scratch keeps the last call's contents: the record and the table are overwritten, the partial sums start at zero
     // (pageable sources: the runtime stages them before the call returns, so the locals may die)
     CK(cudaMemcpyAsync(d_args, &ea, sizeof(ea), cudaMemcpyHostToDevice, h->stream));
