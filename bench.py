@@ -256,7 +256,8 @@ def main():
         Kr = min(steps, 200)
         runner.execute(I0 + warm + steps, Kr, record=False)
         n_ev, ms_ev, _ = (grp or md0).kernel_time(reset=2)
-        return ms, launches, clk, ms_ev / max(n_ev, 1) * 1e-3, n_ev
+        ms_ff = (grp or md0).prepass_time()        # the far-field pre-pass launches of the same steps
+        return ms, launches, clk, ms_ev / max(n_ev, 1) * 1e-3, n_ev, ms_ff / max(n_ev, 1) * 1e-3
 
     def algorithmic_work(mds):
         """F = 8 L + Nx (5 K + 5) per chain (asym == 0); executed: the background term only where bins are taken one by one."""
@@ -273,7 +274,7 @@ def main():
 
     mds, grp = build_group(S, rank * S)
     md = mds[0]
-    ms, launches, clk, t_kernel, n_ev = timed_run(mds, grp, W_run, K, clock_rank=(local_rank == 0))
+    ms, launches, clk, t_kernel, n_ev, t_pre = timed_run(mds, grp, W_run, K, clock_rank=(local_rank == 0))
     chains_gpu = S * C_star
     value = world * chains_gpu * K / (ms * 1e-3)
     F_launch, F_exec, L_mean, Kh = algorithmic_work(mds)
@@ -293,6 +294,11 @@ def main():
                 "algorithmic_flop_per_launch": F_launch, "executed_flop_per_launch": F_exec,
                 "L_component_bins_per_chain": L_mean, "K_harvey": Kh,
                 "kernel_share_of_step": t_kernel / (ms * 1e-3 / K),
+                "prepass_kernel": "tg_k_ff", "prepass_avg_launch_us": t_pre * 1e6,
+                "frac_with_prepass": F_launch / (t_kernel + t_pre) / 1e12 / peak_tflops,
+                "model_kernels_share_of_step": (t_kernel + t_pre) / (ms * 1e-3 / K),
+                "prepass_note": "tg_k_ff prepares, per chain and 256-bin micro-tile under the truncation windows, the Chebyshev interpolant of the far components and the "
+                                "records of the near ones; frac counts the fused kernel alone, frac_with_prepass the two launches that evaluate the model",
                 "peak_source": "DFMA microkernel measured in this run (MEASURED_PEAKS.json has no FP64 figure); peak_nominal = SMs x 64 lanes x 2 x max SM clock",
                 "frac_executed_note": "algorithmic flops of the work the kernel runs: the Nx(5K+5) background term only over bins taken one by one, "
                                       "14 exact background evaluations per (moment tile, chain) elsewhere",
@@ -352,12 +358,13 @@ def main():
             m_.close()
         S5 = 8
         mds5, grp5 = build_group(S5, 1000 + rank * S5)
-        ms5, launches5, _, tk5, n5 = timed_run(mds5, grp5, 2 * STEPS_PER_GRAPH, max(K, 4 * STEPS_PER_GRAPH))
+        ms5, launches5, _, tk5, n5, tp5 = timed_run(mds5, grp5, 2 * STEPS_PER_GRAPH, max(K, 4 * STEPS_PER_GRAPH))
         K5 = max(K, 4 * STEPS_PER_GRAPH)
         F5, Fx5, _, _ = algorithmic_work(mds5)
         cfg5 = {"value": world * S5 * C_CHAINS * K5 / (ms5 * 1e-3), "unit": "chain-steps/s", "stars_per_gpu": S5, "chains_per_gpu": S5 * C_CHAINS,
                 "steps": K5, "ms_per_step": ms5 / K5, "fused_kernel_us": tk5 * 1e6, "units_per_launch": grp5.sizes()[2],
                 "roofline_frac": F5 / tk5 / 1e12 / peak_tflops, "roofline_frac_executed": Fx5 / tk5 / 1e12 / peak_tflops,
+                "prepass_us": tp5 * 1e6, "roofline_frac_with_prepass": F5 / (tk5 + tp5) / 1e12 / peak_tflops,
                 "kernel_share_of_step": tk5 / (ms5 * 1e-3 / K5), "per_gpu_vs_one_star": (S5 * C_CHAINS * K5 / (ms5 * 1e-3)) / (chains_gpu * K / (ms * 1e-3)),
                 "gpu_launches": int(launches5),
                 "what": "configs[4] of BASELINE.json: 8 different synthetic stars (own spectrum, parameters, Philox key) x 10 tempered chains per GPU, "

@@ -168,6 +168,7 @@ int tg_batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs);
 int tg_batch_destroy(tg_batch *b);
 int tg_batch_sizes(tg_batch *b, int *nstars, int *Ctot, int *units);
 int tg_batch_kernel_time(tg_batch *b, int reset, long *launches, double *ms_eval, long *total_launches);
+int tg_batch_prepass_time(tg_batch *b, double *ms_ff);   /* total time of the far-field pre-pass launches timed together with tg_batch_kernel_time (reset = 1 clears it) */
 int tg_batch_event_record(tg_batch *b, int which);   /* stopwatch on the group's stream; read with tg_event_elapsed_ms(handles[0]) */
 
 /* Sizes implied by the problem. */
@@ -188,6 +189,10 @@ int tg_sync(tg_handle *h);
 /* Kernel timing of the dominant kernel (CUDA events on the handle's stream), accumulated since
  * the last reset: number of launches and total milliseconds. */
 int tg_kernel_time(tg_handle *h, int reset, long *launches, double *ms_eval, long *total_launches);
+/* The far-field pre-pass (the kernel that prepares, per chain and 256-bin micro-tile under the truncation windows, the
+ * interpolant of the far components and the records of the near ones for the fused kernel): total milliseconds of its launches
+ * in the sampler steps timed together with tg_kernel_time. */
+int tg_prepass_time(tg_handle *h, double *ms_ff);
 /* Tuning of the fused kernel (never changes results; 0 / -1 = keep): chains per work unit at most, chains per
  * unit where truncation windows are expected, sub-tiles of 1024 bins per unit in the noise-only parts of the
  * spectrum, CUDA-graph replay of tg_run. */

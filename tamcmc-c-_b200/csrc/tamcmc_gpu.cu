@@ -32,6 +32,9 @@ struct EvalBuf {                 // tables + results for a batch of B parameter 
     TgEvalArgs *d_args = nullptr;                      // the fused kernel reads its arguments from device memory (tg_load_args)
     TgEvalArgs  h_args;                                // what d_args holds
     bool        args_valid = false;
+    // far-field pre-pass (tg_farfield.cuh): coefficients, headers and exact records per (vector, micro-tile); its argument record
+    double     *ffc = nullptr; TgFFHdr *ffh = nullptr; TgFFRec *ffr = nullptr;
+    TgFFArgs   *d_ffargs = nullptr; TgFFArgs h_ffargs; bool ffargs_valid = false;
     void layout(int b, int Np) {
         B = b; params = in; T = in + (size_t)b * Np;
         logL = out; logPrior = out + b; logPost = out + 2 * (size_t)b; status = (int *)(out + 3 * (size_t)b);
@@ -51,7 +54,9 @@ struct tg_handle {
     TgRecDev   rec{};
     double    *x = nullptr, *y = nullptr, *lnx = nullptr, *sig = nullptr;
     double    *mom = nullptr; int mom_sub = 4, mom_run = 16; int *mom_fail = nullptr; long n_mom_tiles = 0;
-    double    *ffw = nullptr; double ff_r2 = 30.25;    // far-field path of the fused kernel (tg_ff_setup): matrix + nodes, (pole distance / half-width)^2 from which a component is far
+    double    *ffw = nullptr; double ff_r2 = 30.25;    // far-field path (tg_farfield.cuh): matrix + nodes, (pole distance / half-width)^2 from which a component is far
+    TgFFGeo   *ffgeo = nullptr; int ff_stride = 0;    // geometry of the micro-tiles of the spectrum; micro-tiles per vector the buffers hold
+    int        ff_mt0 = 0, ff_nmt = 0;                 // micro-tiles the pre-pass prepares: where truncation windows are expected (the heavy items)
     int        hybrid_pct = 0, hybrid_group = 2;
     int       *mom_note = nullptr;                      // pinned, mapped: the kernel stores 1 when it flags a tile for the first time          // Chebyshev moments of the data over aligned tiles (tg_eval.cuh), NULL = off
     double    *pri = nullptr; int *sw = nullptr;
@@ -94,6 +99,8 @@ struct tg_batch {
     std::vector<TgEvalArgs>    h_ev;   TgEvalArgs    *d_ev = nullptr;
     std::vector<TgProposeArgs> h_pm, h_ps; TgProposeArgs *d_pm = nullptr, *d_ps = nullptr;
     std::vector<TgFinishArgs>  h_fin;  TgFinishArgs  *d_fin = nullptr;
+    std::vector<TgFFArgs>      h_ff;   TgFFArgs      *d_ff = nullptr;   // far-field pre-pass
+    int          ff_cpc = 0; size_t ff_smem = 0;
     int2        *d_cmap = nullptr;
     bool         args_valid = false;
     int          side_rows = 0; size_t propose_smem = 0, eval_smem = 0;
@@ -102,9 +109,10 @@ struct tg_batch {
     cudaGraphExec_t graph = nullptr;       // steps_per_graph steps
     cudaGraphExec_t graph_small[2] = {nullptr, nullptr};   // 4 steps and 1 step: the remainder of a call is replayed too, never launched kernel by kernel
     bool         probed = false;           // the look at the flagged background tiles after the first graph of a long run
-    // eval-kernel timing
+    // eval-kernel timing (and, beside it, the far-field pre-pass)
     bool         timing = false;
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
+    std::vector<cudaEvent_t> ffev_pool; size_t ffev_used = 0; double ms_ff = 0;
     long         n_eval_launch = 0, n_launch_total = 0; double ms_eval = 0;
     std::vector<void *> allocs;
 };
@@ -161,6 +169,11 @@ static int alloc_evalbuf(tg_handle *h, EvalBuf &b, int B)
     DA(b.t.ncomp, B); DA(b.t.wlo, B); DA(b.t.whi, B); DA(b.t.noise, (size_t)B * TG_NOISE_STRIDE); DA(b.t.status, B); DA(b.t.pstatus, B); DA(b.t.work, B); DA(b.t.logprior, B);
     DA(b.in, (size_t)B * (h->d.Np + 1)); DA(b.out, (size_t)B * 4);
     DA(b.partials, (size_t)B * h->max_items); DA(b.sums, B);
+    if (h->ffw) {
+        const size_t n = (size_t)B * h->ff_stride;
+        DA(b.ffc, n * TG_FF_N); DA(b.ffh, n); DA(b.ffr, n * TG_FF_E);
+        b.ffargs_valid = false;
+    }
     if (b.pin_in) cudaFreeHost(b.pin_in);
     if (b.pin_out) cudaFreeHost(b.pin_out);
     CK(cudaHostAlloc((void **)&b.pin_in, (size_t)B * (h->d.Np + 1) * 8, cudaHostAllocDefault));
@@ -255,6 +268,24 @@ static int harvest_events(tg_handle *h)
 
 static int build_units(tg_handle *h, tg_handle::UnitTable &u, int B);
 
+// Far-field pre-pass of the B points held in `b`: view for the fused kernel, argument record, launch geometry
+static TgFFView ff_view(const tg_handle *h, const EvalBuf &b)
+{
+    TgFFView v; memset(&v, 0, sizeof(v));
+    if (!h->ffw || !b.ffc || h->ff_nmt <= 0) return v;
+    v.c = b.ffc; v.hdr = b.ffh; v.rec = b.ffr; v.geo = h->ffgeo; v.stride = h->ff_stride; v.mt0 = h->ff_mt0; v.nmt = h->ff_nmt;
+    return v;
+}
+static TgFFArgs ff_args(const tg_handle *h, const EvalBuf &b, int B)
+{
+    TgFFArgs a; memset(&a, 0, sizeof(a));
+    a.d = h->d; a.t = b.t; a.ffw = h->ffw; a.r2 = h->ff_r2; a.c = b.ffc; a.hdr = b.ffh; a.rec = b.ffr; a.geo = h->ffgeo;
+    a.stride = h->ff_stride; a.mt0 = h->ff_mt0; a.nmt = (h->ffw && b.ffc) ? h->ff_nmt : 0; a.B = B;
+    return a;
+}
+static int ff_ctas_per_chain(int nmt) { return (nmt + TG_FF_MT - 1) / TG_FF_MT; }    // one CTA per pair of sub-tiles
+static size_t ff_smem(const tg_handle *h) { return TG_FF_SMEM(std::max(h->d.ncomp_max, 1)); }
+
 // The argument record of the fused kernel for the points held in `b` -> device memory (uploaded only when it changed; never
 // called with a change pending inside a stream capture: the callers bring it up to date before they begin one).
 static int sync_eval_args(tg_handle *h, EvalBuf &b, double *model, int B)
@@ -262,7 +293,17 @@ static int sync_eval_args(tg_handle *h, EvalBuf &b, double *model, int B)
     TgEvalArgs ea; memset(&ea, 0, sizeof(ea));
     ea.d = h->d; ea.t = b.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = b.partials; ea.model = model;
     ea.B = B; ea.nitems = h->nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
-    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ffw = h->ffw; ea.ff_r2 = h->ff_r2;
+    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note;
+    if (!model) ea.ff = ff_view(h, b);
+    if (h->ffw) {
+        const TgFFArgs fa = ff_args(h, b, B);
+        if (!(b.d_ffargs && b.ffargs_valid && memcmp(&fa, &b.h_ffargs, sizeof(fa)) == 0)) {
+            if (!b.d_ffargs) DA(b.d_ffargs, 1);
+            memcpy(&b.h_ffargs, &fa, sizeof(fa));
+            CK(cudaMemcpyAsync(b.d_ffargs, &b.h_ffargs, sizeof(fa), cudaMemcpyHostToDevice, h->stream));
+            b.ffargs_valid = true;
+        }
+    }
     if (b.d_args && b.args_valid && memcmp(&ea, &b.h_args, sizeof(ea)) == 0) return TG_OK;
     if (!b.d_args) DA(b.d_args, 1);
     memcpy(&b.h_args, &ea, sizeof(ea));
@@ -284,6 +325,11 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
     { int r = sync_eval_args(h, b, model, B); if (r) return r; }
     const size_t esm = TG_EVAL_SMEM(h->chains_per_block, h->list_cap);
     dim3 grid(u.n);
+    if (h->ffw && !model && h->ff_nmt > 0 && b.ffc) {   // far-field pre-pass of the B points (tg_farfield.cuh)
+        const int cpc = ff_ctas_per_chain(h->ff_nmt);
+        tg_k_ff<<<(unsigned)B * cpc, 256, ff_smem(h), h->stream>>>((const TgFFArgs *)b.d_ffargs, (const int2 *)nullptr, cpc);
+        h->n_launch_total++;
+    }
     if (h->timing) {
         if (h->ev_used >= 8192) { int r = harvest_events(h); if (r) return r; }
         cudaEventRecord(next_event(h), h->stream);
@@ -322,6 +368,9 @@ static int build_items(tg_handle *h, EvalBuf &b, int B)
         for (int c = 0; c < B; c++) if (whi[c] > wlo[c]) { ulo = std::min(ulo, wlo[c]); uhi = std::max(uhi, whi[c]); }
         int t0 = nt, t1 = nt;                       // heavy tiles [t0, t1), one tile of margin for drifting windows
         if (uhi > ulo) { t0 = std::max(0, ulo / SUB - 1); t1 = std::min(nt, (uhi + SUB - 1) / SUB + 1); }
+        // the far-field pre-pass prepares the micro-tiles of the window region (whole pairs of sub-tiles inside the spectrum)
+        { const int mt0 = t0 * (SUB / TG_FF_BINS), nmt = std::max(0, std::min(t1 * (SUB / TG_FF_BINS), h->ff_stride) - mt0);
+          if (h->ffw && (mt0 != h->ff_mt0 || nmt != h->ff_nmt)) { h->ff_mt0 = mt0; h->ff_nmt = nmt; h->sp.args_valid = h->ev.args_valid = false; h->sp.ffargs_valid = h->ev.ffargs_valid = false; drop_graphs(h); } }
         std::vector<int> diff(nt + 1, 0), w(nt, 0);
         for (int k = 0; k < ncomp && k < nc; k++) {
             if (hi[k] <= lo[k]) continue;
@@ -329,7 +378,8 @@ static int build_items(tg_handle *h, EvalBuf &b, int B)
             if (a1 >= a0) { diff[a0]++; diff[a1 + 1]--; }
         }
         for (int t = 0, c = 0; t < nt; t++) { c += diff[t]; w[t] = c; }
-        const int L = std::max(1, h->light_sub);
+        // bin-by-bin background runs: shorter when the window region is cheap (far-field path), or they become the tail of the launch
+        const int L = h->ffw ? std::max(1, std::min(h->light_sub, 4)) : std::max(1, h->light_sub);
         // background-only stretches: runs of aligned moment tiles the kernel evaluates through the moments of the data (kind 2, cheap),
         // bin-by-bin runs (kind 0) for misaligned ends and for the tiles earlier launches flagged (their polynomial check failed)
         const int ms = h->mom ? h->mom_sub : 0;
@@ -383,12 +433,14 @@ static void make_units(tg_handle *h, int B, int star, std::vector<int4> &units, 
     }
     for (size_t k = 0; k < h->items_host.size(); k++) {
         const int4 it = h->items_host[k];
-        const int gmax = (it.w == 1 && !h->no_order) ? (big[k] ? std::max(1, std::min(h->hybrid_group, gl)) : gh) : gl;
+        int gmax = (it.w == 1 && !h->no_order) ? (big[k] ? std::max(1, std::min(h->hybrid_group, gl)) : gh) : gl;
+        if (it.w == 0 && h->ffw && !h->no_order) gmax = std::min(gmax, 2);
         const int groups = (B + gmax - 1) / gmax, g = (B + groups - 1) / groups;      // balanced
         for (int c0 = 0; c0 < B; c0 += g) {
             const int G = std::min(g, B - c0);
             units.push_back(make_int4(it.x, it.y | (G << 16), c0, (int)k | (star << TG_UNIT_STAR_SHIFT)));
-            cost.push_back(it.w == 2 ? (double)G * (it.y / std::max(1, h->mom_sub)) * 8.0 + 15.0 : (double)G * it.y * (20.0 + 6.25 * it.z) + 15.0);
+            const double per_sub = (it.w == 1 && h->ffw) ? 22.0 + 0.5 * it.z : 20.0 + 6.25 * it.z;      // far-field path: the window crossings hardly matter
+            cost.push_back(it.w == 2 ? (double)G * (it.y / std::max(1, h->mom_sub)) * 8.0 + 15.0 : (double)G * it.y * per_sub + 15.0);
         }
     }
 }
@@ -547,7 +599,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         const char *e = getenv("TG_FARFIELD");
         bool inc = true;
         for (size_t i = 1; i < Nx && inc; i++) inc = p->x[i] > p->x[i - 1];
-        if (e && atoi(e) == 1 && inc && p->model_case >= 2) {      // experimental in this commit: opt-in
+        if (!(e && atoi(e) == 0) && inc && p->model_case >= 2 && !(p->flags & TG_F_NO_TILE_ORDER)) {
             if (const char *e2 = getenv("TG_FF_R2")) h->ff_r2 = std::max(4.0, atof(e2));
             std::vector<double> w((size_t)TG_FF_HDR);
             const long double pi = 3.141592653589793238462643383279502884L;
@@ -556,6 +608,12 @@ static int create_impl(const tg_problem *p, tg_handle *h)
             for (int i = 0; i < TG_FF_N; i++) w[(size_t)TG_FF_N * TG_FF_N + i] = (double)cosl(pi * (i + 0.5L) / TG_FF_N);
             DA(h->ffw, w.size());
             CK(cudaMemcpy(h->ffw, w.data(), w.size() * 8, cudaMemcpyHostToDevice));
+            h->ff_stride = (int)(Nx / TG_FF_BINS);                  // whole micro-tiles of the spectrum
+            if (h->ff_stride < TG_FF_MT) { h->ffw = nullptr; h->ff_stride = 0; }
+            else {
+                DA(h->ffgeo, (size_t)h->ff_stride);
+                tg_k_ffgeo<<<(h->ff_stride + 255) / 256, 256, 0, h->stream>>>(h->x, (int)Nx, h->ffgeo, h->ff_stride);
+            }
         }
     }
     DA(h->pri, (size_t)4 * p->Np); DA(h->sw, p->Np); DA(h->index_to_relax, d.Nv); DA(h->Tcoefs, p->Nchains);
@@ -576,19 +634,20 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     {
         h->list_cap = std::max(4, (d.ncomp_max + 3) & ~3);
         int maxdyn = 0; CK(cudaDeviceGetAttribute(&maxdyn, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
-        const size_t budget = std::min<size_t>((size_t)maxdyn - 2048, 100 * 1024);       // <= 100 KB: two CTAs per SM stay resident
+        const size_t budget = std::min<size_t>((size_t)maxdyn - 2048, 96 * 1024);        // <= 96 KB (+ 14 KB static): two CTAs per SM stay resident
         int m = TG_MAXG;
         while (m > 1 && TG_EVAL_SMEM(m, h->list_cap) > budget) m--;
         if (TG_EVAL_SMEM(m, h->list_cap) > (size_t)maxdyn - 2048) return fail(TG_E_BADARG, "too many Lorentzian components for the shared-memory list of the fused kernel");
         h->max_cpb = m;
         const size_t need = TG_EVAL_SMEM(m, h->list_cap);
         { int r = raise_dyn_smem((const void *)tg_k_eval, need); if (r) return r; }
+        if (h->ffw && ff_smem(h) > 40 * 1024) { int r = raise_dyn_smem((const void *)tg_k_ff, ff_smem(h)); if (r) return r; }
         const int groups = (C + m - 1) / m;                                               // balanced chain groups of <= max_cpb
         h->chains_per_block = (C + groups - 1) / groups;
         // where truncation windows lie: items of two sub-tiles (taken 8 bins per thread); one chain per unit for a single
         // ensemble (more, smaller units: better tail of the grid), three when many chains fill the GPU anyway (measured with the
         // background-only tiles on the moment path: one chain per unit is best up to ~100 chains, 3.9 vs 4.0 us per chain at 80)
-        h->heavy_sub = h->ffw ? 2 * TG_FF_MAXP : 2;       // far-field path: up to four pairs share one list and one set-up
+        h->heavy_sub = 2;
         h->heavy_group = (C >= 128) ? 3 : 1;
         // a spectrum so short that pairs of sub-tiles would not even fill the GPU once (S-local: 10k bins, 10 chains): single
         // sub-tiles, twice the units (25.7 vs 29.9 us per step there)
@@ -599,6 +658,14 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         // (small units for the tail): 70 % of them at 10 chains (49.0 -> 48.1 us), all of them from 32 chains on (-7 %)
         h->hybrid_group = (C < 64) ? 3 : ((C < 128) ? 4 : 5);
         h->hybrid_pct = short_spectrum ? 0 : ((C < 16) ? 70 : ((C < 32) ? 80 : 100));      // short spectra: as many units as possible
+        if (h->ffw && !short_spectrum) {
+            // far-field path: a window-region unit is a run of pairs of sub-tiles x a few chains (per pair and chain one staged
+            // interpolant + the exact records; no lists); measured on cfg3: 4 sub-tiles x 2 chains at 10 chains (32.8 us against
+            // 35-40 for the neighbours), 8 sub-tiles x 3 chains at 80 chains (2.14 us per chain)
+            h->heavy_sub = (C < 32) ? 4 : 8;
+            h->hybrid_pct = 100;
+            h->hybrid_group = (C < 32) ? 2 : 3;
+        }
         if (const char *e = getenv("TG_GRAPH_STEPS")) h->steps_per_graph = std::max(1, std::min(256, atoi(e)));
         if (const char *e = getenv("TG_HYBRID_PCT")) h->hybrid_pct = atoi(e);
         if (const char *e = getenv("TG_HYBRID_GROUP")) h->hybrid_group = std::max(1, atoi(e));
@@ -914,8 +981,14 @@ static cudaEvent_t batch_next_event(tg_batch *b)
 
 static int batch_harvest_events(tg_batch *b)
 {
-    if (b->ev_used == 0) return TG_OK;
+    if (b->ev_used == 0 && b->ffev_used == 0) return TG_OK;
     CK(cudaStreamSynchronize(b->stream));
+    for (size_t k = 0; k + 1 < b->ffev_used; k += 2) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, b->ffev_pool[k], b->ffev_pool[k + 1]));
+        b->ms_ff += ms;
+    }
+    b->ffev_used = 0;
     for (size_t k = 0; k + 1 < b->ev_used; k += 2) {
         float ms = 0;
         CK(cudaEventElapsedTime(&ms, b->ev_pool[k], b->ev_pool[k + 1]));
@@ -942,6 +1015,7 @@ static int batch_destroy(tg_batch *b)
     if (b->side) cudaStreamSynchronize(b->side);
     batch_drop_graph(b);
     for (auto e : b->ev_pool) cudaEventDestroy(e);
+    for (auto e : b->ffev_pool) cudaEventDestroy(e);
     for (void *q : b->allocs) cudaFree(q);
     if (b->ev_fork) cudaEventDestroy(b->ev_fork);
     if (b->ev_join) cudaEventDestroy(b->ev_join);
@@ -976,7 +1050,7 @@ static int batch_create(tg_handle **hs, int n, tg_batch **out)
     for (int k = 0; k < n; k++) for (int c = 0; c < hs[k]->s.C; c++) cmap.push_back(make_int2(k, c));
     b->Ctot = (int)cmap.size();
     if ((r = batch_dalloc(b, &b->d_cmap, cmap.size())) || (r = batch_dalloc(b, &b->d_ev, n)) || (r = batch_dalloc(b, &b->d_pm, n)) ||
-        (r = batch_dalloc(b, &b->d_ps, n)) || (r = batch_dalloc(b, &b->d_fin, n))) return bail(r);
+        (r = batch_dalloc(b, &b->d_ps, n)) || (r = batch_dalloc(b, &b->d_fin, n)) || (r = batch_dalloc(b, &b->d_ff, n))) return bail(r);
     for (int k = 0; k < n; k++) if (cudaStreamSynchronize(hs[k]->stream) != cudaSuccess) return bail(fail(TG_E_CUDA, "tg_batch_create: sync"));
     if (cudaMemcpy(b->d_cmap, cmap.data(), cmap.size() * sizeof(int2), cudaMemcpyHostToDevice) != cudaSuccess) return bail(fail(TG_E_CUDA, "tg_batch_create: chain map"));
     *out = b;
@@ -987,16 +1061,19 @@ static int batch_create(tg_handle **hs, int n, tg_batch **out)
 static int batch_sync_args(tg_batch *b)
 {
     const size_t n = b->hs.size();
-    std::vector<TgEvalArgs> ev(n); std::vector<TgProposeArgs> pm(n), ps(n); std::vector<TgFinishArgs> fin(n);
+    std::vector<TgEvalArgs> ev(n); std::vector<TgProposeArgs> pm(n), ps(n); std::vector<TgFinishArgs> fin(n); std::vector<TgFFArgs> ff(n);
+    int cpc = 0; size_t fsm = 0;
     memset(ev.data(), 0, n * sizeof(TgEvalArgs)); memset(pm.data(), 0, n * sizeof(TgProposeArgs));
-    memset(ps.data(), 0, n * sizeof(TgProposeArgs)); memset(fin.data(), 0, n * sizeof(TgFinishArgs));
+    memset(ps.data(), 0, n * sizeof(TgProposeArgs)); memset(fin.data(), 0, n * sizeof(TgFinishArgs)); memset(ff.data(), 0, n * sizeof(TgFFArgs));
     int rows = 0; size_t psm = 0, esm = 0;
     for (size_t k = 0; k < n; k++) {
         tg_handle *h = b->hs[k];
         TgEvalArgs &ea = ev[k];
         ea.d = h->d; ea.t = h->sp.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = h->sp.partials; ea.model = nullptr;
         ea.B = h->s.C; ea.nitems = h->nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
-        ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ffw = h->ffw; ea.ff_r2 = h->ff_r2;
+        ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ff = ff_view(h, h->sp);
+        ff[k] = ff_args(h, h->sp, h->s.C);
+        if (ff[k].nmt > 0) { cpc = std::max(cpc, ff_ctas_per_chain(ff[k].nmt)); fsm = std::max(fsm, ff_smem(h)); }
         // The adaptation candidates (Robbins-Monro + Cholesky for both outcomes of the decision) depend on the state the previous
         // finish kernel left and on nothing of this step (the CTA of the "accepted" outcome recomputes the proposed point itself),
         // and only the finish kernel needs them: they run on a side stream next to the proposal, the prologue and the fused kernel.
@@ -1014,16 +1091,18 @@ static int batch_sync_args(tg_batch *b)
         f.presummed = b->presummed; f.rec = h->rec; f.record = 1;
     }
     b->side_rows = rows; b->propose_smem = psm; b->eval_smem = esm;
-    const bool same = b->args_valid && b->h_ev.size() == n && memcmp(ev.data(), b->h_ev.data(), n * sizeof(TgEvalArgs)) == 0 &&
+    if (cpc != b->ff_cpc || fsm != b->ff_smem) { b->ff_cpc = cpc; b->ff_smem = fsm; batch_drop_graph(b); }
+    const bool same = b->args_valid && b->h_ev.size() == n && memcmp(ev.data(), b->h_ev.data(), n * sizeof(TgEvalArgs)) == 0 && memcmp(ff.data(), b->h_ff.data(), n * sizeof(TgFFArgs)) == 0 &&
                       memcmp(pm.data(), b->h_pm.data(), n * sizeof(TgProposeArgs)) == 0 && memcmp(ps.data(), b->h_ps.data(), n * sizeof(TgProposeArgs)) == 0 &&
                       memcmp(fin.data(), b->h_fin.data(), n * sizeof(TgFinishArgs)) == 0;
     if (same) return TG_OK;
-    b->h_ev.swap(ev); b->h_pm.swap(pm); b->h_ps.swap(ps); b->h_fin.swap(fin);
+    b->h_ev.swap(ev); b->h_pm.swap(pm); b->h_ps.swap(ps); b->h_fin.swap(fin); b->h_ff.swap(ff);
     CK(cudaStreamSynchronize(b->stream));
     CK(cudaMemcpy(b->d_ev, b->h_ev.data(), n * sizeof(TgEvalArgs), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(b->d_pm, b->h_pm.data(), n * sizeof(TgProposeArgs), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(b->d_ps, b->h_ps.data(), n * sizeof(TgProposeArgs), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(b->d_fin, b->h_fin.data(), n * sizeof(TgFinishArgs), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(b->d_ff, b->h_ff.data(), n * sizeof(TgFFArgs), cudaMemcpyHostToDevice));
     b->args_valid = true;
     return TG_OK;
 }
@@ -1066,6 +1145,15 @@ static int batch_launch_step(tg_batch *b, bool begin, bool end)
             CK(cudaEventRecord(b->ev_join, b->side));
             b->side_pending = true;
             b->n_launch_total++;
+        }
+        if (b->ff_cpc > 0) {      // far-field pre-pass of the proposed points of every star
+            if (b->timing) {
+                if (b->ffev_used + 2 > b->ffev_pool.size()) { cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1); b->ffev_pool.push_back(e0); b->ffev_pool.push_back(e1); }
+                cudaEventRecord(b->ffev_pool[b->ffev_used], b->stream);
+            }
+            CK(launch_k(tg_k_ff, dim3((unsigned)Ct * b->ff_cpc), dim3(256), b->ff_smem, b->stream, b->pdl && !b->timing, (const TgFFArgs *)b->d_ff, (const int2 *)b->d_cmap, b->ff_cpc));
+            b->n_launch_total++;
+            if (b->timing) { cudaEventRecord(b->ffev_pool[b->ffev_used + 1], b->stream); b->ffev_used += 2; }
         }
         if (b->timing) {
             if (b->ev_used >= 8192) { int r = batch_harvest_events(b); if (r) return r; }
@@ -1164,7 +1252,7 @@ static int drain_records(tg_handle *h, cudaStream_t st, tg_records *rec, long do
 
 static int batch_launches_per_step(const tg_batch *b)
 {
-    int n = 3 + (b->side_rows > 0 ? 1 : 0);
+    int n = 3 + (b->side_rows > 0 ? 1 : 0) + (b->ff_cpc > 0 ? 1 : 0);
     for (tg_handle *h : b->hs) { if (h->m.n_learn > 0 && !h->fused_spec) n++; if (b->presummed) n += 1 + (h->nccl_comm ? 1 : 0); }
     return n;
 }
@@ -1247,14 +1335,27 @@ static int batch_kernel_time(tg_batch *b, int reset, long *launches, double *ms_
     if (launches) *launches = b->n_eval_launch;
     if (ms_eval) *ms_eval = b->ms_eval;
     if (total_launches) *total_launches = b->n_launch_total;
-    if (reset == 1) { b->n_eval_launch = 0; b->ms_eval = 0; b->n_launch_total = 0; b->timing = true; }
-    if (reset == 2) { b->n_eval_launch = 0; b->ms_eval = 0; b->n_launch_total = 0; b->timing = false; return batch_refresh(b); }
+    if (reset == 1) { b->n_eval_launch = 0; b->ms_eval = 0; b->ms_ff = 0; b->n_launch_total = 0; b->timing = true; }
+    if (reset == 2) { b->n_eval_launch = 0; b->ms_eval = 0; b->n_launch_total = 0; b->timing = false; return batch_refresh(b); }      // (ms_ff stays readable)
     return TG_OK;
 }
 extern "C" int tg_batch_kernel_time(tg_batch *b, int reset, long *launches, double *ms_eval, long *total_launches)
 {
     if (!b) return fail(TG_E_BADARG, "null batch");
     return batch_kernel_time(b, reset, launches, ms_eval, total_launches);
+}
+extern "C" int tg_batch_prepass_time(tg_batch *b, double *ms_ff)
+{
+    if (!b || !ms_ff) return fail(TG_E_BADARG, "tg_batch_prepass_time: bad argument");
+    CK(cudaSetDevice(b->device));
+    { int r = batch_harvest_events(b); if (r) return r; }
+    *ms_ff = b->ms_ff;
+    return TG_OK;
+}
+extern "C" int tg_prepass_time(tg_handle *h, double *ms_ff)
+{
+    if (!h || !h->self) return fail(TG_E_BADARG, "null handle");
+    return tg_batch_prepass_time(h->self, ms_ff);
 }
 // device-side stopwatch on the group's stream: which = 0 start, 1 stop (then the elapsed time is read with tg_event_elapsed_ms of the first star)
 extern "C" int tg_batch_event_record(tg_batch *b, int which)
@@ -1385,7 +1486,7 @@ extern "C" int tg_event_elapsed_ms(tg_handle *h, double *ms)
 // array until the process exits; every call on a device shares it and finds the previous call's contents in it.
 // ------------------------------------------------------------------------------------------
 #define TG_NA_ARGS_BYTES 4096                                   // the argument record of tg_k_eval
-static_assert(sizeof(TgEvalArgs) <= TG_NA_ARGS_BYTES, "argument record outgrew its slot of the static scratch");
+static_assert(sizeof(TgEvalArgs) <= TG_NA_ARGS_BYTES / 2 && sizeof(TgFFArgs) <= TG_NA_ARGS_BYTES / 2, "argument records outgrew their slot of the static scratch");
 #define TG_NA_OFF_UNITS  ((size_t)TG_NA_ARGS_BYTES)
 #define TG_NA_OFF_PAIRS  (TG_NA_OFF_UNITS + (size_t)TG_NOALLOC_MAX_UNITS * sizeof(int4))
 #define TG_NA_OFF_SUMS   (TG_NA_OFF_PAIRS + (size_t)TG_NOALLOC_MAX_PAIRS * sizeof(double2))
@@ -1447,15 +1548,19 @@ extern "C" int tg_eval_noalloc(tg_handle *h, const double *params, int B, const 
     TgEvalArgs ea; memset(&ea, 0, sizeof(ea));
     ea.d = h->d; ea.t = b.t; ea.x = h->x; ea.y = h->y; ea.lnx = h->lnx; ea.sig = h->sig; ea.partials = d_pairs; ea.model = nullptr;
     ea.B = B; ea.nitems = nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
-    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ffw = h->ffw; ea.ff_r2 = h->ff_r2;
+    ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ff = ff_view(h, b);
+    const TgFFArgs fa = ff_args(h, b, B);
+    TgFFArgs *d_ffa = (TgFFArgs *)(base + TG_NA_ARGS_BYTES / 2);   // the pre-pass's record shares the slot of the argument record
     // the scratch keeps the last call's contents: the record and the table are overwritten, the partial sums start at zero
     // (pageable sources: the runtime stages them before the call returns, so the locals may die)
     CK(cudaMemcpyAsync(d_args, &ea, sizeof(ea), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(d_ffa, &fa, sizeof(fa), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(d_units, units.data(), units.size() * sizeof(int4), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemsetAsync(d_pairs, 0, (size_t)B * nitems * sizeof(double2), h->stream));
     CK(cudaMemsetAsync(d_sums, 0, (size_t)B * sizeof(double2), h->stream));
     TgProArgs pa{h->d, b.t, b.params, h->pri, h->sw};
     tg_k_prologue<<<B, TG_PRO_THREADS, TG_PRO_SMEM(h->d.Np), h->stream>>>(pa);
+    if (fa.nmt > 0) { const int cpc = ff_ctas_per_chain(fa.nmt); tg_k_ff<<<(unsigned)B * cpc, 256, ff_smem(h), h->stream>>>((const TgFFArgs *)d_ffa, (const int2 *)nullptr, cpc); }
     tg_k_eval<<<(unsigned)units.size(), TG_THREADS, TG_EVAL_SMEM(h->chains_per_block, h->list_cap), h->stream>>>((const TgEvalArgs *)d_args, (const int4 *)d_units);
     tg_k_reduce_finalize<<<B, 256, 0, h->stream>>>(h->d, d_pairs, nitems, d_sums, b.T, b.t, b.logL, b.logPrior, b.logPost, b.status);
     CK(cudaGetLastError());
@@ -1466,5 +1571,23 @@ extern "C" int tg_eval_noalloc(tg_handle *h, const double *params, int B, const 
     if (logPrior) memcpy(logPrior, b.pin_out + B, (size_t)B * 8);
     if (logPost) memcpy(logPost, b.pin_out + 2 * (size_t)B, (size_t)B * 8);
     if (status) memcpy(status, b.pin_out + 3 * (size_t)B, (size_t)B * 4);
+    return TG_OK;
+}
+
+// developer check (not part of the ABI): summary of the far-field headers the last tg_eval batch left
+extern "C" int tg_dbg_ff_summary(tg_handle *h, int B, long *out /* [6]: micro-tiles, fallbacks, records, far components, noise-folded, max records */)
+{
+    if (!h || !h->ffw || !h->ev.ffh || B < 1 || B > h->ev.cap) return fail(TG_E_BADARG, "tg_dbg_ff_summary: nothing to look at");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    std::vector<TgFFHdr> hd((size_t)B * h->ff_stride);
+    CK(cudaMemcpy(hd.data(), h->ev.ffh, hd.size() * sizeof(TgFFHdr), cudaMemcpyDeviceToHost));
+    for (int k = 0; k < 6; k++) out[k] = 0;
+    for (int b = 0; b < B; b++) for (int m = 0; m < h->ff_nmt; m++) {
+        const TgFFHdr &q = hd[(size_t)b * h->ff_stride + m];
+        out[0]++; if (q.count < 0) out[1]++; else { out[2] += q.count; out[5] = std::max<long>(out[5], q.count); }
+        out[3] += q.nfar; out[4] += q.flags & 1;
+        if (q.count < 0) fprintf(stderr, "fallback: vector %d micro-tile %d flags %d nfar %d\n", b, m, q.flags, q.nfar);
+    }
     return TG_OK;
 }

@@ -26,6 +26,7 @@
 // All of these change rounding by a few ulp only (tests: 1e-12 relative against the oracle).
 #pragma once
 #include "tg_internal.cuh"
+#include "tg_farfield.cuh"
 
 #ifdef TG_PROFILE
 #define TG_DBG_CTAS 8192
@@ -47,9 +48,7 @@ struct TgEvalArgs {
     int           mom_sub;             // sub-tiles of 1024 bins per moment tile
     int          *mom_fail;            // [Nx / mom_bins] set to 1 when a tile failed its check for some chain (scheduling hint for the host)
     int          *mom_note;            // pinned host word: set to 1 when a tile is flagged for the first time
-    const double *ffw;                 // far-field path under the truncation windows (tg_ff_setup): [TG_FF_N][TG_FF_N] node values -> Chebyshev
-                                       // coefficients, then the TG_FF_N nodes; NULL = off
-    double        ff_r2;               // a component is "far" from a micro-tile when its poles lie at least sqrt(ff_r2) half-widths from the centre
+    TgFFView      ff;                  // far-field path under the truncation windows (tg_farfield.cuh); ff.c == NULL: off
 };
 
 // ---- background-only stretches of the spectrum through Chebyshev moments of the data ------------------------------
@@ -82,26 +81,7 @@ struct __align__(16) TgComp {       // one Lorentzian m-component clipped to the
 // dynamic shared memory of tg_k_eval for a group of G chains and a list capacity of cap components:
 // lists, per-quad "covers the whole tile" flags, noise tables, per-thread partial results
 // (sum, mantissa product, exponent sum)
-// ---- far field under the truncation windows ------------------------------------------------------------------------
-// A pair of sub-tiles is 8 micro-tiles of 256 bins (bin j of a thread lies in micro-tile j).  Over a micro-tile of half-width
-// w centred at xc, a Lorentzian h/(1+q(x-nu)^2) whose window covers the micro-tile and whose poles nu +- i/sqrt(q) lie at
-// least R*w from xc is analytic in the Bernstein ellipse of parameter rho >= R + sqrt(R^2-1): its interpolant at TG_FF_N = 16
-// Chebyshev nodes is exact to rounding (<= 7e-15 of the component's own value at R = 5, 2e-15 at R = 6).  Per (micro-tile,
-// chain) the SUM of the far components is therefore evaluated at 16 nodes (one warp per micro-tile, the two half-warps split
-// the list), turned into Chebyshev coefficients by shuffles, and every bin takes one Clenshaw recurrence (30 FP64
-// instructions) in place of ~27 far components (6.25 each); the few near components (and those whose window edge cuts the
-// micro-tile) are evaluated exactly as before, window predicate included, so the windows stay bin-exact.  The classification
-// is a function of (nu, q, window) and the grid alone -- nothing is assumed about the parameters; a micro-tile whose trailing
-// coefficients are not small (|c14|+|c15| > TG_FF_TOL |c0|: NaN, non-monotonic abscissae, ...) is evaluated exactly.
-#define TG_FF_N    16
-#define TG_FF_MT   8                   // micro-tiles of a pair of sub-tiles == bins per thread
-#define TG_FF_MAXP 4                   // pairs of sub-tiles that share one list and one far-field set-up (a unit spans <= 8 sub-tiles there)
-#define TG_FF_MAXMT (TG_FF_MT * TG_FF_MAXP)
-#define TG_FF_TOL  1.0e-12
-#define TG_FF_HDR  (TG_FF_N * TG_FF_N + TG_FF_N)
-struct TgFFGeom { double xc[TG_FF_MAXMT], hw[TG_FF_MAXMT], ihw[TG_FF_MAXMT]; };   // centre, half-width, 1/half-width of the micro-tiles
-#define TG_EVAL_SMEM(G, cap) ((size_t)(G) * ((size_t)(cap) * sizeof(TgComp) + (size_t)((cap) / 4 + 2 * TG_MAXH) * sizeof(int) + TG_NOISE_STRIDE * sizeof(double) + TG_THREADS * (2 * sizeof(double) + sizeof(int)) \
-                                             + (size_t)(4 * (cap)) * sizeof(int) + (size_t)2 * TG_FF_MAXMT * TG_FF_N * sizeof(double)))
+#define TG_EVAL_SMEM(G, cap) ((size_t)(G) * ((size_t)(cap) * sizeof(TgComp) + (size_t)((cap) / 4 + 2 * TG_MAXH) * sizeof(int) + TG_NOISE_STRIDE * sizeof(double) + TG_THREADS * (2 * sizeof(double) + sizeof(int))))
 
 // height of a component at tile-local bin li: h inside its window, 0 outside
 __device__ __forceinline__ double tg_hsel(double h, int lo, int len, int li)
@@ -153,58 +133,6 @@ __device__ __forceinline__ void tg_accumulate(int n4, const TgComp *L, const int
                 acc[j] = fma(N, tg_rcp_fast(T), acc[j]);
             }
         }
-    }
-}
-
-// Exact part of the far-field path for pair number mt0/8 of the span the lists were built for (8 bins per thread, bin j in
-// micro-tile mt0 + j): the components of xidx (those evaluated exactly somewhere in the span, list order), one at a time, only
-// on the micro-tiles concerned (emask / cvmask are CTA-uniform, the branches do not diverge).  Where the window covers the whole
-// micro-tile no predicate is needed; elsewhere the window predicate is the one of tg_accumulate, in bins of the span.
-__device__ __forceinline__ void tg_accumulate_ff(int nx, const int *xidx, const TgComp *L, const unsigned *emask, const unsigned *cvmask, int mt0,
-                                                 const double (&x)[TG_FF_MT], double (&acc)[TG_FF_MT], int tid)
-{
-#pragma unroll 1
-    for (int e = 0; e < nx; e++) {
-        const int k = xidx[e];
-        const unsigned em = (emask[k] >> mt0) & 0xffu;
-        if (em == 0u) continue;
-        const unsigned cv = (cvmask[k] >> mt0) & 0xffu;
-        const double2 nq = *(const double2 *)&L[k].nu;
-        const double h = L[k].h;
-        const int2 w = *(const int2 *)&L[k].lo;
-#pragma unroll
-        for (int j = 0; j < TG_FF_MT; j++) {
-            if (!((em >> j) & 1u)) continue;
-            const double d = x[j] - nq.x;
-            const double r = tg_rcp_fast(fma(d * d, nq.y, 1.0));
-            if ((cv >> j) & 1u) acc[j] = fma(h, r, acc[j]);
-            else acc[j] = fma(tg_hsel(h, w.x, w.y, tid + (mt0 + j) * TG_THREADS), r, acc[j]);
-        }
-    }
-}
-
-// acc[j] = sum_k c[j][k] T_k(t_j), t_j = (x_j - xc_j) / hw_j: Clenshaw, four bins at a time (independent recurrences interleave),
-// the coefficients two per shared-memory load; c, xc, ihw point at the first micro-tile of the pair
-__device__ __forceinline__ void tg_ff_clenshaw(const double *c, const double *xc, const double *ihw, const double (&x)[TG_FF_MT], double (&acc)[TG_FF_MT])
-{
-    static_assert(TG_FF_N % 2 == 0, "coefficients are loaded in pairs");
-#pragma unroll
-    for (int j0 = 0; j0 < TG_FF_MT; j0 += 4) {
-        double t2[4], b1[4], b2[4], cz[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) { const double t = (x[j0 + u] - xc[j0 + u]) * ihw[j0 + u]; t2[u] = t + t; b1[u] = 0.0; b2[u] = 0.0; }
-#pragma unroll
-        for (int k = TG_FF_N - 2; k >= 0; k -= 2) {
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const double2 cc = *(const double2 *)&c[(j0 + u) * TG_FF_N + k];      // (c_k, c_k+1)
-                const double bh = fma(t2[u], b1[u], cc.y) - b2[u];                   // b_{k+1}
-                if (k > 0) { b2[u] = bh; b1[u] = fma(t2[u], bh, cc.x) - b1[u]; }      // b_k
-                else { b2[u] = b1[u]; b1[u] = bh; cz[u] = cc.x; }
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; u++) acc[j0 + u] = fma(0.5 * t2[u], b1[u], cz[u]) - b2[u];
     }
 }
 
@@ -281,13 +209,99 @@ struct TgEvalSmem {                 // carved out of the dynamic shared memory
     double *nz;                     // [G][TG_NOISE_STRIDE]
     double *sum, *pf;               // [G][TG_THREADS]  running per-thread results of the item
     int    *pe;                     // [G][TG_THREADS]
-    double *ffc;                    // [G][TG_FF_MAXMT][TG_FF_N]  far-field Chebyshev coefficients per micro-tile
-    double *ffv;                    // [G][TG_FF_MAXMT][TG_FF_N]  node values of the far sums
-    unsigned *emask;                // [G][cap]    per component: micro-tiles (bits) its window meets; after tg_ff_setup: where it is evaluated exactly
-    unsigned *fmask;                // [G][cap]    per component: micro-tiles where it is far
-    unsigned *cvmask;               // [G][cap]    per component: micro-tiles its window covers completely
-    int      *xidx;                 // [G][cap]    components evaluated exactly somewhere in the span (list order); counts in s_nx
 };
+
+// Noise background, likelihood terms and the running results of chain g for the NB bins of a thread whose Lorentzian part is in
+// acc (shared by every path of the fused kernel).  FF: nfold = micro-tiles (bits) whose acc already holds the background and N0.
+template <int NB, bool GEN, bool FF>
+__device__ __forceinline__ void tg_bins_tail(const TgEvalArgs &a, const TgEvalSmem &S, int g, int c0, int b0, int tid, const double (&x)[NB], const double (&y)[NB],
+                                             const int (&ii)[NB], double (&acc)[NB], int nfold)
+{
+    const int Nx = a.d.Nx;
+    const double *nz = S.nz + (size_t)g * TG_NOISE_STRIDE;
+    // ---- Harvey-like background: y += H/(1+(1e-3*tc*x)^p) ; y += N0  (noise_models.cpp:30-38).
+    //      The prologue lists only the active terms (tc != 0); consecutive pairs share a reciprocal.
+    // (far-field path: where the interpolant of a micro-tile already holds the background and N0, nothing is added;
+    //  after a failed check on some micro-tile the background is evaluated for all bins and used where it is missing)
+    double accf[FF ? NB : 1];
+    if constexpr (FF) {
+        if (nfold != 0 && nfold != 0xff) {
+#pragma unroll
+            for (int j = 0; j < NB; j++) { accf[j] = acc[j]; acc[j] = 0.0; }
+        }
+    }
+    const int nH = (FF && nfold == 0xff) ? 0 : S.nh[g];
+    for (int k = 0; k < nH; k += 2) {
+        double ta[NB], tb[NB];
+        tg_harvey_t<NB>(S.cls[g * TG_MAXH + k], nz + TG_HS * k, x, a.lnx, ii, ta);
+        const double Ha = nz[TG_HS * k + TG_H_H];
+        if (k + 1 < nH) {
+            tg_harvey_t<NB>(S.cls[g * TG_MAXH + k + 1], nz + TG_HS * (k + 1), x, a.lnx, ii, tb);
+            const double Hb = nz[TG_HS * (k + 1) + TG_H_H];
+#pragma unroll
+            for (int j = 0; j < NB; j++) acc[j] = fma(fma(Ha, tb[j], Hb * ta[j]), tg_rcp_fast(ta[j] * tb[j]), acc[j]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < NB; j++) acc[j] = fma(Ha, tg_rcp_fast(ta[j]), acc[j]);
+        }
+    }
+    const double N0 = (FF && nfold == 0xff) ? 0.0 : nz[TG_N_N0];
+    double m[NB];
+#pragma unroll
+    for (int j = 0; j < NB; j++) {
+        m[j] = acc[j] + N0;
+        if constexpr (FF) { if (nfold != 0 && nfold != 0xff) m[j] = ((nfold >> j) & 1) ? accf[j] : accf[j] + m[j]; }
+        if (GEN) {
+            const int idx = b0 + j * TG_THREADS + tid;
+            if (idx < Nx) { if (a.model) a.model[(size_t)(c0 + g) * Nx + idx] = m[j]; }
+            else m[j] = 1.0;
+        }
+    }
+    // running results of this thread for chain g over the whole item
+    double sum = S.sum[g * TG_THREADS + tid];     // sum y/m (or chi-square) + logs taken the slow way
+    double pf = S.pf[g * TG_THREADS + tid];       // product of the model values: pf * 2^pe, pf in [1,2)
+    int pe = S.pe[g * TG_THREADS + tid];
+    if (a.d.like_case == 0) {                 // likelihoods.cpp:23
+#pragma unroll
+        for (int j0 = 0; j0 < NB; j0 += 4) {
+            double mm[4], yy[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const bool in = (j0 + u < NB);
+                mm[u] = in ? m[in ? (j0 + u) : 0] : 1.0;
+                yy[u] = in ? y[in ? (j0 + u) : 0] : 0.0;
+            }
+            const double p01 = mm[0] * mm[1], p23 = mm[2] * mm[3], P = p01 * p23;
+            // all four positive (sign bits clear) and the product a normal number far from the range ends
+            const int sgn = __double2hiint(mm[0]) | __double2hiint(mm[1]) | __double2hiint(mm[2]) | __double2hiint(mm[3]);
+            const int hiP = __double2hiint(P);
+            const int eP = (hiP >> 20) & 0x7ff;
+            if (sgn >= 0 && (unsigned)(eP - 200) < 1646u) {            // 2^-823 < P < 2^823
+                const double n = fma(fma(yy[0], mm[1], yy[1] * mm[0]), p23, fma(yy[2], mm[3], yy[3] * mm[2]) * p01);
+                sum = fma(n, tg_rcp_fast(P), sum);
+                // fold P into the running product; the exponent is kept apart so it can never overflow
+                pf *= __hiloint2double((hiP & 0x000fffff) | 0x3ff00000, __double2loint(P));      // [1,2) x [1,2)
+                const int h2 = __double2hiint(pf);
+                pe += (eP - 1023) + (((h2 >> 20) & 0x7ff) - 1023);
+                pf = __hiloint2double((h2 & 0x000fffff) | 0x3ff00000, __double2loint(pf));
+            } else {                          // zero / negative / NaN / huge model values: the plain way
+#pragma unroll
+                for (int u = 0; u < 4; u++) if (j0 + u < NB && (!GEN || b0 + (j0 + u) * TG_THREADS + tid < Nx)) sum += yy[u] * tg_rcp(mm[u]) + log(mm[u]);
+            }
+        }
+    } else {                                  // likelihoods.cpp:36
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            const int idx = b0 + j * TG_THREADS + tid;
+            if (!GEN || idx < Nx) {
+                const double sg = __ldg(a.sig + idx);
+                const double dd = y[j] - m[j];
+                sum += (dd * dd) * tg_rcp(sg * sg);
+            }
+        }
+    }
+    S.sum[g * TG_THREADS + tid] = sum; S.pf[g * TG_THREADS + tid] = pf; S.pe[g * TG_THREADS + tid] = pe;
+}
 
 // Every chain of the group on NB*TG_THREADS consecutive bins starting at b0, held in registers; no CTA
 // barrier inside, so warps drift apart and hide each other's latencies.  LISTS: the sub-tile meets
@@ -295,11 +309,9 @@ struct TgEvalSmem {                 // carved out of the dynamic shared memory
 // NB may be 8 (two sub-tiles at once: twice the instruction-level parallelism, half the per-chain
 // overhead).  GEN = false is the interior fast path (all bins inside the spectrum, no model output, no
 // Gaussian test model): no index clamps, no selects.
-template <int NB, bool GEN, bool LISTS, bool FF = false>
-__device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalSmem &S, const int *s_tot, int G, int c0, int b0, int tid, unsigned gmask = 0xffffffffu,
-                                              const TgFFGeom *geo = nullptr, const unsigned *s_nfold = nullptr, int mt0 = 0, const int *s_nx = nullptr)
+template <int NB, bool GEN, bool LISTS>
+__device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalSmem &S, const int *s_tot, int G, int c0, int b0, int tid, unsigned gmask = 0xffffffffu)
 {
-    static_assert(!FF || (NB == TG_FF_MT && LISTS && !GEN), "the far-field path is the 8-bins-per-thread interior path");
     const int Nx = a.d.Nx, cap = a.list_cap;
     double x[NB], y[NB];
     int ii[NB];
@@ -322,16 +334,7 @@ __device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalS
 #pragma unroll
             for (int j = 0; j < NB; j++) acc[j] = 0.0;
         }
-        if constexpr (FF) {
-            // the far components of every micro-tile through their interpolant, the near ones exactly (tg_ff_setup put an
-            // asymmetric chain's components all on the exact side, so the plain predicated path below serves it)
-            const int n4 = (s_tot[g] + 3) & ~3;
-            const double asym = nz[TG_N_ASYM];
-            if (asym == 0.0) {
-                tg_ff_clenshaw(S.ffc + ((size_t)g * TG_FF_MAXMT + mt0) * TG_FF_N, geo->xc + mt0, geo->ihw + mt0, x, acc);
-                tg_accumulate_ff(s_nx[g], S.xidx + (size_t)g * cap, S.lists + (size_t)g * cap, S.emask + (size_t)g * cap, S.cvmask + (size_t)g * cap, mt0, x, acc, tid);
-            } else if (n4 > 0) tg_accumulate<NB, true>(n4, S.lists + (size_t)g * cap, S.full + g * (cap >> 2), x, acc, asym, tid, mt0 * TG_THREADS);
-        } else if constexpr (LISTS) {
+        if constexpr (LISTS) {
             const int n4 = (s_tot[g] + 3) & ~3;
             const double asym = nz[TG_N_ASYM];
             if (n4 > 0) {
@@ -339,90 +342,39 @@ __device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalS
                 else             tg_accumulate<NB, false>(n4, S.lists + (size_t)g * cap, S.full + g * (cap >> 2), x, acc, asym, tid);
             }
         }
-        // ---- Harvey-like background: y += H/(1+(1e-3*tc*x)^p) ; y += N0  (noise_models.cpp:30-38).
-        //      The prologue lists only the active terms (tc != 0); consecutive pairs share a reciprocal.
-        // (far-field path: where the interpolant of a micro-tile already holds the background and N0, nothing is added;
-        //  after a failed check on some micro-tile the background is evaluated for all bins and used where it is missing)
-        int nfold = 0;
-        if constexpr (FF) nfold = (int)((s_nfold[g] >> mt0) & 0xffu);
-        double accf[FF ? NB : 1];
-        if constexpr (FF) {
-            if (nfold != 0 && nfold != 0xff) {
+        tg_bins_tail<NB, GEN, false>(a, S, g, c0, b0, tid, x, y, ii, acc, 0);
+    }
+}
+
+// npair consecutive pairs of sub-tiles starting at bin b0, all of them inside the range the far-field pre-pass prepared, for the
+// G chains of the unit: per (pair, chain) the staged interpolant + exact records (tg_farfield.cuh), then the common tail.  What
+// the pre-pass left travels from L2 one (pair, chain) ahead of the arithmetic (two staging buffers, one barrier per step).
+__device__ __forceinline__ void tg_ff_run(const TgEvalArgs &a, const TgEvalSmem &S, int G, int c0, int b0, int npair, int tid, TgFFStage *stage)
+{
+    TgFFFetch q;
+    tg_ff_fetch(a.ff, c0, b0, tid, q);
+    const int nstep = npair * G;
+    int g = 0, pr = 0;
+    double x[TG_FF_MT], y[TG_FF_MT];
+    int ii[TG_FF_MT];
+    for (int s = 0; s < nstep; s++) {
+        const int bp = b0 + pr * 2 * TG_THREADS * 4;
+        if (g == 0) {
 #pragma unroll
-                for (int j = 0; j < NB; j++) { accf[j] = acc[j]; acc[j] = 0.0; }
-            }
+            for (int j = 0; j < TG_FF_MT; j++) { ii[j] = bp + j * TG_THREADS + tid; x[j] = __ldg(a.x + ii[j]); y[j] = __ldg(a.y + ii[j]); }
         }
-        const int nH = (FF && nfold == 0xff) ? 0 : S.nh[g];
-        for (int k = 0; k < nH; k += 2) {
-            double ta[NB], tb[NB];
-            tg_harvey_t<NB>(S.cls[g * TG_MAXH + k], nz + TG_HS * k, x, a.lnx, ii, ta);
-            const double Ha = nz[TG_HS * k + TG_H_H];
-            if (k + 1 < nH) {
-                tg_harvey_t<NB>(S.cls[g * TG_MAXH + k + 1], nz + TG_HS * (k + 1), x, a.lnx, ii, tb);
-                const double Hb = nz[TG_HS * (k + 1) + TG_H_H];
+        TgFFStage &st = stage[s & 1];
+        tg_ff_stage(st, tid, q);
+        __syncthreads();
+        int gn = g + 1, pn = pr;
+        if (gn == G) { gn = 0; pn++; }
+        if (s + 1 < nstep) tg_ff_fetch(a.ff, c0 + gn, b0 + pn * 2 * TG_THREADS * 4, tid, q);
+        double acc[TG_FF_MT];
 #pragma unroll
-                for (int j = 0; j < NB; j++) acc[j] = fma(fma(Ha, tb[j], Hb * ta[j]), tg_rcp_fast(ta[j] * tb[j]), acc[j]);
-            } else {
-#pragma unroll
-                for (int j = 0; j < NB; j++) acc[j] = fma(Ha, tg_rcp_fast(ta[j]), acc[j]);
-            }
-        }
-        const double N0 = (FF && nfold == 0xff) ? 0.0 : nz[TG_N_N0];
-        double m[NB];
-#pragma unroll
-        for (int j = 0; j < NB; j++) {
-            m[j] = acc[j] + N0;
-            if constexpr (FF) { if (nfold != 0 && nfold != 0xff) m[j] = ((nfold >> j) & 1) ? accf[j] : accf[j] + m[j]; }
-            if (GEN) {
-                const int idx = b0 + j * TG_THREADS + tid;
-                if (idx < Nx) { if (a.model) a.model[(size_t)(c0 + g) * Nx + idx] = m[j]; }
-                else m[j] = 1.0;
-            }
-        }
-        // running results of this thread for chain g over the whole item
-        double sum = S.sum[g * TG_THREADS + tid];     // sum y/m (or chi-square) + logs taken the slow way
-        double pf = S.pf[g * TG_THREADS + tid];       // product of the model values: pf * 2^pe, pf in [1,2)
-        int pe = S.pe[g * TG_THREADS + tid];
-        if (a.d.like_case == 0) {                 // likelihoods.cpp:23
-#pragma unroll
-            for (int j0 = 0; j0 < NB; j0 += 4) {
-                double mm[4], yy[4];
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const bool in = (j0 + u < NB);
-                    mm[u] = in ? m[in ? (j0 + u) : 0] : 1.0;
-                    yy[u] = in ? y[in ? (j0 + u) : 0] : 0.0;
-                }
-                const double p01 = mm[0] * mm[1], p23 = mm[2] * mm[3], P = p01 * p23;
-                // all four positive (sign bits clear) and the product a normal number far from the range ends
-                const int sgn = __double2hiint(mm[0]) | __double2hiint(mm[1]) | __double2hiint(mm[2]) | __double2hiint(mm[3]);
-                const int hiP = __double2hiint(P);
-                const int eP = (hiP >> 20) & 0x7ff;
-                if (sgn >= 0 && (unsigned)(eP - 200) < 1646u) {            // 2^-823 < P < 2^823
-                    const double n = fma(fma(yy[0], mm[1], yy[1] * mm[0]), p23, fma(yy[2], mm[3], yy[3] * mm[2]) * p01);
-                    sum = fma(n, tg_rcp_fast(P), sum);
-                    // fold P into the running product; the exponent is kept apart so it can never overflow
-                    pf *= __hiloint2double((hiP & 0x000fffff) | 0x3ff00000, __double2loint(P));      // [1,2) x [1,2)
-                    const int h2 = __double2hiint(pf);
-                    pe += (eP - 1023) + (((h2 >> 20) & 0x7ff) - 1023);
-                    pf = __hiloint2double((h2 & 0x000fffff) | 0x3ff00000, __double2loint(pf));
-                } else {                          // zero / negative / NaN / huge model values: the plain way
-#pragma unroll
-                    for (int u = 0; u < 4; u++) if (j0 + u < NB && (!GEN || b0 + (j0 + u) * TG_THREADS + tid < Nx)) sum += yy[u] * tg_rcp(mm[u]) + log(mm[u]);
-                }
-            }
-        } else {                                  // likelihoods.cpp:36
-#pragma unroll
-            for (int j = 0; j < NB; j++) {
-                const int idx = b0 + j * TG_THREADS + tid;
-                if (!GEN || idx < Nx) {
-                    const double sg = __ldg(a.sig + idx);
-                    const double dd = y[j] - m[j];
-                    sum += (dd * dd) * tg_rcp(sg * sg);
-                }
-            }
-        }
-        S.sum[g * TG_THREADS + tid] = sum; S.pf[g * TG_THREADS + tid] = pf; S.pe[g * TG_THREADS + tid] = pe;
+        for (int j = 0; j < TG_FF_MT; j++) acc[j] = 0.0;
+        const int nfold = tg_ff_pair(st, a.t, a.d.ncomp_max, c0 + g, bp, tid, x, acc);
+        tg_bins_tail<TG_FF_MT, false, true>(a, S, g, c0, bp, tid, x, y, ii, acc, nfold);
+        g = gn; pr = pn;
     }
 }
 
@@ -565,132 +517,6 @@ __device__ void tg_build_lists(const TgEvalArgs &a, const TgEvalSmem &S, int (*s
     __syncthreads();
 }
 
-// Far-field set-up of nmt = 8, 16, 24 or 32 micro-tiles (1..4 pairs of sub-tiles that share the lists tg_build_lists made for the
-// whole span) for the G chains of the unit; whole CTA, five barriers: geometry (xa, xb: first / last abscissa of micro-tile tid,
-// loaded by the caller before the lists were built), far / exact classification of every listed component on every micro-tile,
-// node values of the far sums (+ the background where it is far too) -> Chebyshev coefficients, trailing-coefficient check, final
-// exact masks per component and per quad.  s_nfold[g]: micro-tiles of chain g whose interpolant includes the background and N0.
-__device__ void tg_ff_setup(const TgEvalArgs &a, const TgEvalSmem &S, const int *s_tot, TgFFGeom &geo, double (*s_W)[TG_FF_N + 1], const double *s_tn,
-                            unsigned *s_ffail, unsigned *s_nfold, int *s_nx, int G, int nmt, double xa, double xb)
-{
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, cap = a.list_cap;
-    if (tid < nmt) {
-        const double hw = 0.5 * (xb - xa);
-        geo.xc[tid] = 0.5 * (xa + xb); geo.hw[tid] = hw; geo.ihw[tid] = (hw > 0.0) ? 1.0 / hw : 0.0;
-    }
-    if (tid < TG_MAXG) s_ffail[tid] = 0u;
-    __syncthreads();
-    const unsigned allmt = (nmt >= 32) ? 0xffffffffu : ((1u << nmt) - 1u);
-    // ---- is the background far from the whole span for chain g?  Its poles lie on |x| = 1/a_k (and x = 0 is a branch point of a
-    //      non-integer power): far when the lower edge of the span stays sqrt(r2) half-widths above all of them ----
-    if (tid < G) {
-        const double *nz = S.nz + (size_t)tid * TG_NOISE_STRIDE;
-        const double edge = geo.xc[0] - sqrt(a.ff_r2) * geo.hw[0];
-        bool farn = (edge > 0.0) && (nz[TG_N_GAUSS] == 0.0) && (nz[TG_N_ASYM] == 0.0);
-        const int nH = S.nh[tid];
-        for (int k = 0; k < nH; k++) farn = farn && (nz[TG_HS * k + TG_H_A] * edge >= 1.0);
-        s_nfold[tid] = farn ? allmt : 0u;
-    }
-    // ---- classification, one thread per (component, group of 8 micro-tiles): emask bit m = the window meets micro-tile m,
-    //      fmask bit m = far there: covered by the window and q d^2 + 1 >= r2 w^2 q, i.e. (d^2 + Gamma^2/4) / w^2 >= r2 ----
-    {
-        const int npair = nmt >> 3;
-        int base = 0;
-        for (int g = 0; g < G; g++) base += (s_tot[g] + 3) & ~3;       // listed components of all chains
-        for (int e = tid; e < base * npair; e += TG_THREADS) {
-            int k = e / npair, g = 0;
-            const int pr = e - k * npair;
-            for (; g < G; g++) { const int n4 = (s_tot[g] + 3) & ~3; if (k < n4) break; k -= n4; }
-            const TgComp *q = S.lists + (size_t)g * cap + k;
-            const bool sym = (S.nz[(size_t)g * TG_NOISE_STRIDE + TG_N_ASYM] == 0.0);
-            const int lo = q->lo, hi = q->lo + q->len;
-            const double nu = q->nu, qq = q->q, r2q = a.ff_r2 * qq;
-            unsigned ov = 0u, fr = 0u, cv = 0u;
-#pragma unroll
-            for (int j = 0; j < TG_FF_MT; j++) {
-                const int m = pr * TG_FF_MT + j, t0 = m * TG_THREADS, t1 = t0 + TG_THREADS;
-                const double d = nu - geo.xc[m], w = geo.hw[m];
-                const bool o = (lo < t1) && (hi > t0), c = (lo <= t0) && (hi >= t1);
-                const bool f = sym && c && (w > 0.0) && (fma(qq * d, d, 1.0) >= r2q * (w * w));   // false for NaN
-                ov |= (o ? 1u : 0u) << m; fr |= (f ? 1u : 0u) << m; cv |= (c ? 1u : 0u) << m;
-            }
-            atomicOr(S.emask + (size_t)g * cap + k, ov);               // (zeroed by the caller before the lists were built)
-            atomicOr(S.fmask + (size_t)g * cap + k, fr);
-            atomicOr(S.cvmask + (size_t)g * cap + k, cv);
-        }
-    }
-    __syncthreads();
-    // ---- far sums at the nodes: one thread per (micro-tile, node), the whole list of a chain; two chains interleave ----
-    for (int e = tid; e < nmt * TG_FF_N; e += TG_THREADS) {
-        const int m = e >> 4, i = e & 15;
-        const double xn = fma(geo.hw[m], s_tn[i], geo.xc[m]);
-        for (int g = 0; g < G; g++) {
-            const int n4 = (s_tot[g] + 3) & ~3;
-            const TgComp *L = S.lists + (size_t)g * cap;
-            const unsigned *fm = S.fmask + (size_t)g * cap;
-            double v0 = 0.0, v1 = 0.0;
-#pragma unroll 1
-            for (int k = 0; k < n4; k += 8) {
-#pragma unroll
-                for (int hq = 0; hq < 2; hq++) {
-                    const int kk = k + 4 * hq;
-                    if (kk < n4) {
-                        const double2 a0 = *(const double2 *)&L[kk].nu, a1 = *(const double2 *)&L[kk + 1].nu, a2 = *(const double2 *)&L[kk + 2].nu, a3 = *(const double2 *)&L[kk + 3].nu;
-                        const uint4 f4 = *(const uint4 *)&fm[kk];
-                        const double g0 = ((f4.x >> m) & 1u) ? L[kk].h : 0.0, g1 = ((f4.y >> m) & 1u) ? L[kk + 1].h : 0.0;
-                        const double g2 = ((f4.z >> m) & 1u) ? L[kk + 2].h : 0.0, g3 = ((f4.w >> m) & 1u) ? L[kk + 3].h : 0.0;
-                        const double d0 = xn - a0.x, d1 = xn - a1.x, d2 = xn - a2.x, d3 = xn - a3.x;
-                        const double t0 = fma(d0 * d0, a0.y, 1.0), t1 = fma(d1 * d1, a1.y, 1.0);
-                        const double t2 = fma(d2 * d2, a2.y, 1.0), t3 = fma(d3 * d3, a3.y, 1.0);
-                        const double t01 = t0 * t1, t23 = t2 * t3;
-                        const double n01 = fma(g0, t1, g1 * t0), n23 = fma(g2, t3, g3 * t2);
-                        const double r = fma(n01, t23, n23 * t01) * tg_rcp_fast(t01 * t23);
-                        if (hq == 0) v0 += r; else v1 += r;
-                    }
-                }
-            }
-            double v = v0 + v1;
-            if (s_nfold[g]) v += tg_background_at(S.nz + (size_t)g * TG_NOISE_STRIDE, S.cls + g * TG_MAXH, S.nh[g], xn);
-            S.ffv[((size_t)g * TG_FF_MAXMT + m) * TG_FF_N + i] = v;
-        }
-    }
-    __syncthreads();
-    // ---- node values -> Chebyshev coefficients, one thread per (chain, micro-tile, coefficient); trailing-coefficient check ----
-    for (int e = tid; e < G * nmt * TG_FF_N; e += TG_THREADS) {       // multiples of 128: whole warps run
-        const int g = e / (nmt * TG_FF_N), r = e - g * (nmt * TG_FF_N), m = r >> 4, k = r & 15;
-        const double *v = S.ffv + ((size_t)g * TG_FF_MAXMT + m) * TG_FF_N;
-        double c0 = 0.0, c1 = 0.0, c2 = 0.0, c3 = 0.0;
-#pragma unroll
-        for (int n = 0; n < TG_FF_N; n += 4) { c0 = fma(s_W[k][n], v[n], c0); c1 = fma(s_W[k][n + 1], v[n + 1], c1); c2 = fma(s_W[k][n + 2], v[n + 2], c2); c3 = fma(s_W[k][n + 3], v[n + 3], c3); }
-        const double c = (c0 + c1) + (c2 + c3);
-        const int l0 = lane & 16;
-        const double tail = fabs(__shfl_sync(0xffffffffu, c, l0 + TG_FF_N - 1)) + fabs(__shfl_sync(0xffffffffu, c, l0 + TG_FF_N - 2));
-        const double cz = __shfl_sync(0xffffffffu, c, l0);
-        const bool good = (tail <= TG_FF_TOL * fabs(cz)) && (geo.hw[m] > 0.0);          // false for NaN; 0 <= 0 when nothing is far
-        S.ffc[((size_t)g * TG_FF_MAXMT + m) * TG_FF_N + k] = good ? c : 0.0;
-        if (!good && k == 0) atomicOr(s_ffail + g, 1u << m);
-    }
-    __syncthreads();
-    // ---- final masks: exact = meets the micro-tile and is not (validly) far there; the noise stays folded where the check
-    //      passed; warp g compacts the components of chain g that are exact somewhere (order-preserving) ----
-    if (tid < G) s_nfold[tid] &= ~s_ffail[tid];
-    if (warp < G) {
-        const int g = warp, n4 = (s_tot[g] + 3) & ~3;
-        const unsigned fail = s_ffail[g];
-        int n = 0;
-        for (int k0 = 0; k0 < n4; k0 += 32) {
-            const int k = k0 + lane;
-            unsigned em = 0u;
-            if (k < n4) { const size_t ix = (size_t)g * cap + k; em = S.emask[ix] & ~(S.fmask[ix] & ~fail); S.emask[ix] = em; }
-            const unsigned bal = __ballot_sync(0xffffffffu, em != 0u);
-            if (em != 0u) S.xidx[(size_t)g * cap + n + __popc(bal & ((1u << lane) - 1u))] = k;
-            n += __popc(bal);
-        }
-        if (lane == 0) s_nx[g] = n;
-    }
-    __syncthreads();
-}
-
 // The fused kernel.  grid.x = work units = (item, chain group); an item is a run of sub-tiles of 1024 bins:
 // ONE sub-tile where truncation windows are expected (few chains per unit), long runs in the noise-only
 // parts of the spectrum (more chains per unit).  The unit table is a scheduling hint only: every sub-tile is classified again from the per-chain
@@ -710,13 +536,9 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
     __shared__ double s_tn[TG_MD + TG_MCHK];
     __shared__ double s_lw[TG_MAXG][NW];              // moment path: sum of ln b per chain and warp
     __shared__ unsigned s_fail[32], s_flag[32];       // moment path: chains that take the tile bin by bin / that flag it for the host
-    __shared__ double s_ffW[TG_FF_N][TG_FF_N + 1];    // far-field path: node values -> Chebyshev coefficients (padded rows: lanes read different rows)
-    __shared__ double s_fftn[TG_FF_N];
-    __shared__ TgFFGeom s_geo;
-    __shared__ unsigned s_ffail[TG_MAXG], s_nfold[TG_MAXG];
-    __shared__ int s_nx[TG_MAXG];
 
     __shared__ __align__(16) TgEvalArgs s_args;
+    __shared__ TgFFStage s_ffstage[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int4 unit = __ldg(units + blockIdx.x);
     tg_load_args(&s_args, argv + ((unsigned)unit.w >> TG_UNIT_STAR_SHIFT));
@@ -735,13 +557,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
     S.nz    = (double *)(S.lists + (size_t)cpb * cap);
     S.sum   = S.nz + (size_t)cpb * TG_NOISE_STRIDE;
     S.pf    = S.sum + (size_t)cpb * TG_THREADS;
-    S.ffc   = S.pf + (size_t)cpb * TG_THREADS;
-    S.ffv   = S.ffc + (size_t)cpb * TG_FF_MAXMT * TG_FF_N;
-    S.emask = (unsigned *)(S.ffv + (size_t)cpb * TG_FF_MAXMT * TG_FF_N);   // 16-byte aligned: everything before it is a multiple of 16 bytes per chain
-    S.fmask = S.emask + (size_t)cpb * cap;
-    S.cvmask = S.fmask + (size_t)cpb * cap;
-    S.xidx  = (int *)(S.cvmask + (size_t)cpb * cap);
-    S.pe    = S.xidx + (size_t)cpb * cap;
+    S.pe    = (int *)(S.pf + (size_t)cpb * TG_THREADS);
     S.full  = S.pe + (size_t)cpb * TG_THREADS;
     S.cls   = S.full + (size_t)cpb * (cap >> 2);
     S.nh    = S.cls + (size_t)cpb * TG_MAXH;
@@ -751,8 +567,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
     const bool use_mom = (a.mom != nullptr) && (a.d.like_case == 0) && (a.model == nullptr) && (a.d.model_case > 1);
     if (tid < TG_MAXG * NW) (&s_lw[0][0])[tid] = 0.0;
     bool we_loaded = false;                       // the interpolation matrices are staged by the first moment tile of the unit (most units have none)
-    bool ff_loaded = false;                       // likewise the far-field matrix, by the first pair of sub-tiles under truncation windows
-    const bool use_ff = (a.ffw != nullptr);
+    const bool ff_on = (a.ff.c != nullptr) && (a.model == nullptr);
     tg_pdl_wait();                                // everything above (unit table, shared-memory set-up) may overlap the proposal kernel
     tg_pdl_trigger();
     for (int e = tid; e < G * TG_NOISE_STRIDE; e += TG_THREADS) S.nz[e] = a.t.noise[(size_t)c0 * TG_NOISE_STRIDE + e];
@@ -768,6 +583,8 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
     int wlo = 0x7fffffff, whi = 0;                // union of the group's windows
     for (int g = 0; g < G; g++) if (s_w[1][g] > s_w[0][g]) { wlo = min(wlo, s_w[0][g]); whi = max(whi, s_w[1][g]); }
     const bool gen_all = (a.model != nullptr) || (a.d.model_case <= 1);
+    bool sym_all = true;                          // no chain of the unit has an asymmetric profile
+    for (int g = 0; g < G; g++) sym_all = sym_all && (S.nz[(size_t)g * TG_NOISE_STRIDE + TG_N_ASYM] == 0.0);
     __syncthreads();
 #ifdef TG_PROFILE
     if (tid == 0 && dbg_id < TG_DBG_CTAS) tg_dbg_cta[dbg_id][1] = clock64();
@@ -806,37 +623,13 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
         if (!gen_all && sub + 1 < item.y && b0 + 2 * SUB <= Nx && wlo < b0 + 2 * SUB && whi > b0) {
             // truncation windows meet this pair of sub-tiles: 8 bins per thread against one list (half the list traffic and
             // loop overhead per bin, twice the independent work per warp behind every reciprocal)
-            if (use_ff) {
-                // up to four pairs share one list and one far-field set-up (the windows are many sub-tiles wide)
+            // inside the range the pre-pass covered (and no chain of the unit with an asymmetric profile): no lists at all, and
+            // every following pair of the item that lies inside it too (whether windows meet it or not) in the same run
+            if (ff_on && sym_all && (b0 >> 8) >= a.ff.mt0 && (b0 >> 8) + TG_FF_MT <= a.ff.mt0 + a.ff.nmt) {
                 int npair = 1;
-                while (npair < TG_FF_MAXP && sub + 2 * (npair + 1) <= item.y && b0 + 2 * (npair + 1) * SUB <= Nx) npair++;
-                const int nmt = npair * TG_FF_MT;
-                double ffxa = 0.0, ffxb = 0.0;        // ends of micro-tile tid: in flight while the lists are built
-                if (tid < nmt) { ffxa = __ldg(a.x + b0 + tid * TG_THREADS); ffxb = __ldg(a.x + b0 + tid * TG_THREADS + TG_THREADS - 1); }
-#ifdef TG_PROFILE
-                const long long ck0 = clock64();
-#endif
-                __syncthreads();                  // the masks of the previous span are dead
-                for (int e = tid; e < G * cap; e += TG_THREADS) { S.emask[e] = 0u; S.fmask[e] = 0u; S.cvmask[e] = 0u; }
-                tg_build_lists(a, S, s_cnt, s_tot, G, c0, b0, 2 * SUB * npair);
-#ifdef TG_PROFILE
-                const long long ck1 = clock64();
-#endif
-                if (!ff_loaded) {                 // constants of the library, not of the step
-                    (&s_ffW[0][0])[(tid >> 4) * (TG_FF_N + 1) + (tid & 15)] = a.ffw[tid];
-                    if (tid < TG_FF_N) s_fftn[tid] = a.ffw[TG_FF_N * TG_FF_N + tid];
-                    ff_loaded = true;
-                }
-                tg_ff_setup(a, S, s_tot, s_geo, s_ffW, s_fftn, s_ffail, s_nfold, s_nx, G, nmt, ffxa, ffxb);
-#ifdef TG_PROFILE
-                if (tid == 0 && dbg_id < TG_DBG_CTAS) {
-                    long long ex = 0, qa = 0;
-                    for (int g = 0; g < G; g++) { const int n4 = (s_tot[g] + 3) & ~3; for (int q = 0; q < n4; q++) { ex += __popc(S.emask[(size_t)g * cap + q]); qa += nmt; } }
-                    tg_dbg_ff[dbg_id][0] += ck1 - ck0; tg_dbg_ff[dbg_id][1] += clock64() - ck1; tg_dbg_ff[dbg_id][2] += ex; tg_dbg_ff[dbg_id][3] += qa;
-                }
-#endif
-                for (int pr = 0; pr < npair; pr++)
-                    tg_chain_loop<8, false, true, true>(a, S, s_tot, G, c0, b0 + pr * 2 * SUB, tid, 0xffffffffu, &s_geo, s_nfold, pr * TG_FF_MT, s_nx);
+                while (sub + 2 * (npair + 1) <= item.y && b0 + 2 * (npair + 1) * SUB <= Nx && (b0 >> 8) + (npair + 1) * TG_FF_MT <= a.ff.mt0 + a.ff.nmt) npair++;
+                __syncthreads();                  // the staging buffers of an earlier run are dead
+                tg_ff_run(a, S, G, c0, b0, npair, tid, s_ffstage);
                 sub += 2 * npair;
             } else {
                 tg_build_lists(a, S, s_cnt, s_tot, G, c0, b0, 2 * SUB);

@@ -1,0 +1,391 @@
+// tg_farfield.cuh -- far field of the truncated Lorentzian sums (the part of the fused kernel under the truncation windows).
+//
+// Reference arithmetic being reproduced: build_lorentzian.cpp:61-102 (profile h/(1+4(x-nu)^2/Gamma^2)), :365-460 (window
+// [imin, imax) of every m-component).  Inside the windows ~30 components overlap on every bin, but all except one or two are
+// many line widths away and vary slowly across a few hundred bins.  A micro-tile is 256 consecutive bins (half-width w, centre
+// xc).  A component whose window covers the micro-tile and whose poles nu +- i Gamma/2 lie at least R w from xc is analytic
+// inside the Bernstein ellipse of parameter rho >= R + sqrt(R^2 - 1) of the micro-tile: its interpolant at TG_FF_N = 16
+// Chebyshev nodes is exact to rounding (<= 7e-15 of the component's own value at R = 5, 2e-15 at R = 6; R^2 = ff_r2 = 30.25).
+//
+//   pre-pass  tg_k_ff   one warp per (chain, micro-tile): classifies the chain's components (far / exact / not there), sums
+//                       the far ones (+ the noise background where its poles are far too) at the 16 nodes, turns the node
+//                       values into Chebyshev coefficients, checks the trailing coefficients, and leaves in HBM per
+//                       (chain, micro-tile): 16 coefficients, a header, and the records (nu, 4/Gamma^2, height, window) of the
+//                       components to be evaluated exactly there (near ones, and those whose window edge cuts the micro-tile);
+//   fused kernel        per bin: one Clenshaw recurrence (30 FP64 instructions) + the exact records of its micro-tile, window
+//                       predicate included -- the windows stay bin-exact -- instead of ~30 profile evaluations (6.25 each).
+//
+// Nothing is assumed about the parameters: the classification is a function of (nu, Gamma, window) and the grid alone; a
+// micro-tile whose trailing coefficients are not small (|c14| + |c15| > TG_FF_TOL |c0|: NaN parameters, ...) or that has more
+// exact components than a record holds is marked and evaluated by the fused kernel component by component from the chain's
+// table (slow, exact, never taken in the tests' workloads).  Chains with an asymmetric profile, spectra whose abscissae do not
+// increase, and the model-output (parity / getmodel) calls do not use the path at all.
+#pragma once
+#include "tg_internal.cuh"
+
+#define TG_FF_N    16                  // Chebyshev nodes / coefficients per micro-tile
+#define TG_FF_MT   8                   // micro-tiles of a pair of sub-tiles == bins per thread of the fused kernel there
+#define TG_FF_BINS 256                 // bins per micro-tile == threads of the fused kernel
+#define TG_FF_E    32                  // exact components a micro-tile record holds
+#define TG_FF_TOL  1.0e-12
+#define TG_FF_HDR  (TG_FF_N * TG_FF_N + TG_FF_N)   // doubles of the constant buffer: node values -> coefficients [k][i], then the nodes
+#define TG_FF_FALLBACK (-1)
+
+struct __align__(16) TgFFRec { double nu, q, h; int lo, len; };            // 32 bytes; window [lo, lo+len) in LOCAL bin indices
+struct __align__(16) TgFFHdr { int count; unsigned pred; int flags; int nfar; };   // count: records, or TG_FF_FALLBACK; pred bit e: record e needs
+                                                                            // the window predicate; flags bit 0: background + N0 folded in
+struct __align__(16) TgFFGeo { double xc, hw, ihw, pad; };                 // centre, half-width, 1/half-width of a micro-tile (constants of the spectrum)
+
+struct TgFFView {                      // what the fused kernel reads (part of its per-star argument record)
+    const double  *c;                  // [B][stride][TG_FF_N]
+    const TgFFHdr *hdr;                // [B][stride]
+    const TgFFRec *rec;                // [B][stride][TG_FF_E]
+    const TgFFGeo *geo;                // [Nx / 256]  (global micro-tile index = bin >> 8)
+    int            stride;             // micro-tiles per chain the buffers hold
+    int            mt0, nmt;           // micro-tiles [mt0, mt0 + nmt) were prepared by the pre-pass of this launch
+    int            pad_;
+};
+
+struct TgFFArgs {                      // per-star argument record of the pre-pass
+    TgDesc         d;
+    TgTables       t;
+    const double  *ffw;                // constant buffer (TG_FF_HDR doubles)
+    double         r2;
+    double        *c; TgFFHdr *hdr; TgFFRec *rec; const TgFFGeo *geo;
+    int            stride, mt0, nmt, B;
+};
+
+__global__ void tg_k_ffgeo(const double *x, int Nx, TgFFGeo *geo, int nmt)
+{
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= nmt) return;
+    TgFFGeo g; g.xc = 0.0; g.hw = 0.0; g.ihw = 0.0; g.pad = 0.0;
+    if ((m + 1) * TG_FF_BINS <= Nx) {
+        const double xa = x[m * TG_FF_BINS], xb = x[m * TG_FF_BINS + TG_FF_BINS - 1];
+        g.xc = 0.5 * (xa + xb); g.hw = 0.5 * (xb - xa); g.ihw = (g.hw > 0.0) ? 1.0 / g.hw : 0.0;
+    }
+    geo[m] = g;
+}
+
+// Exact background at one abscissa from a noise table in shared memory (same arithmetic as the fused kernel's bin-by-bin path up
+// to the shared reciprocals): N0 + sum_k H_k / (1 + (a_k x)^p_k)
+__device__ __forceinline__ double tg_ff_background(const double *nz, const int *cls, int nH, double x)
+{
+    double acc = 0.0;
+    for (int k = 0; k < nH; k++) {
+        const double *q = nz + TG_HS * k;
+        const double ap = q[TG_H_AP];
+        double t;
+        switch (cls[k]) {
+        case 0: t = 2.0; break;
+        case 1: t = fma(ap, x, 1.0); break;
+        case 2: t = fma(ap * x, x, 1.0); break;
+        case 3: t = fma((ap * x) * x, x, 1.0); break;
+        case 4: { const double x2 = x * x; t = fma(ap * x2, x2, 1.0); break; }
+        default: t = exp(q[TG_H_P] * (q[TG_H_LNA] + log(x))) + 1.0; break;
+        }
+        acc = fma(q[TG_H_H], tg_rcp(t), acc);
+    }
+    return acc + nz[TG_N_N0];
+}
+
+// Dynamic shared memory of the pre-pass for tables of ncm components: the chain's table (nu, q, h, lo, hi), the pair-level lists
+// (pair-far, local) and one mid-far list per warp
+#define TG_FF_SMEM(ncm) ((size_t)(ncm) * (3 * sizeof(double) + 2 * sizeof(int) + (2 + 8) * sizeof(unsigned short)) + 64)
+
+// 16 partial products of the node-values -> coefficients matrix per half-warp, then the two halves: lane k (and k + 16) of the
+// warp returns coefficient k of the values v held by lanes 0..15 (and, identically, 16..31)
+__device__ __forceinline__ double tg_ff_transform(const double (*s_W)[TG_FF_N + 1], double v, int lane)
+{
+    const int i = lane & 15, n0 = (lane >> 4) * (TG_FF_N / 2);
+    double ca = 0.0, cb = 0.0;
+#pragma unroll
+    for (int n = 0; n < TG_FF_N / 2; n += 2) {
+        ca = fma(s_W[i][n0 + n], __shfl_sync(0xffffffffu, v, n0 + n), ca);
+        cb = fma(s_W[i][n0 + n + 1], __shfl_sync(0xffffffffu, v, n0 + n + 1), cb);
+    }
+    const double c = ca + cb;
+    return c + __shfl_xor_sync(0xffffffffu, c, 16);
+}
+
+// The pre-pass.  grid.x = chains of the launch x ctas_per_chain; cmap[chain of the launch] = (star, chain of that star) or NULL
+// (one star, identity); argv[star] = its argument record.  CTA r of a chain takes pair r of the prepared range: the 8 micro-tiles
+// 8r .. 8r+7, one per warp.  Two levels: the components whose poles are far from the whole PAIR (2048 bins) are summed at the 16
+// nodes of the pair by all threads and interpolated once (they are about half of those that overlap it); every warp then sums
+// the components that are far from its micro-tile only, adds the pair's interpolant at its nodes (a polynomial of the same
+// degree: reproduced exactly), and leaves coefficients, header and exact records of its micro-tile in HBM.
+__global__ void __launch_bounds__(256) tg_k_ff(const TgFFArgs *__restrict__ argv, const int2 *__restrict__ cmap, int ctas_per_chain)
+{
+    extern __shared__ __align__(16) unsigned char tg_ff_smem[];
+    __shared__ double s_W[TG_FF_N][TG_FF_N + 1];
+    __shared__ double s_tn[TG_FF_N];
+    __shared__ double s_nz[TG_NOISE_STRIDE];
+    __shared__ int s_cls[TG_MAXH];
+    __shared__ int s_xl[8][TG_FF_E];                                    // exact list of every warp's micro-tile
+    __shared__ double s_part[TG_FF_N][TG_FF_N + 1];                     // pair level: [slice][node]
+    __shared__ double s_cp[TG_FF_N];                                    // pair level: coefficients
+    __shared__ int s_cnt[2][8], s_tot[2];
+    __shared__ __align__(16) TgFFArgs s_args;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int chain_l = blockIdx.x / ctas_per_chain, r = blockIdx.x - chain_l * ctas_per_chain;
+    int2 cm = make_int2(0, chain_l);
+    if (cmap) cm = __ldg(cmap + chain_l);
+    tg_load_args(&s_args, argv + cm.x);
+    const TgFFArgs &a = s_args;
+    const int b = cm.y;
+    const int m_first = r * TG_FF_MT;                                   // within the prepared range
+    if (m_first >= a.nmt) return;                                       // another star of the launch has the longer range
+    const int ncm = a.d.ncomp_max;
+    double *t_nu = (double *)tg_ff_smem, *t_q = t_nu + ncm, *t_h = t_q + ncm;
+    int *t_lo = (int *)(t_h + ncm), *t_hi = t_lo + ncm;
+    unsigned short *l_pf = (unsigned short *)(t_hi + ncm), *l_loc = l_pf + ncm, *l_mid = l_loc + ncm + (size_t)warp * ncm;
+    s_W[tid >> 4][tid & 15] = __ldg(a.ffw + tid);
+    if (tid < TG_FF_N) s_tn[tid] = __ldg(a.ffw + TG_FF_N * TG_FF_N + tid);
+    if (tid < 2) s_tot[tid] = 0;
+    // geometry: the pair (first .. last whole micro-tile of it inside the range) and the warp's micro-tile
+    const int m_last = min(m_first + TG_FF_MT, a.nmt) - 1;
+    const TgFFGeo g0 = a.geo[a.mt0 + m_first], g1 = a.geo[a.mt0 + m_last];
+    const double pxa = g0.xc - g0.hw, pxb = g1.xc + g1.hw, pxc = 0.5 * (pxa + pxb), phw = 0.5 * (pxb - pxa);
+    const int P0 = (a.mt0 + m_first) * TG_FF_BINS, P1 = (a.mt0 + m_last + 1) * TG_FF_BINS;
+    const bool geo_ok = (g0.hw > 0.0) && (g1.hw > 0.0) && (phw > 0.0);
+    tg_pdl_wait();                                                      // the tables of the proposed points are complete
+    tg_pdl_trigger();
+    // (one round trip: the noise table, the component count and the first 256 entries of the table are requested together)
+    int lo_r = 0, hi_r = 0;
+    double nu_r = 0.0, q_r = 0.0, h_r = 0.0;
+    if (tid < ncm) { const size_t e = (size_t)b * ncm + tid; lo_r = a.t.lo[e]; hi_r = a.t.hi[e]; nu_r = a.t.nu[e]; q_r = a.t.q[e]; h_r = a.t.h[e]; }
+    if (tid < TG_NOISE_STRIDE) s_nz[tid] = a.t.noise[(size_t)b * TG_NOISE_STRIDE + tid];
+    const int ncomp = min(a.t.ncomp[b], ncm);
+    __syncthreads();
+    if (tid < TG_MAXH) s_cls[tid] = (int)s_nz[TG_HS * tid + TG_H_CLS];
+    const int nH = (int)s_nz[TG_N_NH];
+    const bool sym = (s_nz[TG_N_ASYM] == 0.0) && (s_nz[TG_N_GAUSS] == 0.0);
+    // ---- the chain's table -> shared memory; pair-level classification: pair-far / local (meets the pair, not pair-far) ----
+    for (int k0 = 0; k0 < ncomp; k0 += 256) {
+        const int k = k0 + tid;
+        bool pf = false, loc = false;
+        if (k < ncomp) {
+            const size_t e = (size_t)b * ncm + k;
+            const int lo = k0 ? a.t.lo[e] : lo_r, hi = k0 ? a.t.hi[e] : hi_r;
+            const double nu = k0 ? a.t.nu[e] : nu_r, qq = k0 ? a.t.q[e] : q_r;
+            t_lo[k] = lo; t_hi[k] = hi; t_nu[k] = nu; t_q[k] = qq; t_h[k] = k0 ? a.t.h[e] : h_r;
+            const bool ov = (hi > lo) && (lo < P1) && (hi > P0);
+            const double dd = nu - pxc;
+            pf = ov && sym && geo_ok && (lo <= P0) && (hi >= P1) && (fma(qq * dd, dd, 1.0) >= (a.r2 * qq) * (phw * phw));   // false for NaN
+            loc = ov && !pf;
+        }
+        const unsigned bp = __ballot_sync(0xffffffffu, pf), bl = __ballot_sync(0xffffffffu, loc);
+        if (lane == 0) { s_cnt[0][warp] = __popc(bp); s_cnt[1][warp] = __popc(bl); }
+        __syncthreads();
+        int op = s_tot[0], ol = s_tot[1];
+        for (int w = 0; w < warp; w++) { op += s_cnt[0][w]; ol += s_cnt[1][w]; }
+        const unsigned below = (1u << lane) - 1u;
+        if (pf) l_pf[op + __popc(bp & below)] = (unsigned short)k;
+        if (loc) l_loc[ol + __popc(bl & below)] = (unsigned short)k;
+        __syncthreads();
+        if (tid < 2) { int t = s_tot[tid]; for (int w = 0; w < 8; w++) t += s_cnt[tid][w]; s_tot[tid] = t; }
+    }
+    __syncthreads();
+    const int npf = s_tot[0], nloc = s_tot[1];
+    // is the background far from the whole pair?  Its poles lie on |x| = 1/a_k (x = 0: branch point of a non-integer power)
+    const double pedge = pxa - (sqrt(a.r2) - 1.0) * phw;                // = pxc - sqrt(r2) phw
+    bool bg_pair = sym && geo_ok && (pedge > 0.0);
+    for (int k = 0; k < nH; k++) bg_pair = bg_pair && (s_nz[TG_HS * k + TG_H_A] * pedge >= 1.0);
+    // ---- pair level: thread (slice, node) sums every 16th pair-far component at a node of the pair ----
+    {
+        const int i = tid & 15, sl = tid >> 4;
+        const double xn = fma(phw, s_tn[i], pxc);
+        double v = 0.0;
+        for (int e = sl; e < npf; e += 16) {
+            const int k = l_pf[e];
+            const double d = xn - t_nu[k];
+            v = fma(t_h[k], tg_rcp_fast(fma(d * d, t_q[k], 1.0)), v);
+        }
+        if (sl == 15 && bg_pair) v += tg_ff_background(s_nz, s_cls, nH, xn);
+        s_part[sl][i] = v;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        double v = 0.0;
+        if (lane < TG_FF_N) {
+#pragma unroll
+            for (int sl = 0; sl < 16; sl++) v += s_part[sl][lane];      // fixed order
+        }
+        v = __shfl_sync(0xffffffffu, v, lane & 15);
+        const double c = tg_ff_transform(s_W, v, lane);
+        if (lane < TG_FF_N) s_cp[lane] = c;
+    }
+    __syncthreads();
+    // ---- micro-tile level: warp = micro-tile ----
+    const int m = m_first + warp;
+    if (m >= a.nmt) return;
+    const TgFFGeo gm = a.geo[a.mt0 + m];
+    const double xc = gm.xc, hw = gm.hw;
+    const int t0 = (a.mt0 + m) * TG_FF_BINS, t1 = t0 + TG_FF_BINS;
+    const double r2w2 = a.r2 * (hw * hw);
+    int nmid = 0, nex = 0;
+    for (int e0 = 0; e0 < nloc; e0 += 32) {
+        const int e = e0 + lane;
+        bool mid = false, ex = false;
+        int k = 0;
+        if (e < nloc) {
+            k = l_loc[e];
+            const int lo = t_lo[k], hi = t_hi[k];
+            const bool ov = (lo < t1) && (hi > t0), cv = (lo <= t0) && (hi >= t1);
+            const double dd = t_nu[k] - xc, qq = t_q[k];
+            mid = ov && cv && sym && (hw > 0.0) && (fma(qq * dd, dd, 1.0) >= r2w2 * qq);      // far from the micro-tile; false for NaN
+            ex = ov && !mid;
+        }
+        const unsigned bm = __ballot_sync(0xffffffffu, mid), be = __ballot_sync(0xffffffffu, ex);
+        const unsigned below = (1u << lane) - 1u;
+        if (mid) l_mid[nmid + __popc(bm & below)] = (unsigned short)k;
+        if (ex) { const int pos = nex + __popc(be & below); if (pos < TG_FF_E) s_xl[warp][pos] = k; }
+        nmid += __popc(bm); nex += __popc(be);
+    }
+    __syncwarp();
+    const int i = lane & 15, half = lane >> 4;
+    const double xn = fma(hw, s_tn[i], xc);
+    double v0 = 0.0, v1 = 0.0;
+    for (int e = 2 * half; e < nmid; e += 4) {                          // half-warp h: entries 2h, 2h+1, 2h+4, 2h+5, ...
+        const int k0 = l_mid[e];
+        const double d0 = xn - t_nu[k0];
+        v0 = fma(t_h[k0], tg_rcp_fast(fma(d0 * d0, t_q[k0], 1.0)), v0);
+        if (e + 1 < nmid) {
+            const int k1 = l_mid[e + 1];
+            const double d1 = xn - t_nu[k1];
+            v1 = fma(t_h[k1], tg_rcp_fast(fma(d1 * d1, t_q[k1], 1.0)), v1);
+        }
+    }
+    double v = v0 + v1;
+    // the background: with the pair's interpolant, else at this micro-tile's nodes if far from it, else left to the fused kernel
+    bool bg_here = false;
+    if (!bg_pair) {
+        const double edge = xc - sqrt(a.r2) * hw;
+        bg_here = sym && (edge > 0.0) && (hw > 0.0);
+        for (int k = 0; k < nH; k++) bg_here = bg_here && (s_nz[TG_HS * k + TG_H_A] * edge >= 1.0);
+    }
+    if (half == 1) {
+        if (bg_here) v += tg_ff_background(s_nz, s_cls, nH, xn);
+    } else if (geo_ok) {                                                // the pair's interpolant at this node: Clenshaw
+        const double tt = (xn - pxc) / phw, t2 = tt + tt;
+        double b1 = 0.0, b2 = 0.0;
+#pragma unroll
+        for (int k = TG_FF_N - 1; k >= 1; k--) { const double bk = fma(t2, b1, s_cp[k]) - b2; b2 = b1; b1 = bk; }
+        v += fma(tt, b1, s_cp[0]) - b2;
+    }
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    const double c = tg_ff_transform(s_W, v, lane);
+    const double tail = fabs(__shfl_sync(0xffffffffu, c, TG_FF_N - 1)) + fabs(__shfl_sync(0xffffffffu, c, TG_FF_N - 2));
+    const double cz = __shfl_sync(0xffffffffu, c, 0);
+    const bool good_tail = (tail <= TG_FF_TOL * fabs(cz));              // false for NaN; 0 <= 0 when nothing is far
+    const bool good = good_tail && (hw > 0.0) && (nex <= TG_FF_E);
+    const size_t slot = (size_t)b * a.stride + m;
+    if (lane < TG_FF_N) a.c[slot * TG_FF_N + lane] = good ? c : 0.0;
+    unsigned need = 0u;                                                 // exact records (list order), one lane each
+    if (good && lane < nex) {
+        const int k = s_xl[warp][lane];
+        TgFFRec rc; rc.nu = t_nu[k]; rc.q = t_q[k]; rc.h = t_h[k]; rc.lo = t_lo[k]; rc.len = t_hi[k] - rc.lo;
+        need = !((rc.lo <= t0) && (rc.lo + rc.len >= t1));
+        a.rec[slot * TG_FF_E + lane] = rc;
+    }
+    const unsigned pm = __ballot_sync(0xffffffffu, need != 0u);
+    if (lane == 0) {
+        TgFFHdr hd; hd.count = good ? nex : TG_FF_FALLBACK; hd.pred = pm;
+        hd.flags = ((good && (bg_pair || bg_here)) ? 1 : 0) | (good_tail ? 0 : 2) | (nex <= TG_FF_E ? 0 : 4) | (hw > 0.0 ? 0 : 8); hd.nfar = nmid + npf;
+        a.hdr[slot] = hd;
+    }
+}
+
+// ---- fused-kernel side --------------------------------------------------------------------------------------------------
+// What the pre-pass left for one chain on one pair of sub-tiles (8 consecutive micro-tiles), staged in shared memory by the
+// whole CTA in ONE round trip to L2 (three 16-byte loads per thread) and double-buffered over the chains of a unit.
+struct __align__(16) TgFFStage {
+    TgFFRec rec[TG_FF_MT][TG_FF_E];    // 8192 bytes
+    double  c[TG_FF_MT][TG_FF_N];      // 1024 bytes
+    TgFFHdr hdr[TG_FF_MT];             //  128 bytes
+    TgFFGeo geo[TG_FF_MT];             //  256 bytes
+};
+struct TgFFFetch { int4 r0, r1, r2; };
+static_assert(sizeof(TgFFRec) * TG_FF_MT * TG_FF_E == 2 * 16 * 256, "two 16-byte pieces of the records per thread");
+
+__device__ __forceinline__ void tg_ff_fetch(const TgFFView &f, int chain, int b0, int tid, TgFFFetch &q)
+{
+    const int mg = b0 >> 8;
+    const size_t slot0 = (size_t)chain * f.stride + (mg - f.mt0);
+    q.r0 = __ldg((const int4 *)(f.rec + slot0 * TG_FF_E) + tid);
+    q.r2 = __ldg((const int4 *)(f.rec + slot0 * TG_FF_E) + 256 + tid);
+    q.r1 = make_int4(0, 0, 0, 0);
+    if (tid < 64)      q.r1 = __ldg((const int4 *)(f.c + slot0 * TG_FF_N) + tid);
+    else if (tid < 72) q.r1 = __ldg((const int4 *)(f.hdr + slot0) + (tid - 64));
+    else if (tid < 88) q.r1 = __ldg((const int4 *)(f.geo + mg) + (tid - 72));
+}
+__device__ __forceinline__ void tg_ff_stage(TgFFStage &st, int tid, const TgFFFetch &q)
+{
+    ((int4 *)&st.rec[0][0])[tid] = q.r0;
+    ((int4 *)&st.rec[0][0])[256 + tid] = q.r2;
+    if (tid < 64)      ((int4 *)&st.c[0][0])[tid] = q.r1;
+    else if (tid < 72) ((int4 *)&st.hdr[0])[tid - 64] = q.r1;
+    else if (tid < 88) ((int4 *)&st.geo[0])[tid - 72] = q.r1;
+}
+
+// Far + exact parts of chain `chain` on the pair of sub-tiles starting at bin b0 (8 bins per thread, bin j in micro-tile
+// (b0 >> 8) + j) from the staged data: acc[j] += interpolant + exact records.  Returns the mask of micro-tiles whose interpolant
+// includes the background and N0.
+template <int NB>
+__device__ __forceinline__ int tg_ff_pair(const TgFFStage &st, const TgTables &t, int ncm, int chain, int b0, int tid, const double (&x)[NB], double (&acc)[NB])
+{
+    static_assert(NB == TG_FF_MT, "8 bins per thread");
+    int nfold = 0;
+    // Clenshaw, four bins at a time (independent recurrences interleave), the coefficients two per load
+#pragma unroll
+    for (int j0 = 0; j0 < TG_FF_MT; j0 += 4) {
+        double t2[4], b1[4], b2[4], cz[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { const double tt = (x[j0 + u] - st.geo[j0 + u].xc) * st.geo[j0 + u].ihw; t2[u] = tt + tt; b1[u] = 0.0; b2[u] = 0.0; }
+#pragma unroll
+        for (int k = TG_FF_N - 2; k >= 0; k -= 2) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const double2 cc = *(const double2 *)&st.c[j0 + u][k];                                  // (c_k, c_k+1)
+                const double bh = fma(t2[u], b1[u], cc.y) - b2[u];                                      // b_{k+1}
+                if (k > 0) { b2[u] = bh; b1[u] = fma(t2[u], bh, cc.x) - b1[u]; }                         // b_k
+                else { b2[u] = b1[u]; b1[u] = bh; cz[u] = cc.x; }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) acc[j0 + u] += fma(0.5 * t2[u], b1[u], cz[u]) - b2[u];
+    }
+    // exact records of every micro-tile (uniform counts: no divergence).  (Taking record e of all eight micro-tiles in one round,
+    // eight independent chains, was measured and is slower: it costs more registers than it hides latency.)
+#pragma unroll
+    for (int j = 0; j < TG_FF_MT; j++) {
+        const int4 h4 = *(const int4 *)&st.hdr[j];
+        const int cnt = h4.x;
+        nfold |= (h4.z & 1) << j;
+        const int bin = b0 + j * TG_FF_BINS + tid;
+        if (cnt >= 0) {
+#pragma unroll 1
+            for (int e = 0; e < cnt; e++) {
+                const double2 r0 = *(const double2 *)&st.rec[j][e].nu;      // (nu, q)
+                const double d = x[j] - r0.x;
+                const double rr = tg_rcp_fast(fma(d * d, r0.y, 1.0));
+                double hh = st.rec[j][e].h;
+                if (((unsigned)h4.y >> e) & 1u) { const int2 w = *(const int2 *)&st.rec[j][e].lo; hh = ((unsigned)(bin - w.x) < (unsigned)w.y) ? hh : 0.0; }
+                acc[j] = fma(hh, rr, acc[j]);
+            }
+        } else {
+            // marked micro-tile (failed check / too many exact components): every component of the chain, window predicate included
+            const int nc = min(t.ncomp[chain], ncm);
+#pragma unroll 1
+            for (int k = 0; k < nc; k++) {
+                const size_t e = (size_t)chain * ncm + k;
+                const int lo = t.lo[e], hi = t.hi[e];
+                if ((unsigned)(bin - lo) < (unsigned)(hi - lo)) {
+                    const double d = x[j] - t.nu[e];
+                    acc[j] = fma(t.h[e], tg_rcp_fast(fma(d * d, t.q[e], 1.0)), acc[j]);
+                }
+            }
+        }
+    }
+    return nfold;
+}

@@ -21,7 +21,8 @@ EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", 
            "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
            "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_work_profile", "tg_event_record", "tg_event_elapsed_ms",
-           "tg_batch_create", "tg_batch_run", "tg_batch_destroy", "tg_batch_sizes", "tg_batch_kernel_time", "tg_batch_event_record"]
+           "tg_batch_create", "tg_batch_run", "tg_batch_destroy", "tg_batch_sizes", "tg_batch_kernel_time", "tg_batch_event_record",
+           "tg_batch_prepass_time", "tg_prepass_time"]
 # include/tamcmc_outputs.h (host code in the same library)
 EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_close", "tg_restore_read"]
 
@@ -101,6 +102,8 @@ class GpuLibrary:
         L.tg_batch_sizes.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 3
         L.tg_batch_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_double), C.POINTER(C.c_long)]
         L.tg_batch_event_record.argtypes = [C.c_void_p, C.c_int]
+        L.tg_batch_prepass_time.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.tg_prepass_time.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.tg_out_last_error.restype = C.c_char_p
         for name in EXPORTS_OUT[1:]:
             getattr(L, name).restype = C.c_int
@@ -366,6 +369,11 @@ class GpuModelDef:
         self.lib.check(self.lib.lib.tg_kernel_time(self.h, reset, C.byref(n), C.byref(ms), C.byref(tot)))
         return n.value, ms.value, tot.value
 
+    def prepass_time(self):
+        ms = C.c_double(0)
+        self.lib.check(self.lib.lib.tg_prepass_time(self.h, C.byref(ms)))
+        return ms.value
+
 
 class GpuMALA:
     """MALA-shaped driver: ``execute`` runs the sampling loop on the device (MALA.cpp:540-739)."""
@@ -462,6 +470,11 @@ class GpuBatch:
         n, ms, tot = C.c_long(0), C.c_double(0), C.c_long(0)
         self.lib.check(self.lib.lib.tg_batch_kernel_time(self.b, reset, C.byref(n), C.byref(ms), C.byref(tot)))
         return n.value, ms.value, tot.value
+
+    def prepass_time(self):
+        ms = C.c_double(0)
+        self.lib.check(self.lib.lib.tg_batch_prepass_time(self.b, C.byref(ms)))
+        return ms.value
 
     def timer_start(self):
         self.lib.check(self.lib.lib.tg_batch_event_record(self.b, 0))
