@@ -100,7 +100,7 @@ struct tg_batch {
     std::vector<TgProposeArgs> h_pm, h_ps; TgProposeArgs *d_pm = nullptr, *d_ps = nullptr;
     std::vector<TgFinishArgs>  h_fin;  TgFinishArgs  *d_fin = nullptr;
     std::vector<TgFFArgs>      h_ff;   TgFFArgs      *d_ff = nullptr;   // far-field pre-pass
-    int          ff_cpc = 0; size_t ff_smem = 0;
+    int          ff_cpc = 0, ff_ppc = 1; size_t ff_smem = 0;
     int2        *d_cmap = nullptr;
     bool         args_valid = false;
     int          side_rows = 0; size_t propose_smem = 0, eval_smem = 0;
@@ -279,11 +279,20 @@ static TgFFView ff_view(const tg_handle *h, const EvalBuf &b)
 static TgFFArgs ff_args(const tg_handle *h, const EvalBuf &b, int B)
 {
     TgFFArgs a; memset(&a, 0, sizeof(a));
-    a.d = h->d; a.t = b.t; a.ffw = h->ffw; a.r2 = h->ff_r2; a.c = b.ffc; a.hdr = b.ffh; a.rec = b.ffr; a.geo = h->ffgeo;
+    a.d = h->d; a.t = b.t; a.ffw = h->ffw; a.r2 = h->ff_r2; a.rs = std::sqrt(h->ff_r2); a.c = b.ffc; a.hdr = b.ffh; a.rec = b.ffr; a.geo = h->ffgeo;
     a.stride = h->ff_stride; a.mt0 = h->ff_mt0; a.nmt = (h->ffw && b.ffc) ? h->ff_nmt : 0; a.B = B;
     return a;
 }
-static int ff_ctas_per_chain(int nmt) { return (nmt + TG_FF_MT - 1) / TG_FF_MT; }    // one CTA per pair of sub-tiles
+// launch geometry of the pre-pass: pairs of sub-tiles per CTA (the chain's table is staged once per CTA) so that the grid stays at
+// a few waves of 4 CTAs per SM, and CTAs per chain
+static int ff_pairs_per_cta(int nmt, int chains, int n_sm)
+{
+    static const int forced = getenv("TG_FF_PPC") ? atoi(getenv("TG_FF_PPC")) : 0;      // developer knob
+    if (forced > 0) return forced;
+    const long pairs = (long)((nmt + TG_FF_MT - 1) / TG_FF_MT) * chains;
+    return (int)std::max<long>(1, std::min<long>(4, (pairs + (long)n_sm * 2) / ((long)n_sm * 4)));     // about one wave of 4 CTAs per SM, 4 pairs at most (measured: 2 at 10 chains, 3-4 at 80)
+}
+static int ff_ctas_per_chain(int nmt, int ppc) { return ((nmt + TG_FF_MT - 1) / TG_FF_MT + ppc - 1) / ppc; }
 static size_t ff_smem(const tg_handle *h) { return TG_FF_SMEM(std::max(h->d.ncomp_max, 1)); }
 
 // The argument record of the fused kernel for the points held in `b` -> device memory (uploaded only when it changed; never
@@ -326,8 +335,8 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
     const size_t esm = TG_EVAL_SMEM(h->chains_per_block, h->list_cap);
     dim3 grid(u.n);
     if (h->ffw && !model && h->ff_nmt > 0 && b.ffc) {   // far-field pre-pass of the B points (tg_farfield.cuh)
-        const int cpc = ff_ctas_per_chain(h->ff_nmt);
-        tg_k_ff<<<(unsigned)B * cpc, 256, ff_smem(h), h->stream>>>((const TgFFArgs *)b.d_ffargs, (const int2 *)nullptr, cpc);
+        const int ppc = ff_pairs_per_cta(h->ff_nmt, B, h->n_sm), cpc = ff_ctas_per_chain(h->ff_nmt, ppc);
+        tg_k_ff<<<dim3(cpc, B), 256, ff_smem(h), h->stream>>>((const TgFFArgs *)b.d_ffargs, (const int2 *)nullptr, ppc);
         h->n_launch_total++;
     }
     if (h->timing) {
@@ -1062,7 +1071,7 @@ static int batch_sync_args(tg_batch *b)
 {
     const size_t n = b->hs.size();
     std::vector<TgEvalArgs> ev(n); std::vector<TgProposeArgs> pm(n), ps(n); std::vector<TgFinishArgs> fin(n); std::vector<TgFFArgs> ff(n);
-    int cpc = 0; size_t fsm = 0;
+    int cpc = 0, ppc = 1, nmt_max = 0; size_t fsm = 0;
     memset(ev.data(), 0, n * sizeof(TgEvalArgs)); memset(pm.data(), 0, n * sizeof(TgProposeArgs));
     memset(ps.data(), 0, n * sizeof(TgProposeArgs)); memset(fin.data(), 0, n * sizeof(TgFinishArgs)); memset(ff.data(), 0, n * sizeof(TgFFArgs));
     int rows = 0; size_t psm = 0, esm = 0;
@@ -1073,7 +1082,7 @@ static int batch_sync_args(tg_batch *b)
         ea.B = h->s.C; ea.nitems = h->nitems; ea.max_group = h->chains_per_block; ea.list_cap = h->list_cap;
         ea.mom = h->mom; ea.mom_sub = h->mom_sub; ea.mom_fail = h->mom_fail; ea.mom_note = h->mom_note; ea.ff = ff_view(h, h->sp);
         ff[k] = ff_args(h, h->sp, h->s.C);
-        if (ff[k].nmt > 0) { cpc = std::max(cpc, ff_ctas_per_chain(ff[k].nmt)); fsm = std::max(fsm, ff_smem(h)); }
+        if (ff[k].nmt > 0) { nmt_max = std::max(nmt_max, ff[k].nmt); fsm = std::max(fsm, ff_smem(h)); }
         // The adaptation candidates (Robbins-Monro + Cholesky for both outcomes of the decision) depend on the state the previous
         // finish kernel left and on nothing of this step (the CTA of the "accepted" outcome recomputes the proposed point itself),
         // and only the finish kernel needs them: they run on a side stream next to the proposal, the prologue and the fused kernel.
@@ -1091,7 +1100,8 @@ static int batch_sync_args(tg_batch *b)
         f.presummed = b->presummed; f.rec = h->rec; f.record = 1;
     }
     b->side_rows = rows; b->propose_smem = psm; b->eval_smem = esm;
-    if (cpc != b->ff_cpc || fsm != b->ff_smem) { b->ff_cpc = cpc; b->ff_smem = fsm; batch_drop_graph(b); }
+    if (nmt_max > 0) { ppc = ff_pairs_per_cta(nmt_max, b->Ctot, b->hs[0]->n_sm); cpc = ff_ctas_per_chain(nmt_max, ppc); }
+    if (cpc != b->ff_cpc || ppc != b->ff_ppc || fsm != b->ff_smem) { b->ff_cpc = cpc; b->ff_ppc = ppc; b->ff_smem = fsm; batch_drop_graph(b); }
     const bool same = b->args_valid && b->h_ev.size() == n && memcmp(ev.data(), b->h_ev.data(), n * sizeof(TgEvalArgs)) == 0 && memcmp(ff.data(), b->h_ff.data(), n * sizeof(TgFFArgs)) == 0 &&
                       memcmp(pm.data(), b->h_pm.data(), n * sizeof(TgProposeArgs)) == 0 && memcmp(ps.data(), b->h_ps.data(), n * sizeof(TgProposeArgs)) == 0 &&
                       memcmp(fin.data(), b->h_fin.data(), n * sizeof(TgFinishArgs)) == 0;
@@ -1151,7 +1161,7 @@ static int batch_launch_step(tg_batch *b, bool begin, bool end)
                 if (b->ffev_used + 2 > b->ffev_pool.size()) { cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1); b->ffev_pool.push_back(e0); b->ffev_pool.push_back(e1); }
                 cudaEventRecord(b->ffev_pool[b->ffev_used], b->stream);
             }
-            CK(launch_k(tg_k_ff, dim3((unsigned)Ct * b->ff_cpc), dim3(256), b->ff_smem, b->stream, b->pdl && !b->timing, (const TgFFArgs *)b->d_ff, (const int2 *)b->d_cmap, b->ff_cpc));
+            CK(launch_k(tg_k_ff, dim3((unsigned)b->ff_cpc, (unsigned)Ct), dim3(256), b->ff_smem, b->stream, b->pdl && !b->timing, (const TgFFArgs *)b->d_ff, (const int2 *)b->d_cmap, b->ff_ppc));
             b->n_launch_total++;
             if (b->timing) { cudaEventRecord(b->ffev_pool[b->ffev_used + 1], b->stream); b->ffev_used += 2; }
         }
@@ -1560,7 +1570,10 @@ extern "C" int tg_eval_noalloc(tg_handle *h, const double *params, int B, const 
     CK(cudaMemsetAsync(d_sums, 0, (size_t)B * sizeof(double2), h->stream));
     TgProArgs pa{h->d, b.t, b.params, h->pri, h->sw};
     tg_k_prologue<<<B, TG_PRO_THREADS, TG_PRO_SMEM(h->d.Np), h->stream>>>(pa);
-    if (fa.nmt > 0) { const int cpc = ff_ctas_per_chain(fa.nmt); tg_k_ff<<<(unsigned)B * cpc, 256, ff_smem(h), h->stream>>>((const TgFFArgs *)d_ffa, (const int2 *)nullptr, cpc); }
+    if (fa.nmt > 0) {
+        const int ppc = ff_pairs_per_cta(fa.nmt, B, h->n_sm), cpc = ff_ctas_per_chain(fa.nmt, ppc);
+        tg_k_ff<<<dim3(cpc, B), 256, ff_smem(h), h->stream>>>((const TgFFArgs *)d_ffa, (const int2 *)nullptr, ppc);
+    }
     tg_k_eval<<<(unsigned)units.size(), TG_THREADS, TG_EVAL_SMEM(h->chains_per_block, h->list_cap), h->stream>>>((const TgEvalArgs *)d_args, (const int4 *)d_units);
     tg_k_reduce_finalize<<<B, 256, 0, h->stream>>>(h->d, d_pairs, nitems, d_sums, b.T, b.t, b.logL, b.logPrior, b.logPost, b.status);
     CK(cudaGetLastError());

@@ -50,7 +50,7 @@ struct TgFFArgs {                      // per-star argument record of the pre-pa
     TgDesc         d;
     TgTables       t;
     const double  *ffw;                // constant buffer (TG_FF_HDR doubles)
-    double         r2;
+    double         r2, rs;             // (pole distance / half-width)^2 from which a component is far, and its square root
     double        *c; TgFFHdr *hdr; TgFFRec *rec; const TgFFGeo *geo;
     int            stride, mt0, nmt, B;
 };
@@ -108,13 +108,14 @@ __device__ __forceinline__ double tg_ff_transform(const double (*s_W)[TG_FF_N + 
     return c + __shfl_xor_sync(0xffffffffu, c, 16);
 }
 
-// The pre-pass.  grid.x = chains of the launch x ctas_per_chain; cmap[chain of the launch] = (star, chain of that star) or NULL
-// (one star, identity); argv[star] = its argument record.  CTA r of a chain takes pair r of the prepared range: the 8 micro-tiles
-// 8r .. 8r+7, one per warp.  Two levels: the components whose poles are far from the whole PAIR (2048 bins) are summed at the 16
-// nodes of the pair by all threads and interpolated once (they are about half of those that overlap it); every warp then sums
-// the components that are far from its micro-tile only, adds the pair's interpolant at its nodes (a polynomial of the same
-// degree: reproduced exactly), and leaves coefficients, header and exact records of its micro-tile in HBM.
-__global__ void __launch_bounds__(256) tg_k_ff(const TgFFArgs *__restrict__ argv, const int2 *__restrict__ cmap, int ctas_per_chain)
+// The pre-pass.  grid = (CTAs per chain, chains of the launch); cmap[chain of the launch] = (star, chain of that star) or NULL
+// (one star, identity); argv[star] = its argument record.  CTA r of a chain takes the pairs r*ppc .. r*ppc + ppc - 1 of the
+// prepared range, one after the other (the chain's table is staged once), and of each pair the 8 micro-tiles, one per warp.  Two
+// levels: the components whose poles are far from the whole PAIR (2048 bins) are summed at the 16 nodes of the pair by all
+// threads and interpolated once (they are about half of those that overlap it); every warp then sums the components that are
+// far from its micro-tile only, adds the pair's interpolant at its nodes (a polynomial of the same degree: reproduced exactly),
+// and leaves coefficients, header and exact records of its micro-tile in HBM.
+__global__ void __launch_bounds__(256, 4) tg_k_ff(const TgFFArgs *__restrict__ argv, const int2 *__restrict__ cmap, int ppc)
 {
     extern __shared__ __align__(16) unsigned char tg_ff_smem[];
     __shared__ double s_W[TG_FF_N][TG_FF_N + 1];
@@ -124,175 +125,184 @@ __global__ void __launch_bounds__(256) tg_k_ff(const TgFFArgs *__restrict__ argv
     __shared__ int s_xl[8][TG_FF_E];                                    // exact list of every warp's micro-tile
     __shared__ double s_part[TG_FF_N][TG_FF_N + 1];                     // pair level: [slice][node]
     __shared__ double s_cp[TG_FF_N];                                    // pair level: coefficients
-    __shared__ int s_cnt[2][8], s_tot[2];
+    __shared__ int s_cnt[2][8], s_tot[2], s_bgpair;
     __shared__ __align__(16) TgFFArgs s_args;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int chain_l = blockIdx.x / ctas_per_chain, r = blockIdx.x - chain_l * ctas_per_chain;
+    const int chain_l = blockIdx.y;
     int2 cm = make_int2(0, chain_l);
     if (cmap) cm = __ldg(cmap + chain_l);
     tg_load_args(&s_args, argv + cm.x);
     const TgFFArgs &a = s_args;
     const int b = cm.y;
-    const int m_first = r * TG_FF_MT;                                   // within the prepared range
-    if (m_first >= a.nmt) return;                                       // another star of the launch has the longer range
+    if ((int)blockIdx.x * ppc * TG_FF_MT >= a.nmt) return;              // another star of the launch has the longer range
     const int ncm = a.d.ncomp_max;
     double *t_nu = (double *)tg_ff_smem, *t_q = t_nu + ncm, *t_h = t_q + ncm;
     int *t_lo = (int *)(t_h + ncm), *t_hi = t_lo + ncm;
     unsigned short *l_pf = (unsigned short *)(t_hi + ncm), *l_loc = l_pf + ncm, *l_mid = l_loc + ncm + (size_t)warp * ncm;
     s_W[tid >> 4][tid & 15] = __ldg(a.ffw + tid);
     if (tid < TG_FF_N) s_tn[tid] = __ldg(a.ffw + TG_FF_N * TG_FF_N + tid);
-    if (tid < 2) s_tot[tid] = 0;
-    // geometry: the pair (first .. last whole micro-tile of it inside the range) and the warp's micro-tile
-    const int m_last = min(m_first + TG_FF_MT, a.nmt) - 1;
-    const TgFFGeo g0 = a.geo[a.mt0 + m_first], g1 = a.geo[a.mt0 + m_last];
-    const double pxa = g0.xc - g0.hw, pxb = g1.xc + g1.hw, pxc = 0.5 * (pxa + pxb), phw = 0.5 * (pxb - pxa);
-    const int P0 = (a.mt0 + m_first) * TG_FF_BINS, P1 = (a.mt0 + m_last + 1) * TG_FF_BINS;
-    const bool geo_ok = (g0.hw > 0.0) && (g1.hw > 0.0) && (phw > 0.0);
     tg_pdl_wait();                                                      // the tables of the proposed points are complete
     tg_pdl_trigger();
-    // (one round trip: the noise table, the component count and the first 256 entries of the table are requested together)
-    int lo_r = 0, hi_r = 0;
-    double nu_r = 0.0, q_r = 0.0, h_r = 0.0;
-    if (tid < ncm) { const size_t e = (size_t)b * ncm + tid; lo_r = a.t.lo[e]; hi_r = a.t.hi[e]; nu_r = a.t.nu[e]; q_r = a.t.q[e]; h_r = a.t.h[e]; }
+    // ---- the chain's noise table and component table -> shared memory (one round trip) ----
     if (tid < TG_NOISE_STRIDE) s_nz[tid] = a.t.noise[(size_t)b * TG_NOISE_STRIDE + tid];
     const int ncomp = min(a.t.ncomp[b], ncm);
+    for (int k = tid; k < ncm; k += 256) {
+        const size_t e = (size_t)b * ncm + k;
+        t_lo[k] = a.t.lo[e]; t_hi[k] = a.t.hi[e]; t_nu[k] = a.t.nu[e]; t_q[k] = a.t.q[e]; t_h[k] = a.t.h[e];
+    }
     __syncthreads();
     if (tid < TG_MAXH) s_cls[tid] = (int)s_nz[TG_HS * tid + TG_H_CLS];
     const int nH = (int)s_nz[TG_N_NH];
     const bool sym = (s_nz[TG_N_ASYM] == 0.0) && (s_nz[TG_N_GAUSS] == 0.0);
-    // ---- the chain's table -> shared memory; pair-level classification: pair-far / local (meets the pair, not pair-far) ----
-    for (int k0 = 0; k0 < ncomp; k0 += 256) {
-        const int k = k0 + tid;
-        bool pf = false, loc = false;
-        if (k < ncomp) {
-            const size_t e = (size_t)b * ncm + k;
-            const int lo = k0 ? a.t.lo[e] : lo_r, hi = k0 ? a.t.hi[e] : hi_r;
-            const double nu = k0 ? a.t.nu[e] : nu_r, qq = k0 ? a.t.q[e] : q_r;
-            t_lo[k] = lo; t_hi[k] = hi; t_nu[k] = nu; t_q[k] = qq; t_h[k] = k0 ? a.t.h[e] : h_r;
-            const bool ov = (hi > lo) && (lo < P1) && (hi > P0);
-            const double dd = nu - pxc;
-            pf = ov && sym && geo_ok && (lo <= P0) && (hi >= P1) && (fma(qq * dd, dd, 1.0) >= (a.r2 * qq) * (phw * phw));   // false for NaN
-            loc = ov && !pf;
-        }
-        const unsigned bp = __ballot_sync(0xffffffffu, pf), bl = __ballot_sync(0xffffffffu, loc);
-        if (lane == 0) { s_cnt[0][warp] = __popc(bp); s_cnt[1][warp] = __popc(bl); }
-        __syncthreads();
-        int op = s_tot[0], ol = s_tot[1];
-        for (int w = 0; w < warp; w++) { op += s_cnt[0][w]; ol += s_cnt[1][w]; }
-        const unsigned below = (1u << lane) - 1u;
-        if (pf) l_pf[op + __popc(bp & below)] = (unsigned short)k;
-        if (loc) l_loc[ol + __popc(bl & below)] = (unsigned short)k;
-        __syncthreads();
-        if (tid < 2) { int t = s_tot[tid]; for (int w = 0; w < 8; w++) t += s_cnt[tid][w]; s_tot[tid] = t; }
-    }
-    __syncthreads();
-    const int npf = s_tot[0], nloc = s_tot[1];
-    // is the background far from the whole pair?  Its poles lie on |x| = 1/a_k (x = 0: branch point of a non-integer power)
-    const double pedge = pxa - (sqrt(a.r2) - 1.0) * phw;                // = pxc - sqrt(r2) phw
-    bool bg_pair = sym && geo_ok && (pedge > 0.0);
-    for (int k = 0; k < nH; k++) bg_pair = bg_pair && (s_nz[TG_HS * k + TG_H_A] * pedge >= 1.0);
-    // ---- pair level: thread (slice, node) sums every 16th pair-far component at a node of the pair ----
-    {
-        const int i = tid & 15, sl = tid >> 4;
-        const double xn = fma(phw, s_tn[i], pxc);
-        double v = 0.0;
-        for (int e = sl; e < npf; e += 16) {
-            const int k = l_pf[e];
-            const double d = xn - t_nu[k];
-            v = fma(t_h[k], tg_rcp_fast(fma(d * d, t_q[k], 1.0)), v);
-        }
-        if (sl == 15 && bg_pair) v += tg_ff_background(s_nz, s_cls, nH, xn);
-        s_part[sl][i] = v;
-    }
-    __syncthreads();
-    if (warp == 0) {
-        double v = 0.0;
-        if (lane < TG_FF_N) {
-#pragma unroll
-            for (int sl = 0; sl < 16; sl++) v += s_part[sl][lane];      // fixed order
-        }
-        v = __shfl_sync(0xffffffffu, v, lane & 15);
-        const double c = tg_ff_transform(s_W, v, lane);
-        if (lane < TG_FF_N) s_cp[lane] = c;
-    }
-    __syncthreads();
-    // ---- micro-tile level: warp = micro-tile ----
-    const int m = m_first + warp;
-    if (m >= a.nmt) return;
-    const TgFFGeo gm = a.geo[a.mt0 + m];
-    const double xc = gm.xc, hw = gm.hw;
-    const int t0 = (a.mt0 + m) * TG_FF_BINS, t1 = t0 + TG_FF_BINS;
-    const double r2w2 = a.r2 * (hw * hw);
-    int nmid = 0, nex = 0;
-    for (int e0 = 0; e0 < nloc; e0 += 32) {
-        const int e = e0 + lane;
-        bool mid = false, ex = false;
-        int k = 0;
-        if (e < nloc) {
-            k = l_loc[e];
-            const int lo = t_lo[k], hi = t_hi[k];
-            const bool ov = (lo < t1) && (hi > t0), cv = (lo <= t0) && (hi >= t1);
-            const double dd = t_nu[k] - xc, qq = t_q[k];
-            mid = ov && cv && sym && (hw > 0.0) && (fma(qq * dd, dd, 1.0) >= r2w2 * qq);      // far from the micro-tile; false for NaN
-            ex = ov && !mid;
-        }
-        const unsigned bm = __ballot_sync(0xffffffffu, mid), be = __ballot_sync(0xffffffffu, ex);
-        const unsigned below = (1u << lane) - 1u;
-        if (mid) l_mid[nmid + __popc(bm & below)] = (unsigned short)k;
-        if (ex) { const int pos = nex + __popc(be & below); if (pos < TG_FF_E) s_xl[warp][pos] = k; }
-        nmid += __popc(bm); nex += __popc(be);
-    }
-    __syncwarp();
+    const double r2 = a.r2, rs = a.rs;
     const int i = lane & 15, half = lane >> 4;
-    const double xn = fma(hw, s_tn[i], xc);
-    double v0 = 0.0, v1 = 0.0;
-    for (int e = 2 * half; e < nmid; e += 4) {                          // half-warp h: entries 2h, 2h+1, 2h+4, 2h+5, ...
-        const int k0 = l_mid[e];
-        const double d0 = xn - t_nu[k0];
-        v0 = fma(t_h[k0], tg_rcp_fast(fma(d0 * d0, t_q[k0], 1.0)), v0);
-        if (e + 1 < nmid) {
-            const int k1 = l_mid[e + 1];
-            const double d1 = xn - t_nu[k1];
-            v1 = fma(t_h[k1], tg_rcp_fast(fma(d1 * d1, t_q[k1], 1.0)), v1);
+    const double tn_i = s_tn[i];
+
+#pragma unroll 1
+    for (int pq = 0; pq < ppc; pq++) {
+        const int m_first = ((int)blockIdx.x * ppc + pq) * TG_FF_MT;    // within the prepared range
+        if (m_first >= a.nmt) break;
+        // geometry: the pair (first .. last whole micro-tile of it inside the range)
+        const int m_last = min(m_first + TG_FF_MT, a.nmt) - 1;
+        const TgFFGeo g0 = a.geo[a.mt0 + m_first], g1 = a.geo[a.mt0 + m_last];
+        const double pxa = g0.xc - g0.hw, pxb = g1.xc + g1.hw, pxc = 0.5 * (pxa + pxb), phw = 0.5 * (pxb - pxa);
+        const int P0 = (a.mt0 + m_first) * TG_FF_BINS, P1 = (a.mt0 + m_last + 1) * TG_FF_BINS;
+        const bool geo_ok = (g0.hw > 0.0) && (g1.hw > 0.0) && (phw > 0.0);
+        __syncthreads();                                                // the lists of the previous pair are dead
+        if (tid < 2) s_tot[tid] = 0;
+        if (tid == 32) {
+            // is the background far from the whole pair?  Its poles lie on |x| = 1/a_k (x = 0: branch point of a non-integer power)
+            const double pedge = pxc - rs * phw;
+            bool bg = sym && geo_ok && (pedge > 0.0);
+            for (int k = 0; k < nH; k++) bg = bg && (s_nz[TG_HS * k + TG_H_A] * pedge >= 1.0);
+            s_bgpair = bg ? 1 : 0;
         }
-    }
-    double v = v0 + v1;
-    // the background: with the pair's interpolant, else at this micro-tile's nodes if far from it, else left to the fused kernel
-    bool bg_here = false;
-    if (!bg_pair) {
-        const double edge = xc - sqrt(a.r2) * hw;
-        bg_here = sym && (edge > 0.0) && (hw > 0.0);
-        for (int k = 0; k < nH; k++) bg_here = bg_here && (s_nz[TG_HS * k + TG_H_A] * edge >= 1.0);
-    }
-    if (half == 1) {
-        if (bg_here) v += tg_ff_background(s_nz, s_cls, nH, xn);
-    } else if (geo_ok) {                                                // the pair's interpolant at this node: Clenshaw
-        const double tt = (xn - pxc) / phw, t2 = tt + tt;
-        double b1 = 0.0, b2 = 0.0;
+        // ---- pair-level classification: pair-far / local (meets the pair, not pair-far) ----
+        const double r2p = r2 * (phw * phw);
+        for (int k0 = 0; k0 < ncomp; k0 += 256) {
+            const int k = k0 + tid;
+            bool pf = false, loc = false;
+            if (k < ncomp) {
+                const int lo = t_lo[k], hi = t_hi[k];
+                const double dd = t_nu[k] - pxc, qq = t_q[k];
+                const bool ov = (hi > lo) && (lo < P1) && (hi > P0);
+                pf = ov && sym && geo_ok && (lo <= P0) && (hi >= P1) && (fma(qq * dd, dd, 1.0) >= r2p * qq);   // false for NaN
+                loc = ov && !pf;
+            }
+            const unsigned bp = __ballot_sync(0xffffffffu, pf), bl = __ballot_sync(0xffffffffu, loc);
+            if (lane == 0) { s_cnt[0][warp] = __popc(bp); s_cnt[1][warp] = __popc(bl); }
+            __syncthreads();
+            int op = s_tot[0], ol = s_tot[1];
+            for (int w = 0; w < warp; w++) { op += s_cnt[0][w]; ol += s_cnt[1][w]; }
+            const unsigned below = (1u << lane) - 1u;
+            if (pf) l_pf[op + __popc(bp & below)] = (unsigned short)k;
+            if (loc) l_loc[ol + __popc(bl & below)] = (unsigned short)k;
+            __syncthreads();
+            if (tid < 2) { int t = s_tot[tid]; for (int w = 0; w < 8; w++) t += s_cnt[tid][w]; s_tot[tid] = t; }
+        }
+        __syncthreads();
+        const int npf = s_tot[0], nloc = s_tot[1];
+        const bool bg_pair = (s_bgpair != 0);
+        // ---- pair level: thread (slice, node) sums every 16th pair-far component at a node of the pair ----
+        {
+            const int sl = tid >> 4;
+            const double xn = fma(phw, tn_i, pxc);
+            double v = 0.0;
+            for (int e = sl; e < npf; e += 16) {
+                const int k = l_pf[e];
+                const double d = xn - t_nu[k];
+                v = fma(t_h[k], tg_rcp_fast(fma(d * d, t_q[k], 1.0)), v);
+            }
+            if (sl == 15 && bg_pair) v += tg_ff_background(s_nz, s_cls, nH, xn);
+            s_part[sl][i] = v;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            double v = 0.0;
 #pragma unroll
-        for (int k = TG_FF_N - 1; k >= 1; k--) { const double bk = fma(t2, b1, s_cp[k]) - b2; b2 = b1; b1 = bk; }
-        v += fma(tt, b1, s_cp[0]) - b2;
-    }
-    v += __shfl_xor_sync(0xffffffffu, v, 16);
-    const double c = tg_ff_transform(s_W, v, lane);
-    const double tail = fabs(__shfl_sync(0xffffffffu, c, TG_FF_N - 1)) + fabs(__shfl_sync(0xffffffffu, c, TG_FF_N - 2));
-    const double cz = __shfl_sync(0xffffffffu, c, 0);
-    const bool good_tail = (tail <= TG_FF_TOL * fabs(cz));              // false for NaN; 0 <= 0 when nothing is far
-    const bool good = good_tail && (hw > 0.0) && (nex <= TG_FF_E);
-    const size_t slot = (size_t)b * a.stride + m;
-    if (lane < TG_FF_N) a.c[slot * TG_FF_N + lane] = good ? c : 0.0;
-    unsigned need = 0u;                                                 // exact records (list order), one lane each
-    if (good && lane < nex) {
-        const int k = s_xl[warp][lane];
-        TgFFRec rc; rc.nu = t_nu[k]; rc.q = t_q[k]; rc.h = t_h[k]; rc.lo = t_lo[k]; rc.len = t_hi[k] - rc.lo;
-        need = !((rc.lo <= t0) && (rc.lo + rc.len >= t1));
-        a.rec[slot * TG_FF_E + lane] = rc;
-    }
-    const unsigned pm = __ballot_sync(0xffffffffu, need != 0u);
-    if (lane == 0) {
-        TgFFHdr hd; hd.count = good ? nex : TG_FF_FALLBACK; hd.pred = pm;
-        hd.flags = ((good && (bg_pair || bg_here)) ? 1 : 0) | (good_tail ? 0 : 2) | (nex <= TG_FF_E ? 0 : 4) | (hw > 0.0 ? 0 : 8); hd.nfar = nmid + npf;
-        a.hdr[slot] = hd;
+            for (int sl = 0; sl < 16; sl++) v += s_part[sl][i];         // fixed order (both half-warps: the same sums)
+            const double c = tg_ff_transform(s_W, v, lane);
+            if (lane < TG_FF_N) s_cp[lane] = c;
+        }
+        __syncthreads();
+        // ---- micro-tile level: warp = micro-tile ----
+        const int m = m_first + warp;
+        if (m < a.nmt) {
+            const TgFFGeo gm = a.geo[a.mt0 + m];
+            const double xc = gm.xc, hw = gm.hw;
+            const int t0 = (a.mt0 + m) * TG_FF_BINS, t1 = t0 + TG_FF_BINS;
+            const double r2w2 = r2 * (hw * hw);
+            int nmid = 0, nex = 0;
+            for (int e0 = 0; e0 < nloc; e0 += 32) {
+                const int e = e0 + lane;
+                bool mid = false, ex = false;
+                int k = 0;
+                if (e < nloc) {
+                    k = l_loc[e];
+                    const int lo = t_lo[k], hi = t_hi[k];
+                    const bool ov = (lo < t1) && (hi > t0), cv = (lo <= t0) && (hi >= t1);
+                    const double dd = t_nu[k] - xc, qq = t_q[k];
+                    mid = ov && cv && sym && (hw > 0.0) && (fma(qq * dd, dd, 1.0) >= r2w2 * qq);      // far from the micro-tile; false for NaN
+                    ex = ov && !mid;
+                }
+                const unsigned bm = __ballot_sync(0xffffffffu, mid), be = __ballot_sync(0xffffffffu, ex);
+                const unsigned below = (1u << lane) - 1u;
+                if (mid) l_mid[nmid + __popc(bm & below)] = (unsigned short)k;
+                if (ex) { const int pos = nex + __popc(be & below); if (pos < TG_FF_E) s_xl[warp][pos] = k; }
+                nmid += __popc(bm); nex += __popc(be);
+            }
+            __syncwarp();
+            const double xn = fma(hw, tn_i, xc);
+            double v0 = 0.0, v1 = 0.0;
+            for (int e = 2 * half; e < nmid; e += 4) {                  // half-warp h: entries 2h, 2h+1, 2h+4, 2h+5, ...
+                const int k0 = l_mid[e];
+                const double d0 = xn - t_nu[k0];
+                v0 = fma(t_h[k0], tg_rcp_fast(fma(d0 * d0, t_q[k0], 1.0)), v0);
+                if (e + 1 < nmid) {
+                    const int k1 = l_mid[e + 1];
+                    const double d1 = xn - t_nu[k1];
+                    v1 = fma(t_h[k1], tg_rcp_fast(fma(d1 * d1, t_q[k1], 1.0)), v1);
+                }
+            }
+            double v = v0 + v1;
+            // the background: with the pair's interpolant, else at this micro-tile's nodes if far from it, else left to the fused kernel
+            bool bg_here = false;
+            if (!bg_pair) {
+                const double edge = xc - rs * hw;
+                bg_here = sym && (edge > 0.0) && (hw > 0.0);
+                for (int k = 0; k < nH; k++) bg_here = bg_here && (s_nz[TG_HS * k + TG_H_A] * edge >= 1.0);
+            }
+            if (half == 1) {
+                if (bg_here) v += tg_ff_background(s_nz, s_cls, nH, xn);
+            } else if (geo_ok) {                                        // the pair's interpolant at this node: Clenshaw
+                const double tt = (xn - pxc) * tg_rcp(phw), t2 = tt + tt;
+                double b1 = 0.0, b2 = 0.0;
+#pragma unroll
+                for (int k = TG_FF_N - 1; k >= 1; k--) { const double bk = fma(t2, b1, s_cp[k]) - b2; b2 = b1; b1 = bk; }
+                v += fma(tt, b1, s_cp[0]) - b2;
+            }
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            const double c = tg_ff_transform(s_W, v, lane);
+            const double tail = fabs(__shfl_sync(0xffffffffu, c, TG_FF_N - 1)) + fabs(__shfl_sync(0xffffffffu, c, TG_FF_N - 2));
+            const double cz = __shfl_sync(0xffffffffu, c, 0);
+            const bool good_tail = (tail <= TG_FF_TOL * fabs(cz));      // false for NaN; 0 <= 0 when nothing is far
+            const bool good = good_tail && (hw > 0.0) && (nex <= TG_FF_E);
+            const size_t slot = (size_t)b * a.stride + m;
+            if (lane < TG_FF_N) a.c[slot * TG_FF_N + lane] = good ? c : 0.0;
+            unsigned need = 0u;                                         // exact records (list order), one lane each
+            if (good && lane < nex) {
+                const int k = s_xl[warp][lane];
+                TgFFRec rc; rc.nu = t_nu[k]; rc.q = t_q[k]; rc.h = t_h[k]; rc.lo = t_lo[k]; rc.len = t_hi[k] - rc.lo;
+                need = !((rc.lo <= t0) && (rc.lo + rc.len >= t1));
+                a.rec[slot * TG_FF_E + lane] = rc;
+            }
+            const unsigned pm = __ballot_sync(0xffffffffu, need != 0u);
+            if (lane == 0) {
+                TgFFHdr hd; hd.count = good ? nex : TG_FF_FALLBACK; hd.pred = pm;
+                hd.flags = ((good && (bg_pair || bg_here)) ? 1 : 0) | (good_tail ? 0 : 2) | (nex <= TG_FF_E ? 0 : 4) | (hw > 0.0 ? 0 : 8); hd.nfar = nmid + npf;
+                a.hdr[slot] = hd;
+            }
+        }
     }
 }
 
