@@ -308,7 +308,7 @@ def main():
 
     # ---- e2e: the reference-facing call (batched Model_def::generate_model) with HOST buffers, star after star ----
     g = np.random.Generator(np.random.Philox(key=99 + rank))
-    Ke = min(K, 400) if S == 1 else min(K, 100)
+    Ke = min(max(K, 100), 400) if S == 1 else min(K, 100)      # at least 100 calls: a pipeline of 20 would mostly measure its own filling
     tg_eval = lib.lib.tg_eval
     calls = []
     for m_ in mds:
@@ -336,6 +336,29 @@ def main():
     t0 = time.perf_counter()
     for k in range(Ke):
         host_step(3 + k)
+    dt_sync = time.perf_counter() - t0
+    # the same calls in two halves (tg_eval_async / tg_eval_wait, two staging slots per star): the host hands over the vectors of
+    # step k+1 while the GPU evaluates step k -- what a host-side sampler that prepares its next proposal during the evaluation sees
+    ev_async, ev_wait = lib.lib.tg_eval_async, lib.lib.tg_eval_wait
+
+    def submit(k):
+        for (h, p0, nb, cn, pT, po, _) in calls:
+            rc = ev_async(h, p0 + k * nb, cn, pT, k & 1)
+            if rc != 0:
+                lib.check(rc)
+
+    def collect(k):
+        for (h, p0, nb, cn, pT, po, _) in calls:
+            rc = ev_wait(h, k & 1, po[0], po[1], po[2], po[3])
+            if rc != 0:
+                lib.check(rc)
+    barrier(md)
+    t0 = time.perf_counter()
+    submit(3)
+    for k in range(1, Ke):
+        submit(3 + k)
+        collect(3 + k - 1)
+    collect(3 + Ke - 1)
     dt_e2e = time.perf_counter() - t0
     if dist is not None:
         t = torch.tensor([dt_e2e], dtype=torch.float64, device="cuda")
@@ -343,7 +366,9 @@ def main():
         dt_e2e = float(t.item())
     e2e = {"value": world * chains_gpu * Ke / dt_e2e, "unit": "chain-steps/s",
            "h2d_bytes_per_step": chains_gpu * md.Nparams * 8 + chains_gpu * 8, "d2h_bytes_per_step": chains_gpu * (3 * 8 + 4),
-           "call": "tg_eval == batched Model_def::generate_model, pinned host params in, logL/logPrior/logPost/status out, one call per star and step",
+           "call": "tg_eval_async + tg_eval_wait == batched Model_def::generate_model in two halves through two staging slots: pinned host params in, "
+                   "logL/logPrior/logPost/status out, one call per star and step; the host submits step k+1 while step k is evaluated",
+           "blocking_call_value": world * chains_gpu * Ke / dt_sync, "blocking_call": "tg_eval (one blocking call per star and step)",
            "steps": Ke}
     nv = md.Nvars
     for m_ in mds:

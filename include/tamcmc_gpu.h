@@ -113,6 +113,15 @@ int tg_destroy(tg_handle *h);
 int tg_eval(tg_handle *h, const double *params, int B, const double *T,
             double *logL, double *logPrior, double *logPost, int *status, double *model);
 
+/* The same call in two halves, through one of two staging slots (0, 1), so that a host-side sampler (the loop of MALA.cpp:632-655
+ * with its proposal on the host) prepares the parameter vectors of step k+1 while the GPU evaluates step k: tg_eval_async copies
+ * the inputs into the slot's pinned buffer, enqueues the whole call (one graph launch: copy in, kernels, copy out) and returns;
+ * tg_eval_wait blocks until that slot's results have arrived and copies them out.  Calls of a handle are still issued from one
+ * host thread and run on the device in submission order; at most one submission per slot may be outstanding, and two outstanding
+ * submissions must have the same B. */
+int tg_eval_async(tg_handle *h, const double *params, int B, const double *T, int slot);
+int tg_eval_wait(tg_handle *h, int slot, double *logL, double *logPrior, double *logPost, int *status);
+
 /* tg_eval for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
  * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments, meaning
  * and results as tg_eval without the model pointer (HOST buffers in and out), but the call performs no cudaMalloc / cudaFree /

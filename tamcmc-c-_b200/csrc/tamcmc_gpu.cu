@@ -29,6 +29,7 @@ struct EvalBuf {                 // tables + results for a batch of B parameter 
     int      *status = nullptr;
     int       B = 0;               // batch size the pointers above are laid out for
     double   *pin_in = nullptr, *pin_out = nullptr;    // pinned host staging of the same layout
+    double   *pin_in2 = nullptr, *pin_out2 = nullptr;  // second staging slot (tg_eval_async: the host fills one while the GPU works from the other)
     TgEvalArgs *d_args = nullptr;                      // the fused kernel reads its arguments from device memory (tg_load_args)
     TgEvalArgs  h_args;                                // what d_args holds
     bool        args_valid = false;
@@ -72,6 +73,8 @@ struct tg_handle {
     std::vector<int4> items_host;          // bin partition: (first bin, sub-tiles, weight = windows crossing, heavy?)
     bool       no_order = false;
     cudaGraphExec_t ev_graph = nullptr; int ev_graph_B = 0;   // tg_eval: copy in, prologue, fused kernel, reduce+finalize, copy out
+    cudaGraphExec_t ev_graph2 = nullptr;                       // the same through the second staging slot
+    cudaEvent_t ev_done[2] = {nullptr, nullptr}; int slot_B[2] = {0, 0};   // tg_eval_async / tg_eval_wait
     // eval-kernel timing
     bool       timing = false;
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
@@ -156,6 +159,7 @@ extern "C" int tg_dbg_clocks(long long *out) { return cudaMemcpyFromSymbol(out, 
 static void drop_graphs(tg_handle *h)
 {
     if (h->ev_graph) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }
+    if (h->ev_graph2) { cudaGraphExecDestroy(h->ev_graph2); h->ev_graph2 = nullptr; }
     h->items_version++;                                   // batches holding this star re-capture their step graph
 }
 
@@ -165,6 +169,7 @@ static int alloc_evalbuf(tg_handle *h, EvalBuf &b, int B)
     const size_t nc = (size_t)B * h->d.ncomp_max;
     b.cap = B;
     if (h->ev_graph) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }     // the buffers move
+    if (h->ev_graph2) { cudaGraphExecDestroy(h->ev_graph2); h->ev_graph2 = nullptr; }
     DA(b.t.nu, nc); DA(b.t.h, nc); DA(b.t.q, nc); DA(b.t.ifc, nc); DA(b.t.t2sq, nc); DA(b.t.lo, nc); DA(b.t.hi, nc);
     DA(b.t.ncomp, B); DA(b.t.wlo, B); DA(b.t.whi, B); DA(b.t.noise, (size_t)B * TG_NOISE_STRIDE); DA(b.t.status, B); DA(b.t.pstatus, B); DA(b.t.work, B); DA(b.t.logprior, B);
     DA(b.in, (size_t)B * (h->d.Np + 1)); DA(b.out, (size_t)B * 4);
@@ -176,8 +181,12 @@ static int alloc_evalbuf(tg_handle *h, EvalBuf &b, int B)
     }
     if (b.pin_in) cudaFreeHost(b.pin_in);
     if (b.pin_out) cudaFreeHost(b.pin_out);
+    if (b.pin_in2) cudaFreeHost(b.pin_in2);
+    if (b.pin_out2) cudaFreeHost(b.pin_out2);
     CK(cudaHostAlloc((void **)&b.pin_in, (size_t)B * (h->d.Np + 1) * 8, cudaHostAllocDefault));
     CK(cudaHostAlloc((void **)&b.pin_out, (size_t)B * 4 * 8, cudaHostAllocDefault));
+    CK(cudaHostAlloc((void **)&b.pin_in2, (size_t)B * (h->d.Np + 1) * 8, cudaHostAllocDefault));
+    CK(cudaHostAlloc((void **)&b.pin_out2, (size_t)B * 4 * 8, cudaHostAllocDefault));
     b.layout(B, h->d.Np);
     return TG_OK;
 }
@@ -336,7 +345,7 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
     dim3 grid(u.n);
     if (h->ffw && !model && h->ff_nmt > 0 && b.ffc) {   // far-field pre-pass of the B points (tg_farfield.cuh)
         const int ppc = ff_pairs_per_cta(h->ff_nmt, B, h->n_sm), cpc = ff_ctas_per_chain(h->ff_nmt, ppc);
-        tg_k_ff<<<dim3(cpc, B), 256, ff_smem(h), h->stream>>>((const TgFFArgs *)b.d_ffargs, (const int2 *)nullptr, ppc);
+        CK(launch_k(tg_k_ff, dim3(cpc, B), dim3(256), ff_smem(h), h->stream, pdl && !h->timing, (const TgFFArgs *)b.d_ffargs, (const int2 *)nullptr, ppc));
         h->n_launch_total++;
     }
     if (h->timing) {
@@ -780,7 +789,8 @@ extern "C" int tg_destroy(tg_handle *h)
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
     for (void *q : h->allocs) cudaFree(q);
-    for (EvalBuf *b : {&h->sp, &h->ev}) { if (b->pin_in) cudaFreeHost(b->pin_in); if (b->pin_out) cudaFreeHost(b->pin_out); }
+    for (EvalBuf *b : {&h->sp, &h->ev}) { if (b->pin_in) cudaFreeHost(b->pin_in); if (b->pin_out) cudaFreeHost(b->pin_out); if (b->pin_in2) cudaFreeHost(b->pin_in2); if (b->pin_out2) cudaFreeHost(b->pin_out2); }
+    for (int k = 0; k < 2; k++) if (h->ev_done[k]) cudaEventDestroy(h->ev_done[k]);
     if (h->mom_note) cudaFreeHost(h->mom_note);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -811,11 +821,12 @@ extern "C" int tg_eval_upload(tg_handle *h, const double *params, int B, const d
     return TG_OK;
 }
 
-static int eval_resident(tg_handle *h, int B, double *model_dev)
+static int eval_resident(tg_handle *h, int B, double *model_dev, bool pdl = false)
 {
     if (B < 1 || B != h->ev.B) return fail(TG_E_BADARG, "tg_eval_resident: B differs from the uploaded batch");
-    int r = launch_eval_kernels(h, h->ev, h->ev.params, B, model_dev, true, false); if (r) return r;
-    tg_k_reduce_finalize<<<B, 256, 0, h->stream>>>(h->d, h->ev.partials, h->nitems, h->ev.sums, h->ev.T, h->ev.t, h->ev.logL, h->ev.logPrior, h->ev.logPost, h->ev.status);
+    int r = launch_eval_kernels(h, h->ev, h->ev.params, B, model_dev, true, false, pdl); if (r) return r;
+    CK(launch_k(tg_k_reduce_finalize, dim3(B), dim3(256), 0, h->stream, pdl && !h->timing, h->d, (const double2 *)h->ev.partials, h->nitems, h->ev.sums, (const double *)h->ev.T, h->ev.t,
+                h->ev.logL, h->ev.logPrior, h->ev.logPost, h->ev.status));
     h->n_launch_total++;
     CK(cudaGetLastError());
     return TG_OK;
@@ -843,45 +854,85 @@ extern "C" int tg_eval_fetch(tg_handle *h, int B, double *logL, double *logPrior
     return TG_OK;
 }
 
+// The whole batched generate_model call as ONE graph launch through staging slot `slot` (0 or 1): H2D of the packed inputs,
+// prologue, far-field pre-pass, fused kernel, reduce+finalize, D2H of the packed results.  eval_submit returns once the work is
+// enqueued; eval_collect blocks until that slot's results are in its pinned buffer.
+static int eval_submit(tg_handle *h, const double *params, int B, const double *T, int slot)
+{
+    CK(cudaSetDevice(h->device));
+    { int r = alloc_evalbuf(h, h->ev, B); if (r) return r; }
+    EvalBuf &b = h->ev;
+    if (b.B != B) { CK(cudaStreamSynchronize(h->stream)); b.layout(B, h->d.Np); }
+    if (h->ev_graph_B != B) {
+        if (h->ev_graph) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }
+        if (h->ev_graph2) { cudaGraphExecDestroy(h->ev_graph2); h->ev_graph2 = nullptr; }
+    }
+    cudaGraphExec_t &ge = slot ? h->ev_graph2 : h->ev_graph;
+    double *pin = slot ? b.pin_in2 : b.pin_in, *pout = slot ? b.pin_out2 : b.pin_out;
+    if (!ge) {
+        if (h->u_ev.B != B) { int r = build_units(h, h->u_ev, B); if (r) return r; }
+        { int r = sync_eval_args(h, b, nullptr, B); if (r) return r; }        // not inside the capture
+        cudaGraph_t g;
+        const long lt = h->n_launch_total, le = h->n_eval_launch;
+        CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+        cudaMemcpyAsync(b.in, pin, (size_t)B * (h->d.Np + 1) * 8, cudaMemcpyHostToDevice, h->stream);
+        int r = eval_resident(h, B, nullptr, getenv("TG_PDL") ? atoi(getenv("TG_PDL")) != 0 : true);
+        cudaMemcpyAsync(pout, b.out, (size_t)B * 28, cudaMemcpyDeviceToHost, h->stream);
+        cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
+        h->n_launch_total = lt; h->n_eval_launch = le;
+        if (r) return r;
+        CK(ce);
+        CK(cudaGraphInstantiate(&ge, g, 0));
+        cudaGraphDestroy(g);
+        h->ev_graph_B = B;
+    }
+    memcpy(pin, params, (size_t)B * h->d.Np * 8);
+    memcpy(pin + (size_t)B * h->d.Np, T, (size_t)B * 8);
+    CK(cudaGraphLaunch(ge, h->stream));
+    h->n_launch_total += 3 + ((h->ffw && h->ff_nmt > 0) ? 1 : 0); h->n_eval_launch += 1;
+    if (!h->ev_done[slot]) CK(cudaEventCreateWithFlags(&h->ev_done[slot], cudaEventDisableTiming));
+    CK(cudaEventRecord(h->ev_done[slot], h->stream));
+    h->slot_B[slot] = B;
+    return TG_OK;
+}
+static int eval_collect(tg_handle *h, int slot, double *logL, double *logPrior, double *logPost, int *status)
+{
+    const int B = h->slot_B[slot];
+    if (B < 1 || !h->ev_done[slot]) return fail(TG_E_BADARG, "tg_eval_wait: nothing was submitted through this slot");
+    CK(cudaSetDevice(h->device));
+    CK(cudaEventSynchronize(h->ev_done[slot]));
+    const double *pout = slot ? h->ev.pin_out2 : h->ev.pin_out;
+    if (logL) memcpy(logL, pout, (size_t)B * 8);
+    if (logPrior) memcpy(logPrior, pout + B, (size_t)B * 8);
+    if (logPost) memcpy(logPost, pout + 2 * (size_t)B, (size_t)B * 8);
+    if (status) memcpy(status, pout + 3 * (size_t)B, (size_t)B * 4);
+    h->slot_B[slot] = 0;
+    return TG_OK;
+}
+
+extern "C" int tg_eval_async(tg_handle *h, const double *params, int B, const double *T, int slot)
+{
+    if (!h || !params || !T || B < 1 || slot < 0 || slot > 1) return fail(TG_E_BADARG, "tg_eval_async: bad argument");
+    if (h->slot_B[slot] != 0) return fail(TG_E_BADARG, "tg_eval_async: this slot still holds results that were not collected (tg_eval_wait)");
+    if (h->slot_B[1 - slot] != 0 && h->slot_B[1 - slot] != B) return fail(TG_E_BADARG, "tg_eval_async: the two slots in flight must hold batches of the same size");
+    if (h->slot_B[1 - slot] == 0) { int r = refresh_items_if_flagged(h); if (r) return r; }      // (scheduling only; never with work in flight)
+    if (!h->use_graph || h->timing) return fail(TG_E_UNSUPPORTED, "tg_eval_async needs the graph path (tg_set_tuning use_graph = 1, no kernel timing)");
+    return eval_submit(h, params, B, T, slot);
+}
+extern "C" int tg_eval_wait(tg_handle *h, int slot, double *logL, double *logPrior, double *logPost, int *status)
+{
+    if (!h || slot < 0 || slot > 1) return fail(TG_E_BADARG, "tg_eval_wait: bad argument");
+    return eval_collect(h, slot, logL, logPrior, logPost, status);
+}
+
 extern "C" int tg_eval(tg_handle *h, const double *params, int B, const double *T,
                        double *logL, double *logPrior, double *logPost, int *status, double *model)
 {
     if (!h || !params || !T || B < 1) return fail(TG_E_BADARG, "tg_eval: bad argument");
     { int r = refresh_items_if_flagged(h); if (r) return r; }
     if (!model && h->use_graph && !h->timing) {
-        // the whole call as one graph launch: H2D of the packed inputs, prologue, fused kernel, reduce+finalize, D2H of the packed results
-        CK(cudaSetDevice(h->device));
-        { int r = alloc_evalbuf(h, h->ev, B); if (r) return r; }
-        EvalBuf &b = h->ev;
-        if (b.B != B) { CK(cudaStreamSynchronize(h->stream)); b.layout(B, h->d.Np); }
-        if (h->ev_graph && h->ev_graph_B != B) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }
-        if (!h->ev_graph) {
-            if (h->u_ev.B != B) { int r = build_units(h, h->u_ev, B); if (r) return r; }
-            { int r = sync_eval_args(h, b, nullptr, B); if (r) return r; }        // not inside the capture
-            cudaGraph_t g;
-            const long lt = h->n_launch_total, le = h->n_eval_launch;
-            CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-            cudaMemcpyAsync(b.in, b.pin_in, (size_t)B * (h->d.Np + 1) * 8, cudaMemcpyHostToDevice, h->stream);
-            int r = eval_resident(h, B, nullptr);
-            cudaMemcpyAsync(b.pin_out, b.out, (size_t)B * 28, cudaMemcpyDeviceToHost, h->stream);
-            cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
-            h->n_launch_total = lt; h->n_eval_launch = le;
-            if (r) return r;
-            CK(ce);
-            CK(cudaGraphInstantiate(&h->ev_graph, g, 0));
-            cudaGraphDestroy(g);
-            h->ev_graph_B = B;
-        }
-        memcpy(b.pin_in, params, (size_t)B * h->d.Np * 8);
-        memcpy(b.pin_in + (size_t)B * h->d.Np, T, (size_t)B * 8);
-        CK(cudaGraphLaunch(h->ev_graph, h->stream));
-        h->n_launch_total += 3; h->n_eval_launch += 1;
-        CK(cudaStreamSynchronize(h->stream));
-        if (logL) memcpy(logL, b.pin_out, (size_t)B * 8);
-        if (logPrior) memcpy(logPrior, b.pin_out + B, (size_t)B * 8);
-        if (logPost) memcpy(logPost, b.pin_out + 2 * (size_t)B, (size_t)B * 8);
-        if (status) memcpy(status, b.pin_out + 3 * (size_t)B, (size_t)B * 4);
-        return TG_OK;
+        int r = eval_submit(h, params, B, T, 0); if (r) return r;
+        return eval_collect(h, 0, logL, logPrior, logPost, status);
     }
     int r = tg_eval_upload(h, params, B, T); if (r) return r;
     double *model_dev = nullptr;

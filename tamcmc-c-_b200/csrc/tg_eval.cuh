@@ -739,6 +739,7 @@ __global__ void __launch_bounds__(256) tg_k_reduce_finalize(TgDesc d, const doub
 {
     __shared__ double2 s_part[8];
     const int c = blockIdx.x, tid = threadIdx.x;
+    tg_pdl_wait();                                // (a no-op unless launched with the programmatic-serialization attribute)
     double a1 = 0, a2 = 0;
     for (int k = tid; k < ntiles; k += 256) { const double2 v = partials[(size_t)c * ntiles + k]; a1 += v.x; a2 += v.y; }
     const double2 sm = tg_block_sum2(a1, a2, s_part);

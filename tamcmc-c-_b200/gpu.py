@@ -17,7 +17,7 @@ from .build import LIB_PATH, build_library
 ST_EMPTY_WINDOW, ST_NAN_WINDOW, ST_NAN_LOGL, ST_BAD_PRIOR, ST_CHOL_FAIL, ST_MODE_OVERFLOW = 1, 2, 4, 8, 16, 32
 F_FIX_SWAP_BOOKKEEPING = 1
 
-EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", "tg_eval_noalloc", "tg_eval_upload", "tg_eval_resident",
+EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", "tg_eval_async", "tg_eval_wait", "tg_eval_noalloc", "tg_eval_upload", "tg_eval_resident",
            "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
            "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_work_profile", "tg_event_record", "tg_event_elapsed_ms",
@@ -76,6 +76,8 @@ class GpuLibrary:
         L.tg_create.argtypes = [C.POINTER(_Problem), C.POINTER(C.c_void_p)]
         L.tg_destroy.argtypes = [C.c_void_p]
         L.tg_eval.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p] + [C.c_void_p] * 5
+        L.tg_eval_async.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.tg_eval_wait.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
         L.tg_eval_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p] + [C.c_void_p] * 4
         L.tg_eval_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
         L.tg_eval_resident.argtypes = [C.c_void_p, C.c_int]
@@ -273,6 +275,19 @@ class GpuModelDef:
         model = np.empty((B, self.Nx)) if want_model else None
         self.lib.check(self.lib.lib.tg_eval(self.h, _p(params), B, _p(T), _p(logL), _p(logPr), _p(logPo), _p(st), _p(model)))
         return dict(logL=logL, logPrior=logPr, logPost=logPo, status=st, model=model)
+
+    def evaluate_async(self, params, T, slot):
+        """tg_eval_async: enqueue the evaluation of params [B, Np] through staging slot 0 / 1; collect with evaluate_wait."""
+        params = np.ascontiguousarray(np.atleast_2d(params), dtype=np.float64)
+        T = np.ascontiguousarray(T, dtype=np.float64)
+        self.lib.check(self.lib.lib.tg_eval_async(self.h, _p(params), params.shape[0], _p(T), slot))
+        return params.shape[0]
+
+    def evaluate_wait(self, B, slot):
+        logL, logPr, logPo = np.empty(B), np.empty(B), np.empty(B)
+        st = np.zeros(B, dtype=np.int32)
+        self.lib.check(self.lib.lib.tg_eval_wait(self.h, slot, _p(logL), _p(logPr), _p(logPo), _p(st)))
+        return dict(logL=logL, logPrior=logPr, logPost=logPo, status=st)
 
     def evaluate_noalloc(self, params, T=None):
         """tg_eval_noalloc: the same evaluation through the library's static device scratch (no allocation in the call)."""

@@ -218,3 +218,37 @@ def test_background_moments_equal_the_bin_by_bin_path(tb, W, oracle, case, monke
     assert np.array_equal(res["0"]["status"], res["1"]["status"])
     assert relerr(res["1"]["logL"], res["0"]["logL"]) < 2e-14
     assert relerr(res["1"]["logL"], ref["logL"]) < TOL and relerr(res["0"]["logL"], ref["logL"]) < TOL
+
+
+def test_async_eval_equals_the_blocking_call(tb, W, oracle):
+    """tg_eval_async / tg_eval_wait (two staging slots, MALA.cpp:632-655 with the proposal on the host): a pipeline of calls
+    through alternating slots returns, call by call, the bits of tg_eval; misuse of a slot is refused."""
+    prob = W.small_global(3, Nx=20000, step=0.06)
+    st, m, _ = oracle.model(prob.model_case, prob.params, prob.plength, prob.x)
+    prob.y = m * (-np.log(W.philox_uniform(m.size, 5)))
+    Cn, K = 6, 7
+    md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=Cn))
+    T = W.tcoefs(Cn)
+    Ps = [W.perturbed_params(prob, Cn, scale=0.2 + 0.1 * k, seed=20 + k) for k in range(K)]
+    ref = [md.evaluate(P, T) for P in Ps]
+    got = [None] * K
+    md.evaluate_async(Ps[0], T, 0)
+    for k in range(1, K):
+        md.evaluate_async(Ps[k], T, k & 1)
+        got[k - 1] = md.evaluate_wait(Cn, (k - 1) & 1)
+    got[K - 1] = md.evaluate_wait(Cn, (K - 1) & 1)
+    for k in range(K):
+        for key in ("logL", "logPrior", "logPost", "status"):
+            assert np.array_equal(got[k][key], ref[k][key], equal_nan=True), (k, key)
+    orc = oracle.generate_models(prob, Ps[3], T)
+    ok = orc["status"] == 0
+    assert relerr(got[3]["logL"][ok], orc["logL"][ok]) < 1e-12
+    with pytest.raises(tb.TgError):
+        md.evaluate_wait(Cn, 0)                      # nothing outstanding
+    md.evaluate_async(Ps[0], T, 1)
+    with pytest.raises(tb.TgError):
+        md.evaluate_async(Ps[1], T, 1)               # slot 1 not collected yet
+    with pytest.raises(tb.TgError):
+        md.evaluate_async(Ps[1][:3], T[:3], 0)       # another batch size while slot 1 is in flight
+    assert np.array_equal(md.evaluate_wait(Cn, 1)["logL"], ref[0]["logL"])
+    md.close()
