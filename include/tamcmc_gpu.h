@@ -193,6 +193,23 @@ int tg_partials_device_ptr(tg_handle *h, void **ptr, int *count);
  * partial sums in the same buffer; all-reduce it, then call this to install the logL / logPosterior of the current
  * points from the reduced sums (Model_def constructor, model_def.cpp:139-143). */
 int tg_shard_install_current(tg_handle *h);
+/* The same variant driven by the library: tg_shard_unique_id (one rank; ncclGetUniqueId) gives the 128 bytes every rank passes,
+ * with its rank, to tg_shard_attach (ncclCommInitRank; all-reduces the start values like tg_shard_install_current).  From then on
+ * tg_run / tg_set_state all-reduce the 2*C partial sums themselves: one ncclAllReduce (fp64 sum) per step on the handle's stream,
+ * inside the captured step graph, no host synchronisation per step.  NCCL is the libnccl.so.2 already in the process (or
+ * TG_NCCL_LIB).  No reference counterpart (the reference caps a spectrum at 1 000 000 rows, config.cpp:531); SURVEY 8(e)-ii. */
+int tg_shard_unique_id(char *id128);
+int tg_shard_attach(tg_handle *h, const char *id128, int nranks, int rank);
+int tg_shard_detach(tg_handle *h);
+/* The exchange of the bin-sharded variant over NVLink peer memory instead of NCCL (one process per GPU, one node, <= 8 ranks):
+ * tg_shard_ipc_export allocates this rank's exchange buffer and returns its 64-byte CUDA IPC handle; every rank passes the handles
+ * of ALL ranks (rank order, nranks x 64 bytes) to tg_shard_ipc_attach.  Per step ONE kernel stores the rank's 2*C partial sums
+ * into every peer's buffer, waits for the peers' stamps and adds the contributions in rank order (bit-identical totals on every
+ * rank); it is part of the captured step graph.  tg_shard_status reports a peer that stopped answering (the kernel gives up after
+ * 2 s instead of hanging). */
+int tg_shard_ipc_export(tg_handle *h, int nranks, char *handle64);
+int tg_shard_ipc_attach(tg_handle *h, const char *handles, int nranks, int rank);
+int tg_shard_status(tg_handle *h);
 int tg_sync(tg_handle *h);
 
 /* Kernel timing of the dominant kernel (CUDA events on the handle's stream), accumulated since

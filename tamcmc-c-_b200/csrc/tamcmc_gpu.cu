@@ -8,6 +8,7 @@
 #include <limits>
 #include <cmath>
 #include <algorithm>
+#include <dlfcn.h>
 #include "tg_internal.cuh"
 #include "tg_prologue.cuh"
 #include "tg_eval.cuh"
@@ -82,6 +83,8 @@ struct tg_handle {
     std::vector<void *> allocs;
     cudaEvent_t watch[2] = {nullptr, nullptr};
     void       *nccl_comm = nullptr;       // bin-sharded variant: ncclComm_t of the shard group (tg_shard_attach)
+    // bin-sharded variant over peer memory (tg_shard_ipc_*): this rank's exchange buffer, the peers' buffers opened through CUDA IPC
+    bool        xchg_on = false; TgXchg xchg{}; void *xbuf = nullptr; size_t xbuf_bytes = 0; void *xpeer[TG_XCHG_MAXR] = {}; int *xerr_host = nullptr;
 };
 
 // A launch group: the sampler steps of several stars (handles on the same GPU) as ONE propose / fused / finish launch per
@@ -506,6 +509,52 @@ static int refresh_items_if_flagged(tg_handle *h)
     return build_items(h, h->sp, h->s.C);
 }
 
+// NCCL for the bin-sharded variant: the library already in the process (the one torch ships) or the first libnccl.so.2 found;
+// only four entry points are bound (nccl.h: ncclGetUniqueId, ncclCommInitRank, ncclAllReduce, ncclCommDestroy)
+struct tg_nccl_id { char internal[128]; };                       // == ncclUniqueId
+typedef int (*tg_nccl_allreduce_t)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef int (*tg_nccl_getid_t)(tg_nccl_id *);
+typedef int (*tg_nccl_init_t)(void **, int, tg_nccl_id, int);
+typedef int (*tg_nccl_destroy_t)(void *);
+static tg_nccl_allreduce_t g_nccl_allreduce = nullptr;
+static tg_nccl_getid_t g_nccl_getid = nullptr;
+static tg_nccl_init_t g_nccl_init = nullptr;
+static tg_nccl_destroy_t g_nccl_destroy = nullptr;
+static int load_nccl()
+{
+    if (g_nccl_allreduce) return TG_OK;
+    void *lib = nullptr;
+    if (const char *e = getenv("TG_NCCL_LIB")) lib = dlopen(e, RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);                  // already loaded (torch.distributed)
+    if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return fail(TG_E_UNSUPPORTED, std::string("bin-sharded variant: no libnccl.so.2 (set TG_NCCL_LIB): ") + (dlerror() ? dlerror() : ""));
+    g_nccl_getid = (tg_nccl_getid_t)dlsym(lib, "ncclGetUniqueId");
+    g_nccl_init = (tg_nccl_init_t)dlsym(lib, "ncclCommInitRank");
+    g_nccl_destroy = (tg_nccl_destroy_t)dlsym(lib, "ncclCommDestroy");
+    tg_nccl_allreduce_t ar = (tg_nccl_allreduce_t)dlsym(lib, "ncclAllReduce");
+    if (!g_nccl_getid || !g_nccl_init || !g_nccl_destroy || !ar) return fail(TG_E_UNSUPPORTED, "bin-sharded variant: libnccl lacks an entry point");
+    g_nccl_allreduce = ar;
+    return TG_OK;
+}
+
+static int shard_reduce_and_install(tg_handle *h)
+{
+    if (h->xchg_on) {
+        tg_k_xchg<<<1, 256, 0, h->stream>>>(h->xchg, h->sp.sums, h->s.C);
+        tg_k_install_current<<<(h->s.C + 127) / 128, 128, 0, h->stream>>>(h->d, h->s, h->sp.t, h->sp.sums);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(h->stream));
+        if (h->xerr_host && *(volatile int *)h->xerr_host) return fail(TG_E_CUDA, "bin-sharded exchange: a peer did not answer");
+        return TG_OK;
+    }
+    const int rc = g_nccl_allreduce(h->sp.sums, h->sp.sums, (size_t)2 * h->s.C, /*ncclDouble*/ 8, /*ncclSum*/ 0, h->nccl_comm, h->stream);
+    if (rc != 0) return fail(TG_E_CUDA, "ncclAllReduce failed (" + std::to_string(rc) + ")");
+    tg_k_install_current<<<(h->s.C + 127) / 128, 128, 0, h->stream>>>(h->d, h->s, h->sp.t, h->sp.sums);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(h->stream));
+    return TG_OK;
+}
 static int batch_refresh(tg_batch *b);
 static void batch_drop_graph(tg_batch *b);
 
@@ -785,6 +834,10 @@ extern "C" int tg_destroy(tg_handle *h)
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->self) { batch_destroy(h->self); h->self = nullptr; }
+    if (h->nccl_comm && g_nccl_destroy) { g_nccl_destroy(h->nccl_comm); h->nccl_comm = nullptr; }
+    for (int r = 0; r < TG_XCHG_MAXR; r++) if (h->xpeer[r]) cudaIpcCloseMemHandle(h->xpeer[r]);
+    if (h->xbuf) cudaFree(h->xbuf);
+    if (h->xerr_host) cudaFreeHost(h->xerr_host);
     drop_graphs(h);
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
@@ -1015,7 +1068,8 @@ extern "C" int tg_set_state(tg_handle *h, const double *vars, const double *mu, 
         CK(cudaMemcpyAsync(h->s.vars_cur, vars, C * Nv * 8, cudaMemcpyHostToDevice, h->stream));
         tg_k_scatter_vars<<<(unsigned)C, 128, 0, h->stream>>>(h->s);
         int r = launch_eval_kernels(h, h->sp, h->s.params_cur, (int)C, nullptr, true, true); if (r) return r;
-        tg_k_install_current<<<((int)C + 127) / 128, 128, 0, h->stream>>>(h->d, h->s, h->sp.t, h->sp.sums);
+        if (h->nccl_comm || h->xchg_on) { r = shard_reduce_and_install(h); if (r) return r; }
+        else tg_k_install_current<<<((int)C + 127) / 128, 128, 0, h->stream>>>(h->d, h->s, h->sp.t, h->sp.sums);
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(h->stream));
         { int r = build_items(h, h->sp, (int)C); if (r) return r; }
@@ -1178,10 +1232,6 @@ static int batch_build_units(tg_batch *b)
     return TG_OK;
 }
 
-// NCCL for the bin-sharded variant comes from the library torch ships (dlopen, tg_shard_attach)
-typedef int (*tg_nccl_allreduce_t)(const void *, void *, size_t, int, int, void *, cudaStream_t);
-static tg_nccl_allreduce_t g_nccl_allreduce = nullptr;
-
 // One MCMC step of every star of the group: begin = proposal + prologue + fused kernel, end = decision + swaps.
 static int batch_launch_step(tg_batch *b, bool begin, bool end)
 {
@@ -1225,6 +1275,10 @@ static int batch_launch_step(tg_batch *b, bool begin, bool end)
         b->n_eval_launch++; b->n_launch_total++;
         if (b->presummed) for (tg_handle *h : b->hs) {
             tg_k_reduce<<<h->s.C, 256, 0, b->stream>>>(h->sp.partials, h->nitems, h->sp.sums); b->n_launch_total++;
+            if (h->xchg_on) {         // bin-sharded variant over peer memory: one kernel, 2*C doubles per rank over NVLink, part of the step's graph
+                tg_k_xchg<<<1, 256, 0, b->stream>>>(h->xchg, h->sp.sums, h->s.C);
+                b->n_launch_total++;
+            } else
             if (h->nccl_comm) {       // bin-sharded variant: per-chain partial sums of all shards, part of the step's graph
                 const int rc = g_nccl_allreduce(h->sp.sums, h->sp.sums, (size_t)2 * h->s.C, /*ncclDouble*/ 8, /*ncclSum*/ 0, h->nccl_comm, b->stream);
                 if (rc != 0) return fail(TG_E_CUDA, "ncclAllReduce failed (" + std::to_string(rc) + ")");
@@ -1314,7 +1368,7 @@ static int drain_records(tg_handle *h, cudaStream_t st, tg_records *rec, long do
 static int batch_launches_per_step(const tg_batch *b)
 {
     int n = 3 + (b->side_rows > 0 ? 1 : 0) + (b->ff_cpc > 0 ? 1 : 0);
-    for (tg_handle *h : b->hs) { if (h->m.n_learn > 0 && !h->fused_spec) n++; if (b->presummed) n += 1 + (h->nccl_comm ? 1 : 0); }
+    for (tg_handle *h : b->hs) { if (h->m.n_learn > 0 && !h->fused_spec) n++; if (b->presummed) n += 1 + ((h->nccl_comm || h->xchg_on) ? 1 : 0); }
     return n;
 }
 
@@ -1458,6 +1512,108 @@ extern "C" int tg_partials_device_ptr(tg_handle *h, void **ptr, int *count)
     *ptr = (void *)h->sp.sums; *count = 2 * h->s.C;
     return TG_OK;
 }
+// Bin-sharded variant inside the library: every rank holds a contiguous bin range of ONE spectrum (tg_problem.Nx_global, shard_lo, ...)
+// and the same chain state and Philox streams; from tg_shard_attach on, every step all-reduces the 2*C partial sums
+// (sum y/m, sum ln m: likelihoods.cpp:17-28) over the ranks with ONE ncclAllReduce enqueued on the handle's stream between the
+// fused kernel and the decision kernel -- part of the captured step graph, no host synchronisation per step.
+extern "C" int tg_shard_unique_id(char *id128)
+{
+    if (!id128) return fail(TG_E_BADARG, "null argument");
+    { int r = load_nccl(); if (r) return r; }
+    tg_nccl_id id; memset(&id, 0, sizeof(id));
+    const int rc = g_nccl_getid(&id);
+    if (rc != 0) return fail(TG_E_CUDA, "ncclGetUniqueId failed (" + std::to_string(rc) + ")");
+    memcpy(id128, id.internal, 128);
+    return TG_OK;
+}
+extern "C" int tg_shard_attach(tg_handle *h, const char *id128, int nranks, int rank)
+{
+    if (!h || !h->self || !id128 || nranks < 1 || rank < 0 || rank >= nranks) return fail(TG_E_BADARG, "tg_shard_attach: bad argument");
+    if (h->nccl_comm) return fail(TG_E_BADARG, "tg_shard_attach: already attached");
+    { int r = load_nccl(); if (r) return r; }
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    tg_nccl_id id; memcpy(id.internal, id128, 128);
+    void *comm = nullptr;
+    const int rc = g_nccl_init(&comm, nranks, id, rank);
+    if (rc != 0 || !comm) return fail(TG_E_CUDA, "ncclCommInitRank failed (" + std::to_string(rc) + ")");
+    h->nccl_comm = comm;
+    // tg_create evaluated the current points on this rank's bins only: the sums of all ranks make their logL
+    { int r = shard_reduce_and_install(h); if (r) return r; }
+    tg_batch *b = h->self;
+    b->presummed = 1;
+    batch_drop_graph(b);
+    return batch_refresh(b);
+}
+extern "C" int tg_shard_detach(tg_handle *h)
+{
+    if (!h) return fail(TG_E_BADARG, "null handle");
+    if (!h->nccl_comm) return TG_OK;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->self) batch_drop_graph(h->self);
+    g_nccl_destroy(h->nccl_comm);
+    h->nccl_comm = nullptr;
+    return TG_OK;
+}
+
+// The same exchange without NCCL: the ranks' buffers are mapped into one another through CUDA IPC and ONE kernel per step
+// (tg_k_xchg, tg_sampler.cuh) stores this rank's 2*C sums into every peer's buffer over NVLink, waits for the peers' stamps and adds
+// the contributions in rank order.  tg_shard_ipc_export allocates this rank's buffer and returns its 64-byte IPC handle; every rank
+// passes the handles of all ranks (rank order) to tg_shard_ipc_attach.  One process per GPU, all GPUs of one node, <= 8 ranks.
+extern "C" int tg_shard_ipc_export(tg_handle *h, int nranks, char *handle64)
+{
+    if (!h || !handle64 || nranks < 1 || nranks > TG_XCHG_MAXR) return fail(TG_E_BADARG, "tg_shard_ipc_export: bad argument (<= 8 ranks)");
+    if (h->xbuf) return fail(TG_E_BADARG, "tg_shard_ipc_export: already exported");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    CK(cudaSetDevice(h->device));
+    const size_t n = 2 * (size_t)h->s.C;
+    h->xbuf_bytes = (2 * (size_t)nranks * n) * 8 + 2 * (size_t)nranks * 8 + 64;      // data, stamps, counter + error word
+    CK(cudaMalloc(&h->xbuf, h->xbuf_bytes));
+    CK(cudaMemset(h->xbuf, 0, h->xbuf_bytes));
+    CK(cudaDeviceSynchronize());
+    cudaIpcMemHandle_t ih;
+    CK(cudaIpcGetMemHandle(&ih, h->xbuf));
+    memcpy(handle64, &ih, 64);
+    return TG_OK;
+}
+extern "C" int tg_shard_ipc_attach(tg_handle *h, const char *handles, int nranks, int rank)
+{
+    if (!h || !h->self || !handles || !h->xbuf || nranks < 1 || nranks > TG_XCHG_MAXR || rank < 0 || rank >= nranks) return fail(TG_E_BADARG, "tg_shard_ipc_attach: bad argument");
+    if (h->xchg_on || h->nccl_comm) return fail(TG_E_BADARG, "tg_shard_ipc_attach: already attached");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    const size_t n = 2 * (size_t)h->s.C, data_bytes = (2 * (size_t)nranks * n) * 8, stamp_bytes = 2 * (size_t)nranks * 8;
+    TgXchg &x = h->xchg; memset(&x, 0, sizeof(x));
+    x.nranks = nranks; x.rank = rank;
+    for (int r = 0; r < nranks; r++) {
+        void *p = h->xbuf;
+        if (r != rank) {
+            cudaIpcMemHandle_t ih; memcpy(&ih, handles + 64 * (size_t)r, 64);
+            CK(cudaIpcOpenMemHandle(&p, ih, cudaIpcMemLazyEnablePeerAccess));
+            h->xpeer[r] = p;
+        }
+        x.peer_data[r] = (double *)p;
+        x.peer_stamp[r] = (unsigned long long *)((char *)p + data_bytes);
+    }
+    x.seq = (unsigned long long *)((char *)h->xbuf + data_bytes + stamp_bytes);
+    CK(cudaHostAlloc((void **)&h->xerr_host, sizeof(int), cudaHostAllocMapped));
+    *h->xerr_host = 0;
+    x.err = h->xerr_host;
+    h->xchg_on = true;
+    { int r = shard_reduce_and_install(h); if (r) return r; }      // tg_create evaluated the current points on this rank's bins only
+    tg_batch *b = h->self;
+    b->presummed = 1;
+    batch_drop_graph(b);
+    return batch_refresh(b);
+}
+extern "C" int tg_shard_status(tg_handle *h)
+{
+    if (!h) return fail(TG_E_BADARG, "null handle");
+    if (h->xerr_host && *(volatile int *)h->xerr_host) return fail(TG_E_CUDA, "bin-sharded exchange: a peer did not answer within 2 s; the run is void");
+    return TG_OK;
+}
+
 extern "C" int tg_sync(tg_handle *h)
 {
     if (!h) return fail(TG_E_BADARG, "null handle");

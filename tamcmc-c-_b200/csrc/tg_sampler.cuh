@@ -393,6 +393,59 @@ __global__ void __launch_bounds__(256) tg_k_finish(const TgFinishArgs *__restric
 #endif
 }
 
+// ---- bin-sharded variant: exchange of the per-chain partial sums over NVLink peer memory ---------------------------------
+// Every rank owns one buffer (cudaMalloc, opened by its peers through CUDA IPC): data[2][nranks][2C] doubles and
+// stamp[2][nranks] 64-bit words.  Exchange number `seq` (the same on every rank: all ranks run the same sequence of steps):
+// rank r writes its 2C sums into slot [seq & 1][r] of EVERY rank's buffer (plain stores through the peer pointers), fences, and
+// releases stamp [seq & 1][r] = seq there; it then waits until its own nranks stamps of that parity read seq (acquire) and adds
+// the nranks contributions in rank order -- the same order on every rank, so the totals are bit-identical everywhere, which the
+// replicated accept / swap decisions need.  A rank cannot lap a peer by two exchanges (it needs the peer's stamp of the exchange
+// in between), so two parities suffice.  One CTA; 2C doubles and nranks stamps cross NVLink per rank and step.
+#define TG_XCHG_MAXR 8
+struct TgXchg {
+    int nranks, rank;
+    double *peer_data[TG_XCHG_MAXR];               // [2][nranks][2C] of every rank (own buffer included)
+    unsigned long long *peer_stamp[TG_XCHG_MAXR];  // [2][nranks]
+    unsigned long long *seq;                       // this rank's exchange counter (device memory: graph replays advance it)
+    int *err;                                      // set to 1 if a peer did not answer within ~2 s (the run is void then; no hang)
+};
+__global__ void __launch_bounds__(256) tg_k_xchg(TgXchg x, double2 *sums, int C)
+{
+    const int t = threadIdx.x, n = 2 * C, R = x.nranks;
+    const unsigned long long seq = *x.seq + 1ull;
+    const int par = (int)(seq & 1ull);
+    const double *mine = (const double *)sums;
+    for (int p = 0; p < R; p++) {
+        double *dst = x.peer_data[p] + ((size_t)par * R + x.rank) * n;
+        for (int e = t; e < n; e += blockDim.x) dst[e] = mine[e];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (t < R) {
+        unsigned long long *st = x.peer_stamp[t] + (size_t)par * R + x.rank;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(st), "l"(seq) : "memory");
+        const unsigned long long *my = x.peer_stamp[x.rank] + (size_t)par * R + t;
+        unsigned long long v = 0ull, t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(my) : "memory");
+            if (v == seq) break;
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 2000000000ull) { *x.err = 1; break; }
+        }
+    }
+    __syncthreads();
+    const double *all = x.peer_data[x.rank] + (size_t)par * R * n;
+    for (int e = t; e < n; e += blockDim.x) {
+        double s = 0.0;
+        for (int r = 0; r < R; r++) s += __ldcv(all + (size_t)r * n + e);          // written by peers: not through a stale cache line
+        ((double *)sums)[e] = s;
+    }
+    __syncthreads();
+    if (t == 0) *x.seq = seq;
+}
+
 // Live (mu, Sigma) of every chain -> contiguous [C][Nv], [C][Nv][Nv] (restore files / tg_get_state)
 __global__ void tg_k_gather_live(TgState s, double *mu_out, double *cov_out)
 {

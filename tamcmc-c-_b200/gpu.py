@@ -19,7 +19,7 @@ F_FIX_SWAP_BOOKKEEPING = 1
 
 EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", "tg_eval_async", "tg_eval_wait", "tg_eval_noalloc", "tg_eval_upload", "tg_eval_resident",
            "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
-           "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_sync", "tg_kernel_time", "tg_set_tuning",
+           "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_shard_unique_id", "tg_shard_attach", "tg_shard_detach", "tg_shard_ipc_export", "tg_shard_ipc_attach", "tg_shard_status", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_work_profile", "tg_event_record", "tg_event_elapsed_ms",
            "tg_batch_create", "tg_batch_run", "tg_batch_destroy", "tg_batch_sizes", "tg_batch_kernel_time", "tg_batch_event_record",
            "tg_batch_prepass_time", "tg_prepass_time"]
@@ -91,6 +91,12 @@ class GpuLibrary:
         L.tg_step_end.argtypes = [C.c_void_p, C.c_long]
         L.tg_partials_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int)]
         L.tg_shard_install_current.argtypes = [C.c_void_p]
+        L.tg_shard_unique_id.argtypes = [C.c_char_p]
+        L.tg_shard_attach.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
+        L.tg_shard_detach.argtypes = [C.c_void_p]
+        L.tg_shard_ipc_export.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
+        L.tg_shard_ipc_attach.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int]
+        L.tg_shard_status.argtypes = [C.c_void_p]
         L.tg_sync.argtypes = [C.c_void_p]
         L.tg_kernel_time.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_double), C.POINTER(C.c_long)]
         L.tg_set_tuning.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
@@ -145,6 +151,14 @@ class GpuLibrary:
 
 
 _LIB = None
+
+
+def shard_unique_id(lib=None):
+    """128 bytes of ncclGetUniqueId (call on one rank, broadcast to the others, pass to GpuModelDef.shard_attach)."""
+    lib = lib or load_library()
+    buf = C.create_string_buffer(128)
+    lib.check(lib.lib.tg_shard_unique_id(buf))
+    return buf.raw
 
 
 def load_library(build=True):
@@ -359,6 +373,26 @@ class GpuModelDef:
 
     def sync(self):
         self.lib.check(self.lib.lib.tg_sync(self.h))
+
+    def shard_ipc_export(self, nranks: int) -> bytes:
+        """Bin-sharded variant over peer memory: this rank's exchange buffer as a 64-byte CUDA IPC handle."""
+        buf = C.create_string_buffer(64)
+        self.lib.check(self.lib.lib.tg_shard_ipc_export(self.h, nranks, buf))
+        return buf.raw
+
+    def shard_ipc_attach(self, handles: bytes, nranks: int, rank: int):
+        assert len(handles) == 64 * nranks
+        self.lib.check(self.lib.lib.tg_shard_ipc_attach(self.h, handles, nranks, rank))
+        self.refresh_from_device()
+
+    def shard_status(self):
+        self.lib.check(self.lib.lib.tg_shard_status(self.h))
+
+    def shard_attach(self, unique_id: bytes, nranks: int, rank: int):
+        """Bin-sharded variant inside the library: joins the NCCL communicator of the shard group (tg_shard_attach)."""
+        assert len(unique_id) == 128
+        self.lib.check(self.lib.lib.tg_shard_attach(self.h, unique_id, nranks, rank))
+        self.refresh_from_device()
 
     def set_tuning(self, chains_per_block=0, light_subtiles=0, use_graph=-1, heavy_group=0):
         self.lib.check(self.lib.lib.tg_set_tuning(self.h, chains_per_block, heavy_group, light_subtiles, use_graph))

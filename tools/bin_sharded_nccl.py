@@ -38,6 +38,9 @@ def main():
     ap.add_argument("--check-steps", type=int, default=40)
     ap.add_argument("--chains", type=int, default=10)
     ap.add_argument("--equal-length", action="store_true", help="equal-length shards instead of cost-balanced ones")
+    ap.add_argument("--host-driven", action="store_true", help="the round-1 form: tg_step_begin / all_reduce by torch / tg_step_end with two host synchronisations per step "
+                    "(default: the all-reduce inside the library's captured step graph, tg_shard_attach)")
+    ap.add_argument("--nccl", action="store_true", help="ncclAllReduce inside the library's step graph (tg_shard_attach) instead of the peer-memory exchange kernel (tg_shard_ipc_*)")
     ap.add_argument("--heavy-weight", type=float, default=17.0, help="cost of a bin under truncation windows in units of a background-only bin (measured: 17 .. 2000 give the same step time on 2 GPUs)")
     a = ap.parse_args()
     import torch
@@ -62,19 +65,35 @@ def main():
     ptr, n = mala.partials_ptr()
     part = torch.as_tensor(_DevBuf(ptr, n), device="cuda:%d" % local)
 
-    # the Model_def constructor evaluated every chain on this rank's bins only: install the all-reduced start
-    if world > 1:
+    in_library = world > 1 and not a.host_driven
+    if in_library and not a.nccl:
+        # peer memory: every rank exports its exchange buffer (CUDA IPC handle, 64 bytes), torch.distributed gathers the handles
+        mine = torch.frombuffer(bytearray(md.shard_ipc_export(world)), dtype=torch.uint8).cuda()
+        allh = [torch.zeros(64, dtype=torch.uint8, device="cuda") for _ in range(world)]
+        dist.all_gather(allh, mine)
+        md.shard_ipc_attach(b"".join(bytes(t.cpu().numpy().tobytes()) for t in allh), world, rank)
+    elif in_library:
+        # the library's own communicator: rank 0 draws the id, torch.distributed carries the 128 bytes, every rank attaches
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(tb.gpu.shard_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, src=0)
+        md.shard_attach(bytes(uid.cpu().numpy().tobytes()), world, rank)
+    elif world > 1:
+        # the Model_def constructor evaluated every chain on this rank's bins only: install the all-reduced start
         md.sync()
         dist.all_reduce(part, op=dist.ReduceOp.SUM)
         torch.cuda.synchronize()
         mala.install_current()
 
     def step(i):
+        if in_library or world == 1:
+            mala.execute(i, 1, record=False)                        # one step of tg_run: the all-reduce is inside
+            return
         mala.step_begin(i)
         md.sync()
-        if world > 1:
-            dist.all_reduce(part, op=dist.ReduceOp.SUM)
-            torch.cuda.synchronize()
+        dist.all_reduce(part, op=dist.ReduceOp.SUM)
+        torch.cuda.synchronize()
         mala.step_end(i)
 
     traj = []
@@ -92,12 +111,21 @@ def main():
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    if in_library or world == 1:
+        mala.execute(a.check_steps, 32, record=False)                # (the step graphs are replayed from here on)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        md.timer_start()
+        mala.execute(a.check_steps + 32, a.steps, record=False)      # ONE call: no host synchronisation per step
+        ms_lib = md.timer_stop_ms()
     e0.record()
-    for i in range(a.check_steps, a.check_steps + a.steps):
-        step(i)
+    if not (in_library or world == 1):
+        for i in range(a.check_steps, a.check_steps + a.steps):
+            step(i)
     md.sync()
     e1.record(); torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    ms = torch.tensor([ms_lib if (in_library or world == 1) else e0.elapsed_time(e1)], device="cuda")
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ok = True
@@ -117,10 +145,13 @@ def main():
         print(json.dumps({"metric": "tempered chain-steps/s, bin-sharded variant (one spectrum over all GPUs, all-reduce of 2*C doubles per step)",
                           "value": a.chains * a.steps / (float(ms.item()) * 1e-3), "unit": "chain-steps/s", "n_gpus": world, "steps": a.steps,
                           "ms_per_step": float(ms.item()) / a.steps, "Nx": a.nx, "chains": a.chains, "bins_per_gpu": int(sub.x.size),
-                          "replicas_identical_steps": a.check_steps, "equals_unsharded_run": bool(ok), "collective": "nccl all_reduce fp64 sum, %d doubles" % n}))
+                          "replicas_identical_steps": a.check_steps, "equals_unsharded_run": bool(ok), "collective": (("ncclAllReduce fp64 sum, %d doubles, inside the library's step graph" if a.nccl else "peer-memory exchange kernel (tg_k_xchg over CUDA IPC / NVLink), %d doubles per rank, inside the library's step graph") if in_library else "nccl all_reduce by torch, fp64 sum, %d doubles, host-driven") % n}))
+    if in_library and not a.nccl:
+        md.shard_status()
+    if world > 1:
+        dist.barrier()                                             # nobody unmaps a buffer a peer may still write
     md.close()
     if world > 1:
-        dist.barrier()
         dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 
