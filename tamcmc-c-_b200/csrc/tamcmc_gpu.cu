@@ -59,6 +59,7 @@ struct tg_handle {
     double    *ffw = nullptr; double ff_r2 = 30.25;    // far-field path (tg_farfield.cuh): matrix + nodes, (pole distance / half-width)^2 from which a component is far
     TgFFGeo   *ffgeo = nullptr; int ff_stride = 0;    // geometry of the micro-tiles of the spectrum; micro-tiles per vector the buffers hold
     int        ff_mt0 = 0, ff_nmt = 0;                 // micro-tiles the pre-pass prepares: where truncation windows are expected (the heavy items)
+    int        heavy_t0 = 0, heavy_t1 = 0;             // window region of the current partition, in sub-tiles
     int        hybrid_pct = 0, hybrid_group = 2;
     int       *mom_note = nullptr;                      // pinned, mapped: the kernel stores 1 when it flags a tile for the first time          // Chebyshev moments of the data over aligned tiles (tg_eval.cuh), NULL = off
     double    *pri = nullptr; int *sw = nullptr;
@@ -389,6 +390,12 @@ static int build_items(tg_handle *h, EvalBuf &b, int B)
         for (int c = 0; c < B; c++) if (whi[c] > wlo[c]) { ulo = std::min(ulo, wlo[c]); uhi = std::max(uhi, whi[c]); }
         int t0 = nt, t1 = nt;                       // heavy tiles [t0, t1), one tile of margin for drifting windows
         if (uhi > ulo) { t0 = std::max(0, ulo / SUB - 1); t1 = std::min(nt, (uhi + SUB - 1) / SUB + 1); }
+        // hysteresis: the window region of the previous partition is kept while it still covers the windows and is not more than
+        // eight sub-tiles too wide on either side (the chains' windows breathe by a tile or two between calls; a new partition
+        // means new unit tables and new step graphs)
+        if (uhi > ulo && h->heavy_t1 > h->heavy_t0 && h->heavy_t0 * SUB <= ulo && h->heavy_t1 * SUB >= uhi &&
+            t0 - h->heavy_t0 <= 8 && h->heavy_t1 - t1 <= 8 && h->heavy_t1 <= nt) { t0 = h->heavy_t0; t1 = h->heavy_t1; }
+        h->heavy_t0 = t0; h->heavy_t1 = t1;
         // the far-field pre-pass prepares the micro-tiles of the window region (whole pairs of sub-tiles inside the spectrum)
         { const int mt0 = t0 * (SUB / TG_FF_BINS), nmt = std::max(0, std::min(t1 * (SUB / TG_FF_BINS), h->ff_stride) - mt0);
           if (h->ffw && (mt0 != h->ff_mt0 || nmt != h->ff_nmt)) { h->ff_mt0 = mt0; h->ff_nmt = nmt; h->sp.args_valid = h->ev.args_valid = false; h->sp.ffargs_valid = h->ev.ffargs_valid = false; drop_graphs(h); } }
@@ -1387,7 +1394,7 @@ static int batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs)
         while (b->graph && b->use_graph && !b->timing && k + G <= n) {
             CK(cudaGraphLaunch(b->graph, b->stream)); b->n_launch_total += (long)batch_launches_per_step(b) * G; b->n_eval_launch += G;
             k += G;
-            if (!b->probed && nsteps >= 8L * G) {
+            if (!b->probed && nsteps >= 2L * G) {
                 // first steps of a long run: which background-only tiles fail their polynomial check at the proposed points is known
                 // now; without this look the rest of the call would run with those tiles inside long cheap items
                 b->probed = true;
