@@ -168,6 +168,7 @@ def main():
     ap.add_argument("--config", default="cfg3", choices=["cfg2", "cfg3", "cfg4", "cfg5"])
     ap.add_argument("--stars-per-gpu", type=int, default=0, help="cfg5: stars (tempered ensembles of 10 chains, each its own spectrum) per GPU as one launch group")
     ap.add_argument("--no-cfg5", action="store_true", help="skip the 8-stars-per-GPU measurement carried by the default line")
+    ap.add_argument("--no-bin-sharded", action="store_true", help="N > 1: skip the bin-sharded 10 M-bin measurement carried by the default line")
     ap.add_argument("--extra-out", default=None, help="also write the JSON line to this file")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -188,7 +189,8 @@ def main():
     if world > 1:
         import torch.distributed as dist
         if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
+            os.environ["NCCL_DEBUG"] = "WARN"
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # stdout carries the one JSON line and nothing else
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = tb.load_library()
     peak_tflops, _ = lib.measure_fp64_peak(local_rank)
@@ -399,6 +401,50 @@ def main():
             m_.close()
         mds, grp = [], None
 
+    # ---- N > 1: the bin-sharded variant beside the headline -- ONE spectrum of 10 M bins over all ranks, 10 chains, the 2*C partial
+    #      sums exchanged every step by the library's peer-memory kernel inside its step graph (tools/bin_sharded_nccl.py checks that the
+    #      replicas stay bit-identical and equal the unsharded run); rank 0 also times the unsharded spectrum on its own GPU ----
+    bin_sharded = None
+    if dist is not None and cfg_name == "cfg3" and not args.no_bin_sharded and world <= 8:
+        import copy
+        Sh = tb.sharding
+        nx10 = 10_000_000
+        p10 = W.s_global(Nx=nx10, step=8500.0 / nx10)
+        desc, sl = Sh.balanced_shard_descriptor(p10, world, rank, 17.0)
+        sub = copy.copy(p10)
+        sub.x, sub.y = np.ascontiguousarray(p10.x[sl]), np.ascontiguousarray(p10.y[sl])
+        cfg10 = tb.MalaConfig(Nchains=C_CHAINS, Nt_learn=[0, 10**9], periods_learn=[1], c0=2.0, lambda_temp=1.7, seed=2024)
+        ms10 = tb.GpuModelDef(sub, cfg10, device=local_rank, shard=desc)
+        mine = torch.frombuffer(bytearray(ms10.shard_ipc_export(world)), dtype=torch.uint8).cuda()
+        allh = [torch.zeros(64, dtype=torch.uint8, device="cuda") for _ in range(world)]
+        dist.all_gather(allh, mine)
+        ms10.shard_ipc_attach(b"".join(bytes(t.cpu().numpy().tobytes()) for t in allh), world, rank)
+        r10 = tb.GpuMALA(ms10)
+        r10.execute(I0, 2 * STEPS_PER_GRAPH, record=False)
+        barrier(ms10)
+        ms10.timer_start()
+        r10.execute(I0 + 2 * STEPS_PER_GRAPH, 96, record=False)
+        t10 = torch.tensor([ms10.timer_stop_ms()], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t10, op=dist.ReduceOp.MAX)
+        ms10.shard_status()
+        dist.barrier()
+        ms10.close()
+        one = None
+        if rank == 0:
+            m1 = tb.GpuModelDef(p10, cfg10, device=local_rank)
+            r1 = tb.GpuMALA(m1)
+            r1.execute(I0, 2 * STEPS_PER_GRAPH, record=False)
+            m1.timer_start()
+            r1.execute(I0 + 2 * STEPS_PER_GRAPH, 96, record=False)
+            one = m1.timer_stop_ms() / 96
+            m1.close()
+        dist.barrier()
+        bin_sharded = {"workload": "S-10M: one 10 000 000-bin spectrum over %d GPUs (contiguous bin ranges of equal estimated cost), 10 chains replicated" % world,
+                       "ms_per_step": float(t10.item()) / 96, "chain_steps_per_s": C_CHAINS * 96 / (float(t10.item()) * 1e-3), "steps": 96,
+                       "one_gpu_ms_per_step": one, "speedup_vs_one_gpu": (one / (float(t10.item()) / 96)) if one else None,
+                       "exchange": "tg_k_xchg: 2*C doubles per rank and step over NVLink peer memory (CUDA IPC), inside the captured step graph; "
+                                   "ncclAllReduce variant: tools/bin_sharded_nccl.py --nccl"}
+
     # ---- CPU baseline on this box's host cores (rank 0, N=1 only; bounded sample) ----
     cpu = None
     if rank == 0 and world == 1 and cfg_name in ("cfg3", "cfg5"):
@@ -434,7 +480,7 @@ def main():
                 "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": config,
                 "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-                "bin_evals_per_s": value * nx_star, "cfg5_8_stars_per_gpu": cfg5}
+                "bin_evals_per_s": value * nx_star, "cfg5_8_stars_per_gpu": cfg5, "bin_sharded_10M": bin_sharded}
         txt = json.dumps(line)
         print(txt, flush=True)
         if args.extra_out:
