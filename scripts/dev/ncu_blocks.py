@@ -2,7 +2,7 @@
 import csv, collections, sys
 src, unit = sys.argv[1], float(sys.argv[2])
 rows = list(csv.reader(open(src)))
-hdr = rows[1]; data = rows[2:]
+hdr = rows[1]; data = [r for r in rows[2:] if len(r) == len(hdr) and r[hdr.index('Instructions Executed')].isdigit()]
 iI = hdr.index("Instructions Executed"); iS = hdr.index("Warp Stall Sampling (All Samples)")
 tot = sum(int(r[iI]) for r in data); tots = sum(int(r[iS]) for r in data)
 print("total warp-inst", tot, "per unit %.1f" % (tot / unit), "samples", tots)

@@ -150,6 +150,8 @@ static int raise_dyn_smem(const void *func, size_t bytes)
     return TG_OK;
 }
 
+static long g_dbg_count[4] = {0, 0, 0, 0};      // developer counters: work-item partitions built, step graphs captured, probe syncs, argument uploads
+extern "C" int tg_dbg_counters(long *out) { for (int k = 0; k < 4; k++) out[k] = g_dbg_count[k]; return 0; }
 extern "C" const char *tg_last_error(void) { return g_err.c_str(); }
 extern "C" int tg_version(void) { return 100; }
 #ifdef TG_PROFILE
@@ -430,13 +432,17 @@ static int build_items(tg_handle *h, EvalBuf &b, int B)
         };
         light_region(0, t0);
         const int Hs = std::max(1, h->heavy_sub);   // sub-tiles per item where windows are expected (2: the kernel takes them 8 bins per thread)
-        for (int t = t0; t < t1; t += Hs) { int wm = 0; for (int q = t; q < std::min(t + Hs, t1); q++) wm = std::max(wm, w[q]); items.push_back(make_int4(t * SUB, std::min(Hs, t1 - t), wm, 1)); }
+        // (item.z = window crossings, a cost estimate only.  On the far-field path the crossings hardly matter for the cost, and a
+        // value that follows every breath of the windows would make a new partition -- new unit tables, new step graphs -- of
+        // every long call: it stays 0 there.)
+        for (int t = t0; t < t1; t += Hs) { int wm = 0; if (!h->ffw) for (int q = t; q < std::min(t + Hs, t1); q++) wm = std::max(wm, w[q]); items.push_back(make_int4(t * SUB, std::min(Hs, t1 - t), wm, 1)); }
         light_region(t1, nt);
     }
     bool same = items.size() == h->items_host.size();
     for (size_t k = 0; same && k < items.size(); k++) same = items[k].x == h->items_host[k].x && items[k].y == h->items_host[k].y && items[k].z == h->items_host[k].z && items[k].w == h->items_host[k].w;
     if (same) return TG_OK;
     h->items_host = items;
+    g_dbg_count[0]++;
     h->nitems = (int)items.size();
     h->u_sp.B = h->u_ev.B = -1;                     // units are rebuilt at the next launch
     drop_graphs(h);                                 // grid size changed
@@ -1218,6 +1224,7 @@ static int batch_sync_args(tg_batch *b)
                       memcmp(pm.data(), b->h_pm.data(), n * sizeof(TgProposeArgs)) == 0 && memcmp(ps.data(), b->h_ps.data(), n * sizeof(TgProposeArgs)) == 0 &&
                       memcmp(fin.data(), b->h_fin.data(), n * sizeof(TgFinishArgs)) == 0;
     if (same) return TG_OK;
+    g_dbg_count[3]++;
     b->h_ev.swap(ev); b->h_pm.swap(pm); b->h_ps.swap(ps); b->h_fin.swap(fin); b->h_ff.swap(ff);
     CK(cudaStreamSynchronize(b->stream));
     CK(cudaMemcpy(b->d_ev, b->h_ev.data(), n * sizeof(TgEvalArgs), cudaMemcpyHostToDevice));
@@ -1316,7 +1323,7 @@ static int batch_capture_one(tg_batch *b, int nsteps, cudaGraphExec_t *out)
         b->n_launch_total = lt; b->n_eval_launch = le; b->side_pending = false;
         if (ce == cudaSuccess && r == TG_OK) ce = cudaGraphInstantiate(out, g, 0);
         if (g) cudaGraphDestroy(g);
-        if (ce == cudaSuccess && r == TG_OK) { cudaGraphUpload(*out, b->stream); break; }
+        if (ce == cudaSuccess && r == TG_OK) { cudaGraphUpload(*out, b->stream); g_dbg_count[1]++; break; }
         *out = nullptr;
         if (!b->pdl || attempt == 1) { if (r) return r; CK(ce); }
         cudaGetLastError();                  // a driver that cannot capture programmatic edges: the same graphs with full dependencies
@@ -1398,6 +1405,7 @@ static int batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs)
                 // first steps of a long run: which background-only tiles fail their polynomial check at the proposed points is known
                 // now; without this look the rest of the call would run with those tiles inside long cheap items
                 b->probed = true;
+                g_dbg_count[2]++;
                 CK(cudaStreamSynchronize(b->stream));
                 int r = batch_refresh(b); if (r) return r;
             }
