@@ -686,6 +686,13 @@ static int create_impl(const tg_problem *p, tg_handle *h)
             for (int k = 0; k < TG_FF_N; k++) for (int i = 0; i < TG_FF_N; i++)
                 w[(size_t)k * TG_FF_N + i] = (double)((k == 0 ? 1.0L : 2.0L) / TG_FF_N * cosl(pi * k * (i + 0.5L) / TG_FF_N));
             for (int i = 0; i < TG_FF_N; i++) w[(size_t)TG_FF_N * TG_FF_N + i] = (double)cosl(pi * (i + 0.5L) / TG_FF_N);
+            {   // T_j(t) = sum_k M[k][j] t^k by the three-term recurrence, in integers (|M| <= 92160 at degree 15: exact in double)
+                long long T[TG_FF_N][TG_FF_N] = {};
+                T[0][0] = 1; T[1][1] = 1;
+                for (int j = 2; j < TG_FF_N; j++) for (int k = 0; k <= j; k++) T[j][k] = (k > 0 ? 2 * T[j - 1][k - 1] : 0) - T[j - 2][k];
+                double *M = w.data() + (size_t)TG_FF_N * TG_FF_N + TG_FF_N;
+                for (int k = 0; k < TG_FF_N; k++) for (int j = 0; j < TG_FF_N; j++) M[(size_t)k * TG_FF_N + j] = (double)T[j][k];
+            }
             DA(h->ffw, w.size());
             CK(cudaMemcpy(h->ffw, w.data(), w.size() * 8, cudaMemcpyHostToDevice));
             h->ff_stride = (int)(Nx / TG_FF_BINS);                  // whole micro-tiles of the spectrum

@@ -28,12 +28,13 @@
 #define TG_FF_BINS 256                 // bins per micro-tile == threads of the fused kernel
 #define TG_FF_E    32                  // exact components a micro-tile record holds
 #define TG_FF_TOL  1.0e-12
-#define TG_FF_HDR  (TG_FF_N * TG_FF_N + TG_FF_N)   // doubles of the constant buffer: node values -> coefficients [k][i], then the nodes
+#define TG_FF_HDR  (2 * TG_FF_N * TG_FF_N + TG_FF_N)   // doubles of the constant buffer: node values -> Chebyshev coefficients [k][i], the nodes,
+                                                        // then the Chebyshev -> power-basis matrix M[k][j] (T_j = sum_k M[k][j] t^k: integers, exact)
 #define TG_FF_FALLBACK (-1)
 
 struct __align__(16) TgFFRec { double nu, q, h; int lo, len; };            // 32 bytes; window [lo, lo+len) in LOCAL bin indices
-struct __align__(16) TgFFHdr { int count; unsigned pred; int flags; int nfar; };   // count: records, or TG_FF_FALLBACK; pred bit e: record e needs
-                                                                            // the window predicate; flags bit 0: background + N0 folded in
+struct __align__(16) TgFFHdr { int count; int nfree; int flags; int nfar; };       // count: records, or TG_FF_FALLBACK; the first nfree of them cover the
+                                                                            // whole micro-tile (no window predicate), the rest need it; flags bit 0: background + N0 folded in
 struct __align__(16) TgFFGeo { double xc, hw, ihw, pad; };                 // centre, half-width, 1/half-width of a micro-tile (constants of the spectrum)
 
 struct TgFFView {                      // what the fused kernel reads (part of its per-star argument record)
@@ -108,6 +109,25 @@ __device__ __forceinline__ double tg_ff_transform(const double (*s_W)[TG_FF_N + 
     return c + __shfl_xor_sync(0xffffffffu, c, 16);
 }
 
+// Chebyshev coefficients c (lane k and k + 16 hold c_k) -> coefficients of the same polynomial in powers of t, a_k = sum_j M[k][j] c_j
+// (only j >= k of the parity of k: four terms per half-warp).  Why this is safe here and not in general: the interpolated functions
+// are analytic in a Bernstein ellipse of parameter rho >= 10.9, so |c_j| <= ~rho^-j |c_0| and |a_k| ~ (2/rho)^k |c_0|: the power
+// series is as well conditioned on [-1, 1] as the Chebyshev one, every term M[k][j] c_j is below |c_0|, and the rounding noise of the
+// trailing c_j enters a as M (delta c) exactly (M holds integers), i.e. as the same small polynomial sum_j delta c_j T_j(t).  The
+// fused kernel then takes one Horner recurrence (15 FMA per bin) instead of Clenshaw's (30).
+__device__ __forceinline__ double tg_ff_to_powers(const double (*s_M)[TG_FF_N + 1], double c, int lane)
+{
+    const int k = lane & 15, h4 = (lane >> 4) * 4;
+    double s = 0.0;
+#pragma unroll
+    for (int t = 3; t >= 0; t--) {                                      // smallest terms first
+        const int j = k + 2 * (h4 + t);
+        const double cj = __shfl_sync(0xffffffffu, c, j & 15);
+        s = fma((j < TG_FF_N) ? s_M[k][j & 15] : 0.0, cj, s);
+    }
+    return s + __shfl_xor_sync(0xffffffffu, s, 16);
+}
+
 // The pre-pass.  grid = (CTAs per chain, chains of the launch); cmap[chain of the launch] = (star, chain of that star) or NULL
 // (one star, identity); argv[star] = its argument record.  CTA r of a chain takes the pairs r*ppc .. r*ppc + ppc - 1 of the
 // prepared range, one after the other (the chain's table is staged once), and of each pair the 8 micro-tiles, one per warp.  Two
@@ -119,6 +139,7 @@ __global__ void __launch_bounds__(256, 4) tg_k_ff(const TgFFArgs *__restrict__ a
 {
     extern __shared__ __align__(16) unsigned char tg_ff_smem[];
     __shared__ double s_W[TG_FF_N][TG_FF_N + 1];
+    __shared__ double s_M[TG_FF_N][TG_FF_N + 1];
     __shared__ double s_tn[TG_FF_N];
     __shared__ double s_nz[TG_NOISE_STRIDE];
     __shared__ int s_cls[TG_MAXH];
@@ -140,6 +161,7 @@ __global__ void __launch_bounds__(256, 4) tg_k_ff(const TgFFArgs *__restrict__ a
     int *t_lo = (int *)(t_h + ncm), *t_hi = t_lo + ncm;
     unsigned short *l_pf = (unsigned short *)(t_hi + ncm), *l_loc = l_pf + ncm, *l_mid = l_loc + ncm + (size_t)warp * ncm;
     s_W[tid >> 4][tid & 15] = __ldg(a.ffw + tid);
+    s_M[tid >> 4][tid & 15] = __ldg(a.ffw + TG_FF_N * TG_FF_N + TG_FF_N + tid);
     if (tid < TG_FF_N) s_tn[tid] = __ldg(a.ffw + TG_FF_N * TG_FF_N + tid);
     tg_pdl_wait();                                                      // the tables of the proposed points are complete
     tg_pdl_trigger();
@@ -221,7 +243,7 @@ __global__ void __launch_bounds__(256, 4) tg_k_ff(const TgFFArgs *__restrict__ a
             double v = 0.0;
 #pragma unroll
             for (int sl = 0; sl < 16; sl++) v += s_part[sl][i];         // fixed order (both half-warps: the same sums)
-            const double c = tg_ff_transform(s_W, v, lane);
+            const double c = tg_ff_to_powers(s_M, tg_ff_transform(s_W, v, lane), lane);
             if (lane < TG_FF_N) s_cp[lane] = c;
         }
         __syncthreads();
@@ -274,12 +296,12 @@ __global__ void __launch_bounds__(256, 4) tg_k_ff(const TgFFArgs *__restrict__ a
             }
             if (half == 1) {
                 if (bg_here) v += tg_ff_background(s_nz, s_cls, nH, xn);
-            } else if (geo_ok) {                                        // the pair's interpolant at this node: Clenshaw
-                const double tt = (xn - pxc) * tg_rcp(phw), t2 = tt + tt;
-                double b1 = 0.0, b2 = 0.0;
+            } else if (geo_ok) {                                        // the pair's interpolant at this node: Horner
+                const double tt = (xn - pxc) * tg_rcp(phw);
+                double pv = s_cp[TG_FF_N - 1];
 #pragma unroll
-                for (int k = TG_FF_N - 1; k >= 1; k--) { const double bk = fma(t2, b1, s_cp[k]) - b2; b2 = b1; b1 = bk; }
-                v += fma(tt, b1, s_cp[0]) - b2;
+                for (int k = TG_FF_N - 2; k >= 0; k--) pv = fma(tt, pv, s_cp[k]);
+                v += pv;
             }
             v += __shfl_xor_sync(0xffffffffu, v, 16);
             const double c = tg_ff_transform(s_W, v, lane);
@@ -288,17 +310,22 @@ __global__ void __launch_bounds__(256, 4) tg_k_ff(const TgFFArgs *__restrict__ a
             const bool good_tail = (tail <= TG_FF_TOL * fabs(cz));      // false for NaN; 0 <= 0 when nothing is far
             const bool good = good_tail && (hw > 0.0) && (nex <= TG_FF_E);
             const size_t slot = (size_t)b * a.stride + m;
-            if (lane < TG_FF_N) a.c[slot * TG_FF_N + lane] = good ? c : 0.0;
-            unsigned need = 0u;                                         // exact records (list order), one lane each
-            if (good && lane < nex) {
-                const int k = s_xl[warp][lane];
-                TgFFRec rc; rc.nu = t_nu[k]; rc.q = t_q[k]; rc.h = t_h[k]; rc.lo = t_lo[k]; rc.len = t_hi[k] - rc.lo;
-                need = !((rc.lo <= t0) && (rc.lo + rc.len >= t1));
-                a.rec[slot * TG_FF_E + lane] = rc;
+            const double ap = tg_ff_to_powers(s_M, c, lane);
+            if (lane < TG_FF_N) a.c[slot * TG_FF_N + lane] = good ? ap : 0.0;
+            // exact records, one lane each: those whose window covers the whole micro-tile first (list order kept inside both groups),
+            // so the fused kernel's loop over them carries no window predicate
+            const bool have = good && lane < nex;
+            TgFFRec rc; rc.nu = 0.0; rc.q = 0.0; rc.h = 0.0; rc.lo = 0; rc.len = 0;
+            if (have) { const int k = s_xl[warp][lane]; rc.nu = t_nu[k]; rc.q = t_q[k]; rc.h = t_h[k]; rc.lo = t_lo[k]; rc.len = t_hi[k] - rc.lo; }
+            const bool need = have && !((rc.lo <= t0) && (rc.lo + rc.len >= t1));
+            const unsigned pm = __ballot_sync(0xffffffffu, need), fm = __ballot_sync(0xffffffffu, have && !need);
+            const int nfree = __popc(fm);
+            if (have) {
+                const unsigned below = (1u << lane) - 1u;
+                a.rec[slot * TG_FF_E + (need ? nfree + __popc(pm & below) : __popc(fm & below))] = rc;
             }
-            const unsigned pm = __ballot_sync(0xffffffffu, need != 0u);
             if (lane == 0) {
-                TgFFHdr hd; hd.count = good ? nex : TG_FF_FALLBACK; hd.pred = pm;
+                TgFFHdr hd; hd.count = good ? nex : TG_FF_FALLBACK; hd.nfree = nfree;
                 hd.flags = ((good && (bg_pair || bg_here)) ? 1 : 0) | (good_tail ? 0 : 2) | (nex <= TG_FF_E ? 0 : 4) | (hw > 0.0 ? 0 : 8); hd.nfar = nmid + npf;
                 a.hdr[slot] = hd;
             }
@@ -346,41 +373,55 @@ __device__ __forceinline__ int tg_ff_pair(const TgFFStage &st, const TgTables &t
 {
     static_assert(NB == TG_FF_MT, "8 bins per thread");
     int nfold = 0;
-    // Clenshaw, four bins at a time (independent recurrences interleave), the coefficients two per load
+    // Horner in the local variable t = (x - centre) / half-width, four bins at a time (independent recurrences interleave), the
+    // coefficients two per load
 #pragma unroll
     for (int j0 = 0; j0 < TG_FF_MT; j0 += 4) {
-        double t2[4], b1[4], b2[4], cz[4];
+        double tt[4], pv[4];
 #pragma unroll
-        for (int u = 0; u < 4; u++) { const double tt = (x[j0 + u] - st.geo[j0 + u].xc) * st.geo[j0 + u].ihw; t2[u] = tt + tt; b1[u] = 0.0; b2[u] = 0.0; }
+        for (int u = 0; u < 4; u++) { tt[u] = (x[j0 + u] - st.geo[j0 + u].xc) * st.geo[j0 + u].ihw; pv[u] = 0.0; }
 #pragma unroll
         for (int k = TG_FF_N - 2; k >= 0; k -= 2) {
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const double2 cc = *(const double2 *)&st.c[j0 + u][k];                                  // (c_k, c_k+1)
-                const double bh = fma(t2[u], b1[u], cc.y) - b2[u];                                      // b_{k+1}
-                if (k > 0) { b2[u] = bh; b1[u] = fma(t2[u], bh, cc.x) - b1[u]; }                         // b_k
-                else { b2[u] = b1[u]; b1[u] = bh; cz[u] = cc.x; }
+                const double2 cc = *(const double2 *)&st.c[j0 + u][k];                                  // (a_k, a_k+1)
+                pv[u] = (k == TG_FF_N - 2) ? fma(tt[u], cc.y, cc.x) : fma(tt[u], fma(tt[u], pv[u], cc.y), cc.x);
             }
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) acc[j0 + u] += fma(0.5 * t2[u], b1[u], cz[u]) - b2[u];
+        for (int u = 0; u < 4; u++) acc[j0 + u] += pv[u];
     }
-    // exact records of every micro-tile (uniform counts: no divergence).  (Taking record e of all eight micro-tiles in one round,
-    // eight independent chains, was measured and is slower: it costs more registers than it hides latency.)
+    // exact records of every micro-tile (uniform counts: no divergence): first those whose window covers the whole micro-tile, two at
+    // a time, then those that need the window predicate.  (Taking record e of all eight micro-tiles in one round, eight independent
+    // chains, was measured and is slower: it costs more registers than it hides latency.)
 #pragma unroll
     for (int j = 0; j < TG_FF_MT; j++) {
         const int4 h4 = *(const int4 *)&st.hdr[j];
-        const int cnt = h4.x;
+        const int cnt = h4.x, nfree = h4.y;
         nfold |= (h4.z & 1) << j;
         const int bin = b0 + j * TG_FF_BINS + tid;
         if (cnt >= 0) {
+            int e = 0;
 #pragma unroll 1
-            for (int e = 0; e < cnt; e++) {
-                const double2 r0 = *(const double2 *)&st.rec[j][e].nu;      // (nu, q)
+            for (; e + 2 <= nfree; e += 2) {
+                const double2 ra = *(const double2 *)&st.rec[j][e].nu, rb = *(const double2 *)&st.rec[j][e + 1].nu;      // (nu, q)
+                const double da = x[j] - ra.x, db = x[j] - rb.x;
+                const double ta = fma(da * da, ra.y, 1.0), tb = fma(db * db, rb.y, 1.0);
+                acc[j] = fma(fma(st.rec[j][e].h, tb, st.rec[j][e + 1].h * ta), tg_rcp_fast(ta * tb), acc[j]);              // one reciprocal for the two
+            }
+            if (e < nfree) {
+                const double2 r0 = *(const double2 *)&st.rec[j][e].nu;
+                const double d = x[j] - r0.x;
+                acc[j] = fma(st.rec[j][e].h, tg_rcp_fast(fma(d * d, r0.y, 1.0)), acc[j]);
+                e++;
+            }
+#pragma unroll 1
+            for (; e < cnt; e++) {
+                const double2 r0 = *(const double2 *)&st.rec[j][e].nu;
+                const int2 w = *(const int2 *)&st.rec[j][e].lo;
                 const double d = x[j] - r0.x;
                 const double rr = tg_rcp_fast(fma(d * d, r0.y, 1.0));
-                double hh = st.rec[j][e].h;
-                if (((unsigned)h4.y >> e) & 1u) { const int2 w = *(const int2 *)&st.rec[j][e].lo; hh = ((unsigned)(bin - w.x) < (unsigned)w.y) ? hh : 0.0; }
+                const double hh = ((unsigned)(bin - w.x) < (unsigned)w.y) ? st.rec[j][e].h : 0.0;
                 acc[j] = fma(hh, rr, acc[j]);
             }
         } else {

@@ -220,6 +220,45 @@ def test_background_moments_equal_the_bin_by_bin_path(tb, W, oracle, case, monke
     assert relerr(res["1"]["logL"], ref["logL"]) < TOL and relerr(res["0"]["logL"], ref["logL"]) < TOL
 
 
+@pytest.mark.parametrize("case", ["cfg3", "hot_chains", "narrow_modes", "general_p"])
+def test_far_field_path_equals_the_exact_path(tb, W, oracle, case, monkeypatch):
+    """Under the truncation windows (build_lorentzian.cpp:365-460) the fused kernel takes, per 256-bin micro-tile, a polynomial
+    interpolant of the components whose poles are far (prepared by the pre-pass tg_k_ff, tg_farfield.cuh) plus the exact
+    records of the near ones, instead of every component bin by bin.  Both paths must agree to rounding and both with the
+    oracle: at the usual perturbation, with hot-chain excursions three times wider, with line widths five times narrower (more
+    components inside the near radius of a micro-tile edge) and with non-integer Harvey exponents under the windows."""
+    import ctypes as C_
+    prob = W.s_global(Nx=400000, step=0.02)
+    if case == "narrow_modes":
+        iw = [i for i, n in enumerate(prob.names) if n.startswith("Width")]
+        assert iw
+        prob.params[iw] *= 0.2
+    if case == "general_p":
+        ip = [i for i, n in enumerate(prob.names) if n == "Harvey-Noise_p"]
+        prob.params[ip[1]], prob.params[ip[2]] = 3.37, 1.83
+    prob = _with_y(prob, oracle, W, seed=9)
+    Cn = 8
+    P, T = W.perturbed_params(prob, Cn, scale=3.0 if case == "hot_chains" else 1.0, seed=31), W.tcoefs(Cn, 1.3)
+    res, summ = {}, None
+    for mode in ("0", "1"):
+        monkeypatch.setenv("TG_FARFIELD", mode)
+        md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=Cn))
+        res[mode] = md.evaluate(P, T)
+        if mode == "1":
+            out = (C_.c_long * 6)()
+            assert md.lib.lib.tg_dbg_ff_summary(md.h, Cn, out) == 0
+            summ = list(out)
+        md.close()
+    ref = oracle.generate_models(prob, P, T)
+    # the path was taken: micro-tiles prepared, components interpolated, none fell back to the component-by-component loop
+    assert summ[0] > 0 and summ[3] > 10 * summ[0] and summ[1] == 0, summ
+    assert np.array_equal(res["0"]["status"], res["1"]["status"]) and np.array_equal(res["1"]["status"], ref["status"])
+    ok = ref["status"] == 0
+    assert ok.sum() >= 2
+    assert relerr(res["1"]["logL"][ok], res["0"]["logL"][ok]) < 2e-14
+    assert relerr(res["1"]["logL"][ok], ref["logL"][ok]) < TOL and relerr(res["0"]["logL"][ok], ref["logL"][ok]) < TOL
+
+
 def test_async_eval_equals_the_blocking_call(tb, W, oracle):
     """tg_eval_async / tg_eval_wait (two staging slots, MALA.cpp:632-655 with the proposal on the host): a pipeline of calls
     through alternating slots returns, call by call, the bits of tg_eval; misuse of a slot is refused."""
