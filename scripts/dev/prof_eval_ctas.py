@@ -56,20 +56,13 @@ slots_busy = dur.sum() / (148 * 2)
 print("sum of CTA durations / 296 slots = %.1f us  (efficiency vs span %.3f)" % (slots_busy, slots_busy / end.max()))
 # idle tail per SM: span - finish time of the SM
 print("idle tail per SM us: mean %.2f max %.2f" % ((end.max() - last).mean(), (end.max() - last).max()))
-# far-field path: where a heavy unit's time goes, and how much of the list is still evaluated exactly
-try:
-    fb = (C.c_longlong * (8192 * 4))()
-    lib.lib.tg_dbg_ffstats.argtypes = [C.POINTER(C.c_longlong)]
-    lib.lib.tg_dbg_ffstats(fb)
-    ffs = np.array(fb, dtype=np.int64).reshape(8192, 4)
-    full = np.array(buf, dtype=np.int64).reshape(8192, 6)
-    ok = (full[:, 5] > 0) & (ffs[:, 3] > 0)
-    hv = ffs[ok]; dd = (full[ok, 5] - full[ok, 4]) / 1e3
-    alld = (full[full[:, 5] > 0, 5] - full[full[:, 5] > 0, 4]) / 1e3
-    oth = (full[:, 5] > 0) & (ffs[:, 3] == 0)
-    do = (full[oth, 5] - full[oth, 4]) / 1e3
-    print("slot time: far-field units %.0f us in %d units, other units %.0f us in %d units (mean %.2f, max %.2f)" % (dd.sum(), ok.sum(), do.sum(), oth.sum(), do.mean() if oth.sum() else 0, do.max() if oth.sum() else 0))
-    print("far-field units: %d, duration mean %.2f us; lists %.2f us, ff set-up %.2f us; exact (quad, micro-tile) pairs %.1f of %.1f per unit (%.1f %%)" % (
-        ok.sum(), dd.mean(), hv[:, 0].mean() / f, hv[:, 1].mean() / f, hv[:, 2].mean(), hv[:, 3].mean(), 100.0 * hv[:, 2].sum() / hv[:, 3].sum()))
-except Exception as e:
-    print("no far-field stats:", e)
+# far-field path: where a unit's time goes (thread 0's clock: stage + barrier + fetch issue | interpolant + exact records | background, likelihood, running sums)
+fb = (C.c_longlong * (8192 * 4))()
+lib.lib.tg_dbg_ffstats.argtypes = [C.POINTER(C.c_longlong)]
+lib.lib.tg_dbg_ffstats(fb)
+ffs = np.array(fb, dtype=np.int64).reshape(8192, 4)
+full = np.array(buf, dtype=np.int64).reshape(8192, 6)
+ok = (full[:, 5] > 0) & (ffs[:, 3] > 0)
+hv = ffs[ok]; dd = (full[ok, 5] - full[ok, 4]) / 1e3; tot = (full[ok, 2] - full[ok, 0]) / f
+print("far-field units: %d, %.1f (pair, chain) steps each, duration mean %.2f us (clock %.2f): stage+barrier %.2f us, interpolant+records %.2f us, tail %.2f us, rest %.2f us"
+      % (ok.sum(), hv[:, 3].mean(), dd.mean(), tot.mean(), hv[:, 0].mean() / f, hv[:, 1].mean() / f, hv[:, 2].mean() / f, tot.mean() - hv[:, :3].sum(axis=1).mean() / f))

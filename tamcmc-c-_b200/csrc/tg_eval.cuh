@@ -212,7 +212,8 @@ struct TgEvalSmem {                 // carved out of the dynamic shared memory
 };
 
 // Noise background, likelihood terms and the running results of chain g for the NB bins of a thread whose Lorentzian part is in
-// acc (shared by every path of the fused kernel).  FF: nfold = micro-tiles (bits) whose acc already holds the background and N0.
+// acc (shared by every path of the fused kernel).  FF: nfold = 0xff when acc already holds the background and N0 (the far-field
+// interpolant of the thread's micro-tile folded them in), 0 otherwise.
 template <int NB, bool GEN, bool FF>
 __device__ __forceinline__ void tg_bins_tail(const TgEvalArgs &a, const TgEvalSmem &S, int g, int c0, int b0, int tid, const double (&x)[NB], const double (&y)[NB],
                                              const int (&ii)[NB], double (&acc)[NB], int nfold)
@@ -221,15 +222,7 @@ __device__ __forceinline__ void tg_bins_tail(const TgEvalArgs &a, const TgEvalSm
     const double *nz = S.nz + (size_t)g * TG_NOISE_STRIDE;
     // ---- Harvey-like background: y += H/(1+(1e-3*tc*x)^p) ; y += N0  (noise_models.cpp:30-38).
     //      The prologue lists only the active terms (tc != 0); consecutive pairs share a reciprocal.
-    // (far-field path: where the interpolant of a micro-tile already holds the background and N0, nothing is added;
-    //  after a failed check on some micro-tile the background is evaluated for all bins and used where it is missing)
-    double accf[FF ? NB : 1];
-    if constexpr (FF) {
-        if (nfold != 0 && nfold != 0xff) {
-#pragma unroll
-            for (int j = 0; j < NB; j++) { accf[j] = acc[j]; acc[j] = 0.0; }
-        }
-    }
+    // (far-field path: where the interpolant of the micro-tile already holds the background and N0, nothing is added)
     const int nH = (FF && nfold == 0xff) ? 0 : S.nh[g];
     for (int k = 0; k < nH; k += 2) {
         double ta[NB], tb[NB];
@@ -250,7 +243,6 @@ __device__ __forceinline__ void tg_bins_tail(const TgEvalArgs &a, const TgEvalSm
 #pragma unroll
     for (int j = 0; j < NB; j++) {
         m[j] = acc[j] + N0;
-        if constexpr (FF) { if (nfold != 0 && nfold != 0xff) m[j] = ((nfold >> j) & 1) ? accf[j] : accf[j] + m[j]; }
         if (GEN) {
             const int idx = b0 + j * TG_THREADS + tid;
             if (idx < Nx) { if (a.model) a.model[(size_t)(c0 + g) * Nx + idx] = m[j]; }
@@ -347,35 +339,52 @@ __device__ __forceinline__ void tg_chain_loop(const TgEvalArgs &a, const TgEvalS
 }
 
 // npair consecutive pairs of sub-tiles starting at bin b0, all of them inside the range the far-field pre-pass prepared, for the
-// G chains of the unit: per (pair, chain) the staged interpolant + exact records (tg_farfield.cuh), then the common tail.  What
-// the pre-pass left travels from L2 one (pair, chain) ahead of the arithmetic (two staging buffers, one barrier per step).
-__device__ __forceinline__ void tg_ff_run(const TgEvalArgs &a, const TgEvalSmem &S, int G, int c0, int b0, int npair, int tid, TgFFStage *stage)
+// G chains of the unit: per (pair, chain) the staged interpolant + exact records of the warp's micro-tile (tg_farfield.cuh), then
+// the common tail.  What the pre-pass left travels from L2 one (pair, chain) ahead of the arithmetic, warp by warp: no CTA barrier.
+__device__ __forceinline__ void tg_ff_run(const TgEvalArgs &a, const TgEvalSmem &S, int G, int c0, int b0, int npair, int tid, TgFFStage &st)
 {
+    const int lane = tid & 31, warp = tid >> 5;
     TgFFFetch q;
-    tg_ff_fetch(a.ff, c0, b0, tid, q);
+    tg_ff_fetch(a.ff, c0, b0, warp, lane, q);
     const int nstep = npair * G;
     int g = 0, pr = 0;
     double x[TG_FF_MT], y[TG_FF_MT];
     int ii[TG_FF_MT];
+#ifdef TG_PROFILE
+    long long pk[3] = {0, 0, 0};
+#endif
     for (int s = 0; s < nstep; s++) {
-        const int bp = b0 + pr * 2 * TG_THREADS * 4;
+        const int bp = b0 + pr * 2 * TG_THREADS * 4, bw = bp + warp * TG_FF_BINS;
         if (g == 0) {
 #pragma unroll
-            for (int j = 0; j < TG_FF_MT; j++) { ii[j] = bp + j * TG_THREADS + tid; x[j] = __ldg(a.x + ii[j]); y[j] = __ldg(a.y + ii[j]); }
+            for (int j = 0; j < TG_FF_MT; j++) { ii[j] = bw + 32 * j + lane; x[j] = __ldg(a.x + ii[j]); y[j] = __ldg(a.y + ii[j]); }
         }
-        TgFFStage &st = stage[s & 1];
-        tg_ff_stage(st, tid, q);
-        __syncthreads();
+#ifdef TG_PROFILE
+        const long long pk0 = clock64();
+#endif
+        __syncwarp();                                 // the lanes are done with the previous step's data
+        tg_ff_stage(st, warp, lane, q);
+        __syncwarp();
         int gn = g + 1, pn = pr;
         if (gn == G) { gn = 0; pn++; }
-        if (s + 1 < nstep) tg_ff_fetch(a.ff, c0 + gn, b0 + pn * 2 * TG_THREADS * 4, tid, q);
+        if (s + 1 < nstep) tg_ff_fetch(a.ff, c0 + gn, b0 + pn * 2 * TG_THREADS * 4, warp, lane, q);
         double acc[TG_FF_MT];
-#pragma unroll
-        for (int j = 0; j < TG_FF_MT; j++) acc[j] = 0.0;
-        const int nfold = tg_ff_pair(st, a.t, a.d.ncomp_max, c0 + g, bp, tid, x, acc);
-        tg_bins_tail<TG_FF_MT, false, true>(a, S, g, c0, bp, tid, x, y, ii, acc, nfold);
+#ifdef TG_PROFILE
+        const long long pk1 = clock64();
+#endif
+        const bool folded = tg_ff_microtile(st, a.t, a.d.ncomp_max, c0 + g, bw, warp, lane, x, acc);
+#ifdef TG_PROFILE
+        const long long pk2 = clock64();
+#endif
+        tg_bins_tail<TG_FF_MT, false, true>(a, S, g, c0, bp, tid, x, y, ii, acc, folded ? 0xff : 0);
+#ifdef TG_PROFILE
+        pk[0] += pk1 - pk0; pk[1] += pk2 - pk1; pk[2] += clock64() - pk2;
+#endif
         g = gn; pr = pn;
     }
+#ifdef TG_PROFILE
+    if (tid == 0 && blockIdx.x < TG_DBG_CTAS) { tg_dbg_ff[blockIdx.x][0] += pk[0]; tg_dbg_ff[blockIdx.x][1] += pk[1]; tg_dbg_ff[blockIdx.x][2] += pk[2]; tg_dbg_ff[blockIdx.x][3] += nstep; }
+#endif
 }
 
 // Exact background at one abscissa (noise table of one chain in shared memory): N0 + sum_k H_k / (1 + (a_k x)^p_k)
@@ -538,7 +547,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
     __shared__ unsigned s_fail[32], s_flag[32];       // moment path: chains that take the tile bin by bin / that flag it for the host
 
     __shared__ __align__(16) TgEvalArgs s_args;
-    __shared__ TgFFStage s_ffstage[2];
+    __shared__ TgFFStage s_ffstage;                  // far-field path: slot w of every array belongs to warp w
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int4 unit = __ldg(units + blockIdx.x);
     tg_load_args(&s_args, argv + ((unsigned)unit.w >> TG_UNIT_STAR_SHIFT));

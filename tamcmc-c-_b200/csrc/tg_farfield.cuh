@@ -334,109 +334,100 @@ __global__ void __launch_bounds__(256, 4) tg_k_ff(const TgFFArgs *__restrict__ a
 }
 
 // ---- fused-kernel side --------------------------------------------------------------------------------------------------
-// What the pre-pass left for one chain on one pair of sub-tiles (8 consecutive micro-tiles), staged in shared memory by the
-// whole CTA in ONE round trip to L2 (three 16-byte loads per thread) and double-buffered over the chains of a unit.
+// On a pair of sub-tiles (8 consecutive micro-tiles) WARP w of the CTA takes micro-tile w: lane l holds its bins l, l + 32, ...,
+// l + 224.  Everything the pre-pass left for (chain, micro-tile) -- 16 coefficients, header, geometry, records -- is therefore
+// private to one warp: it travels from L2 into the warp's slot of the staging buffer one (pair, chain) step ahead of the
+// arithmetic (three 16-byte loads per lane) and is handed over with __syncwarp only -- no CTA barrier inside a run, the warps drift
+// apart and hide each other's latencies.  The eight bins of a thread share one interpolant and one record list: every coefficient
+// and every record is read once for eight independent chains of arithmetic.
 struct __align__(16) TgFFStage {
-    TgFFRec rec[TG_FF_MT][TG_FF_E];    // 8192 bytes
-    double  c[TG_FF_MT][TG_FF_N];      // 1024 bytes
+    TgFFRec rec[TG_FF_MT][TG_FF_E];    // 8192 bytes   [warp][record]
+    double  c[TG_FF_MT][TG_FF_N];      // 1024 bytes   [warp][k]: coefficient of t^k
     TgFFHdr hdr[TG_FF_MT];             //  128 bytes
     TgFFGeo geo[TG_FF_MT];             //  256 bytes
 };
 struct TgFFFetch { int4 r0, r1, r2; };
-static_assert(sizeof(TgFFRec) * TG_FF_MT * TG_FF_E == 2 * 16 * 256, "two 16-byte pieces of the records per thread");
+static_assert(sizeof(TgFFRec) == 32 && TG_FF_E == 32, "one record per lane: two 16-byte pieces");
+static_assert(TG_FF_MT * 32 == TG_FF_BINS, "one micro-tile per warp, eight bins per lane");
 
-__device__ __forceinline__ void tg_ff_fetch(const TgFFView &f, int chain, int b0, int tid, TgFFFetch &q)
+// what the pre-pass left for `chain` on the micro-tile of this warp in the pair starting at bin bp -> registers
+__device__ __forceinline__ void tg_ff_fetch(const TgFFView &f, int chain, int bp, int warp, int lane, TgFFFetch &q)
 {
-    const int mg = b0 >> 8;
-    const size_t slot0 = (size_t)chain * f.stride + (mg - f.mt0);
-    q.r0 = __ldg((const int4 *)(f.rec + slot0 * TG_FF_E) + tid);
-    q.r2 = __ldg((const int4 *)(f.rec + slot0 * TG_FF_E) + 256 + tid);
-    q.r1 = make_int4(0, 0, 0, 0);
-    if (tid < 64)      q.r1 = __ldg((const int4 *)(f.c + slot0 * TG_FF_N) + tid);
-    else if (tid < 72) q.r1 = __ldg((const int4 *)(f.hdr + slot0) + (tid - 64));
-    else if (tid < 88) q.r1 = __ldg((const int4 *)(f.geo + mg) + (tid - 72));
+    const int mg = (bp >> 8) + warp;
+    const size_t slot = (size_t)chain * f.stride + (mg - f.mt0);
+    const int4 *rp = (const int4 *)(f.rec + slot * TG_FF_E) + 2 * lane;
+    q.r0 = __ldg(rp); q.r1 = __ldg(rp + 1);                            // record `lane` (slots past the count are never read back)
+    q.r2 = make_int4(0, 0, 0, 0);
+    if (lane < 8)       q.r2 = __ldg((const int4 *)(f.c + slot * TG_FF_N) + lane);
+    else if (lane == 8) q.r2 = __ldg((const int4 *)(f.hdr + slot));
+    else if (lane < 11) q.r2 = __ldg((const int4 *)(f.geo + mg) + (lane - 9));
 }
-__device__ __forceinline__ void tg_ff_stage(TgFFStage &st, int tid, const TgFFFetch &q)
+__device__ __forceinline__ void tg_ff_stage(TgFFStage &st, int warp, int lane, const TgFFFetch &q)
 {
-    ((int4 *)&st.rec[0][0])[tid] = q.r0;
-    ((int4 *)&st.rec[0][0])[256 + tid] = q.r2;
-    if (tid < 64)      ((int4 *)&st.c[0][0])[tid] = q.r1;
-    else if (tid < 72) ((int4 *)&st.hdr[0])[tid - 64] = q.r1;
-    else if (tid < 88) ((int4 *)&st.geo[0])[tid - 72] = q.r1;
+    int4 *rp = (int4 *)&st.rec[warp][lane];
+    rp[0] = q.r0; rp[1] = q.r1;
+    if (lane < 8)       ((int4 *)&st.c[warp][0])[lane] = q.r2;
+    else if (lane == 8) *(int4 *)&st.hdr[warp] = q.r2;
+    else if (lane < 11) ((int4 *)&st.geo[warp])[lane - 9] = q.r2;
 }
 
-// Far + exact parts of chain `chain` on the pair of sub-tiles starting at bin b0 (8 bins per thread, bin j in micro-tile
-// (b0 >> 8) + j) from the staged data: acc[j] += interpolant + exact records.  Returns the mask of micro-tiles whose interpolant
-// includes the background and N0.
+// Far + exact parts of chain `chain` on this warp's micro-tile (first bin bw; bin j of the lane = bw + 32 j + lane) from the staged
+// data: acc[j] = interpolant + exact records.  Returns whether the interpolant includes the background and N0.
 template <int NB>
-__device__ __forceinline__ int tg_ff_pair(const TgFFStage &st, const TgTables &t, int ncm, int chain, int b0, int tid, const double (&x)[NB], double (&acc)[NB])
+__device__ __forceinline__ bool tg_ff_microtile(const TgFFStage &st, const TgTables &t, int ncm, int chain, int bw, int warp, int lane, const double (&x)[NB], double (&acc)[NB])
 {
     static_assert(NB == TG_FF_MT, "8 bins per thread");
-    int nfold = 0;
-    // Horner in the local variable t = (x - centre) / half-width, four bins at a time (independent recurrences interleave), the
-    // coefficients two per load
+    const int4 h4 = *(const int4 *)&st.hdr[warp];
+    const int cnt = h4.x, nfree = h4.y;
+    // Horner in the local variable t = (x - centre) / half-width: eight independent recurrences, the coefficients two per load
+    {
+        const double xc = st.geo[warp].xc, ihw = st.geo[warp].ihw;
+        double tt[NB];
 #pragma unroll
-    for (int j0 = 0; j0 < TG_FF_MT; j0 += 4) {
-        double tt[4], pv[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) { tt[u] = (x[j0 + u] - st.geo[j0 + u].xc) * st.geo[j0 + u].ihw; pv[u] = 0.0; }
+        for (int j = 0; j < NB; j++) tt[j] = (x[j] - xc) * ihw;
 #pragma unroll
         for (int k = TG_FF_N - 2; k >= 0; k -= 2) {
+            const double2 cc = *(const double2 *)&st.c[warp][k];                                        // (a_k, a_k+1)
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const double2 cc = *(const double2 *)&st.c[j0 + u][k];                                  // (a_k, a_k+1)
-                pv[u] = (k == TG_FF_N - 2) ? fma(tt[u], cc.y, cc.x) : fma(tt[u], fma(tt[u], pv[u], cc.y), cc.x);
-            }
+            for (int j = 0; j < NB; j++) acc[j] = (k == TG_FF_N - 2) ? fma(tt[j], cc.y, cc.x) : fma(tt[j], fma(tt[j], acc[j], cc.y), cc.x);
         }
-#pragma unroll
-        for (int u = 0; u < 4; u++) acc[j0 + u] += pv[u];
     }
-    // exact records of every micro-tile (uniform counts: no divergence): first those whose window covers the whole micro-tile, two at
-    // a time, then those that need the window predicate.  (Taking record e of all eight micro-tiles in one round, eight independent
-    // chains, was measured and is slower: it costs more registers than it hides latency.)
+    if (cnt >= 0) {
+        // exact records: those whose window covers the whole micro-tile first (no predicate), then the ones cut by a window edge
+#pragma unroll 1
+        for (int e = 0; e < nfree; e++) {
+            const double2 r0 = *(const double2 *)&st.rec[warp][e].nu;      // (nu, q)
+            const double hh = st.rec[warp][e].h;
 #pragma unroll
-    for (int j = 0; j < TG_FF_MT; j++) {
-        const int4 h4 = *(const int4 *)&st.hdr[j];
-        const int cnt = h4.x, nfree = h4.y;
-        nfold |= (h4.z & 1) << j;
-        const int bin = b0 + j * TG_FF_BINS + tid;
-        if (cnt >= 0) {
-            int e = 0;
+            for (int j = 0; j < NB; j++) { const double d = x[j] - r0.x; acc[j] = fma(hh, tg_rcp_fast(fma(d * d, r0.y, 1.0)), acc[j]); }
+        }
 #pragma unroll 1
-            for (; e + 2 <= nfree; e += 2) {
-                const double2 ra = *(const double2 *)&st.rec[j][e].nu, rb = *(const double2 *)&st.rec[j][e + 1].nu;      // (nu, q)
-                const double da = x[j] - ra.x, db = x[j] - rb.x;
-                const double ta = fma(da * da, ra.y, 1.0), tb = fma(db * db, rb.y, 1.0);
-                acc[j] = fma(fma(st.rec[j][e].h, tb, st.rec[j][e + 1].h * ta), tg_rcp_fast(ta * tb), acc[j]);              // one reciprocal for the two
-            }
-            if (e < nfree) {
-                const double2 r0 = *(const double2 *)&st.rec[j][e].nu;
-                const double d = x[j] - r0.x;
-                acc[j] = fma(st.rec[j][e].h, tg_rcp_fast(fma(d * d, r0.y, 1.0)), acc[j]);
-                e++;
-            }
-#pragma unroll 1
-            for (; e < cnt; e++) {
-                const double2 r0 = *(const double2 *)&st.rec[j][e].nu;
-                const int2 w = *(const int2 *)&st.rec[j][e].lo;
+        for (int e = nfree; e < cnt; e++) {
+            const double2 r0 = *(const double2 *)&st.rec[warp][e].nu;
+            const double hh = st.rec[warp][e].h;
+            const int2 w = *(const int2 *)&st.rec[warp][e].lo;
+            const int rel = bw + lane - w.x;
+#pragma unroll
+            for (int j = 0; j < NB; j++) {
                 const double d = x[j] - r0.x;
                 const double rr = tg_rcp_fast(fma(d * d, r0.y, 1.0));
-                const double hh = ((unsigned)(bin - w.x) < (unsigned)w.y) ? st.rec[j][e].h : 0.0;
-                acc[j] = fma(hh, rr, acc[j]);
+                acc[j] = fma(((unsigned)(rel + 32 * j) < (unsigned)w.y) ? hh : 0.0, rr, acc[j]);
             }
-        } else {
-            // marked micro-tile (failed check / too many exact components): every component of the chain, window predicate included
-            const int nc = min(t.ncomp[chain], ncm);
+        }
+    } else {
+        // marked micro-tile (failed check / too many exact components): every component of the chain, window predicate included
+        const int nc = min(t.ncomp[chain], ncm);
 #pragma unroll 1
-            for (int k = 0; k < nc; k++) {
-                const size_t e = (size_t)chain * ncm + k;
-                const int lo = t.lo[e], hi = t.hi[e];
-                if ((unsigned)(bin - lo) < (unsigned)(hi - lo)) {
-                    const double d = x[j] - t.nu[e];
-                    acc[j] = fma(t.h[e], tg_rcp_fast(fma(d * d, t.q[e], 1.0)), acc[j]);
-                }
+        for (int k = 0; k < nc; k++) {
+            const size_t e = (size_t)chain * ncm + k;
+            const int lo = t.lo[e], len = t.hi[e] - lo;
+            const double nu = t.nu[e], q = t.q[e], hh = t.h[e];
+            const int rel = bw + lane - lo;
+#pragma unroll
+            for (int j = 0; j < NB; j++) {
+                if ((unsigned)(rel + 32 * j) < (unsigned)len) { const double d = x[j] - nu; acc[j] = fma(hh, tg_rcp_fast(fma(d * d, q, 1.0)), acc[j]); }
             }
         }
     }
-    return nfold;
+    return (h4.z & 1) != 0;
 }
