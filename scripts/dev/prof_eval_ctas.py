@@ -64,5 +64,14 @@ ffs = np.array(fb, dtype=np.int64).reshape(8192, 4)
 full = np.array(buf, dtype=np.int64).reshape(8192, 6)
 ok = (full[:, 5] > 0) & (ffs[:, 3] > 0)
 hv = ffs[ok]; dd = (full[ok, 5] - full[ok, 4]) / 1e3; tot = (full[ok, 2] - full[ok, 0]) / f
-print("far-field units: %d, %.1f (pair, chain) steps each, duration mean %.2f us (clock %.2f): stage+barrier %.2f us, interpolant+records %.2f us, tail %.2f us, rest %.2f us"
-      % (ok.sum(), hv[:, 3].mean(), dd.mean(), tot.mean(), hv[:, 0].mean() / f, hv[:, 1].mean() / f, hv[:, 2].mean() / f, tot.mean() - hv[:, :3].sum(axis=1).mean() / f))
+print("far-field units: %d, %.1f (pair, chain) steps each, duration mean %.2f us (clock %.2f): in the steps, mean over warps %.2f us, slowest warp %.2f us (staging waits %.2f us per warp)"
+      % (ok.sum(), hv[:, 3].mean(), dd.mean(), tot.mean(), hv[:, 0].mean() / 8 / f, hv[:, 1].mean() / f, hv[:, 2].mean() / 8 / f))
+# units outside the far-field path (background-only: moment tiles, bin-by-bin runs): how long, where
+oth = (full[:, 5] > 0) & (ffs[:, 3] == 0)
+do = (full[oth, 5] - full[oth, 4]) / 1e3; to = full[oth, 3] & 0xffffffff; so = (full[oth, 4] - full[full[:, 5] > 0, 4].min()) / 1e3
+order = np.argsort(-do)
+print("other units: %d, duration mean %.2f max %.2f; sum %.0f us (far-field units: sum %.0f us)" % (oth.sum(), do.mean(), do.max(), do.sum(), dd.sum()))
+print("longest other units (dur us, first bin, start us):", [(round(float(do[k]), 1), int(to[k]), round(float(so[k]), 1)) for k in order[:16]])
+ffd = (full[ok, 5] - full[ok, 4]) / 1e3; fft = full[ok, 3] & 0xffffffff; ffst = (full[ok, 4] - full[full[:, 5] > 0, 4].min()) / 1e3
+order = np.argsort(-ffd)
+print("longest far-field units (dur us, first bin, start us, mean warp, slowest warp):", [(round(float(ffd[k]), 1), int(fft[k]), round(float(ffst[k]), 1), round(float(hv[k, 0] / 8 / f), 1), round(float(hv[k, 1] / f), 1)) for k in order[:8]])

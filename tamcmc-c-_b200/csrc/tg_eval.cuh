@@ -383,7 +383,12 @@ __device__ __forceinline__ void tg_ff_run(const TgEvalArgs &a, const TgEvalSmem 
         g = gn; pr = pn;
     }
 #ifdef TG_PROFILE
-    if (tid == 0 && blockIdx.x < TG_DBG_CTAS) { tg_dbg_ff[blockIdx.x][0] += pk[0]; tg_dbg_ff[blockIdx.x][1] += pk[1]; tg_dbg_ff[blockIdx.x][2] += pk[2]; tg_dbg_ff[blockIdx.x][3] += nstep; }
+    if (lane == 0 && blockIdx.x < TG_DBG_CTAS) {      // [0] sum over warps of the cycles in the steps, [1] the slowest warp's, [2] sum over warps of the staging waits, [3] steps
+        atomicAdd((unsigned long long *)&tg_dbg_ff[blockIdx.x][0], (unsigned long long)(pk[0] + pk[1] + pk[2]));
+        atomicMax((unsigned long long *)&tg_dbg_ff[blockIdx.x][1], (unsigned long long)(pk[0] + pk[1] + pk[2]));
+        atomicAdd((unsigned long long *)&tg_dbg_ff[blockIdx.x][2], (unsigned long long)pk[0]);
+        if (tid == 0) tg_dbg_ff[blockIdx.x][3] += nstep;
+    }
 #endif
 }
 
