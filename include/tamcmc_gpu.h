@@ -229,6 +229,12 @@ int tg_set_tuning(tg_handle *h, int chains_per_block, int heavy_group, int light
  * (14 exact evaluations of the background per tile and chain instead of one per bin), work units per launch. */
 int tg_work_profile(tg_handle *h, long *bins_direct, long *moment_tiles, int *units);
 
+/* What the far-field pre-pass left for the B vectors of the last tg_eval batch (measurement support, no reference counterpart):
+ * out[0] micro-tiles of 256 bins prepared (B x micro-tiles of the window region), out[1] of them marked for the
+ * component-by-component loop, out[2] exact records in all of them, out[3] far components interpolated (summed over the
+ * micro-tiles), out[4] micro-tiles whose interpolant also holds the background and N0.  All zero when the path is off. */
+int tg_farfield_profile(tg_handle *h, int B, long *out);
+
 /* Device-side stopwatch on the handle's stream (CUDA events): which = 0 start, 1 stop. */
 int tg_event_record(tg_handle *h, int which);
 int tg_event_elapsed_ms(tg_handle *h, double *ms);

@@ -1816,6 +1816,23 @@ extern "C" int tg_eval_noalloc(tg_handle *h, const double *params, int B, const 
     return TG_OK;
 }
 
+// What the far-field pre-pass left for the B vectors of the last tg_eval batch (measurement support: the flops the two kernels
+// actually execute under the truncation windows follow from these counts)
+extern "C" int tg_farfield_profile(tg_handle *h, int B, long *out)
+{
+    if (!h || !out || B < 1) return fail(TG_E_BADARG, "tg_farfield_profile: bad argument");
+    for (int k = 0; k < 5; k++) out[k] = 0;
+    if (!h->ffw || !h->ev.ffh || h->ff_nmt <= 0 || B > h->ev.cap) return TG_OK;      // path off: nothing prepared
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    std::vector<TgFFHdr> hd((size_t)h->ff_nmt);
+    for (int b = 0; b < B; b++) {
+        CK(cudaMemcpy(hd.data(), h->ev.ffh + (size_t)b * h->ff_stride, hd.size() * sizeof(TgFFHdr), cudaMemcpyDeviceToHost));
+        for (const TgFFHdr &q : hd) { out[0]++; if (q.count < 0) out[1]++; else out[2] += q.count; out[3] += q.nfar; out[4] += q.flags & 1; }
+    }
+    return TG_OK;
+}
+
 // developer check (not part of the ABI): summary of the far-field headers the last tg_eval batch left
 extern "C" int tg_dbg_ff_summary(tg_handle *h, int B, long *out /* [6]: micro-tiles, fallbacks, records, far components, noise-folded, max records */)
 {

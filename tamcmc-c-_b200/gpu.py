@@ -22,7 +22,7 @@ EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", 
            "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_shard_unique_id", "tg_shard_attach", "tg_shard_detach", "tg_shard_ipc_export", "tg_shard_ipc_attach", "tg_shard_status", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_work_profile", "tg_event_record", "tg_event_elapsed_ms",
            "tg_batch_create", "tg_batch_run", "tg_batch_destroy", "tg_batch_sizes", "tg_batch_kernel_time", "tg_batch_event_record",
-           "tg_batch_prepass_time", "tg_prepass_time"]
+           "tg_batch_prepass_time", "tg_prepass_time", "tg_farfield_profile"]
 # include/tamcmc_outputs.h (host code in the same library)
 EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_close", "tg_restore_read"]
 
@@ -112,6 +112,7 @@ class GpuLibrary:
         L.tg_batch_event_record.argtypes = [C.c_void_p, C.c_int]
         L.tg_batch_prepass_time.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.tg_prepass_time.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.tg_farfield_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long)]
         L.tg_out_last_error.restype = C.c_char_p
         for name in EXPORTS_OUT[1:]:
             getattr(L, name).restype = C.c_int
@@ -412,6 +413,12 @@ class GpuModelDef:
         b, m, u = C.c_long(0), C.c_long(0), C.c_int(0)
         self.lib.check(self.lib.lib.tg_work_profile(self.h, C.byref(b), C.byref(m), C.byref(u)))
         return b.value, m.value, u.value
+
+    def farfield_profile(self, B):
+        """(micro-tiles prepared, marked, exact records, far components interpolated, micro-tiles holding the background) of the last evaluate() batch."""
+        out = (C.c_long * 5)()
+        self.lib.check(self.lib.lib.tg_farfield_profile(self.h, B, out))
+        return tuple(out)
 
     def kernel_time(self, reset=0):
         n, ms, tot = C.c_long(0), C.c_double(0), C.c_long(0)
