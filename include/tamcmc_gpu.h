@@ -78,6 +78,7 @@ typedef struct tg_problem {
 } tg_problem;
 
 #define TG_F_NO_TILE_ORDER        2 /* one work item per 1024-bin sub-tile in index order instead of heaviest-first + long noise-only items (scheduling only; results identical) */
+#define TG_F_RESTORE_MEANS        4 /* keep running sums of (sigma, mu, covarmat, vars) of every step on the device: the *_mean blocks of the restore files (outputs.cpp:1758-1818), read by tg_get_state_means */
 #define TG_F_FIX_SWAP_BOOKKEEPING 1 /* fix quirk Q8 (stale logPosterior[B] after a swap, MALA.cpp:417-428); default replicates */
 
 /* Per-step records the reference hands to Outputs (MALA.cpp:696-707), for nsteps steps.
@@ -158,6 +159,13 @@ int tg_last_work(tg_handle *h, int B, double *L, int *K);
 int tg_get_state(tg_handle *h, double *vars, double *mu, double *sigma, double *covarmat,
                  double *logL, double *logPrior, double *logPost);
 int tg_set_state(tg_handle *h, const double *vars, const double *mu, const double *sigma, const double *covarmat);
+/* The averages the reference keeps for its restore files (Outputs::update_buffer_restore, outputs.cpp:1758-1818: sigmas_mean,
+ * mus_mean, covarmats_mean, vars_mean = means over the steps since the files were last written; MALA::restore_proposal uses them
+ * instead of the last values when do_restore_proposal_mean = 1, MALA.cpp:206-232).  Needs TG_F_RESTORE_MEANS in tg_problem.flags
+ * (TG_E_UNSUPPORTED otherwise): the sums are accumulated on the device by the decision kernel of every step.  Returns the means
+ * over the *count steps run since the last reset (count = 0: the current values); reset != 0 starts a new average.  NULL
+ * pointers are skipped; layouts as tg_get_state. */
+int tg_get_state_means(tg_handle *h, double *vars_mean, double *mu_mean, double *sigma_mean, double *covarmat_mean, long *count, int reset);
 
 /* MALA::execute (MALA.cpp:608-737) for iterations i0 .. i0+nsteps-1, entirely on the device:
  * proposal (new_prop_values :335-353), generate_model, MH accept (update_position_MH :447-538),

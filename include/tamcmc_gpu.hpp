@@ -71,6 +71,13 @@ public:
     {
         check(tg_get_state(h_, vars, mu, sigma, covarmat, logLikelihood, logPrior, logPosterior));
     }
+    // buf_restore.*_mean of the reference (outputs.cpp:1758-1818); the problem must carry TG_F_RESTORE_MEANS
+    long get_state_means(double *vars_mean, double *mu_mean, double *sigma_mean, double *covarmat_mean, bool reset = true)
+    {
+        long n = 0;
+        check(tg_get_state_means(h_, vars_mean, mu_mean, sigma_mean, covarmat_mean, &n, reset ? 1 : 0));
+        return n;
+    }
     void set_state(const double *vars, const double *mu, const double *sigma, const double *covarmat)
     {
         check(tg_set_state(h_, vars, mu, sigma, covarmat));

@@ -45,12 +45,20 @@ int tg_out_append(tg_out *o, const tg_records *rec, long nsteps, int n_ensembles
  * Values are written with 17 significant digits (the reference's stream default keeps 6: a restart from its
  * own files is not exact; its reader accepts any precision). */
 int tg_out_write_restore(tg_out *o, long iteration, const double *vars, const double *mu, const double *sigma, const double *covarmat);
+/* The same with the averages of the reference's restore files (buf_restore.*_mean, outputs.cpp:1758-1818: means of sigma, mu,
+ * covarmat and vars over the steps since the files were last written -- tg_get_state_means gives them).  A NULL mean pointer
+ * falls back to what tg_out_write_restore writes in that block. */
+int tg_out_write_restore_means(tg_out *o, long iteration, const double *vars, const double *mu, const double *sigma, const double *covarmat,
+                               const double *vars_mean, const double *mu_mean, const double *sigma_mean, const double *covarmat_mean);
 int tg_out_close(tg_out *o);
 
 /* Reader of the restore triplet.  First call with all arrays NULL to get the sizes.  do_restore_last_index == 0
  * forces iteration = 0 (config.cpp:1370-1378).  Returns TG_OK, TG_E_BADARG (missing file / keyword). */
 int tg_restore_read(const char *restore_root, int do_restore_last_index, int *Nchains, int *Nvars, long *iteration,
                     double *vars, double *mu, double *sigma, double *covarmat);
+/* The *_mean blocks of the same files (what MALA::restore_proposal installs when do_restore_proposal_mean = 1, MALA.cpp:206-232). */
+int tg_restore_read_means(const char *restore_root, int do_restore_last_index, int *Nchains, int *Nvars, long *iteration,
+                          double *vars_mean, double *mu_mean, double *sigma_mean, double *covarmat_mean);
 const char *tg_out_last_error(void);
 
 #ifdef __cplusplus

@@ -779,6 +779,13 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     DA(s.mu, 3 * C * Nv); DA(s.sigma, C); DA(s.cov, 3 * C * Nv * Nv); DA(s.chol, 3 * C * Nv * Nv); DA(s.live, C); DA(s.chol_fail, 3 * C); DA(s.sticky_status, C);
     DA(h->stage_mu, C * Nv); DA(h->stage_cov, C * Nv * Nv);
     DA(s.ctrl, 1); DA(s.ens_ticket, s.E);
+    s.acc_sigma = s.acc_mu = s.acc_cov = s.acc_vars = nullptr; s.acc_count = nullptr;
+    if (p->flags & TG_F_RESTORE_MEANS) {
+        DA(s.acc_sigma, C); DA(s.acc_mu, C * Nv); DA(s.acc_cov, C * Nv * Nv); DA(s.acc_vars, C * Nv); DA(s.acc_count, 1);
+        CK(cudaMemsetAsync(s.acc_sigma, 0, C * 8, h->stream)); CK(cudaMemsetAsync(s.acc_mu, 0, C * Nv * 8, h->stream));
+        CK(cudaMemsetAsync(s.acc_cov, 0, C * Nv * Nv * 8, h->stream)); CK(cudaMemsetAsync(s.acc_vars, 0, C * Nv * 8, h->stream));
+        CK(cudaMemsetAsync(s.acc_count, 0, 8, h->stream));
+    }
     CK(cudaMemsetAsync(s.ens_ticket, 0, (size_t)s.E * 4, h->stream));
     s.index_to_relax = h->index_to_relax; s.Tcoefs = h->Tcoefs;
     {
@@ -1057,6 +1064,39 @@ extern "C" int tg_get_state(tg_handle *h, double *vars, double *mu, double *sigm
     if (logL) CK(cudaMemcpy(logL, h->s.logL_cur, C * 8, cudaMemcpyDeviceToHost));
     if (logPrior) CK(cudaMemcpy(logPrior, h->s.logPrior_cur, C * 8, cudaMemcpyDeviceToHost));
     if (logPost) CK(cudaMemcpy(logPost, h->s.logPost_cur, C * 8, cudaMemcpyDeviceToHost));
+    return TG_OK;
+}
+
+extern "C" int tg_get_state_means(tg_handle *h, double *vars_mean, double *mu_mean, double *sigma_mean, double *covarmat_mean, long *count, int reset)
+{
+    if (!h) return fail(TG_E_BADARG, "null handle");
+    if (!h->s.acc_cov) return fail(TG_E_UNSUPPORTED, "tg_get_state_means: the handle was created without TG_F_RESTORE_MEANS");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    const size_t C = h->s.C, Nv = h->s.Nv;
+    long long n = 0;
+    CK(cudaMemcpy(&n, h->s.acc_count, 8, cudaMemcpyDeviceToHost));
+    if (count) *count = (long)n;
+    if (n == 0) {      // nothing summed yet: the current values (what the reference's first write after a restore holds)
+        int r = tg_get_state(h, vars_mean, mu_mean, sigma_mean, covarmat_mean, nullptr, nullptr, nullptr); if (r) return r;
+    } else {
+        const double inv = 1.0 / (double)n;
+        auto fetch = [&](double *dst, const double *src, size_t len) -> int {
+            if (!dst) return TG_OK;
+            CK(cudaMemcpy(dst, src, len * 8, cudaMemcpyDeviceToHost));
+            for (size_t k = 0; k < len; k++) dst[k] *= inv;
+            return TG_OK;
+        };
+        int r;
+        if ((r = fetch(vars_mean, h->s.acc_vars, C * Nv)) || (r = fetch(mu_mean, h->s.acc_mu, C * Nv)) || (r = fetch(sigma_mean, h->s.acc_sigma, C)) ||
+            (r = fetch(covarmat_mean, h->s.acc_cov, C * Nv * Nv))) return r;
+    }
+    if (reset) {
+        CK(cudaMemsetAsync(h->s.acc_sigma, 0, C * 8, h->stream)); CK(cudaMemsetAsync(h->s.acc_mu, 0, C * Nv * 8, h->stream));
+        CK(cudaMemsetAsync(h->s.acc_cov, 0, C * Nv * Nv * 8, h->stream)); CK(cudaMemsetAsync(h->s.acc_vars, 0, C * Nv * 8, h->stream));
+        CK(cudaMemsetAsync(h->s.acc_count, 0, 8, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
     return TG_OK;
 }
 

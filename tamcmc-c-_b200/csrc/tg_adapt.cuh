@@ -55,6 +55,10 @@ struct TgState {
     const int    *index_to_relax;          // [Nv]
     const double *Tcoefs;                  // [C]
     TgCtrl *ctrl;
+    // Running sums of (sigma, mu, Sigma, vars) over the steps since the last drain: the *_mean blocks of the restore files
+    // (outputs.cpp:1758-1818).  NULL unless the problem asks for them (TG_F_RESTORE_MEANS).
+    double *acc_sigma, *acc_mu, *acc_cov, *acc_vars;   // [C], [C][Nv], [C][Nv][Nv], [C][Nv]
+    long long *acc_count;                              // steps summed
 };
 
 __device__ __forceinline__ size_t tg_slot_vec(const TgState &s, int slot, int c) { return ((size_t)slot * s.C + c) * s.Nv; }

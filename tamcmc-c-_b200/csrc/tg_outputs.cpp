@@ -166,8 +166,15 @@ static void restore_preamble(std::ofstream &f, int number, const char *what, con
 
 extern "C" int tg_out_write_restore(tg_out *o, long iteration, const double *vars, const double *mu, const double *sigma, const double *covarmat)
 {
+    return tg_out_write_restore_means(o, iteration, vars, mu, sigma, covarmat, nullptr, nullptr, nullptr, nullptr);
+}
+
+extern "C" int tg_out_write_restore_means(tg_out *o, long iteration, const double *vars, const double *mu, const double *sigma, const double *covarmat,
+                                          const double *vars_mean, const double *mu_mean, const double *sigma_mean, const double *covarmat_mean)
+{
     if (!o || o->restore_root.empty() || !vars || !mu || !sigma || !covarmat) return fail(TG_E_BADARG, "tg_out_write_restore: bad argument");
     const int C = o->C, Nv = o->Nv, P = 17;
+    if (!vars_mean) vars_mean = o->written ? o->vars_mean.data() : vars;
     {
         std::ofstream f((o->restore_root + "1.dat").c_str());
         if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->restore_root + "1.dat");
@@ -175,16 +182,17 @@ extern "C" int tg_out_write_restore(tg_out *o, long iteration, const double *var
         f << "! vars= \n";
         for (int c = 0; c < C; c++) f << eigen_row(vars + (size_t)c * Nv, Nv, P) << "\n";
         f << "! vars_mean= \n";
-        for (int c = 0; c < C; c++) f << eigen_row((o->written ? o->vars_mean.data() : vars) + (size_t)c * Nv, Nv, P) << "\n";
+        for (int c = 0; c < C; c++) f << eigen_row(vars_mean + (size_t)c * Nv, Nv, P) << "\n";
     }
     {
         std::ofstream f((o->restore_root + "2.dat").c_str());
         if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->restore_root + "2.dat");
         restore_preamble(f, 2, "# Contains the last values of (a) sigmas[0:Nchains-1] and (b) mus[0:Nchains-1, 0:Nvars-1].  sigmas_mean and mus_mean denotes averaged values of Nbuffer\n", o, iteration, "do_restore");
         for (int rep = 0; rep < 2; rep++) {
-            f << (rep ? "! sigmas_mean= " : "! sigmas= ") << eigen_row(sigma, C, P) << "\n";
+            const double *sg = (rep && sigma_mean) ? sigma_mean : sigma, *m = (rep && mu_mean) ? mu_mean : mu;
+            f << (rep ? "! sigmas_mean= " : "! sigmas= ") << eigen_row(sg, C, P) << "\n";
             f << (rep ? "! mus_mean= \n" : "! mus= \n");
-            for (int c = 0; c < C; c++) f << eigen_row(mu + (size_t)c * Nv, Nv, P) << "\n";
+            for (int c = 0; c < C; c++) f << eigen_row(m + (size_t)c * Nv, Nv, P) << "\n";
         }
     }
     {
@@ -192,10 +200,11 @@ extern "C" int tg_out_write_restore(tg_out *o, long iteration, const double *var
         if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->restore_root + "3.dat");
         restore_preamble(f, 3, "# Contains the last value of the covariance matrix covarmats[0:Nchains-1, 0:Nvars-1, 0:Nvars-1]. covarmats_mean denotes the averaged values over Nbuffer\n", o, iteration, "do_restore");
         for (int rep = 0; rep < 2; rep++) {
+            const double *cv = (rep && covarmat_mean) ? covarmat_mean : covarmat;
             f << (rep ? "! covarmats_mean= \n" : "! covarmats= \n");
             for (int c = 0; c < C; c++) {
                 f << "*" << c << "\n";
-                for (int i = 0; i < Nv; i++) f << eigen_row(covarmat + ((size_t)c * Nv + i) * Nv, Nv, P) << "\n";
+                for (int i = 0; i < Nv; i++) f << eigen_row(cv + ((size_t)c * Nv + i) * Nv, Nv, P) << "\n";
             }
         }
     }
@@ -221,10 +230,24 @@ static bool parse_row(const std::string &line, double *dst, int n)
     return true;
 }
 
+static int restore_read_impl(const char *root, int last_index, int *Nchains, int *Nvars, long *iteration,
+                             double *vars, double *mu, double *sigma, double *covarmat, bool mean);
 extern "C" int tg_restore_read(const char *root, int last_index, int *Nchains, int *Nvars, long *iteration,
                                double *vars, double *mu, double *sigma, double *covarmat)
 {
+    return restore_read_impl(root, last_index, Nchains, Nvars, iteration, vars, mu, sigma, covarmat, false);
+}
+extern "C" int tg_restore_read_means(const char *root, int last_index, int *Nchains, int *Nvars, long *iteration,
+                                     double *vars_mean, double *mu_mean, double *sigma_mean, double *covarmat_mean)
+{
+    return restore_read_impl(root, last_index, Nchains, Nvars, iteration, vars_mean, mu_mean, sigma_mean, covarmat_mean, true);
+}
+static int restore_read_impl(const char *root, int last_index, int *Nchains, int *Nvars, long *iteration,
+                             double *vars, double *mu, double *sigma, double *covarmat, bool mean)
+{
     if (!root) return fail(TG_E_BADARG, "tg_restore_read: bad argument");
+    const std::string k_vars = mean ? "! vars_mean" : "! vars", k_mus = mean ? "! mus_mean" : "! mus", k_sig = mean ? "! sigmas_mean" : "! sigmas",
+                      k_cov = mean ? "! covarmats_mean" : "! covarmats";
     int C = -1, Nv = -1;
     long it = 0;
     for (int number = 1; number <= 3; number++) {
@@ -241,22 +264,22 @@ extern "C" int tg_restore_read(const char *root, int last_index, int *Nchains, i
             if (key == "! Nchains") C = atoi(val.c_str());
             else if (key == "! Nvars") Nv = atoi(val.c_str());
             else if (key == "! iteration") it = last_index ? atol(val.c_str()) : 0;
-            else if (key == "! vars" || key == "! mus") {
+            else if (key == k_vars || key == k_mus) {
                 if (C < 1 || Nv < 1) return fail(TG_E_BADARG, "restore file: sizes must precede the values");
-                double *dst = (key == "! vars") ? vars : mu;
+                double *dst = (key == k_vars) ? vars : mu;
                 std::vector<double> tmp((size_t)Nv);
                 for (int c = 0; c < C; c++) {
                     if (!std::getline(f, line) || !parse_row(line, tmp.data(), Nv)) return fail(TG_E_BADARG, "restore file: short row in " + key);
                     if (dst) memcpy(dst + (size_t)c * Nv, tmp.data(), (size_t)Nv * 8);
                 }
                 found++;
-            } else if (key == "! sigmas") {
+            } else if (key == k_sig) {
                 if (C < 1) return fail(TG_E_BADARG, "restore file: sizes must precede the values");
                 std::vector<double> tmp((size_t)C);
                 if (!parse_row(val, tmp.data(), C)) return fail(TG_E_BADARG, "restore file: short sigmas");
                 if (sigma) memcpy(sigma, tmp.data(), (size_t)C * 8);
                 found++;
-            } else if (key == "! covarmats") {
+            } else if (key == k_cov) {
                 if (C < 1 || Nv < 1) return fail(TG_E_BADARG, "restore file: sizes must precede the values");
                 std::vector<double> tmp((size_t)Nv);
                 for (int c = 0; c < C; c++) {

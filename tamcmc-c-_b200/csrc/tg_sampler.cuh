@@ -318,6 +318,18 @@ __global__ void __launch_bounds__(256) tg_k_finish(const TgFinishArgs *__restric
     }
     __syncthreads();
     if (a.record) tg_write_record(a, slot, c, -1, tid, nt);
+    // running sums of the proposal law after this step's update (Outputs::update_buffer_restore, outputs.cpp:1758-1818; the
+    // reference sums sigma, mu and covarmat of every step and divides when it writes the restore files)
+    if (s.acc_cov) {
+        const int lv = s.live[c];                                    // written by thread 0 before the barriers above
+        const size_t nn = (size_t)Nv * Nv;
+        const double *cv = s.cov + tg_slot_mat(s, lv, c);
+        double *ac = s.acc_cov + (size_t)c * nn;
+        for (size_t e = tid; e < nn; e += nt) ac[e] += cv[e];
+        const double *m = s.mu + tg_slot_vec(s, lv, c);
+        for (int v = tid; v < Nv; v += nt) s.acc_mu[(size_t)c * Nv + v] += m[v];
+        if (tid == 0) s.acc_sigma[c] += s.sigma[c];
+    }
 
     // 4. last CTA of the ensemble: its tempering swap (MALA.cpp:381-445, :676-692)
     const int e = c / s.Ce;
@@ -382,11 +394,16 @@ __global__ void __launch_bounds__(256) tg_k_finish(const TgFinishArgs *__restric
             a.rec.swap_Pswap[re] = doswap ? s_sw[0] : 0.0; a.rec.swap_done[re] = doswap;
         }
     }
+    // the variables of the ensemble's chains as the step leaves them (after the swap): running sums for vars_mean
+    if (s.acc_vars) {
+        __syncthreads();                                             // the swapped rows are written
+        for (int q = tid; q < s.Ce * Nv; q += nt) { const size_t k = (size_t)e * s.Ce * Nv + q; s.acc_vars[k] += __ldcg(s.vars_cur + k); }
+    }
     // 5. the last ensemble of the star advances the iteration
     if (tid == 0) {
         s.ens_ticket[e] = 0u;
         const unsigned t2 = atomicAdd(&s.ctrl->ticket, 1u);
-        if (t2 == (unsigned)(s.E - 1)) { s.ctrl->ticket = 0u; s.ctrl->i = it + 1; }
+        if (t2 == (unsigned)(s.E - 1)) { s.ctrl->ticket = 0u; s.ctrl->i = it + 1; if (s.acc_count) *s.acc_count += 1; }
     }
 #ifdef TG_PROFILE
     if (tid == 0) tg_dbg_tl[4] = globaltimer_ns();

@@ -16,15 +16,16 @@ from .build import LIB_PATH, build_library
 
 ST_EMPTY_WINDOW, ST_NAN_WINDOW, ST_NAN_LOGL, ST_BAD_PRIOR, ST_CHOL_FAIL, ST_MODE_OVERFLOW = 1, 2, 4, 8, 16, 32
 F_FIX_SWAP_BOOKKEEPING = 1
+F_RESTORE_MEANS = 4
 
 EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", "tg_eval_async", "tg_eval_wait", "tg_eval_noalloc", "tg_eval_upload", "tg_eval_resident",
            "tg_eval_fetch", "tg_last_work", "tg_get_state", "tg_set_state", "tg_run", "tg_sizes", "tg_step_begin",
            "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_shard_unique_id", "tg_shard_attach", "tg_shard_detach", "tg_shard_ipc_export", "tg_shard_ipc_attach", "tg_shard_status", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_work_profile", "tg_event_record", "tg_event_elapsed_ms",
            "tg_batch_create", "tg_batch_run", "tg_batch_destroy", "tg_batch_sizes", "tg_batch_kernel_time", "tg_batch_event_record",
-           "tg_batch_prepass_time", "tg_prepass_time", "tg_farfield_profile"]
+           "tg_batch_prepass_time", "tg_prepass_time", "tg_farfield_profile", "tg_get_state_means"]
 # include/tamcmc_outputs.h (host code in the same library)
-EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_close", "tg_restore_read"]
+EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_write_restore_means", "tg_out_close", "tg_restore_read", "tg_restore_read_means"]
 
 
 # include/tamcmc_frontend.h (host code in the same library)
@@ -113,14 +114,17 @@ class GpuLibrary:
         L.tg_batch_prepass_time.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.tg_prepass_time.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.tg_farfield_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long)]
+        L.tg_get_state_means.argtypes = [C.c_void_p] + [C.c_void_p] * 4 + [C.POINTER(C.c_long), C.c_int]
         L.tg_out_last_error.restype = C.c_char_p
         for name in EXPORTS_OUT[1:]:
             getattr(L, name).restype = C.c_int
         L.tg_out_open.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
         L.tg_out_append.argtypes = [C.c_void_p, C.POINTER(_Records), C.c_long, C.c_int]
         L.tg_out_write_restore.argtypes = [C.c_void_p, C.c_long] + [C.c_void_p] * 4
+        L.tg_out_write_restore_means.argtypes = [C.c_void_p, C.c_long] + [C.c_void_p] * 8
         L.tg_out_close.argtypes = [C.c_void_p]
         L.tg_restore_read.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_long)] + [C.c_void_p] * 4
+        L.tg_restore_read_means.argtypes = L.tg_restore_read.argtypes
         L.tg_fe_last_error.restype = C.c_char_p
         for name in ("tg_fe_open", "tg_fe_counts", "tg_fe_nslices", "tg_fe_setup", "tg_fe_problem", "tg_fe_run_info", "tg_evidence", "tg_acceptance"):
             getattr(L, name).restype = C.c_int
@@ -365,6 +369,15 @@ class GpuModelDef:
         mu, sigma, cov = np.empty((Cn, Nv)), np.empty(Cn), np.empty((Cn, Nv, Nv))
         self.lib.check(self.lib.lib.tg_get_state(self.h, None, _p(mu), _p(sigma), _p(cov), None, None, None))
         return mu, sigma, cov
+
+    def get_state_means(self, reset=True):
+        """buf_restore.*_mean of the reference (outputs.cpp:1758-1818): means of vars, mu, sigma, covarmat over the steps since the last
+        reset, and their number.  Needs MalaConfig(flags=F_RESTORE_MEANS)."""
+        Cn, Nv = self.Nmodels, self.Nvars
+        v, mu, sigma, cov = np.empty((Cn, Nv)), np.empty((Cn, Nv)), np.empty(Cn), np.empty((Cn, Nv, Nv))
+        n = C.c_long(0)
+        self.lib.check(self.lib.lib.tg_get_state_means(self.h, _p(v), _p(mu), _p(sigma), _p(cov), C.byref(n), int(bool(reset))))
+        return dict(vars=v, mu=mu, sigma=sigma, covarmat=cov, count=n.value)
 
     def set_state(self, vars_=None, mu=None, sigma=None, covarmat=None):
         f = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)

@@ -65,10 +65,15 @@ class Outputs:
         v = np.ascontiguousarray(model_def.vars, dtype=np.float64)
         _check(self.lib, self.lib.lib.tg_out_write_restore(self.h, int(iteration), _p(v), _p(mu), _p(sigma), _p(cov)))
 
-    def write_restore_arrays(self, iteration, vars_, mu, sigma, cov):
+    def write_restore_arrays(self, iteration, vars_, mu, sigma, cov, means=None):
+        """means: dict(vars, mu, sigma, covarmat) as GpuModelDef.get_state_means returns it -> the *_mean blocks."""
         f = lambda a: np.ascontiguousarray(a, dtype=np.float64)
         v, m, s, c = f(vars_), f(mu), f(sigma), f(cov)
-        _check(self.lib, self.lib.lib.tg_out_write_restore(self.h, int(iteration), _p(v), _p(m), _p(s), _p(c)))
+        if means is None:
+            _check(self.lib, self.lib.lib.tg_out_write_restore(self.h, int(iteration), _p(v), _p(m), _p(s), _p(c)))
+        else:
+            mv, mm, ms, mc = f(means["vars"]), f(means["mu"]), f(means["sigma"]), f(means["covarmat"])
+            _check(self.lib, self.lib.lib.tg_out_write_restore_means(self.h, int(iteration), _p(v), _p(m), _p(s), _p(c), _p(mv), _p(mm), _p(ms), _p(mc)))
 
     def close(self):
         if self.h:
@@ -84,4 +89,15 @@ def read_restore(restore_root, do_restore_last_index=True, lib=None):
     _check(lib, lib.lib.tg_restore_read(root, int(do_restore_last_index), C.byref(Cn), C.byref(Nv), C.byref(it), None, None, None, None))
     v, mu, sg, cov = np.empty((Cn.value, Nv.value)), np.empty((Cn.value, Nv.value)), np.empty(Cn.value), np.empty((Cn.value, Nv.value, Nv.value))
     _check(lib, lib.lib.tg_restore_read(root, int(do_restore_last_index), C.byref(Cn), C.byref(Nv), C.byref(it), _p(v), _p(mu), _p(sg), _p(cov)))
+    return dict(iteration=it.value, vars=v, mu=mu, sigma=sg, covarmat=cov)
+
+
+def read_restore_means(restore_root, do_restore_last_index=True, lib=None):
+    """The *_mean blocks of the same files (MALA::restore_proposal with do_restore_proposal_mean = 1, MALA.cpp:206-232)."""
+    lib = lib or load_library()
+    Cn, Nv, it = C.c_int(0), C.c_int(0), C.c_long(0)
+    root = restore_root.encode()
+    _check(lib, lib.lib.tg_restore_read_means(root, int(do_restore_last_index), C.byref(Cn), C.byref(Nv), C.byref(it), None, None, None, None))
+    v, mu, sg, cov = np.empty((Cn.value, Nv.value)), np.empty((Cn.value, Nv.value)), np.empty(Cn.value), np.empty((Cn.value, Nv.value, Nv.value))
+    _check(lib, lib.lib.tg_restore_read_means(root, int(do_restore_last_index), C.byref(Cn), C.byref(Nv), C.byref(it), _p(v), _p(mu), _p(sg), _p(cov)))
     return dict(iteration=it.value, vars=v, mu=mu, sigma=sg, covarmat=cov)

@@ -126,6 +126,16 @@ def test_cli_three_phases_write_the_reference_files(tb, tmp_path):
         if n == "Frequency_l":
             f_true = prob.params[prob.index_to_relax[k]]
             assert abs(va[:, k].mean() - f_true) < (0.15 if abs(f_true - 1030.0) < 1e-6 else 0.5)
+    # the *_mean blocks of the restore files are averages over the last buffer (Outputs::update_buffer_restore, outputs.cpp:1758-1818):
+    # vars_mean = mean of the last 100 samples of the params files (Nbuffer = 500: 600 = 500 + 100), and while the proposal is
+    # being learnt mu_mean / sigmas_mean are not the last values
+    root_l = os.path.join(rs, "star_1_restore_L_")
+    last_l, mean_l = tb.outputs.read_restore(root_l), tb.outputs.read_restore_means(root_l)
+    for m in range(Cn):
+        vm = np.fromfile(os.path.join(o, "star_1_L_params_chain-%d.bin" % m)).reshape(600, Nv)[500:].mean(axis=0)
+        assert np.allclose(mean_l["vars"][m], vm, rtol=1e-12, atol=1e-300)
+    assert not np.allclose(mean_l["mu"], last_l["mu"], rtol=1e-9) and not np.allclose(mean_l["covarmat"], last_l["covarmat"], rtol=1e-9)
+    assert np.all(mean_l["sigma"] > 0) and np.all(np.linalg.eigvalsh(mean_l["covarmat"][0]) > -1e-12)
     # same seed, same files
     r2 = subprocess.run([exe, "execute", "1", "1", "1", "1", "2"], cwd=wd, capture_output=True, text=True, env=env, timeout=600)
     assert r2.returncode == 0

@@ -268,3 +268,46 @@ def test_resume_through_the_restore_files(tb, W, tmp_path):
     assert np.array_equal(v0, ra["vars"][:, 0])
     for m in (a, b, c):
         m.close()
+
+
+@pytest.mark.parametrize("problem,per_ensemble", [("gauss", 0), ("global", 0), ("gauss", 2)])
+def test_restore_means_equal_a_step_by_step_average(tb, W, oracle, problem, per_ensemble):
+    """buf_restore.*_mean of the reference (Outputs::update_buffer_restore, outputs.cpp:1758-1818: sums of sigma, mu, covarmat
+    and vars of every step, divided when the restore files are written; used by MALA::restore_proposal when
+    do_restore_proposal_mean = 1, MALA.cpp:206-232).  The device keeps the sums (TG_F_RESTORE_MEANS); they must equal the average
+    of the states a second handle with the same seed shows step after step -- learning on, swaps on, one and two ensembles."""
+    if problem == "gauss":
+        prob = _gauss(W)
+    else:
+        prob = W.small_global(3, Nx=3000, step=0.06)
+        st, m, _ = oracle.model(prob.model_case, prob.params, prob.plength, prob.x)
+        prob.y = m * (-np.log(W.philox_uniform(m.size, 4)))
+    n, Cn = 37, 4
+    mk = lambda flags: tb.MalaConfig(Nchains=Cn, chains_per_ensemble=per_ensemble, Nt_learn=[5, 10000], periods_learn=[1], c0=3.0, seed=21, flags=flags)
+    a = tb.GpuModelDef(prob, mk(tb.gpu.F_RESTORE_MEANS))
+    assert a.get_state_means(reset=False)["count"] == 0
+    ra = tb.GpuMALA(a).execute(0, n)
+    ma = a.get_state_means(reset=True)
+    b = tb.GpuModelDef(prob, mk(0))
+    with pytest.raises(tb.TgError):
+        b.get_state_means()
+    run_b = tb.GpuMALA(b)
+    acc = dict(vars=0.0, mu=0.0, sigma=0.0, covarmat=0.0)
+    for i in range(n):
+        rb = run_b.execute(i, 1)
+        assert np.array_equal(rb["vars"][0], ra["vars"][i])          # the flag does not touch the trajectory
+        mu, sigma, cov = b.get_proposal()
+        acc["vars"] = acc["vars"] + b.vars; acc["mu"] = acc["mu"] + mu; acc["sigma"] = acc["sigma"] + sigma; acc["covarmat"] = acc["covarmat"] + cov
+    assert ma["count"] == n
+    for k in acc:
+        ref = acc[k] / n
+        assert np.allclose(ma[k], ref, rtol=1e-12, atol=1e-13 * np.max(np.abs(ref))), k
+    assert np.allclose(ma["vars"], ra["vars"].mean(axis=0), rtol=1e-12, atol=1e-300)
+    # a new average starts after the reset: nothing summed -> the current values; then the next block alone
+    cur = a.get_state_means(reset=False)
+    mu, sigma, cov = a.get_proposal()
+    assert cur["count"] == 0 and np.array_equal(cur["mu"], mu) and np.array_equal(cur["sigma"], sigma) and np.array_equal(cur["covarmat"], cov)
+    r2 = tb.GpuMALA(a).execute(n, 20)
+    m2 = a.get_state_means(reset=True)
+    assert m2["count"] == 20 and np.allclose(m2["vars"], r2["vars"].mean(axis=0), rtol=1e-12, atol=1e-300)
+    a.close(); b.close()

@@ -114,6 +114,73 @@ def test_append_mode_and_restore_round_trip(tb, W, tmp_path):
     assert int(_hdr(str(tmp_path / "r_params.hdr"))["Nsamples_done"]) == 10
 
 
+def test_restore_mean_blocks_round_trip(tb, W, tmp_path):
+    """buf_restore.*_mean (outputs.cpp:1758-1818): written from the device's running means, read back by tg_restore_read_means
+    (MALA::restore_proposal with do_restore_proposal_mean = 1, MALA.cpp:206-232); the last values are untouched by them."""
+    prob = W.small_global(3, Nx=2000)
+    Cn, Nv = 3, prob.index_to_relax.size
+    a = tb.outputs.Outputs(prob, W.tcoefs(Cn), str(tmp_path), root="m", Nsamples=30)
+    g = np.random.default_rng(11)
+    last = dict(vars=g.standard_normal((Cn, Nv)), mu=g.standard_normal((Cn, Nv)), sigma=g.random(Cn) + 0.1, covarmat=g.standard_normal((Cn, Nv, Nv)))
+    mean = dict(vars=g.standard_normal((Cn, Nv)), mu=g.standard_normal((Cn, Nv)), sigma=g.random(Cn) + 0.1, covarmat=g.standard_normal((Cn, Nv, Nv)))
+    a.write_restore_arrays(7, last["vars"], last["mu"], last["sigma"], last["covarmat"], means=mean)
+    a.close()
+    root = str(tmp_path / "m_restore_")
+    rl, rm = tb.outputs.read_restore(root), tb.outputs.read_restore_means(root)
+    assert rl["iteration"] == 7 and rm["iteration"] == 7
+    for k in ("vars", "mu", "sigma", "covarmat"):
+        assert np.array_equal(rl[k], last[k]) and np.array_equal(rm[k], mean[k]), k
+
+
+REF = "/root/reference"
+REFBIN = os.path.join(ROOT, "oracle", "_ref", "cpptamcmc")
+LOCAL_ID = "TF_3443483_local-v3"
+
+
+@pytest.mark.skipif(not (os.path.isdir(os.path.join(REF, "Config")) and os.path.exists(REFBIN)), reason="reference tree / oracle/_ref/cpptamcmc absent")
+def test_reference_program_restores_from_our_mean_blocks(tb, tmp_path):
+    """a restore triplet written by this repo, read by the UNMODIFIED reference program with
+    do_restore_proposal_mean = 1 -- its Acquire phase prints the sigma / mu it starts from (MALA::restore_proposal,
+    MALA.cpp:206-244): they are the *_mean blocks we wrote, not the last values."""
+    import shutil, subprocess
+    from test_frontend_cpu import _ref_tree
+    wd, out = _ref_tree(tmp_path, os.path.join(REF, "test", "inputs"), [LOCAL_ID], "io_local", nsamples="40     ,  30  , 40")
+    pcfg = os.path.join(wd, "Config", "default", "config_default.cfg")
+    s = open(pcfg).read()
+    assert "do_restore_proposal_mean=0;" in s
+    open(pcfg, "w").write(s.replace("do_restore_proposal_mean=0;", "do_restore_proposal_mean=1;"))
+    ppre = os.path.join(wd, "Config", "config_presets.cfg")
+    s = open(ppre).read()
+    import re
+    s = re.sub(r"start_index_processing\s*=\s*\d+;", "start_index_processing=2;", s)
+    s = re.sub(r"last_index_processing\s*=\s*\d+;", "last_index_processing=2;", s)
+    open(ppre, "w").write(s)
+    fe = tb.frontend.FrontEnd(wd)
+    run = fe.setup(0, 0, 2)                                        # star 0, slice 0, Acquire: restores variables and proposal from the Learning files
+    prob, cfg = fe.problem()
+    fe.close()
+    assert run["do_restore_proposal"] and run["do_restore_proposal_mean"]
+    Cn, Nv = cfg.Nchains, prob.index_to_relax.size
+    g = np.random.default_rng(3)
+    x0 = prob.params[prob.index_to_relax]
+    last = dict(vars=np.tile(x0, (Cn, 1)), mu=np.tile(x0, (Cn, 1)) * (1 + 1e-3 * g.standard_normal((Cn, Nv))), sigma=0.5 + g.random(Cn))
+    B = 1e-2 * g.standard_normal((Cn, Nv, Nv)); last["covarmat"] = B @ np.swapaxes(B, 1, 2) + 1e-4 * np.eye(Nv)
+    mean = dict(vars=last["vars"], mu=last["mu"] * 1.01, sigma=last["sigma"] + 3.0, covarmat=2.0 * last["covarmat"])
+    o = tb.outputs.Outputs(prob, cfg.Tcoefs, str(tmp_path / "w"), root="w", Nsamples=40)
+    o.write_restore_arrays(40, last["vars"], last["mu"], last["sigma"], last["covarmat"], means=mean)
+    o.close()
+    os.makedirs(run["restore_dir"], exist_ok=True)
+    for k in (1, 2, 3):
+        shutil.copy(str(tmp_path / "w" / ("w_restore_%d.dat" % k)), run["restore_dir"] + run["restore_file_in"] + "%d.dat" % k)
+    r = subprocess.run([REFBIN, "execute", "1", "1", "1", "1", "2"], cwd=wd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-800:]
+    assert "Use the averaged values over Nbuffer" in r.stdout
+    sig = [float(ln.split("=")[1]) for ln in r.stdout.splitlines() if ln.startswith("scaling factor sigma[")]
+    assert len(sig) >= Cn and np.allclose(sig[:Cn], mean["sigma"], rtol=2e-5), (sig[:Cn], mean["sigma"])
+    mus = [np.array([float(v) for v in ln.split("=")[1].split()]) for ln in r.stdout.splitlines() if ln.startswith("Initial Vectors mu[")]
+    assert len(mus) >= Cn and all(np.allclose(mus[c], mean["mu"][c], rtol=2e-5, atol=1e-12) for c in range(Cn))
+
+
 def test_header_declares_every_outputs_symbol(tb):
     import re
     decl = set(re.findall(r"\b(tg_\w+)\s*\(", open(os.path.join(ROOT, "include", "tamcmc_outputs.h")).read()))

@@ -45,6 +45,7 @@ static void run_phase(tg_frontend *fe, int star, int slice, int phase, unsigned 
     fe_check(tg_fe_problem(fe, &prob));
     fe_check(tg_fe_run_info(fe, &run));
     prob.seed = seed; prob.device = device;
+    prob.flags |= TG_F_RESTORE_MEANS;      // the restore files carry the averages over each buffer (Outputs::update_buffer_restore, outputs.cpp:1758-1818)
     printf(" - Model: %s   likelihood: %s   priors: %s\n", run.model_fct_name, run.likelihood_fct_name, run.prior_fct_name);
     printf(" - Ndata=%ld  Nparams=%d  Nvars=%d  Nchains=%d  Nsamples=%ld  c0=%g  dN_mixing=%ld\n", prob.Nx, prob.Np, run.Nvars, prob.Nchains, run.Nsamples, prob.c0, prob.dN_mixing);
 
@@ -59,9 +60,13 @@ static void run_phase(tg_frontend *fe, int star, int slice, int phase, unsigned 
         std::vector<double> v((size_t)C * Nv), mu((size_t)C * Nv), sg((size_t)C), cov((size_t)C * Nv * Nv);
         out_check(tg_restore_read(root.c_str(), run.do_restore_last_index, &rc_, &rv, &it, v.data(), mu.data(), sg.data(), cov.data()));
         const bool rp = run.do_restore_proposal != 0;
+        if (rp && run.do_restore_proposal_mean) {                      // MALA::restore_proposal, MALA.cpp:206-232: the averaged proposal law instead of the last one
+            std::vector<double> vm((size_t)C * Nv);
+            out_check(tg_restore_read_means(root.c_str(), run.do_restore_last_index, &rc_, &rv, &it, vm.data(), mu.data(), sg.data(), cov.data()));
+        }
         model.set_state(run.do_restore_variables ? v.data() : nullptr, rp ? mu.data() : nullptr, rp ? sg.data() : nullptr, rp ? cov.data() : nullptr);
         if (run.do_restore_last_index) i0 = it;
-        printf(" - Restored %s%s from %s*.dat (iteration %ld)\n", run.do_restore_variables ? "variables " : "", rp ? "proposal " : "", root.c_str(), it);
+        printf(" - Restored %s%s%s from %s*.dat (iteration %ld)\n", run.do_restore_variables ? "variables " : "", rp ? "proposal " : "", (rp && run.do_restore_proposal_mean) ? "(averaged over the last buffer) " : "", root.c_str(), it);
     }
     {   // the consistency print of the Model_def constructor (model_def.cpp:139-150)
         std::vector<double> l((size_t)C), p((size_t)C), q((size_t)C);
@@ -90,6 +95,8 @@ static void run_phase(tg_frontend *fe, int star, int slice, int phase, unsigned 
     const long Nbuffer = run.Nbuffer > 0 ? run.Nbuffer : run.Nsamples;
     std::vector<double> all_logL;                                      // tempered logL of every sample, for the evidence
     std::vector<double> v((size_t)C * Nv), mu((size_t)C * Nv), sg((size_t)C), cov((size_t)C * Nv * Nv), rate((size_t)C), Lb((size_t)C);
+    std::vector<double> vm((size_t)C * Nv), mum((size_t)C * Nv), sgm((size_t)C), covm((size_t)C * Nv * Nv);
+    model.get_state_means(nullptr, nullptr, nullptr, nullptr, true);          // the averages start with this phase
     long done = i0, ncopy = 0;
     const clock_t t0 = clock(); time_t w0 = time(nullptr);
     while (done < run.Nsamples) {
@@ -98,7 +105,8 @@ static void run_phase(tg_frontend *fe, int star, int slice, int phase, unsigned 
         mala.execute(done, n, &rec);
         out_check(tg_out_append(out, &rec.view, n, E));
         model.get_state(v.data(), mu.data(), sg.data(), cov.data());
-        out_check(tg_out_write_restore(out, done + n, v.data(), mu.data(), sg.data(), cov.data()));
+        model.get_state_means(vm.data(), mum.data(), sgm.data(), covm.data(), true);
+        out_check(tg_out_write_restore_means(out, done + n, v.data(), mu.data(), sg.data(), cov.data(), vm.data(), mum.data(), sgm.data(), covm.data()));
         // acceptance rates of the block (Outputs::reject_rate + write_txt_acceptance, outputs.cpp:747-789, :1824-1843)
         double xaxis = 0;
         fe_check(tg_acceptance(rec.moved.data(), n, C, Nbuffer, ncopy, i0, rate.data(), &xaxis));
