@@ -220,6 +220,43 @@ def test_background_moments_equal_the_bin_by_bin_path(tb, W, oracle, case, monke
     assert relerr(res["1"]["logL"], ref["logL"]) < TOL and relerr(res["0"]["logL"], ref["logL"]) < TOL
 
 
+def test_background_moments_over_the_prior_ranges(tb, W, oracle, monkeypatch):
+    """the acceptance of a moment tile rests on an a-posteriori check at five points, so the path is compared with
+    the bin-by-bin one for backgrounds drawn over (and beyond) the prior ranges of the Harvey parameters -- heights over five
+    decades, time scales from far below to far above the spectrum's range (knees inside, left and right of it), exponents
+    1 ... 4.5 (integer and not), white noise from negligible to dominant -- and with the oracle."""
+    prob = W.s_global(Nx=400000, step=0.02)
+    prob = _with_y(prob, oracle, W, seed=17)
+    iH = [i for i, n in enumerate(prob.names) if n == "Harvey-Noise_H"]
+    itc = [i for i, n in enumerate(prob.names) if n == "Harvey-Noise_tc"]
+    ip = [i for i, n in enumerate(prob.names) if n == "Harvey-Noise_p"]
+    iN = [i for i, n in enumerate(prob.names) if n == "White_Noise_N0"]
+    Cn = 24
+    g = np.random.Generator(np.random.Philox(key=2025))
+    P = np.tile(prob.params, (Cn, 1))
+    for c in range(1, Cn):
+        for k in range(len(iH)):
+            if prob.params[itc[k]] == 0.0 and g.random() < 0.5:
+                continue                                   # an inactive term stays inactive in half of the draws
+            P[c, iH[k]] = 10.0 ** g.uniform(-2, 3)
+            P[c, itc[k]] = 10.0 ** g.uniform(-2.5, 2.5)     # knee at 1e3 / tc microHz: from 3e5 (far right) down to 3 (far left)
+            P[c, ip[k]] = [1.0, 2.0, 3.0, 4.0, g.uniform(1.0, 4.5), g.uniform(1.0, 4.5)][int(g.integers(0, 6))]
+        P[c, iN[0]] = 10.0 ** g.uniform(-3, 1)
+    T = np.ones(Cn)
+    res = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("TG_MOMENTS", mode)
+        md = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=Cn))
+        res[mode] = md.evaluate(P, T)
+        md.close()
+    ref = oracle.generate_models(prob, P, T)
+    assert np.array_equal(res["0"]["status"], res["1"]["status"]) and np.array_equal(res["1"]["status"], ref["status"])
+    ok = ref["status"] == 0
+    assert ok.sum() >= Cn - 2
+    assert relerr(res["1"]["logL"][ok], res["0"]["logL"][ok]) < 2e-14
+    assert relerr(res["1"]["logL"][ok], ref["logL"][ok]) < TOL
+
+
 @pytest.mark.parametrize("case", ["cfg3", "hot_chains", "narrow_modes", "general_p"])
 def test_far_field_path_equals_the_exact_path(tb, W, oracle, case, monkeypatch):
     """Under the truncation windows (build_lorentzian.cpp:365-460) the fused kernel takes, per 256-bin micro-tile, a polynomial
