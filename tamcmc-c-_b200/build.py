@@ -6,7 +6,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libtamcmc_gpu.so")
 SOURCES = ["tamcmc_gpu.cu", "tg_outputs.cpp", "tg_frontend.cpp"]
-HEADERS = ["tg_internal.cuh", "tg_prologue.cuh", "tg_eval.cuh", "tg_adapt.cuh", "tg_sampler.cuh",
+HEADERS = ["tg_internal.cuh", "tg_prologue.cuh", "tg_eval.cuh", "tg_farfield.cuh", "tg_adapt.cuh", "tg_sampler.cuh",
            os.path.join("..", "..", "include", "tamcmc_gpu.h"), os.path.join("..", "..", "include", "tamcmc_outputs.h"),
            os.path.join("..", "..", "include", "tamcmc_frontend.h")]
 
@@ -36,7 +36,8 @@ def build_library(force=False, verbose=False):
     """Compile csrc/*.cu -> csrc/libtamcmc_gpu.so.  Returns the library path."""
     if not force and not needs_build():
         return LIB_PATH
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
+    extra = os.environ.get("TG_NVCC_EXTRA", "").split()            # developer builds (e.g. -DTG_EVAL_MINBLOCKS=3)
+    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + \
           ["-o", LIB_PATH] + [os.path.join(CSRC, s) for s in SOURCES]
     env = dict(os.environ)
     # the image exports CC/CXX wrappers; nvcc should use the system host compiler

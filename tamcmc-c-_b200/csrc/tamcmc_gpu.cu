@@ -662,6 +662,10 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     {   // moments of the data for the background-only stretches (chi22p likelihood only; TG_MOMENTS=0 turns the path off)
         const char *e = getenv("TG_MOMENTS"), *e2 = getenv("TG_MOM_SUB");
         if (e2) h->mom_sub = std::max(1, std::min(8, atoi(e2)));
+        // moment tiles per work item: a run of 16 tiles x 5 chains is the longest unit of a launch (23 us: ten rounds of one
+        // (tile, chain) per warp) -- with few chains, where the launch is one wave and a bit, shorter runs end it earlier
+        // (live step at 10 chains 64.4 -> 62.7 us); with many chains the longer runs amortise their set-up (measured at 80 chains)
+        h->mom_run = (p->Nchains < 32) ? 4 : 16;
         if (const char *e3 = getenv("TG_MOM_RUN")) h->mom_run = std::max(1, atoi(e3));
         if (!(e && atoi(e) == 0) && p->likelihood_case == 0 && (long)Nx >= (long)h->mom_sub * TG_THREADS * 4) {
             std::vector<double> mom;
@@ -721,7 +725,8 @@ static int create_impl(const tg_problem *p, tg_handle *h)
     {
         h->list_cap = std::max(4, (d.ncomp_max + 3) & ~3);
         int maxdyn = 0; CK(cudaDeviceGetAttribute(&maxdyn, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
-        const size_t budget = std::min<size_t>((size_t)maxdyn - 2048, 96 * 1024);        // <= 96 KB (+ 14 KB static): two CTAs per SM stay resident
+        size_t budget = std::min<size_t>((size_t)maxdyn - 2048, 96 * 1024);              // <= 96 KB (+ 14 KB static): two CTAs per SM stay resident
+        if (const char *e = getenv("TG_SMEM_BUDGET_KB")) budget = std::min<size_t>(budget, (size_t)std::max(16, atoi(e)) * 1024);   // developer knob (occupancy experiments)
         int m = TG_MAXG;
         while (m > 1 && TG_EVAL_SMEM(m, h->list_cap) > budget) m--;
         if (TG_EVAL_SMEM(m, h->list_cap) > (size_t)maxdyn - 2048) return fail(TG_E_BADARG, "too many Lorentzian components for the shared-memory list of the fused kernel");

@@ -93,7 +93,8 @@ static void run_phase(tg_frontend *fe, int star, int slice, int phase, unsigned 
 
     tamcmc_gpu::MALA mala(model);
     const long Nbuffer = run.Nbuffer > 0 ? run.Nbuffer : run.Nsamples;
-    std::vector<double> all_logL;                                      // tempered logL of every sample, for the evidence
+    std::vector<long double> sumL((size_t)C, 0.0L);                    // running sums of the tempered logL of every chain, for the evidence
+    long nL = 0;                                                       // samples in them (those of this process: a resumed run averages what it computed)
     std::vector<double> v((size_t)C * Nv), mu((size_t)C * Nv), sg((size_t)C), cov((size_t)C * Nv * Nv), rate((size_t)C), Lb((size_t)C);
     std::vector<double> vm((size_t)C * Nv), mum((size_t)C * Nv), sgm((size_t)C), covm((size_t)C * Nv * Nv);
     model.get_state_means(nullptr, nullptr, nullptr, nullptr, true);          // the averages start with this phase
@@ -119,10 +120,13 @@ static void run_phase(tg_frontend *fe, int star, int slice, int phase, unsigned 
             fclose(f);
         }
         // evidence from every sample so far (Diagnostics::evidence_calc + write_evidence, diagnostics.cpp:218-224, :924-1001)
-        all_logL.insert(all_logL.end(), rec.logL.begin(), rec.logL.end());
+        for (long k = 0; k < n; k++) for (int m = 0; m < C; m++) sumL[(size_t)m] += (long double)rec.logL[(size_t)k * C + m];
+        nL += n;
         if (run.evidence_diags) {
             double ev = 0;
-            fe_check(tg_evidence(prob.Tcoefs, C, all_logL.data(), (long)(all_logL.size() / (size_t)C), run.evidence_interpolation_factor, Lb.data(), &ev));
+            std::vector<double> meanL((size_t)C);
+            for (int m = 0; m < C; m++) meanL[(size_t)m] = (double)(sumL[(size_t)m] / (long double)nL);
+            fe_check(tg_evidence(prob.Tcoefs, C, meanL.data(), 1, run.evidence_interpolation_factor, Lb.data(), &ev));   // L_beta = the means; O(C) per buffer
             const bool fresh = (ncopy == 0);
             FILE *f = fopen(f_evid.c_str(), fresh ? "w" : "a");
             if (!f) throw tamcmc_gpu::Error(TG_E_BADARG, "cannot open " + f_evid);
@@ -132,7 +136,7 @@ static void run_phase(tg_frontend *fe, int star, int slice, int phase, unsigned 
                 for (int m = 0; m < C; m++) fprintf(f, "%g ", 1. / prob.Tcoefs[m]);
                 fprintf(f, "\n! interpolation_factor=%d\n", run.evidence_interpolation_factor);
             }
-            fprintf(f, "%ld ", done + n - 1); for (int m = 0; m < C; m++) fprintf(f, "%20.10g ", Lb[(size_t)m]); fprintf(f, " %20.10g\n", ev);
+            fprintf(f, "%ld ", nL - 1); for (int m = 0; m < C; m++) fprintf(f, "%20.10g ", Lb[(size_t)m]); fprintf(f, " %20.10g\n", ev);
             fclose(f);
         }
         done += n; ncopy++;
