@@ -114,12 +114,13 @@ int tg_destroy(tg_handle *h);
 int tg_eval(tg_handle *h, const double *params, int B, const double *T,
             double *logL, double *logPrior, double *logPost, int *status, double *model);
 
-/* The same call in two halves, through one of two staging slots (0, 1), so that a host-side sampler (the loop of MALA.cpp:632-655
+/* The same call in two halves, through one of two slots (0, 1), so that a host-side sampler (the loop of MALA.cpp:632-655
  * with its proposal on the host) prepares the parameter vectors of step k+1 while the GPU evaluates step k: tg_eval_async copies
  * the inputs into the slot's pinned buffer, enqueues the whole call (one graph launch: copy in, kernels, copy out) and returns;
- * tg_eval_wait blocks until that slot's results have arrived and copies them out.  Calls of a handle are still issued from one
- * host thread and run on the device in submission order; at most one submission per slot may be outstanding, and two outstanding
- * submissions must have the same B. */
+ * tg_eval_wait blocks until that slot's results have arrived and copies them out.  Each slot has its own device tables, staging
+ * buffers and stream (slot 1's are made at its first use), so the copy-in, prologue and far-field pre-pass of one submission run
+ * beside the fused kernel of the other; results are the bits of tg_eval.  Calls of a handle are still issued from one host thread;
+ * at most one submission per slot may be outstanding, and two outstanding submissions must have the same B. */
 int tg_eval_async(tg_handle *h, const double *params, int B, const double *T, int slot);
 int tg_eval_wait(tg_handle *h, int slot, double *logL, double *logPrior, double *logPost, int *status);
 

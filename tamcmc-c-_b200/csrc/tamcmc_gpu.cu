@@ -65,6 +65,8 @@ struct tg_handle {
     double    *pri = nullptr; int *sw = nullptr;
     int       *index_to_relax = nullptr; double *Tcoefs = nullptr;
     EvalBuf    ev;               // tg_eval batches
+    EvalBuf    ev2;              // tg_eval_async, slot 1: its own tables and results on its own stream, so that the copy-in, prologue and pre-pass of one
+    cudaStream_t stream2 = nullptr;   // submission run beside the fused kernel of the other
     EvalBuf    sp;               // sampler's proposed points (cap == C)
     int        nitems = 0, max_items = 0, light_sub = 8, heavy_sub = 2, chains_per_block = 0, heavy_group = 2, use_graph = 1, steps_per_graph = 16;
     int        smem_matrix = 0, tri_smem = 0; size_t propose_smem = 0, spec_smem = 0; int fused_spec = 0;
@@ -337,11 +339,12 @@ static int sync_eval_args(tg_handle *h, EvalBuf &b, double *model, int B)
 }
 
 // prologue (optional) + fused kernel + per-chain reduction for B points of ONE handle (tg_eval, create / restore)
-static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_dev, int B, double *model, bool do_prologue, bool do_reduce, bool pdl = false)
+static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_dev, int B, double *model, bool do_prologue, bool do_reduce, bool pdl = false, cudaStream_t st = nullptr)
 {
+    if (!st) st = h->stream;
     if (do_prologue) {
         TgProArgs pa{h->d, b.t, params_dev, h->pri, h->sw};
-        tg_k_prologue<<<B, TG_PRO_THREADS, TG_PRO_SMEM(h->d.Np), h->stream>>>(pa);
+        tg_k_prologue<<<B, TG_PRO_THREADS, TG_PRO_SMEM(h->d.Np), st>>>(pa);
         h->n_launch_total++;
     }
     tg_handle::UnitTable &u = (&b == &h->sp) ? h->u_sp : h->u_ev;
@@ -351,17 +354,17 @@ static int launch_eval_kernels(tg_handle *h, EvalBuf &b, const double *params_de
     dim3 grid(u.n);
     if (h->ffw && !model && h->ff_nmt > 0 && b.ffc) {   // far-field pre-pass of the B points (tg_farfield.cuh)
         const int ppc = ff_pairs_per_cta(h->ff_nmt, B, h->n_sm), cpc = ff_ctas_per_chain(h->ff_nmt, ppc);
-        CK(launch_k(tg_k_ff, dim3(cpc, B), dim3(256), ff_smem(h), h->stream, pdl && !h->timing, (const TgFFArgs *)b.d_ffargs, (const int2 *)nullptr, ppc));
+        CK(launch_k(tg_k_ff, dim3(cpc, B), dim3(256), ff_smem(h), st, pdl && !h->timing, (const TgFFArgs *)b.d_ffargs, (const int2 *)nullptr, ppc));
         h->n_launch_total++;
     }
     if (h->timing) {
         if (h->ev_used >= 8192) { int r = harvest_events(h); if (r) return r; }
-        cudaEventRecord(next_event(h), h->stream);
+        cudaEventRecord(next_event(h), st);
     }
-    CK(launch_k(tg_k_eval, grid, dim3(TG_THREADS), esm, h->stream, pdl && !h->timing, (const TgEvalArgs *)b.d_args, (const int4 *)u.dev));
-    if (h->timing) cudaEventRecord(next_event(h), h->stream);
+    CK(launch_k(tg_k_eval, grid, dim3(TG_THREADS), esm, st, pdl && !h->timing, (const TgEvalArgs *)b.d_args, (const int4 *)u.dev));
+    if (h->timing) cudaEventRecord(next_event(h), st);
     h->n_eval_launch++; h->n_launch_total++;
-    if (do_reduce) { tg_k_reduce<<<B, 256, 0, h->stream>>>(b.partials, h->nitems, b.sums); h->n_launch_total++; }
+    if (do_reduce) { tg_k_reduce<<<B, 256, 0, st>>>(b.partials, h->nitems, b.sums); h->n_launch_total++; }
     CK(cudaGetLastError());
     return TG_OK;
 }
@@ -865,6 +868,7 @@ extern "C" int tg_destroy(tg_handle *h)
     if (!h) return TG_OK;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->stream2) cudaStreamSynchronize(h->stream2);
     if (h->self) { batch_destroy(h->self); h->self = nullptr; }
     if (h->nccl_comm && g_nccl_destroy) { g_nccl_destroy(h->nccl_comm); h->nccl_comm = nullptr; }
     for (int r = 0; r < TG_XCHG_MAXR; r++) if (h->xpeer[r]) cudaIpcCloseMemHandle(h->xpeer[r]);
@@ -874,9 +878,10 @@ extern "C" int tg_destroy(tg_handle *h)
     for (auto e : h->ev_pool) cudaEventDestroy(e);
     for (int k = 0; k < 2; k++) if (h->watch[k]) cudaEventDestroy(h->watch[k]);
     for (void *q : h->allocs) cudaFree(q);
-    for (EvalBuf *b : {&h->sp, &h->ev}) { if (b->pin_in) cudaFreeHost(b->pin_in); if (b->pin_out) cudaFreeHost(b->pin_out); if (b->pin_in2) cudaFreeHost(b->pin_in2); if (b->pin_out2) cudaFreeHost(b->pin_out2); }
+    for (EvalBuf *b : {&h->sp, &h->ev, &h->ev2}) { if (b->pin_in) cudaFreeHost(b->pin_in); if (b->pin_out) cudaFreeHost(b->pin_out); if (b->pin_in2) cudaFreeHost(b->pin_in2); if (b->pin_out2) cudaFreeHost(b->pin_out2); }
     for (int k = 0; k < 2; k++) if (h->ev_done[k]) cudaEventDestroy(h->ev_done[k]);
     if (h->mom_note) cudaFreeHost(h->mom_note);
+    if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return TG_OK;
@@ -906,12 +911,14 @@ extern "C" int tg_eval_upload(tg_handle *h, const double *params, int B, const d
     return TG_OK;
 }
 
-static int eval_resident(tg_handle *h, int B, double *model_dev, bool pdl = false)
+static int eval_resident(tg_handle *h, int B, double *model_dev, bool pdl = false, EvalBuf *buf = nullptr, cudaStream_t st = nullptr)
 {
-    if (B < 1 || B != h->ev.B) return fail(TG_E_BADARG, "tg_eval_resident: B differs from the uploaded batch");
-    int r = launch_eval_kernels(h, h->ev, h->ev.params, B, model_dev, true, false, pdl); if (r) return r;
-    CK(launch_k(tg_k_reduce_finalize, dim3(B), dim3(256), 0, h->stream, pdl && !h->timing, h->d, (const double2 *)h->ev.partials, h->nitems, h->ev.sums, (const double *)h->ev.T, h->ev.t,
-                h->ev.logL, h->ev.logPrior, h->ev.logPost, h->ev.status));
+    EvalBuf &e = buf ? *buf : h->ev;
+    if (!st) st = h->stream;
+    if (B < 1 || B != e.B) return fail(TG_E_BADARG, "tg_eval_resident: B differs from the uploaded batch");
+    int r = launch_eval_kernels(h, e, e.params, B, model_dev, true, false, pdl, st); if (r) return r;
+    CK(launch_k(tg_k_reduce_finalize, dim3(B), dim3(256), 0, st, pdl && !h->timing, h->d, (const double2 *)e.partials, h->nitems, e.sums, (const double *)e.T, e.t,
+                e.logL, e.logPrior, e.logPost, e.status));
     h->n_launch_total++;
     CK(cudaGetLastError());
     return TG_OK;
@@ -945,25 +952,32 @@ extern "C" int tg_eval_fetch(tg_handle *h, int B, double *logL, double *logPrior
 static int eval_submit(tg_handle *h, const double *params, int B, const double *T, int slot)
 {
     CK(cudaSetDevice(h->device));
-    { int r = alloc_evalbuf(h, h->ev, B); if (r) return r; }
-    EvalBuf &b = h->ev;
-    if (b.B != B) { CK(cudaStreamSynchronize(h->stream)); b.layout(B, h->d.Np); }
+    if (slot && !h->stream2) CK(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking));
+    EvalBuf &b = slot ? h->ev2 : h->ev;
+    cudaStream_t st = slot ? h->stream2 : h->stream;
+    if (B > b.cap) { CK(cudaStreamSynchronize(h->stream)); if (h->stream2) CK(cudaStreamSynchronize(h->stream2)); }
+    { int r = alloc_evalbuf(h, b, B); if (r) return r; }
+    if (b.B != B) { CK(cudaStreamSynchronize(st)); b.layout(B, h->d.Np); }
     if (h->ev_graph_B != B) {
         if (h->ev_graph) { cudaGraphExecDestroy(h->ev_graph); h->ev_graph = nullptr; }
         if (h->ev_graph2) { cudaGraphExecDestroy(h->ev_graph2); h->ev_graph2 = nullptr; }
     }
     cudaGraphExec_t &ge = slot ? h->ev_graph2 : h->ev_graph;
-    double *pin = slot ? b.pin_in2 : b.pin_in, *pout = slot ? b.pin_out2 : b.pin_out;
+    double *pin = b.pin_in, *pout = b.pin_out;
     if (!ge) {
-        if (h->u_ev.B != B) { int r = build_units(h, h->u_ev, B); if (r) return r; }
-        { int r = sync_eval_args(h, b, nullptr, B); if (r) return r; }        // not inside the capture
+        if (h->u_ev.B != B) {                                                  // the unit table is shared by the two slots: nothing of the other may be in flight
+            CK(cudaStreamSynchronize(h->stream)); if (h->stream2) CK(cudaStreamSynchronize(h->stream2));
+            int r = build_units(h, h->u_ev, B); if (r) return r;
+        }
+        { int r = sync_eval_args(h, b, nullptr, B); if (r) return r; }        // not inside the capture (uploads on the handle's first stream)
+        CK(cudaStreamSynchronize(h->stream));
         cudaGraph_t g;
         const long lt = h->n_launch_total, le = h->n_eval_launch;
-        CK(cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-        cudaMemcpyAsync(b.in, pin, (size_t)B * (h->d.Np + 1) * 8, cudaMemcpyHostToDevice, h->stream);
-        int r = eval_resident(h, B, nullptr, getenv("TG_PDL") ? atoi(getenv("TG_PDL")) != 0 : true);
-        cudaMemcpyAsync(pout, b.out, (size_t)B * 28, cudaMemcpyDeviceToHost, h->stream);
-        cudaError_t ce = cudaStreamEndCapture(h->stream, &g);
+        CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        cudaMemcpyAsync(b.in, pin, (size_t)B * (h->d.Np + 1) * 8, cudaMemcpyHostToDevice, st);
+        int r = eval_resident(h, B, nullptr, getenv("TG_PDL") ? atoi(getenv("TG_PDL")) != 0 : true, &b, st);
+        cudaMemcpyAsync(pout, b.out, (size_t)B * 28, cudaMemcpyDeviceToHost, st);
+        cudaError_t ce = cudaStreamEndCapture(st, &g);
         h->n_launch_total = lt; h->n_eval_launch = le;
         if (r) return r;
         CK(ce);
@@ -973,10 +987,10 @@ static int eval_submit(tg_handle *h, const double *params, int B, const double *
     }
     memcpy(pin, params, (size_t)B * h->d.Np * 8);
     memcpy(pin + (size_t)B * h->d.Np, T, (size_t)B * 8);
-    CK(cudaGraphLaunch(ge, h->stream));
+    CK(cudaGraphLaunch(ge, st));
     h->n_launch_total += 3 + ((h->ffw && h->ff_nmt > 0) ? 1 : 0); h->n_eval_launch += 1;
     if (!h->ev_done[slot]) CK(cudaEventCreateWithFlags(&h->ev_done[slot], cudaEventDisableTiming));
-    CK(cudaEventRecord(h->ev_done[slot], h->stream));
+    CK(cudaEventRecord(h->ev_done[slot], st));
     h->slot_B[slot] = B;
     return TG_OK;
 }
@@ -986,7 +1000,7 @@ static int eval_collect(tg_handle *h, int slot, double *logL, double *logPrior, 
     if (B < 1 || !h->ev_done[slot]) return fail(TG_E_BADARG, "tg_eval_wait: nothing was submitted through this slot");
     CK(cudaSetDevice(h->device));
     CK(cudaEventSynchronize(h->ev_done[slot]));
-    const double *pout = slot ? h->ev.pin_out2 : h->ev.pin_out;
+    const double *pout = slot ? h->ev2.pin_out : h->ev.pin_out;
     if (logL) memcpy(logL, pout, (size_t)B * 8);
     if (logPrior) memcpy(logPrior, pout + B, (size_t)B * 8);
     if (logPost) memcpy(logPost, pout + 2 * (size_t)B, (size_t)B * 8);
@@ -1686,6 +1700,7 @@ extern "C" int tg_sync(tg_handle *h)
     if (!h) return fail(TG_E_BADARG, "null handle");
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));
+    if (h->stream2) CK(cudaStreamSynchronize(h->stream2));
     return TG_OK;
 }
 
