@@ -13,5 +13,5 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 
 # one step of cfg3 without graphs: every kernel of the step under --set full
 timeout 900 ncu --set full --clock-control none --import-source on -k "regex:tg_k_(ff|eval|finish|propose)" -s 100 -c 5 -o gpurun_out/${TAG}_step_full -f python scripts/dev/steps_for_ncu.py 10 1 > gpurun_out/${TAG}_ncu_step.log 2>&1
 # the fused kernel and the pre-pass at 8 stars x 10 chains (cfg5)
-timeout 900 ncu --set full --clock-control none --import-source on -k "regex:tg_k_(ff|eval)" -s 40 -c 2 -o gpurun_out/${TAG}_cfg5_full -f python scripts/dev/steps_for_ncu.py 10 8 > gpurun_out/${TAG}_ncu_cfg5.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k "regex:^tg_k_(ff|eval)$" -s 90 -c 2 -o gpurun_out/${TAG}_cfg5_full -f python scripts/dev/steps_for_ncu.py 10 8 > gpurun_out/${TAG}_ncu_cfg5.log 2>&1
 ls -la gpurun_out | tail -14

@@ -607,6 +607,43 @@ extern "C" int tg_create(const tg_problem *p, tg_handle **out)
     return TG_OK;
 }
 
+// Shape of the work units by the number of chains a LAUNCH carries (the chains of a handle; of every star of a launch group):
+// scheduling only, results never depend on it.  Developer knobs override.
+static void schedule_defaults(tg_handle *h, int C)
+{
+    const TgDesc &d = h->d;
+    // where truncation windows lie: items of two sub-tiles (taken 8 bins per thread); one chain per unit for a single
+    // ensemble (more, smaller units: better tail of the grid), three when many chains fill the GPU anyway (measured with the
+    // background-only tiles on the moment path: one chain per unit is best up to ~100 chains, 3.9 vs 4.0 us per chain at 80)
+    h->heavy_sub = 2;
+    h->heavy_group = (C >= 128) ? 3 : 1;
+    // a spectrum so short that pairs of sub-tiles would not even fill the GPU once (S-local: 10k bins, 10 chains): single
+    // sub-tiles, twice the units (25.7 vs 29.9 us per step there)
+    const bool short_spectrum = (long)((d.Nx + TG_THREADS * 4 - 1) / (TG_THREADS * 4)) * C < 4L * 296;
+    if (short_spectrum) h->heavy_sub = 1;
+    // the costliest window-region items take three chains per unit (set-up and list building shared), the rest one chain
+    // (small units for the tail): 70 % of them at 10 chains (49.0 -> 48.1 us), all of them from 32 chains on (-7 %)
+    h->hybrid_group = (C < 64) ? 3 : ((C < 128) ? 4 : 5);
+    h->hybrid_pct = short_spectrum ? 0 : ((C < 16) ? 70 : ((C < 32) ? 80 : 100));      // short spectra: as many units as possible
+    if (h->ffw && !short_spectrum) {
+        // far-field path: a window-region unit is a run of pairs of sub-tiles x a few chains (per pair and chain one staged
+        // interpolant + the exact records; no lists); measured on cfg3: 4 sub-tiles x 2 chains at 10 chains (28.8 us against
+        // 30-36 for the neighbours), 8 sub-tiles x 3 chains at 80 chains (1.45 us per chain)
+        h->heavy_sub = (C < 32) ? 4 : 8;
+        h->hybrid_pct = 100;
+        h->hybrid_group = (C < 32) ? 2 : 3;
+    }
+    // moment tiles per work item: a run of 16 tiles x 5 chains is the longest unit of a launch (23 us: ten rounds of one
+    // (tile, chain) per warp) -- with few chains, where the launch is one wave and a bit, shorter runs end it earlier
+    // (live step at 10 chains 64.4 -> 62.7 us); with many chains the longer runs amortise their set-up (measured at 80 chains)
+    h->mom_run = (C < 32) ? 4 : 16;
+    if (const char *e = getenv("TG_MOM_RUN")) h->mom_run = std::max(1, atoi(e));
+    if (const char *e = getenv("TG_HYBRID_PCT")) h->hybrid_pct = atoi(e);
+    if (const char *e = getenv("TG_HYBRID_GROUP")) h->hybrid_group = std::max(1, atoi(e));
+    if (const char *e = getenv("TG_HEAVY_SUB")) h->heavy_sub = std::max(1, atoi(e));
+    if (const char *e = getenv("TG_HEAVY_GROUP")) h->heavy_group = std::max(1, atoi(e));
+}
+
 static int create_impl(const tg_problem *p, tg_handle *h)
 {
     int ndev = 0;
@@ -668,8 +705,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         // moment tiles per work item: a run of 16 tiles x 5 chains is the longest unit of a launch (23 us: ten rounds of one
         // (tile, chain) per warp) -- with few chains, where the launch is one wave and a bit, shorter runs end it earlier
         // (live step at 10 chains 64.4 -> 62.7 us); with many chains the longer runs amortise their set-up (measured at 80 chains)
-        h->mom_run = (p->Nchains < 32) ? 4 : 16;
-        if (const char *e3 = getenv("TG_MOM_RUN")) h->mom_run = std::max(1, atoi(e3));
+        // (the run length itself: schedule_defaults)
         if (!(e && atoi(e) == 0) && p->likelihood_case == 0 && (long)Nx >= (long)h->mom_sub * TG_THREADS * 4) {
             std::vector<double> mom;
             build_moments(p->x, p->y, (long)Nx, h->mom_sub * TG_THREADS * 4, mom);
@@ -739,33 +775,8 @@ static int create_impl(const tg_problem *p, tg_handle *h)
         if (h->ffw && ff_smem(h) > 40 * 1024) { int r = raise_dyn_smem((const void *)tg_k_ff, ff_smem(h)); if (r) return r; }
         const int groups = (C + m - 1) / m;                                               // balanced chain groups of <= max_cpb
         h->chains_per_block = (C + groups - 1) / groups;
-        // where truncation windows lie: items of two sub-tiles (taken 8 bins per thread); one chain per unit for a single
-        // ensemble (more, smaller units: better tail of the grid), three when many chains fill the GPU anyway (measured with the
-        // background-only tiles on the moment path: one chain per unit is best up to ~100 chains, 3.9 vs 4.0 us per chain at 80)
-        h->heavy_sub = 2;
-        h->heavy_group = (C >= 128) ? 3 : 1;
-        // a spectrum so short that pairs of sub-tiles would not even fill the GPU once (S-local: 10k bins, 10 chains): single
-        // sub-tiles, twice the units (25.7 vs 29.9 us per step there)
-        const bool short_spectrum = (long)((d.Nx + TG_THREADS * 4 - 1) / (TG_THREADS * 4)) * C < 4L * 296;
-        if (short_spectrum) h->heavy_sub = 1;
-        // developer knobs for scheduling experiments (never change results)
-        // the costliest window-region items take three chains per unit (set-up and list building shared), the rest one chain
-        // (small units for the tail): 70 % of them at 10 chains (49.0 -> 48.1 us), all of them from 32 chains on (-7 %)
-        h->hybrid_group = (C < 64) ? 3 : ((C < 128) ? 4 : 5);
-        h->hybrid_pct = short_spectrum ? 0 : ((C < 16) ? 70 : ((C < 32) ? 80 : 100));      // short spectra: as many units as possible
-        if (h->ffw && !short_spectrum) {
-            // far-field path: a window-region unit is a run of pairs of sub-tiles x a few chains (per pair and chain one staged
-            // interpolant + the exact records; no lists); measured on cfg3: 4 sub-tiles x 2 chains at 10 chains (32.8 us against
-            // 35-40 for the neighbours), 8 sub-tiles x 3 chains at 80 chains (2.14 us per chain)
-            h->heavy_sub = (C < 32) ? 4 : 8;
-            h->hybrid_pct = 100;
-            h->hybrid_group = (C < 32) ? 2 : 3;
-        }
+        schedule_defaults(h, C);
         if (const char *e = getenv("TG_GRAPH_STEPS")) h->steps_per_graph = std::max(1, std::min(256, atoi(e)));
-        if (const char *e = getenv("TG_HYBRID_PCT")) h->hybrid_pct = atoi(e);
-        if (const char *e = getenv("TG_HYBRID_GROUP")) h->hybrid_group = std::max(1, atoi(e));
-        if (const char *e = getenv("TG_HEAVY_SUB")) h->heavy_sub = std::max(1, atoi(e));
-        if (const char *e = getenv("TG_HEAVY_GROUP")) h->heavy_group = std::max(1, atoi(e));
     }
 
     // ---- MALA configuration ----
@@ -1206,6 +1217,7 @@ static int batch_destroy(tg_batch *b)
     cudaSetDevice(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
     if (b->side) cudaStreamSynchronize(b->side);
+    if (b->hs.size() > 1) for (tg_handle *h : b->hs) if (h->self && h->self != b) { schedule_defaults(h, h->s.C); build_items(h, h->sp, h->s.C); }   // their own shape back
     batch_drop_graph(b);
     for (auto e : b->ev_pool) cudaEventDestroy(e);
     for (auto e : b->ffev_pool) cudaEventDestroy(e);
@@ -1242,6 +1254,9 @@ static int batch_create(tg_handle **hs, int n, tg_batch **out)
     std::vector<int2> cmap;
     for (int k = 0; k < n; k++) for (int c = 0; c < hs[k]->s.C; c++) cmap.push_back(make_int2(k, c));
     b->Ctot = (int)cmap.size();
+    if (n > 1) {         // the units of every star are shaped for the chains of the whole launch
+        for (int k = 0; k < n; k++) { schedule_defaults(hs[k], b->Ctot); int r2 = build_items(hs[k], hs[k]->sp, hs[k]->s.C); if (r2) return bail(r2); }
+    }
     if ((r = batch_dalloc(b, &b->d_cmap, cmap.size())) || (r = batch_dalloc(b, &b->d_ev, n)) || (r = batch_dalloc(b, &b->d_pm, n)) ||
         (r = batch_dalloc(b, &b->d_ps, n)) || (r = batch_dalloc(b, &b->d_fin, n)) || (r = batch_dalloc(b, &b->d_ff, n))) return bail(r);
     for (int k = 0; k < n; k++) if (cudaStreamSynchronize(hs[k]->stream) != cudaSuccess) return bail(fail(TG_E_CUDA, "tg_batch_create: sync"));
