@@ -38,10 +38,12 @@ I0 = 10000          # first iteration of the bench: a run restored into its Lear
 METRIC = "tempered chain-steps/s (model_MS_Global 1M-bin spectrum, 10 chains per ensemble)"
 
 
-def synth_problem(W, make_y, star=0):
-    """S-global; star s > 0 is another star (seed, numax/Dnu jitter) -- cfg5's recipe."""
+def synth_problem(W, make_y, star=0, jitter=True):
+    """S-global; star s > 0 is another star (noise seed, and numax/Dnu jitter -- cfg5's recipe -- unless jitter is off: the headline's
+    one star per GPU is the SAME star observed with independent noise on every GPU, i.e. equal work per GPU, so that the N-GPU value
+    measures the machine and not the spread of window widths between stars)."""
     g = np.random.Generator(np.random.Philox(key=777 + star))
-    jit = (1.0 + 0.1 * (2 * g.random(2) - 1)) if star > 0 else np.ones(2)
+    jit = (1.0 + 0.1 * (2 * g.random(2) - 1)) if (star > 0 and jitter) else np.ones(2)
     return W.s_global(Nx=NX, model_case=3, seed=12345 + star, make_y=make_y, numax=2700.0 * jit[0], dnu=120.186 * jit[1])
 
 
@@ -51,7 +53,8 @@ def workload_config(nv, stars_per_gpu=1):
                         "%d star(s) per GPU, lambda=1.7, learning on (iterations from %d)" % (nv, stars_per_gpu, I0),
             "step": "one MCMC iteration of every chain; the reference arm and e2e time its dominant part, generate_model (model+logL+prior) for the chains of one iteration",
             "l2": "x, y = 16 MB per launch and star (< L2) but the timed kernel is FP64-bound; no L2 flush (steady-state MCMC reuses the spectrum every step by design)",
-            "per_gpu": "independent tempered ensembles (stars) per GPU, no collective"}
+            "per_gpu": "independent tempered ensembles (stars) per GPU, no collective; with one star per GPU every GPU holds the same star with its own noise realisation "
+                       "and Philox key (equal work per GPU), with several stars per GPU the stars differ (numax, Dnu within 10 %)"}
 
 
 class ClockSampler:
@@ -224,7 +227,7 @@ def main():
             if cfg_name == "cfg2":
                 p = W.s_local(make_y=make_y)
             else:
-                p = synth_problem(W, make_y, star)
+                p = synth_problem(W, make_y, star, jitter=(n_stars > 1))
             mds.append(tb.GpuModelDef(p, mala_cfg(C_star, 4242 + star, 8 if cfg_name == "cfg4" else 0), device=local_rank))
         return mds, (tb.GpuBatch(mds) if n_stars > 1 else None)
 
@@ -243,9 +246,10 @@ def main():
         clocks.start()
         (grp or md0).kernel_time(reset=2)
         barrier(md0)
-        (grp or md0).timer_start()
         runner.execute(I0 + warm, steps, record=False)
-        ms = (grp or md0).timer_stop_ms()
+        # CUDA events recorded by the call itself on its stream, right before the first launch and right after the last step: exactly
+        # the K steps on the device's clock, none of this script's host code in between
+        ms = (grp or md0).last_run_ms()
         barrier(md0)
         _, _, launches = (grp or md0).kernel_time(reset=0)
         clk = clocks.stop()
@@ -448,9 +452,8 @@ def main():
         r10 = tb.GpuMALA(ms10)
         r10.execute(I0, 2 * STEPS_PER_GRAPH, record=False)
         barrier(ms10)
-        ms10.timer_start()
         r10.execute(I0 + 2 * STEPS_PER_GRAPH, 96, record=False)
-        t10 = torch.tensor([ms10.timer_stop_ms()], dtype=torch.float64, device="cuda")
+        t10 = torch.tensor([ms10.last_run_ms()], dtype=torch.float64, device="cuda")
         dist.all_reduce(t10, op=dist.ReduceOp.MAX)
         ms10.shard_status()
         dist.barrier()
@@ -460,9 +463,8 @@ def main():
             m1 = tb.GpuModelDef(p10, cfg10, device=local_rank)
             r1 = tb.GpuMALA(m1)
             r1.execute(I0, 2 * STEPS_PER_GRAPH, record=False)
-            m1.timer_start()
             r1.execute(I0 + 2 * STEPS_PER_GRAPH, 96, record=False)
-            one = m1.timer_stop_ms() / 96
+            one = m1.last_run_ms() / 96
             m1.close()
         dist.barrier()
         bin_sharded = {"workload": "S-10M: one 10 000 000-bin spectrum over %d GPUs (contiguous bin ranges of equal estimated cost), 10 chains replicated" % world,

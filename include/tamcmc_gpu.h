@@ -244,6 +244,12 @@ int tg_work_profile(tg_handle *h, long *bins_direct, long *moment_tiles, int *un
  * micro-tiles), out[4] micro-tiles whose interpolant also holds the background and N0.  All zero when the path is off. */
 int tg_farfield_profile(tg_handle *h, int B, long *out);
 
+/* Device time of the steps of the last tg_run / tg_batch_run call: CUDA events recorded by the call itself on its stream, right
+ * before the first launch and right after the last step (before the records are drained), so no host code of the caller lies
+ * between them. */
+int tg_last_run_ms(tg_handle *h, double *ms);
+int tg_batch_last_run_ms(tg_batch *b, double *ms);
+
 /* Device-side stopwatch on the handle's stream (CUDA events): which = 0 start, 1 stop. */
 int tg_event_record(tg_handle *h, int which);
 int tg_event_elapsed_ms(tg_handle *h, double *ms);

@@ -112,6 +112,7 @@ struct tg_batch {
     int          ff_cpc = 0, ff_ppc = 1; size_t ff_smem = 0;
     int2        *d_cmap = nullptr;
     bool         args_valid = false;
+    cudaEvent_t  ev_run[2] = {nullptr, nullptr};   // device-side stopwatch around the steps of the last tg_run / tg_batch_run call
     int          side_rows = 0; size_t propose_smem = 0, eval_smem = 0;
     tg_handle::UnitTable units;            // work units of the fused kernel over all stars, costliest first
     std::vector<long> units_version;       // items_version of every star the table was built from
@@ -1222,6 +1223,7 @@ static int batch_destroy(tg_batch *b)
     for (auto e : b->ev_pool) cudaEventDestroy(e);
     for (auto e : b->ffev_pool) cudaEventDestroy(e);
     for (void *q : b->allocs) cudaFree(q);
+    for (int k = 0; k < 2; k++) if (b->ev_run[k]) cudaEventDestroy(b->ev_run[k]);
     if (b->ev_fork) cudaEventDestroy(b->ev_fork);
     if (b->ev_join) cudaEventDestroy(b->ev_join);
     if (b->side) cudaStreamDestroy(b->side);
@@ -1475,6 +1477,8 @@ static int batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs)
     for (tg_handle *h : b->hs) cap = std::min(cap, h->rec.cap);
     const int G = b->steps_per_graph;
     long done = 0;
+    for (int k = 0; k < 2; k++) if (!b->ev_run[k]) CK(cudaEventCreate(&b->ev_run[k]));
+    CK(cudaEventRecord(b->ev_run[0], b->stream));          // the steps of this call on the device's clock: from here ...
     while (done < nsteps) {
         const long n = std::min(nsteps - done, cap);
         { int r = batch_set_ctrl(b, i0 + done, i0 + done); if (r) return r; }
@@ -1499,6 +1503,7 @@ static int batch_run(tg_batch *b, long i0, long nsteps, tg_records **recs)
             }
         }
         for (; k < n; k++) { int r = batch_launch_step(b, true, true); if (r) return r; }
+        if (done + n >= nsteps) CK(cudaEventRecord(b->ev_run[1], b->stream));     // ... to the end of its last step (before the records are drained)
         for (size_t s2 = 0; s2 < b->hs.size(); s2++) { int r = drain_records(b->hs[s2], b->stream, recs ? recs[s2] : nullptr, done, n); if (r) return r; }
         CK(cudaStreamSynchronize(b->stream));
         done += n;
@@ -1568,6 +1573,18 @@ extern "C" int tg_prepass_time(tg_handle *h, double *ms_ff)
     if (!h || !h->self) return fail(TG_E_BADARG, "null handle");
     return tg_batch_prepass_time(h->self, ms_ff);
 }
+static int batch_last_run_ms(tg_batch *b, double *ms)
+{
+    if (!b || !ms || !b->ev_run[0] || !b->ev_run[1]) return fail(TG_E_BADARG, "tg_last_run_ms: no run yet");
+    CK(cudaSetDevice(b->device));
+    CK(cudaEventSynchronize(b->ev_run[1]));
+    float f = 0; CK(cudaEventElapsedTime(&f, b->ev_run[0], b->ev_run[1]));
+    *ms = f;
+    return TG_OK;
+}
+extern "C" int tg_batch_last_run_ms(tg_batch *b, double *ms) { return batch_last_run_ms(b, ms); }
+extern "C" int tg_last_run_ms(tg_handle *h, double *ms) { return batch_last_run_ms(h ? h->self : nullptr, ms); }
+
 // device-side stopwatch on the group's stream: which = 0 start, 1 stop (then the elapsed time is read with tg_event_elapsed_ms of the first star)
 extern "C" int tg_batch_event_record(tg_batch *b, int which)
 {

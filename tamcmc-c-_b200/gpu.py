@@ -23,7 +23,7 @@ EXPORTS = ["tg_last_error", "tg_version", "tg_create", "tg_destroy", "tg_eval", 
            "tg_step_end", "tg_partials_device_ptr", "tg_shard_install_current", "tg_shard_unique_id", "tg_shard_attach", "tg_shard_detach", "tg_shard_ipc_export", "tg_shard_ipc_attach", "tg_shard_status", "tg_sync", "tg_kernel_time", "tg_set_tuning",
            "tg_measure_fp64_peak", "tg_work_profile", "tg_event_record", "tg_event_elapsed_ms",
            "tg_batch_create", "tg_batch_run", "tg_batch_destroy", "tg_batch_sizes", "tg_batch_kernel_time", "tg_batch_event_record",
-           "tg_batch_prepass_time", "tg_prepass_time", "tg_farfield_profile", "tg_get_state_means"]
+           "tg_batch_prepass_time", "tg_prepass_time", "tg_farfield_profile", "tg_get_state_means", "tg_last_run_ms", "tg_batch_last_run_ms"]
 # include/tamcmc_outputs.h (host code in the same library)
 EXPORTS_OUT = ["tg_out_last_error", "tg_out_open", "tg_out_append", "tg_out_write_restore", "tg_out_write_restore_means", "tg_out_close", "tg_restore_read", "tg_restore_read_means"]
 
@@ -114,6 +114,8 @@ class GpuLibrary:
         L.tg_batch_prepass_time.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.tg_prepass_time.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.tg_farfield_profile.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_long)]
+        L.tg_last_run_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.tg_batch_last_run_ms.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.tg_get_state_means.argtypes = [C.c_void_p] + [C.c_void_p] * 4 + [C.POINTER(C.c_long), C.c_int]
         L.tg_out_last_error.restype = C.c_char_p
         for name in EXPORTS_OUT[1:]:
@@ -411,6 +413,12 @@ class GpuModelDef:
     def set_tuning(self, chains_per_block=0, light_subtiles=0, use_graph=-1, heavy_group=0):
         self.lib.check(self.lib.lib.tg_set_tuning(self.h, chains_per_block, heavy_group, light_subtiles, use_graph))
 
+    def last_run_ms(self):
+        """Device time of the steps of the last execute() on this handle (events recorded inside tg_run)."""
+        ms = C.c_double(0)
+        self.lib.check(self.lib.lib.tg_last_run_ms(self.h, C.byref(ms)))
+        return ms.value
+
     def timer_start(self):
         self.lib.check(self.lib.lib.tg_event_record(self.h, 0))
 
@@ -543,6 +551,11 @@ class GpuBatch:
     def prepass_time(self):
         ms = C.c_double(0)
         self.lib.check(self.lib.lib.tg_batch_prepass_time(self.b, C.byref(ms)))
+        return ms.value
+
+    def last_run_ms(self):
+        ms = C.c_double(0)
+        self.lib.check(self.lib.lib.tg_batch_last_run_ms(self.b, C.byref(ms)))
         return ms.value
 
     def timer_start(self):
