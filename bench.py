@@ -275,23 +275,25 @@ def main():
         F = Fx = Fpre = 0.0
         Lm, Kh = [], 0
         ff_stats = [0, 0, 0, 0, 0]
+        ff_bins_per_mt = 0
         for md in mds:
             md.evaluate(md.params, md.Tcoefs)
             Lw, Kh = md.last_work(md.Nmodels)
             bins_direct, mom_tiles, _ = md.work_profile()
-            mt, marked, recs, nfar, folded = md.farfield_profile(md.Nmodels)
+            mt, marked, recs, nfar, folded, mtb = md.farfield_profile(md.Nmodels)
             ff_stats = [a + b for a, b in zip(ff_stats, (mt, marked, recs, nfar, folded))]
+            ff_bins_per_mt = mtb
             F += float((8.0 * Lw + md.Nx * (5.0 * Kh + 5.0)).sum())
             mom = mom_tiles * (14 * (5.0 * Kh + 5.0) + 2 * 2 * 14 * 9 + 4 * 9)
             if mt > 0 and marked == 0:
-                ff_bins = 256.0 * mt / md.Nmodels                         # per chain
+                ff_bins = float(mtb) * mt / md.Nmodels                    # per chain
                 per_chain = (bins_direct - ff_bins) * (5.0 * Kh + 5.0) + mom
-                Fx += md.Nmodels * per_chain + 256.0 * (mt * (30.0 + 5.0) + 8.0 * recs + (mt - folded) * 5.0 * Kh)
+                Fx += md.Nmodels * per_chain + float(mtb) * (mt * (30.0 + 5.0) + 8.0 * recs + (mt - folded) * 5.0 * Kh)
                 Fpre += 16 * 8.0 * nfar + mt * (2 * 16 * 16 + 2 * 72 + 2 * 15 * 8)
             else:
                 Fx += float((8.0 * Lw + bins_direct * (5.0 * Kh + 5.0) + mom).sum())
             Lm.append(float(Lw.mean()))
-        return F, Fx, float(np.mean(Lm)), Kh, Fpre, ff_stats
+        return F, Fx, float(np.mean(Lm)), Kh, Fpre, ff_stats + [ff_bins_per_mt]
 
     mds, grp = build_group(S, rank * S)
     md = mds[0]
@@ -319,11 +321,11 @@ def main():
                 "frac_with_prepass": F_launch / (t_kernel + t_pre) / 1e12 / peak_tflops,
                 "frac_executed_with_prepass": (F_exec + F_pre) / (t_kernel + t_pre) / 1e12 / peak_tflops,
                 "prepass_executed_flop_per_launch": F_pre,
-                "far_field": {"micro_tiles": ff_stats[0], "marked": ff_stats[1], "exact_records": ff_stats[2], "far_components": ff_stats[3], "background_folded": ff_stats[4],
-                              "note": "per launch, all chains: 256-bin micro-tiles under the truncation windows prepared by tg_k_ff; exact records = components still evaluated "
+                "far_field": {"micro_tiles": ff_stats[0], "marked": ff_stats[1], "exact_records": ff_stats[2], "far_components": ff_stats[3], "background_folded": ff_stats[4], "bins_per_micro_tile": ff_stats[5],
+                              "note": "per launch, all chains: micro-tiles under the truncation windows prepared by tg_k_ff; exact records = components still evaluated "
                                       "exactly per bin there; far components = (component, micro-tile) pairs replaced by the interpolant"},
                 "model_kernels_share_of_step": (t_kernel + t_pre) / (ms * 1e-3 / K),
-                "prepass_note": "tg_k_ff prepares, per chain and 256-bin micro-tile under the truncation windows, the Chebyshev interpolant of the far components and the "
+                "prepass_note": "tg_k_ff prepares, per chain and 512-bin micro-tile under the truncation windows, the Chebyshev interpolant of the far components and the "
                                 "records of the near ones; frac counts the fused kernel alone, frac_with_prepass the two launches that evaluate the model",
                 "peak_source": "DFMA microkernel measured in this run (MEASURED_PEAKS.json has no FP64 figure); peak_nominal = SMs x 64 lanes x 2 x max SM clock",
                 "frac_executed_note": "flops the fused kernel actually runs / its time / peak: under the truncation windows a 15-FMA Horner recurrence + 8 flop per exact record "

@@ -224,7 +224,7 @@ int tg_sync(tg_handle *h);
 /* Kernel timing of the dominant kernel (CUDA events on the handle's stream), accumulated since
  * the last reset: number of launches and total milliseconds. */
 int tg_kernel_time(tg_handle *h, int reset, long *launches, double *ms_eval, long *total_launches);
-/* The far-field pre-pass (the kernel that prepares, per chain and 256-bin micro-tile under the truncation windows, the
+/* The far-field pre-pass (the kernel that prepares, per chain and 512-bin micro-tile under the truncation windows, the
  * interpolant of the far components and the records of the near ones for the fused kernel): total milliseconds of its launches
  * in the sampler steps timed together with tg_kernel_time. */
 int tg_prepass_time(tg_handle *h, double *ms_ff);
@@ -239,9 +239,10 @@ int tg_set_tuning(tg_handle *h, int chains_per_block, int heavy_group, int light
 int tg_work_profile(tg_handle *h, long *bins_direct, long *moment_tiles, int *units);
 
 /* What the far-field pre-pass left for the B vectors of the last tg_eval batch (measurement support, no reference counterpart):
- * out[0] micro-tiles of 256 bins prepared (B x micro-tiles of the window region), out[1] of them marked for the
+ * out[0] micro-tiles prepared (B x micro-tiles of the window region), out[1] of them marked for the
  * component-by-component loop, out[2] exact records in all of them, out[3] far components interpolated (summed over the
- * micro-tiles), out[4] micro-tiles whose interpolant also holds the background and N0.  All zero when the path is off. */
+ * micro-tiles), out[4] micro-tiles whose interpolant also holds the background and N0, out[5] bins per micro-tile.
+ * out[0..4] are zero when the path is off.  out has six entries. */
 int tg_farfield_profile(tg_handle *h, int B, long *out);
 
 /* Device time of the steps of the last tg_run / tg_batch_run call: CUDA events recorded by the call itself on its stream, right

@@ -740,7 +740,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
             DA(h->ffw, w.size());
             CK(cudaMemcpy(h->ffw, w.data(), w.size() * 8, cudaMemcpyHostToDevice));
             h->ff_stride = (int)(Nx / TG_FF_BINS);                  // whole micro-tiles of the spectrum
-            if (h->ff_stride < TG_FF_MT) { h->ffw = nullptr; h->ff_stride = 0; }
+            if (h->ff_stride < TG_FF_PAIR_MT * 4) { h->ffw = nullptr; h->ff_stride = 0; }
             else {
                 DA(h->ffgeo, (size_t)h->ff_stride);
                 tg_k_ffgeo<<<(h->ff_stride + 255) / 256, 256, 0, h->stream>>>(h->x, (int)Nx, h->ffgeo, h->ff_stride);
@@ -1913,7 +1913,8 @@ extern "C" int tg_eval_noalloc(tg_handle *h, const double *params, int B, const 
 extern "C" int tg_farfield_profile(tg_handle *h, int B, long *out)
 {
     if (!h || !out || B < 1) return fail(TG_E_BADARG, "tg_farfield_profile: bad argument");
-    for (int k = 0; k < 5; k++) out[k] = 0;
+    for (int k = 0; k < 6; k++) out[k] = 0;
+    out[5] = TG_FF_BINS;
     if (!h->ffw || !h->ev.ffh || h->ff_nmt <= 0 || B > h->ev.cap) return TG_OK;      // path off: nothing prepared
     CK(cudaSetDevice(h->device));
     CK(cudaStreamSynchronize(h->stream));

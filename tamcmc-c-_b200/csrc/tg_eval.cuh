@@ -354,7 +354,7 @@ __device__ __forceinline__ void tg_ff_run(const TgEvalArgs &a, const TgEvalSmem 
     long long pk[3] = {0, 0, 0};
 #endif
     for (int s = 0; s < nstep; s++) {
-        const int bp = b0 + pr * 2 * TG_THREADS * 4, bw = bp + warp * TG_FF_BINS;
+        const int bp = b0 + pr * 2 * TG_THREADS * 4, bw = bp + warp * TG_FF_WBINS;
         if (g == 0) {
 #pragma unroll
             for (int j = 0; j < TG_FF_MT; j++) { ii[j] = bw + 32 * j + lane; x[j] = __ldg(a.x + ii[j]); y[j] = __ldg(a.y + ii[j]); }
@@ -639,9 +639,9 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
             // loop overhead per bin, twice the independent work per warp behind every reciprocal)
             // inside the range the pre-pass covered (and no chain of the unit with an asymmetric profile): no lists at all, and
             // every following pair of the item that lies inside it too (whether windows meet it or not) in the same run
-            if (ff_on && sym_all && (b0 >> 8) >= a.ff.mt0 && (b0 >> 8) + TG_FF_MT <= a.ff.mt0 + a.ff.nmt) {
+            if (ff_on && sym_all && (b0 >> TG_FF_SHIFT) >= a.ff.mt0 && (b0 >> TG_FF_SHIFT) + TG_FF_PAIR_MT <= a.ff.mt0 + a.ff.nmt) {
                 int npair = 1;
-                while (sub + 2 * (npair + 1) <= item.y && b0 + 2 * (npair + 1) * SUB <= Nx && (b0 >> 8) + (npair + 1) * TG_FF_MT <= a.ff.mt0 + a.ff.nmt) npair++;
+                while (sub + 2 * (npair + 1) <= item.y && b0 + 2 * (npair + 1) * SUB <= Nx && (b0 >> TG_FF_SHIFT) + (npair + 1) * TG_FF_PAIR_MT <= a.ff.mt0 + a.ff.nmt) npair++;
                 __syncthreads();                  // the staging buffers of an earlier run are dead
                 tg_ff_run(a, S, G, c0, b0, npair, tid, s_ffstage);
                 sub += 2 * npair;

@@ -2,7 +2,7 @@
 //
 // Reference arithmetic being reproduced: build_lorentzian.cpp:61-102 (profile h/(1+4(x-nu)^2/Gamma^2)), :365-460 (window
 // [imin, imax) of every m-component).  Inside the windows ~30 components overlap on every bin, but all except one or two are
-// many line widths away and vary slowly across a few hundred bins.  A micro-tile is 256 consecutive bins (half-width w, centre
+// many line widths away and vary slowly across a few hundred bins.  A micro-tile is TG_FF_BINS = 512 consecutive bins (half-width w, centre
 // xc).  A component whose window covers the micro-tile and whose poles nu +- i Gamma/2 lie at least R w from xc is analytic
 // inside the Bernstein ellipse of parameter rho >= R + sqrt(R^2 - 1) of the micro-tile: its interpolant at TG_FF_N = 16
 // Chebyshev nodes is exact to rounding (<= 7e-15 of the component's own value at R = 5, 2e-15 at R = 6; R^2 = ff_r2 = 30.25).
@@ -12,8 +12,10 @@
 //                       values into Chebyshev coefficients, checks the trailing coefficients, and leaves in HBM per
 //                       (chain, micro-tile): 16 coefficients, a header, and the records (nu, 4/Gamma^2, height, window) of the
 //                       components to be evaluated exactly there (near ones, and those whose window edge cuts the micro-tile);
-//   fused kernel        per bin: one Clenshaw recurrence (30 FP64 instructions) + the exact records of its micro-tile, window
-//                       predicate included -- the windows stay bin-exact -- instead of ~30 profile evaluations (6.25 each).
+//                       the coefficients converted to powers of the local variable (tg_ff_to_powers);
+//   fused kernel        per bin: one Horner recurrence (15 FMA) + the exact records of its micro-tile, window predicate where a
+//                       window edge cuts it -- the windows stay bin-exact -- instead of ~30 profile evaluations (6.25 each);
+//                       a warp takes 256 bins (half a micro-tile) per step, eight per lane.
 //
 // Nothing is assumed about the parameters: the classification is a function of (nu, Gamma, window) and the grid alone; a
 // micro-tile whose trailing coefficients are not small (|c14| + |c15| > TG_FF_TOL |c0|: NaN parameters, ...) or that has more
@@ -24,8 +26,15 @@
 #include "tg_internal.cuh"
 
 #define TG_FF_N    16                  // Chebyshev nodes / coefficients per micro-tile
-#define TG_FF_MT   8                   // micro-tiles of a pair of sub-tiles == bins per thread of the fused kernel there
-#define TG_FF_BINS 256                 // bins per micro-tile == threads of the fused kernel
+#define TG_FF_MT   8                   // micro-tiles per group of the pre-pass (one per warp of its CTAs) == bins per lane of the fused kernel there
+#ifndef TG_FF_BINS
+#define TG_FF_BINS 512                 // bins per micro-tile (256 or 512)
+#endif
+#define TG_FF_SHIFT (TG_FF_BINS == 512 ? 9 : 8)      // global micro-tile index = bin >> TG_FF_SHIFT
+#define TG_FF_WBINS 256                // bins a warp of the fused kernel takes per step (8 per lane)
+#define TG_FF_WPM  (TG_FF_BINS / TG_FF_WBINS)        // warps of the fused kernel per micro-tile
+#define TG_FF_PAIR_MT (2048 / TG_FF_BINS)            // micro-tiles of a pair of sub-tiles
+static_assert(TG_FF_BINS == 256 || TG_FF_BINS == 512, "micro-tiles of 256 or 512 bins");
 #define TG_FF_E    32                  // exact components a micro-tile record holds
 #define TG_FF_TOL  1.0e-12
 #define TG_FF_HDR  (2 * TG_FF_N * TG_FF_N + TG_FF_N)   // doubles of the constant buffer: node values -> Chebyshev coefficients [k][i], the nodes,
@@ -41,7 +50,7 @@ struct TgFFView {                      // what the fused kernel reads (part of i
     const double  *c;                  // [B][stride][TG_FF_N]
     const TgFFHdr *hdr;                // [B][stride]
     const TgFFRec *rec;                // [B][stride][TG_FF_E]
-    const TgFFGeo *geo;                // [Nx / 256]  (global micro-tile index = bin >> 8)
+    const TgFFGeo *geo;                // [Nx / TG_FF_BINS]  (global micro-tile index = bin >> TG_FF_SHIFT)
     int            stride;             // micro-tiles per chain the buffers hold
     int            mt0, nmt;           // micro-tiles [mt0, mt0 + nmt) were prepared by the pre-pass of this launch
     int            pad_;
@@ -348,12 +357,12 @@ struct __align__(16) TgFFStage {
 };
 struct TgFFFetch { int4 r0, r1, r2; };
 static_assert(sizeof(TgFFRec) == 32 && TG_FF_E == 32, "one record per lane: two 16-byte pieces");
-static_assert(TG_FF_MT * 32 == TG_FF_BINS, "one micro-tile per warp, eight bins per lane");
+static_assert(TG_FF_MT * 32 == TG_FF_WBINS, "eight bins per lane: 256 bins per warp and step (a whole micro-tile, or half of one)");
 
 // what the pre-pass left for `chain` on the micro-tile of this warp in the pair starting at bin bp -> registers
 __device__ __forceinline__ void tg_ff_fetch(const TgFFView &f, int chain, int bp, int warp, int lane, TgFFFetch &q)
 {
-    const int mg = (bp >> 8) + warp;
+    const int mg = (bp >> TG_FF_SHIFT) + warp / TG_FF_WPM;
     const size_t slot = (size_t)chain * f.stride + (mg - f.mt0);
     const int4 *rp = (const int4 *)(f.rec + slot * TG_FF_E) + 2 * lane;
     q.r0 = __ldg(rp); q.r1 = __ldg(rp + 1);                            // record `lane` (slots past the count are never read back)

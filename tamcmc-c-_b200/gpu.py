@@ -436,8 +436,8 @@ class GpuModelDef:
         return b.value, m.value, u.value
 
     def farfield_profile(self, B):
-        """(micro-tiles prepared, marked, exact records, far components interpolated, micro-tiles holding the background) of the last evaluate() batch."""
-        out = (C.c_long * 5)()
+        """(micro-tiles prepared, marked, exact records, far components interpolated, micro-tiles holding the background, bins per micro-tile) of the last evaluate() batch."""
+        out = (C.c_long * 6)()
         self.lib.check(self.lib.lib.tg_farfield_profile(self.h, B, out))
         return tuple(out)
 

@@ -259,7 +259,7 @@ def test_background_moments_over_the_prior_ranges(tb, W, oracle, monkeypatch):
 
 @pytest.mark.parametrize("case", ["cfg3", "hot_chains", "narrow_modes", "general_p"])
 def test_far_field_path_equals_the_exact_path(tb, W, oracle, case, monkeypatch):
-    """Under the truncation windows (build_lorentzian.cpp:365-460) the fused kernel takes, per 256-bin micro-tile, a polynomial
+    """Under the truncation windows (build_lorentzian.cpp:365-460) the fused kernel takes, per 512-bin micro-tile, a polynomial
     interpolant of the components whose poles are far (prepared by the pre-pass tg_k_ff, tg_farfield.cuh) plus the exact
     records of the near ones, instead of every component bin by bin.  Both paths must agree to rounding and both with the
     oracle: at the usual perturbation, with hot-chain excursions three times wider, with line widths five times narrower (more
