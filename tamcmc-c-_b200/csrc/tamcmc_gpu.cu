@@ -632,7 +632,7 @@ static void schedule_defaults(tg_handle *h, int C)
         // 30-36 for the neighbours), 8 sub-tiles x 3 chains at 80 chains (1.45 us per chain)
         h->heavy_sub = (C < 32) ? 4 : 8;
         h->hybrid_pct = 100;
-        h->hybrid_group = (C < 32) ? 2 : 3;
+        h->hybrid_group = (C < 32) ? 2 : 4;          // (8 x 4 against 8 x 3 at 8 stars x 10 chains: 246 against 254 us per step)
     }
     // moment tiles per work item: a run of 16 tiles x 5 chains is the longest unit of a launch (23 us: ten rounds of one
     // (tile, chain) per warp) -- with few chains, where the launch is one wave and a bit, shorter runs end it earlier
