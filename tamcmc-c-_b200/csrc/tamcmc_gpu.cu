@@ -5,6 +5,8 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <set>
+#include <mutex>
 #include <limits>
 #include <cmath>
 #include <algorithm>
@@ -153,6 +155,11 @@ static int raise_dyn_smem(const void *func, size_t bytes)
     return TG_OK;
 }
 
+// handles that exist (a launch group gives its stars their own unit shapes back when it is destroyed -- but only those that are
+// still there: at interpreter exit a binding may destroy the stars first)
+static std::mutex g_live_mu;
+static std::set<const void *> g_live;
+static bool handle_alive(const void *h) { std::lock_guard<std::mutex> lk(g_live_mu); return g_live.count(h) != 0; }
 static long g_dbg_count[4] = {0, 0, 0, 0};      // developer counters: work-item partitions built, step graphs captured, probe syncs, argument uploads
 extern "C" int tg_dbg_counters(long *out) { for (int k = 0; k < 4; k++) out[k] = g_dbg_count[k]; return 0; }
 extern "C" const char *tg_last_error(void) { return g_err.c_str(); }
@@ -604,6 +611,7 @@ extern "C" int tg_create(const tg_problem *p, tg_handle **out)
     tg_handle *h = new tg_handle();
     const int r = create_impl(p, h);
     if (r != TG_OK) { const std::string keep = g_err; tg_destroy(h); g_err = keep; return r; }
+    { std::lock_guard<std::mutex> lk(g_live_mu); g_live.insert(h); }
     *out = h;
     return TG_OK;
 }
@@ -878,6 +886,7 @@ static int create_impl(const tg_problem *p, tg_handle *h)
 extern "C" int tg_destroy(tg_handle *h)
 {
     if (!h) return TG_OK;
+    { std::lock_guard<std::mutex> lk(g_live_mu); g_live.erase(h); }
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->stream2) cudaStreamSynchronize(h->stream2);
@@ -1216,9 +1225,9 @@ static int batch_destroy(tg_batch *b)
 {
     if (!b) return TG_OK;
     cudaSetDevice(b->device);
-    if (b->stream) cudaStreamSynchronize(b->stream);
+    if (b->stream && !b->hs.empty() && handle_alive(b->hs[0])) cudaStreamSynchronize(b->stream);     // (the stream is the first star's)
     if (b->side) cudaStreamSynchronize(b->side);
-    if (b->hs.size() > 1) for (tg_handle *h : b->hs) if (h->self && h->self != b) { schedule_defaults(h, h->s.C); build_items(h, h->sp, h->s.C); }   // their own shape back
+    if (b->hs.size() > 1) for (tg_handle *h : b->hs) if (handle_alive(h) && h->self && h->self != b) { schedule_defaults(h, h->s.C); build_items(h, h->sp, h->s.C); }   // their own shape back
     batch_drop_graph(b);
     for (auto e : b->ev_pool) cudaEventDestroy(e);
     for (auto e : b->ffev_pool) cudaEventDestroy(e);
@@ -1227,6 +1236,7 @@ static int batch_destroy(tg_batch *b)
     if (b->ev_fork) cudaEventDestroy(b->ev_fork);
     if (b->ev_join) cudaEventDestroy(b->ev_join);
     if (b->side) cudaStreamDestroy(b->side);
+    cudaGetLastError();                  // nothing of a teardown may surface in a later call
     delete b;
     return TG_OK;
 }

@@ -292,6 +292,29 @@ def test_launch_group_of_stars_equals_the_individual_handles(tb, W, oracle, use_
         m.close()
 
 
+def test_launch_group_outliving_its_stars_is_destroyed_safely(tb, W, oracle):
+    """The stars must outlive the group (include/tamcmc_gpu.h), but a binding may tear them down in any order at interpreter
+    exit: destroying the group after its stars must not touch them (it gives the stars their own unit shapes back only while
+    they exist).  And a star that leaves a destroyed group runs on alone, on its own trajectory."""
+    stars = _three_stars(W, oracle)[:2]
+    mk = lambda: [tb.GpuModelDef(p, tb.MalaConfig(Nchains=6, Nt_learn=[8, 10**6], periods_learn=[1], c0=2.0, seed=7 + k)) for k, p in enumerate(stars)]
+    ms = mk()
+    batch = tb.GpuBatch(ms)
+    batch.execute(0, 20, record=False)
+    for m in ms:
+        m.close()                      # stars first ...
+    batch.close()                      # ... then the group
+    ms, solo = mk(), mk()
+    batch = tb.GpuBatch(ms)
+    a = batch.execute(0, 30)
+    batch.close()                      # the group first: its stars get their own unit shapes back
+    b = tb.GpuMALA(ms[0]).execute(30, 30)
+    c0, c1 = tb.GpuMALA(solo[0]).execute(0, 30), tb.GpuMALA(solo[0]).execute(30, 30)
+    assert np.array_equal(a[0]["vars"], c0["vars"]) and np.array_equal(b["vars"], c1["vars"])
+    for m in ms + solo:
+        m.close()
+
+
 def test_launch_group_rejects_bad_input(tb, W, oracle):
     prob = _small(W, oracle)
     m = tb.GpuModelDef(prob, tb.MalaConfig(Nchains=2))
