@@ -41,7 +41,7 @@ with open(os.path.join(P, "%s_launches.md" % T), "w") as f:
     for k, v in t.items():
         f.write("| `%s` | %d | %.1f | %.3f |\n" % (k, len(v), sum(v) / len(v), sum(v) / tot))
     f.write("\nLive run of the same build, driver protocol `--steps 20 --warmup 5` (`profiles/%s_bench.json`, CUDA events, no profiler): %.1f k chain-steps/s, %.4f ms/step; `tg_k_eval` %.1f us per launch "
-            "(share %.2f of the step; algorithmic flops / time / peak = %.2f, executed flops / time / peak = %.2f), `tg_k_ff` %.1f us timed alone with events (about 13 us inside the live step, `scripts/dev/step_timeline.py`), "
+            "(share %.2f of the step; algorithmic flops / time / peak = %.2f, executed flops / time / peak = %.2f), `tg_k_ff` %.1f us timed alone with events (less inside the live step, where it overlaps its neighbours: `scripts/dev/step_timeline.py`), "
             "the two kernels that evaluate the model together %.2f of the step. 2000-step run (`%s_bench_2000steps.json`): %.1f k chain-steps/s. e2e through `tg_eval_async`/`tg_eval_wait` with pinned host buffers: %.1f k chain-steps/s "
             "(blocking `tg_eval`: %.1f k). Reference arm on the same box (`%s_bench_reference.json`): %.1f chain-steps/s on %d of the host cores; lean C port %.0f. " %
             (T, b["value"] / 1e3, b["ms_per_step"], r["avg_launch_us"], r["kernel_share_of_step"], r["frac"], r["frac_executed"], r["prepass_avg_launch_us"], r["model_kernels_share_of_step"],
