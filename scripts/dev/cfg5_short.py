@@ -11,7 +11,7 @@ def make_y(p):
 mds = []
 for s in range(S):
     p = W.s_global(Nx=1000000, seed=12345 + s, make_y=make_y)
-    mds.append(tb.GpuModelDef(p, tb.MalaConfig(Nchains=Cn, lambda_temp=1.7, c0=2.0, Nt_learn=[0, 10**9], periods_learn=[1], dN_mixing=1, seed=4242 + s)))
+    mds.append(tb.GpuModelDef(p, tb.MalaConfig(Nchains=Cn, lambda_temp=1.7, c0=2.0, Nt_learn=([10**8, 10**9] if os.environ.get("TG_NOLEARN") else [0, 10**9]), periods_learn=[1], dN_mixing=1, seed=4242 + s)))
 run = tb.GpuBatch(mds) if S > 1 else tb.GpuMALA(mds[0])
 tm = run if S > 1 else mds[0]
 lib = mds[0].lib.lib
