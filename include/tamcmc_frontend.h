@@ -38,6 +38,7 @@ typedef struct tg_fe_run {
     int   get_params, get_statcriteria, get_parallel_tempering, evidence_diags, evidence_interpolation_factor;
     int   Nslices, Nvars, Ncons;
     double lambda_temp;
+    int   file_format;              /* !Outputs file_format: 0 binary, 1 text, 2 debug (tg_out_desc.file_format)   */
 } tg_fe_run;
 
 const char *tg_fe_last_error(void);

@@ -7,6 +7,7 @@
  *   <stat_root>.bin + .hdr                            outputs.cpp:1472-1540  write_bin_stat_criteria
  *   <ptemp_root>.bin + .hdr                           outputs.cpp:1336-1404  write_bin_parallel_temp_params
  *   <restore_root>{1,2,3}.dat                         outputs.cpp:863-1025   write_buffer_restore
+ *   the ASCII variants (file_format = text / debug)   outputs.cpp:510-613, :615-676, :791-860
  * and the reader of the restore triplet follows config.cpp:1321-1579 (Config::read_restore_files).
  * Consumers in the reference: tools/bin2txt_params.cpp, tools/read_stats.cpp, diagnostics.cpp:677-922.
  */
@@ -34,6 +35,9 @@ typedef struct tg_out_desc {
     const char *const *constant_names;  /* [Ncons]; NULL or Ncons == 0: "None" / -1 as the reference writes   */
     const double *constant_values;      /* [Ncons]                                                            */
     const double *Tcoefs;       /* [Nchains]                                                                  */
+    int   file_format;          /* Outputs::file_format (outputs.cpp:38-56): 0 "binary" (.bin + .hdr), 1 "text" (.txt with the header
+                                 * inside, write_txt_params :510-613, write_txt_stat_criteria :791-860, write_txt_parallel_temp_params
+                                 * :615-676), 2 "debug" (the binary files with extension .dbg and the text ones as .dbg.txt)          */
 } tg_out_desc;
 
 int tg_out_open(const tg_out_desc *d, tg_out **out);

@@ -922,6 +922,7 @@ void setup(tg_frontend &fe, int star, int slice, int ph)
     r.get_params = to_bool(fe.get("!Outputs", "get_params")); r.get_statcriteria = to_bool(fe.get("!Outputs", "get_statcriteria")); r.get_parallel_tempering = to_bool(fe.get("!Outputs", "get_parallel_tempering"));
     r.evidence_diags = to_bool(fe.get("!Diagnostics", "evidence_diags")); r.evidence_interpolation_factor = to_int(fe.need("!Diagnostics", "evidence_interpolation_factor"));
     r.Nslices = fe.Nslices; r.Nvars = nv; r.Ncons = a.size() - nv; r.lambda_temp = fe.lambda;
+    { const std::string ff = fe.get("!Outputs", "file_format"); r.file_format = (ff == "text") ? 1 : ((ff == "debug") ? 2 : 0); }    // outputs.cpp:38-56
     fe.ready = true;
 }
 

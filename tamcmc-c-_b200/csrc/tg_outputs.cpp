@@ -16,7 +16,7 @@ extern "C" const char *tg_out_last_error(void) { return g_err.c_str(); }
 struct tg_out {
     std::string params_root, stat_root, ptemp_root, restore_root;
     long Nsamples = 0, sofar = 0, written = 0;       // written: samples appended through this object
-    int erase = 1, C = 0, Nv = 0, Ncons = 0;
+    int erase = 1, C = 0, Nv = 0, Ncons = 0, format = 0;
     std::vector<int> relax, plength;
     std::vector<std::string> vnames, cnames;
     std::vector<double> cvals, Tcoefs, vars_mean;
@@ -44,6 +44,7 @@ extern "C" int tg_out_open(const tg_out_desc *d, tg_out **out)
     if (d->restore_root) o->restore_root = d->restore_root;
     o->Nsamples = d->Nsamples; o->sofar = d->Nsamples_sofar; o->erase = d->erase_old_files;
     o->C = d->Nchains; o->Nv = d->Nvars; o->Ncons = d->Ncons;
+    o->format = (d->file_format >= 0 && d->file_format <= 2) ? d->file_format : 0;
     if (d->relax) o->relax.assign(d->relax, d->relax + d->Np);
     if (d->plength) o->plength.assign(d->plength, d->plength + d->n_plength);
     for (int i = 0; i < d->Nvars; i++) o->vnames.push_back(d->variable_names ? d->variable_names[i] : "var" + std::to_string(i));
@@ -58,6 +59,71 @@ extern "C" int tg_out_open(const tg_out_desc *d, tg_out **out)
 }
 
 static std::string names_line(const std::vector<std::string> &n) { std::string s; for (const auto &x : n) s += x + "   "; return s; }
+
+// The ASCII variants (file_format = text: extension txt; debug: dbg.txt beside the binary files): the header sits inside the file,
+// written with the first block of a new file only; one line per sample in the stream's default format (6 significant digits,
+// Eigen's column alignment for the vectors).
+static int append_text(tg_out *o, const tg_records *rec, long n, int E)
+{
+    const int C = o->C, Nv = o->Nv;
+    const std::string ext = (o->format == 1) ? "txt" : "dbg.txt";
+    const bool fresh = (o->erase == 1 && o->written == 0);
+    const bool header = (o->written == 0 && o->erase != 0);          // Ncopy == 0 && need_header
+    const std::ios_base::openmode mode = fresh ? std::ios::trunc : std::ios::app;
+    if (!o->params_root.empty() && rec->vars) {                       // outputs.cpp:510-613
+        for (int c = 0; c < C; c++) {
+            std::ofstream f((o->params_root + "_chain-" + std::to_string(c) + "." + ext).c_str(), mode);
+            if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->params_root + "_chain-*." + ext);
+            if (header) {
+                f << "# This is an output file for the model parameters \n";
+                f << "# This file contains values for vars[0:Nchains-1][ 0:Nvars-1]. Each matrix is in a different file, indexed by the chain number\n";
+                f << "! Nsamples= " << o->Nsamples << "\n";
+                f << "! Nchains= " << C << "\n";
+                f << "! Nvars= " << Nv << "\n";
+                f << "! Ncons= " << o->Ncons << "\n";
+                f << "! chain= " << c << "\n";
+                f << "! relax= " << eigen_row(o->relax.data(), (long)o->relax.size(), 6) << "\n";
+                f << "! plength= " << eigen_row(o->plength.data(), (long)o->plength.size(), 6) << "\n";
+                f << "! constant_names= " << (o->cnames.empty() ? std::string("None   ") : names_line(o->cnames)) << "\n";
+                f << "! constant_values= " << (o->cnames.empty() ? std::string("-1") : eigen_row(o->cvals.data(), (long)o->cvals.size(), 6)) << "\n";
+                f << "! variable_names=" << names_line(o->vnames) << "\n";
+            }
+            for (long i = 0; i < n; i++) f << eigen_row(rec->vars + ((size_t)i * C + c) * Nv, Nv, 6) << "\n";
+        }
+    }
+    if (!o->stat_root.empty() && rec->logL && rec->logPrior && rec->logPost) {     // outputs.cpp:791-860
+        std::ofstream f((o->stat_root + "." + ext).c_str(), mode);
+        if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->stat_root + "." + ext);
+        if (header) {
+            f << "# This is an output file for the statistical information.\n";
+            f << "# This file contains values for the logLikelihood (columns 0:Nchains-1), logPrior (columns Nchains:2*Nchains-1) and logPosterior (columns 2*Nchains:3*Nchains-1),  \n";
+            f << "! Nchains= " << C << "\n";
+            f << "! labels= ";
+            const char *labels[3] = {"logLikelihood", "logPrior", "logPosteriors"};
+            for (int k = 0; k < 3; k++) for (int i = 0; i < C; i++) f << labels[k] << "[" << i << "]   ";
+            f << "\n";
+        }
+        for (long i = 0; i < n; i++)
+            f << eigen_row(rec->logL + (size_t)i * C, C, 6) << "     " << eigen_row(rec->logPrior + (size_t)i * C, C, 6) << "     " << eigen_row(rec->logPost + (size_t)i * C, C, 6) << "\n";
+    }
+    if (!o->ptemp_root.empty() && rec->swap_attempt) {                // outputs.cpp:615-676
+        std::ofstream f((o->ptemp_root + "." + ext).c_str(), mode);
+        if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->ptemp_root + "." + ext);
+        if (header) {
+            f << "# This is an output file for the parameters of the parallel tempering.\n";
+            f << "# This file contains values for \n";
+            f << "# Correspondance between chain0=[0:Nchains-1] and temperature Tcoefs[chain] \n";
+            f << "! Tcoefs = " << eigen_row(o->Tcoefs.data(), (long)o->Tcoefs.size(), 6) << "\n";
+            f << "! labels= attempt_mixing    chain0    Pswitch    switched \n";
+        }
+        for (long i = 0; i < n; i++) {
+            const size_t e = (size_t)i * E;
+            f << (rec->swap_attempt[e] ? 1 : 0) << "   " << (rec->swap_chain0 ? rec->swap_chain0[e] : -1) << "   " << (rec->swap_Pswap ? rec->swap_Pswap[e] : 0.0)
+              << "   " << ((rec->swap_done && rec->swap_done[e]) ? 1 : 0) << "\n";
+        }
+    }
+    return TG_OK;
+}
 
 static int write_headers(const tg_out *o)
 {
@@ -109,20 +175,25 @@ extern "C" int tg_out_append(tg_out *o, const tg_records *rec, long n, int E)
     const int C = o->C, Nv = o->Nv;
     const bool fresh = (o->erase == 1 && o->written == 0);          // erase_old_files == 1 && Ncopy == 0: truncate
     const std::ios_base::openmode mode = std::ios::binary | (fresh ? std::ios::trunc : std::ios::app);
-    if (!o->params_root.empty() && rec->vars) {                     // one file per chain, raw f64 [sample][Nv]
+    if (o->format != 0) { int r = append_text(o, rec, n, E); if (r) return r; }
+    const std::string bext = (o->format == 2) ? ".dbg" : ".bin";     // file_ext of the reference: bin, or dbg in debug mode
+    const bool binary = (o->format != 1);
+    if (binary && !o->params_root.empty() && rec->vars) {           // one file per chain, raw f64 [sample][Nv]
         std::vector<double> row((size_t)n * Nv);
         for (int c = 0; c < C; c++) {
-            std::ofstream f((o->params_root + "_chain-" + std::to_string(c) + ".bin").c_str(), mode);
+            std::ofstream f((o->params_root + "_chain-" + std::to_string(c) + bext).c_str(), mode);
             if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->params_root + "_chain-*.bin");
             for (long i = 0; i < n; i++) memcpy(&row[(size_t)i * Nv], rec->vars + ((size_t)i * C + c) * Nv, (size_t)Nv * 8);
             f.write(reinterpret_cast<const char *>(row.data()), (std::streamsize)(row.size() * 8));
         }
+    }
+    if (rec->vars) {
         std::fill(o->vars_mean.begin(), o->vars_mean.end(), 0.0);
         for (long i = 0; i < n; i++) for (size_t k = 0; k < (size_t)C * Nv; k++) o->vars_mean[k] += rec->vars[(size_t)i * C * Nv + k];
         if (n > 0) for (auto &v : o->vars_mean) v /= (double)n;
     }
-    if (!o->stat_root.empty() && rec->logL && rec->logPrior && rec->logPost) {   // per sample: logL[C] | logPrior[C] | logPost[C]
-        std::ofstream f((o->stat_root + ".bin").c_str(), mode);
+    if (binary && !o->stat_root.empty() && rec->logL && rec->logPrior && rec->logPost) {   // per sample: logL[C] | logPrior[C] | logPost[C]
+        std::ofstream f((o->stat_root + bext).c_str(), mode);
         if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->stat_root + ".bin");
         for (long i = 0; i < n; i++) {
             f.write(reinterpret_cast<const char *>(rec->logL + (size_t)i * C), C * 8);
@@ -130,8 +201,8 @@ extern "C" int tg_out_append(tg_out *o, const tg_records *rec, long n, int E)
             f.write(reinterpret_cast<const char *>(rec->logPost + (size_t)i * C), C * 8);
         }
     }
-    if (!o->ptemp_root.empty() && rec->swap_attempt) {              // per sample: bool(1) int(4) double(8) bool(1), packed
-        std::ofstream f((o->ptemp_root + ".bin").c_str(), mode);
+    if (binary && !o->ptemp_root.empty() && rec->swap_attempt) {    // per sample: bool(1) int(4) double(8) bool(1), packed
+        std::ofstream f((o->ptemp_root + bext).c_str(), mode);
         if (!f.is_open()) return fail(TG_E_BADARG, "cannot open " + o->ptemp_root + ".bin");
         for (long i = 0; i < n; i++) {
             const size_t e = (size_t)i * E;
@@ -145,7 +216,7 @@ extern "C" int tg_out_append(tg_out *o, const tg_records *rec, long n, int E)
         }
     }
     o->written += n;
-    if (o->erase == 1) return write_headers(o);                     // appends leave the headers alone (outputs.cpp:1254)
+    if (o->erase == 1 && binary) return write_headers(o);                     // appends leave the headers alone (outputs.cpp:1254)
     return TG_OK;
 }
 

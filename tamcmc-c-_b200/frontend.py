@@ -14,7 +14,7 @@ class _Run(C.Structure):
                [("Nsamples", C.c_long), ("Nbuffer", C.c_long)] + \
                [(k, C.c_int) for k in ("erase_old_files", "do_restore_proposal", "do_restore_variables", "do_restore_last_index", "do_restore_proposal_mean",
                                        "get_params", "get_statcriteria", "get_parallel_tempering", "evidence_diags", "evidence_interpolation_factor",
-                                       "Nslices", "Nvars", "Ncons")] + [("lambda_temp", C.c_double)]
+                                       "Nslices", "Nvars", "Ncons")] + [("lambda_temp", C.c_double), ("file_format", C.c_int)]
 
 
 class FrontEnd:

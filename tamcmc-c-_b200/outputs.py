@@ -14,7 +14,7 @@ class _OutDesc(C.Structure):
                 ("Nsamples", C.c_long), ("Nsamples_sofar", C.c_long), ("erase_old_files", C.c_int),
                 ("Nchains", C.c_int), ("Nvars", C.c_int), ("Ncons", C.c_int), ("Np", C.c_int), ("n_plength", C.c_int),
                 ("relax", C.c_void_p), ("plength", C.c_void_p), ("variable_names", C.POINTER(C.c_char_p)),
-                ("constant_names", C.POINTER(C.c_char_p)), ("constant_values", C.c_void_p), ("Tcoefs", C.c_void_p)]
+                ("constant_names", C.POINTER(C.c_char_p)), ("constant_values", C.c_void_p), ("Tcoefs", C.c_void_p), ("file_format", C.c_int)]
 
 
 def _check(lib, rc):
@@ -27,7 +27,7 @@ class Outputs:
     ``<root>_stat_criteria.bin``, ``<root>_parallel_tempering.bin`` and the restore triplet
     ``<restore_dir>/<root>_restore_{1,2,3}.dat`` -- the names main.cpp/config_presets.cpp give them."""
 
-    def __init__(self, prob, Tcoefs, outdir, root="run", restore_dir=None, Nsamples=0, Nsamples_sofar=0, erase_old_files=True, lib=None):
+    def __init__(self, prob, Tcoefs, outdir, root="run", restore_dir=None, Nsamples=0, Nsamples_sofar=0, erase_old_files=True, lib=None, file_format="binary"):
         self.lib = lib or load_library()
         os.makedirs(outdir, exist_ok=True)
         restore_dir = restore_dir or outdir
@@ -45,7 +45,8 @@ class Outputs:
         k = self._keep
         d = _OutDesc(self.paths["params"].encode(), self.paths["stat"].encode(), self.paths["ptemp"].encode(), self.paths["restore"].encode(),
                      int(Nsamples), int(Nsamples_sofar), 1 if erase_old_files else 0, len(k["T"]), len(vn), len(cn), int(prob.params.size),
-                     int(k["plength"].size), _p(k["relax"]), _p(k["plength"]), k["vn"], k["cn"] if cn else None, _p(k["cvals"]), _p(k["T"]))
+                     int(k["plength"].size), _p(k["relax"]), _p(k["plength"]), k["vn"], k["cn"] if cn else None, _p(k["cvals"]), _p(k["T"]),
+                     {"binary": 0, "text": 1, "debug": 2}[file_format])
         self.h = C.c_void_p()
         _check(self.lib, self.lib.lib.tg_out_open(C.byref(d), C.byref(self.h)))
         self.Nchains, self.Nvars = len(k["T"]), len(vn)

@@ -181,6 +181,54 @@ def test_reference_program_restores_from_our_mean_blocks(tb, tmp_path):
     assert len(mus) >= Cn and all(np.allclose(mus[c], mean["mu"][c], rtol=2e-5, atol=1e-12) for c in range(Cn))
 
 
+@pytest.mark.skipif(not (os.path.isdir(os.path.join(REF, "Config")) and os.path.exists(REFBIN)), reason="reference tree / oracle/_ref/cpptamcmc absent")
+def test_ascii_outputs_equal_the_reference_programs(tb, tmp_path):
+    """file_format = text / debug (outputs.cpp:510-613, :615-676, :791-860).  In debug mode the UNMODIFIED reference program
+    writes every sample twice, binary (.dbg) and ASCII (.dbg.txt): its binary records, fed to this repo's writer in the same mode,
+    must give its ASCII files back byte for byte (headers included) -- and the binary ones."""
+    import re, subprocess
+    from test_frontend_cpu import _ref_tree
+    wd, out = _ref_tree(tmp_path, os.path.join(REF, "test", "inputs"), [LOCAL_ID], "io_local", nsamples="25     ,  30  , 40")
+    pcfg = os.path.join(wd, "Config", "default", "config_default.cfg")
+    s = open(pcfg).read()
+    s2 = re.sub(r"file_format\s*=\s*\w+;", "file_format=debug;", s)
+    assert s2 != s
+    open(pcfg, "w").write(s2)
+    r = subprocess.run([REFBIN, "execute", "1", "1", "1", "1", "2"], cwd=wd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-800:]
+    fe = tb.frontend.FrontEnd(wd)
+    run = fe.setup(0, 0, 0)
+    prob, cfg = fe.problem()
+    fe.close()
+    assert run["file_format"] == 2
+    Cn, Nv, n = cfg.Nchains, prob.index_to_relax.size, 25
+    base = os.path.join(out, LOCAL_ID, "outputs", run["output_root_name"])
+    rec = dict(vars=np.stack([np.fromfile(base + "params_chain-%d.dbg" % c).reshape(n, Nv) for c in range(Cn)], axis=1))
+    st = np.fromfile(base + "stat_criteria.dbg").reshape(n, 3 * Cn)
+    rec.update(logL=st[:, :Cn].copy(), logPrior=st[:, Cn:2 * Cn].copy(), logPost=st[:, 2 * Cn:].copy())
+    pt = np.fromfile(base + "parallel_tempering.dbg", dtype=np.dtype([("a", "u1"), ("c", "<i4"), ("p", "<f8"), ("s", "u1")]))
+    assert pt.size == n
+    rec.update(swap_attempt=pt["a"].astype(np.int32)[:, None], swap_chain0=pt["c"].astype(np.int32)[:, None], swap_Pswap=pt["p"].astype(np.float64)[:, None],
+               swap_done=pt["s"].astype(np.int32)[:, None], Pmove=np.zeros((n, Cn)), moved=np.zeros((n, Cn), dtype=np.uint8), status=np.zeros((n, Cn), dtype=np.int32))
+    root = run["output_root_name"].rstrip("_")
+    o = tb.outputs.Outputs(prob, cfg.Tcoefs, str(tmp_path / "mine"), root=root, Nsamples=25, file_format="debug")
+    o.append({k: rec[k][:10] for k in rec})                   # two blocks: the header goes with the first only
+    o.append({k: rec[k][10:] for k in rec})
+    o.close()
+    mine = str(tmp_path / "mine" / (root + "_"))
+    names = ["params_chain-%d" % c for c in range(Cn)] + ["stat_criteria", "parallel_tempering"]
+    for nm in names:
+        assert open(mine + nm + ".dbg", "rb").read() == open(base + nm + ".dbg", "rb").read(), nm
+        a, b = open(mine + nm + ".dbg.txt").read(), open(base + nm + ".dbg.txt").read()
+        assert a == b, (nm, [(x, y) for x, y in zip(a.splitlines(), b.splitlines()) if x != y][:3])
+    # text mode: the same lines under the extension txt, and no binary files
+    o = tb.outputs.Outputs(prob, cfg.Tcoefs, str(tmp_path / "txt"), root=root, Nsamples=25, file_format="text")
+    o.append(rec); o.close()
+    for nm in names:
+        assert open(str(tmp_path / "txt" / (root + "_" + nm + ".txt"))).read() == open(base + nm + ".dbg.txt").read()
+    assert not [f for f in os.listdir(str(tmp_path / "txt")) if f.endswith((".bin", ".hdr", ".dbg"))]
+
+
 def test_header_declares_every_outputs_symbol(tb):
     import re
     decl = set(re.findall(r"\b(tg_\w+)\s*\(", open(os.path.join(ROOT, "include", "tamcmc_outputs.h")).read()))

@@ -85,7 +85,7 @@ static void run_phase(tg_frontend *fe, int star, int slice, int phase, unsigned 
     tg_out_desc d; memset(&d, 0, sizeof d);
     d.params_root = run.get_params ? f_params.c_str() : nullptr; d.stat_root = run.get_statcriteria ? f_stat.c_str() : nullptr;
     d.ptemp_root = run.get_parallel_tempering ? f_pt.c_str() : nullptr; d.restore_root = f_restore.c_str();
-    d.Nsamples = run.Nsamples; d.Nsamples_sofar = i0; d.erase_old_files = run.erase_old_files;
+    d.Nsamples = run.Nsamples; d.Nsamples_sofar = i0; d.erase_old_files = run.erase_old_files; d.file_format = run.file_format;
     d.Nchains = C; d.Nvars = Nv; d.Ncons = (int)cn.size(); d.Np = prob.Np; d.n_plength = 11; d.relax = prob.relax; d.plength = prob.plength;
     d.variable_names = vnp.data(); d.constant_names = cnp.empty() ? nullptr : cnp.data(); d.constant_values = cv.data(); d.Tcoefs = prob.Tcoefs;
     tg_out *out = nullptr;
