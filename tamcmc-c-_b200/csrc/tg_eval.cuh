@@ -415,49 +415,58 @@ __device__ __noinline__ double tg_background_at(const double *nz, const int *cls
 
 // n_mt background-only moment tiles starting at bin b0 (aligned) for the G chains of the unit: warp w takes the pairs
 // (tile, chain) = w, w + 8, ...; lanes 0..8 evaluate the background at the nodes, lanes 9..13 at the check points.  A pair
-// that passes adds its two sums to the running results of the chain (lane 0's slot of S.sum, s_lw[g][warp]); a pair that
+// that passes adds its two sums to the running results of the chain (the slot of S.sum of its first lane, s_lw[g][half-warp]); a pair that
 // fails sets bit g of s_fail[tile] and is evaluated bin by bin by the caller.  No barrier inside.
 __device__ void tg_moment_tiles(const TgEvalArgs &a, const TgEvalSmem &S, const double (*s_WE)[TG_MD], const double *s_tn,
-                                double (*s_lw)[TG_THREADS / 32], unsigned *s_fail, unsigned *s_flag, int G, int b0, int n_mt)
+                                double (*s_lw)[2 * (TG_THREADS / 32)], unsigned *s_fail, unsigned *s_flag, int G, int b0, int n_mt)
 {
+    // Two (tile, chain) pairs per warp and round, one per half-warp (14 of its 16 lanes work: 9 nodes + 5 check points) -- the
+    // rounds are chains of latencies (background, reciprocal and logarithm at a node, a 9-term product by shuffles, two reductions),
+    // so two of them side by side cost one.
+    static_assert(TG_MD + TG_MCHK <= 16, "nodes + check points of a pair fit a half-warp");
     constexpr int NW = TG_THREADS / 32;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, half = lane >> 4, hl = lane & 15;
+    const unsigned hmask = 0xffffu << (16 * half);
     const int mtb = a.mom_sub * (TG_THREADS * 4);
-    for (int p = warp; p < n_mt * G; p += NW) {
-        const int mt = p / G, g = p - mt * G;
+    const int npairs = n_mt * G;
+    for (int p0 = 2 * warp; p0 < npairs; p0 += 2 * NW) {
+        const int p = p0 + half;
+        const bool active = (p < npairs);
+        const int pc = active ? p : p0;                          // an idle half-warp shadows its neighbour (it takes part in the shuffles, writes nothing)
+        const int mt = pc / G, g = pc - mt * G;
         const int bb = b0 + mt * mtb;
         const double xa = __ldg(a.x + bb), xb = __ldg(a.x + bb + mtb - 1);
         const double xm = 0.5 * (xa + xb), xh = 0.5 * (xb - xa);
         const double *mo = a.mom + TG_MOM_HDR + (size_t)(bb / mtb) * 2 * TG_MD;
         double r = 0.0, l = 0.0, mom_s = 0.0, mom_y = 0.0;
         bool ok = (xh > 0.0), bval = true;
-        if (lane < TG_MD) { mom_s = __ldg(mo + lane); mom_y = __ldg(mo + TG_MD + lane); }
-        if (lane == 0) ok = ok && (mom_s == (double)mtb);       // ST_0 = number of bins; NaN marks a tile the host could not use
-        if (lane < TG_MD + TG_MCHK) {
-            const double b = tg_background_at(S.nz + (size_t)g * TG_NOISE_STRIDE, S.cls + g * TG_MAXH, S.nh[g], fma(xh, s_tn[lane], xm));
+        if (hl < TG_MD) { mom_s = __ldg(mo + hl); mom_y = __ldg(mo + TG_MD + hl); }
+        if (hl == 0) ok = ok && (mom_s == (double)mtb);         // ST_0 = number of bins; NaN marks a tile the host could not use
+        if (hl < TG_MD + TG_MCHK) {
+            const double b = tg_background_at(S.nz + (size_t)g * TG_NOISE_STRIDE, S.cls + g * TG_MAXH, S.nh[g], fma(xh, s_tn[hl], xm));
             bval = (b > 0.0) && (b < 1.0e300);                  // false for NaN
             ok = ok && bval;
             r = tg_rcp(b); l = log(b);
         }
         // a background that is not a positive finite number at the nodes (NaN parameters of a failed proposal, ...) is no
         // statement about the tile: it is evaluated bin by bin like any failure, but the tile is not flagged for the host
-        const bool sane = __all_sync(0xffffffffu, bval);
-        const int row = (lane < TG_MD + TG_MCHK) ? lane : 0;
-        double cr = 0.0, cl = 0.0;                              // lanes 0..8: coefficients; lanes 9..13: interpolants at the check points
+        const bool sane = ((__ballot_sync(0xffffffffu, bval) & hmask) == hmask);
+        const int row = (hl < TG_MD + TG_MCHK) ? hl : 0;
+        double cr = 0.0, cl = 0.0;                              // lanes 0..8 of the half: coefficients; 9..13: interpolants at the check points
 #pragma unroll
         for (int j = 0; j < TG_MD; j++) {
             const double w = s_WE[row][j];
-            cr = fma(w, __shfl_sync(0xffffffffu, r, j), cr);
-            cl = fma(w, __shfl_sync(0xffffffffu, l, j), cl);
+            cr = fma(w, __shfl_sync(0xffffffffu, r, j, 16), cr);
+            cl = fma(w, __shfl_sync(0xffffffffu, l, j, 16), cl);
         }
-        if (lane >= TG_MD && lane < TG_MD + TG_MCHK)
+        if (hl >= TG_MD && hl < TG_MD + TG_MCHK)
             ok = ok && (fabs(cr - r) <= TG_MOM_TOL * fabs(r)) && (fabs(cl - l) <= TG_MOM_TOL * fmax(1.0, fabs(l)));
-        double ps = (lane < TG_MD) ? cr * mom_y : 0.0, pl = (lane < TG_MD) ? cl * mom_s : 0.0;
+        double ps = (hl < TG_MD) ? cr * mom_y : 0.0, pl = (hl < TG_MD) ? cl * mom_s : 0.0;
 #pragma unroll
-        for (int o = 8; o > 0; o >>= 1) { ps += __shfl_down_sync(0xffffffffu, ps, o); pl += __shfl_down_sync(0xffffffffu, pl, o); }
-        const bool all_ok = __all_sync(0xffffffffu, ok);
-        if (lane == 0) {
-            if (all_ok) { S.sum[g * TG_THREADS + tid] += ps; s_lw[g][warp] += pl; }
+        for (int o = 8; o > 0; o >>= 1) { ps += __shfl_down_sync(0xffffffffu, ps, o, 16); pl += __shfl_down_sync(0xffffffffu, pl, o, 16); }
+        const bool all_ok = ((__ballot_sync(0xffffffffu, ok) & hmask) == hmask);
+        if (hl == 0 && active) {
+            if (all_ok) { S.sum[g * TG_THREADS + tid] += ps; s_lw[g][2 * warp + half] += pl; }
             else { atomicOr(s_fail + mt, 1u << g); if (sane) atomicOr(s_flag + mt, 1u << g); }
         }
     }
@@ -548,7 +557,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
     __shared__ int s_w[2][TG_MAXG];
     __shared__ double s_WE[TG_MD + TG_MCHK][TG_MD];   // moment path: node values -> coefficients / check interpolants
     __shared__ double s_tn[TG_MD + TG_MCHK];
-    __shared__ double s_lw[TG_MAXG][NW];              // moment path: sum of ln b per chain and warp
+    __shared__ double s_lw[TG_MAXG][2 * NW];          // moment path: sum of ln b per chain and half-warp
     __shared__ unsigned s_fail[32], s_flag[32];       // moment path: chains that take the tile bin by bin / that flag it for the host
 
     __shared__ __align__(16) TgEvalArgs s_args;
@@ -579,7 +588,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
     // ---- phase 0: noise tables, window unions, running results ----
     for (int g = 0; g < G; g++) { S.sum[g * TG_THREADS + tid] = 0.0; S.pf[g * TG_THREADS + tid] = 1.0; S.pe[g * TG_THREADS + tid] = 0; }
     const bool use_mom = (a.mom != nullptr) && (a.d.like_case == 0) && (a.model == nullptr) && (a.d.model_case > 1);
-    if (tid < TG_MAXG * NW) (&s_lw[0][0])[tid] = 0.0;
+    if (tid < TG_MAXG * 2 * NW) (&s_lw[0][0])[tid] = 0.0;
     bool we_loaded = false;                       // the interpolation matrices are staged by the first moment tile of the unit (most units have none)
     const bool ff_on = (a.ff.c != nullptr) && (a.model == nullptr);
     tg_pdl_wait();                                // everything above (unit table, shared-memory set-up) may overlap the proposal kernel
@@ -688,7 +697,7 @@ __global__ void __launch_bounds__(TG_THREADS, TG_EVAL_MINBLOCKS) tg_k_eval(const
             if (a.d.like_case == 0) {
                 t2 = fma((double)pe, 6.93147180369123816490e-01, fma((double)pe, 1.90821492927058770002e-10, log(pf)));
 #pragma unroll
-                for (int w = 0; w < NW; w++) t2 += s_lw[warp][w];
+                for (int w = 0; w < 2 * NW; w++) t2 += s_lw[warp][w];
             }
             a.partials[(size_t)(c0 + warp) * a.nitems + item_index] = make_double2(sum, t2);
         }
