@@ -22,6 +22,6 @@ print("after create", counters())
 i = 10000
 run.execute(i, 32, record=False); i += 32
 print("after warm-up", counters())
-for n in (64, 64, 64, 20, 20, 1000, 64):
+for n in (64, 64, 64, 20, 20, 1000, 64, 20, 20, 1000, 64, 20, 20):
     mds[0].sync(); tm.timer_start(); run.execute(i, n, record=False); ms = tm.timer_stop_ms(); i += n
     print("%5d steps: %.1f us/step  counters %s" % (n, ms / n * 1e3, counters()))
